@@ -1,0 +1,176 @@
+// common.cuh — shared device helpers for libpsb_kernels (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "psb_kernels.h"
+
+namespace psb {
+
+// ---- host-side error plumbing -------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launches;
+inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+#define PSB_CUDA_OK(expr)                                                                   \
+  do {                                                                                      \
+    cudaError_t _e = (expr);                                                                \
+    if (_e != cudaSuccess) {                                                                \
+      psb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,      \
+                     __LINE__);                                                             \
+      return (int)_e;                                                                       \
+    }                                                                                       \
+  } while (0)
+
+#define PSB_LAUNCH_OK(name)                                                                 \
+  do {                                                                                      \
+    cudaError_t _e = cudaGetLastError();                                                    \
+    if (_e != cudaSuccess) {                                                                \
+      psb::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));              \
+      return (int)_e;                                                                       \
+    }                                                                                       \
+    psb::count_launch();                                                                    \
+  } while (0)
+
+#define PSB_REQUIRE(cond, code, ...)                                                        \
+  do {                                                                                      \
+    if (!(cond)) {                                                                          \
+      psb::set_error(__VA_ARGS__);                                                          \
+      return (code);                                                                        \
+    }                                                                                       \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200
+
+// ---- memory-model primitives (system scope: visible across NVLink peers) ------
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+
+// spin until *p >= target (wrap-safe signed distance)
+__device__ __forceinline__ void wait_ge_sys(const uint32_t* p, uint32_t target) {
+  while ((int32_t)(ld_acquire_sys(p) - target) < 0) {
+    __nanosleep(32);
+  }
+}
+
+// ---- 16-byte streaming loads / stores ------------------------------------------
+// Peer (NVLink) addresses are cached only in the local L1, which is invalidated at
+// every launch; no_allocate keeps streaming data from thrashing it.
+__device__ __forceinline__ uint4 ld_stream_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream_16(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ float4 ld_stream_f4(const float* p) {
+  uint4 r = ld_stream_16(p);
+  return make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
+                     __uint_as_float(r.w));
+}
+__device__ __forceinline__ void st_stream_f4(float* p, const float4& v) {
+  st_stream_16(p, make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z),
+                             __float_as_uint(v.w)));
+}
+
+// ---- bf16 packing ----------------------------------------------------------------
+__device__ __forceinline__ void unpack_bf16x2(uint32_t u, float& lo, float& hi) {
+  lo = __uint_as_float(u << 16);
+  hi = __uint_as_float(u & 0xffff0000u);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void unpack8(const uint4& u, float f[8]) {
+  unpack_bf16x2(u.x, f[0], f[1]);
+  unpack_bf16x2(u.y, f[2], f[3]);
+  unpack_bf16x2(u.z, f[4], f[5]);
+  unpack_bf16x2(u.w, f[6], f[7]);
+}
+__device__ __forceinline__ uint4 pack8(const float f[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]),
+                    pack_bf16x2(f[6], f[7]));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---- optimizer math on 8 contiguous elements --------------------------------------
+// Everything the server-side update needs, pre-digested once per thread.
+struct OptimCoef {
+  int kind;
+  float lr, momentum, beta1, beta2, eps, wd;
+  float inv_bias1;       // 1 / (1 - beta1^t)
+  float inv_sqrt_bias2;  // 1 / sqrt(1 - beta2^t)
+};
+
+__device__ __forceinline__ OptimCoef make_coef(const PsbOptim& o, uint32_t completed_steps) {
+  OptimCoef c;
+  c.kind = o.kind;
+  c.lr = o.lr;
+  c.momentum = o.momentum;
+  c.beta1 = o.beta1;
+  c.beta2 = o.beta2;
+  c.eps = o.eps;
+  c.wd = o.weight_decay;
+  c.inv_bias1 = 1.f;
+  c.inv_sqrt_bias2 = 1.f;
+  if (o.kind == PSB_OPT_ADAM || o.kind == PSB_OPT_ADAMW) {
+    float t = (float)(completed_steps + 1u);
+    c.inv_bias1 = 1.f / (1.f - powf(o.beta1, t));
+    c.inv_sqrt_bias2 = rsqrtf(1.f - powf(o.beta2, t));
+  }
+  return c;
+}
+
+// p, m, v are updated in place; g is the already scaled / clipped mean gradient.
+template <int KIND>
+__device__ __forceinline__ void update1(const OptimCoef& c, float& p, float& m, float& v, float g) {
+  if constexpr (KIND == PSB_OPT_SGD) {
+    g = fmaf(c.wd, p, g);
+    p = fmaf(-c.lr, g, p);
+  } else if constexpr (KIND == PSB_OPT_MOMENTUM) {
+    g = fmaf(c.wd, p, g);
+    m = fmaf(c.momentum, m, g);
+    p = fmaf(-c.lr, m, p);
+  } else {
+    if constexpr (KIND == PSB_OPT_ADAM) {
+      g = fmaf(c.wd, p, g);
+    } else {
+      p = p * (1.f - c.lr * c.wd);
+    }
+    m = fmaf(c.beta1, m, (1.f - c.beta1) * g);
+    v = fmaf(c.beta2, v, (1.f - c.beta2) * g * g);
+    float denom = fmaf(sqrtf(v), c.inv_sqrt_bias2, c.eps);
+    p = fmaf(-c.lr * c.inv_bias1, m / denom, p);
+  }
+}
+
+}  // namespace psb

@@ -1,0 +1,262 @@
+// psb_kernels.h — C ABI of libpsb_kernels.so, the sm_100a device library of the
+// B200-native parameter-server framework.
+//
+// Every entry point is `extern "C"`, takes raw device pointers plus a CUDA
+// stream, launches asynchronously on that stream and returns 0 on success or a
+// non-zero code (a cudaError_t value, or a negative PSB_E* code); the message
+// of the last failure on the calling thread is available from
+// psb_last_error().  The Python package binds these with ctypes, the C++
+// parameter_server / worker_main binaries link them directly.
+//
+// Kernel IDs (K1..K9) refer to SURVEY.md §8.  Reference citations are paths
+// below /root/reference.
+#pragma once
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* psb_stream_t;  // cudaStream_t
+
+#define PSB_MAX_PEERS 8
+#define PSB_MAX_BUCKETS 512
+#define PSB_MAX_GATHER 96
+
+// error codes (negative so they never collide with cudaError_t)
+#define PSB_EINVAL (-1)
+#define PSB_ERANGE (-2)
+#define PSB_EUNSUPPORTED (-3)
+
+// dtypes of gradient payloads
+#define PSB_F32 0
+#define PSB_BF16 1
+
+// optimizer kinds (server-side update; the reference applies only `p -= g`,
+// src/parameter_server.cpp:83-90 — PSB_OPT_SGD with lr = 1 reproduces it)
+#define PSB_OPT_SGD 0
+#define PSB_OPT_MOMENTUM 1
+#define PSB_OPT_ADAM 2   // L2-coupled weight decay
+#define PSB_OPT_ADAMW 3  // decoupled weight decay
+
+const char* psb_last_error(void);
+int psb_version(void);
+// number of kernel launches issued through this library by the calling process
+uint64_t psb_launch_count(void);
+
+// ---------------------------------------------------------------------------
+// Hyper-parameters of the server-side update.
+// ---------------------------------------------------------------------------
+typedef struct PsbOptim {
+  int32_t kind;        // PSB_OPT_*
+  float lr;
+  float momentum;      // PSB_OPT_MOMENTUM
+  float beta1, beta2;  // Adam
+  float eps;
+  float weight_decay;
+  float grad_scale;    // multiplies the *summed* gradient (1/num_workers for the mean,
+                       // src/parameter_server.cpp:57-60)
+} PsbOptim;
+
+// ---------------------------------------------------------------------------
+// K7 — constant fill (replaces the host loop src/worker.cpp:317-320)
+// ---------------------------------------------------------------------------
+int psb_fill_f32(float* dst, size_t n, float value, psb_stream_t stream);
+int psb_fill_bf16(void* dst, size_t n, float value, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// K6 — scale / cast (replaces the host divide src/worker.cpp:436-438)
+// ---------------------------------------------------------------------------
+int psb_cast_f32_to_bf16(const float* src, void* dst, size_t n, float scale, psb_stream_t stream);
+int psb_cast_bf16_to_f32(const void* src, float* dst, size_t n, float scale, psb_stream_t stream);
+
+// Multi-tensor gather: copies `count` separately allocated gradient tensors into
+// one flat bucket (a view of the symmetric heap) in a single launch, casting to
+// the bucket dtype and scaling.  Each source must be 16-byte aligned; each
+// dst_offset (in elements) a multiple of 8.
+typedef struct PsbGatherList {
+  const void* src[PSB_MAX_GATHER];
+  uint64_t dst_offset[PSB_MAX_GATHER];  // elements into the bucket
+  uint64_t numel[PSB_MAX_GATHER];
+  int32_t count;
+  int32_t src_dtype;  // PSB_F32 / PSB_BF16
+  int32_t dst_dtype;
+  float scale;
+} PsbGatherList;
+int psb_gather_to_bucket(const PsbGatherList* list, void* bucket, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// K3 — stand-alone flat-shard optimizer step (H3 of the reference generalised):
+// fp32 master weights (+ optional m, v), gradient in fp32 or bf16, optional bf16
+// copy of the updated weights.  `step` is a device counter holding the number of
+// completed steps (Adam bias correction uses step+1); it is NOT advanced here —
+// call psb_counter_add afterwards (once per optimizer step, not per bucket).
+// `clip_coef` may be NULL, else a device float that multiplies the gradient.
+// ---------------------------------------------------------------------------
+int psb_optim_step(const PsbOptim* opt, float* master, float* m, float* v, const void* grad,
+                   int grad_dtype, void* param_bf16_out, size_t n, const float* clip_coef,
+                   const uint32_t* step, psb_stream_t stream);
+int psb_counter_add(uint32_t* counter, uint32_t delta, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// K4 — gradient norm / clipping.
+// psb_sumsq: out[0] = Σ x², two-phase reduction.  `partials` is caller-provided
+// scratch of at least psb_sumsq_scratch_floats() floats; it need not be zeroed.
+// psb_clip_coef: coef = min(1, max_norm / (sqrt(Σ parts) + eps)).
+// ---------------------------------------------------------------------------
+size_t psb_sumsq_scratch_floats(void);
+int psb_sumsq(const void* x, int dtype, size_t n, float* partials, float* out, psb_stream_t stream);
+int psb_clip_coef(const float* sumsq_parts, int n_parts, float max_norm, float eps, float* coef_out,
+                  float* norm_out, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// Fabric — symmetric heap over the GPUs of one NVSwitch box.  Replaces the
+// reference's per-iteration cudaMalloc + host staging (src/worker.cpp:416-444)
+// and its NCCL clique (src/nccl_manager.cpp:28-85).
+// ---------------------------------------------------------------------------
+#define PSB_IPC_HANDLE_BYTES 64
+int psb_device_count(int* count);
+int psb_set_device(int dev);
+int psb_heap_alloc(size_t bytes, void** ptr);  // cudaMalloc + zero
+int psb_heap_free(void* ptr);
+int psb_ipc_export(void* ptr, unsigned char handle[PSB_IPC_HANDLE_BYTES]);
+int psb_ipc_open(const unsigned char handle[PSB_IPC_HANDLE_BYTES], void** ptr);
+int psb_ipc_close(void* ptr);
+int psb_can_access_peer(int dev, int peer, int* ok);
+int psb_enable_peer_access(int peer);  // from the current device
+int psb_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, psb_stream_t stream);
+int psb_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, psb_stream_t stream);
+int psb_memset(void* dst_dev, int value, size_t bytes, psb_stream_t stream);
+int psb_stream_sync(psb_stream_t stream);
+int psb_device_sync(void);
+
+// Signal pad layout (uint32 words, one pad per GPU, peer-mapped):
+//   ready  [PSB_MAX_BUCKETS][PSB_MAX_PEERS]   written by worker w on the owner's pad
+//   version[PSB_MAX_BUCKETS][PSB_MAX_PEERS]   written by owner r on every worker's pad
+//   barrier[64][PSB_MAX_PEERS]                generic device barriers
+//   clock  [PSB_MAX_PEERS]                    SSP clocks (one word per worker)
+//   norm   [2][PSB_MAX_PEERS] (64-bit words)   {seq, float bits} of per-shard Σg², double-buffered
+//   ack    [PSB_MAX_BUCKETS][PSB_MAX_PEERS]   async mode: owner r consumed worker's clock
+#define PSB_PAD_READY_OFF 0
+#define PSB_PAD_VERSION_OFF (PSB_MAX_BUCKETS * PSB_MAX_PEERS)
+#define PSB_PAD_BARRIER_OFF (2 * PSB_MAX_BUCKETS * PSB_MAX_PEERS)
+#define PSB_PAD_CLOCK_OFF (PSB_PAD_BARRIER_OFF + 64 * PSB_MAX_PEERS)
+#define PSB_PAD_NORM_OFF (PSB_PAD_CLOCK_OFF + PSB_MAX_PEERS)
+#define PSB_PAD_ACK_OFF (PSB_PAD_NORM_OFF + 4 * PSB_MAX_PEERS)
+#define PSB_PAD_WORDS (PSB_PAD_ACK_OFF + PSB_MAX_BUCKETS * PSB_MAX_PEERS)
+size_t psb_pad_bytes(void);
+
+typedef struct PsbFabric {
+  int32_t rank;
+  int32_t world;
+  uint32_t* pad[PSB_MAX_PEERS];  // peer-mapped signal pads; pad[rank] is local
+} PsbFabric;
+
+// ---------------------------------------------------------------------------
+// K1 — fused gradient push: reduce-scatter over NVLink peer loads into the
+// owning shard + server-side optimizer update + (optionally) push-mode
+// all-gather of the updated bf16 slice into every replica, in ONE kernel and
+// without NCCL.  Replaces N1 + H1 + H2 + H3 (+H4) of the reference
+// (src/nccl_manager.cpp:111, src/parameter_server.cpp:49-60,83-90,
+//  src/worker.cpp:436-438).
+//
+// Protocol for bucket b at epoch e = *epoch + 1 (device word, advanced by the
+// kernel itself so a captured CUDA graph can be replayed):
+//   1. every rank w stores ready[b][w] = e on every owner's pad (release.sys)
+//   2. owner r spins until ready[b][0..N) >= e on its own pad (acquire.sys)
+//   3. for its slice: g = Σ_w grad_w (fp32, fixed order w = 0..N-1), scaled,
+//      optimizer update of master/m/v, bf16 slice written locally and, with
+//      PSB_PUSH_BROADCAST, into every peer replica
+//   4. last CTA stores version[b][r] = e on every pad and *epoch = e
+// flags: see PSB_PUSH_* below.
+// ---------------------------------------------------------------------------
+#define PSB_PUSH_BROADCAST 1    // write the updated slice into all replicas (push-mode all-gather)
+#define PSB_PUSH_NO_WAIT 2      // skip steps 1-2 (caller already synchronised; async single-pusher)
+#define PSB_PUSH_REDUCE_ONLY 4  // stop after the reduction: write fp32 sum to `reduced`, Σg² to norm pads
+#define PSB_PUSH_FROM_REDUCED 8 // skip the reduction: gradient comes from `reduced` (after clipping)
+#define PSB_PUSH_MASKED 16      // only sum peers whose bit is set in *peer_mask (async / SSP)
+
+typedef struct PsbPush {
+  PsbFabric fabric;
+  const void* grad[PSB_MAX_PEERS];  // peer-mapped base of this bucket's gradient buffer
+  void* param[PSB_MAX_PEERS];       // peer-mapped base of this bucket's bf16 replica
+  float* master;                    // local shard state, slice_elems each
+  float* m;
+  float* v;
+  float* reduced;                   // optional fp32 scratch, slice_elems (clip path)
+  float* sumsq_acc;                 // optional local float: += Σ(reduced²) (PSB_PUSH_REDUCE_ONLY)
+  uint64_t slice_elems;             // bucket = world * slice_elems elements
+  int32_t bucket;
+  int32_t grad_dtype;
+  uint32_t* epoch;                  // local device word, one per bucket
+  const uint32_t* step;             // local device word, optimizer step counter
+  const float* clip_coef;           // optional
+  const uint32_t* peer_mask;        // optional (PSB_PUSH_MASKED)
+  uint32_t* done_counter;           // local device word, zero-initialised, one per bucket
+  int32_t flags;
+  int32_t grid;                     // CTAs (0 = auto)
+  PsbOptim opt;
+} PsbPush;
+int psb_push_fused(const PsbPush* args, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// K2 — parameter pull: wait for version[b][*] >= *epoch, then gather the N
+// slices of the bucket from their owners into the local replica (peer loads).
+// With PSB_PUSH_BROADCAST the data is already local and only the wait remains
+// (psb_wait_versions).  Replaces ServeParameters + H6/H7
+// (src/parameter_server.cpp:93-97, src/worker.cpp:240-252).
+// ---------------------------------------------------------------------------
+typedef struct PsbPull {
+  PsbFabric fabric;
+  void* param[PSB_MAX_PEERS];  // peer-mapped replicas of this bucket
+  uint64_t slice_bytes;
+  int32_t bucket;
+  const uint32_t* epoch;       // local device word of this bucket
+  int32_t grid;
+  int32_t skip_wait;
+} PsbPull;
+int psb_pull_allgather(const PsbPull* args, psb_stream_t stream);
+
+// K9 — device-side waits / barriers (replace the 50 ms CheckSyncStatus poll and
+// the 500 ms sleeps, src/worker.cpp:359-375).
+// wait until version[b][r] >= epoch_words[b] for b in [bucket_lo, bucket_hi), r in [0, world)
+int psb_wait_versions(const PsbFabric* fabric, const uint32_t* epoch_words, int bucket_lo,
+                      int bucket_hi, psb_stream_t stream);
+// all-rank barrier on slot `slot` (0..63); `seq` is a local device word advanced by the kernel
+int psb_device_barrier(const PsbFabric* fabric, int slot, uint32_t* seq, psb_stream_t stream);
+// cross-shard sum of the N per-shard Σg² written by PSB_PUSH_REDUCE_ONLY, then clip coefficient
+// `local_sumsq` is consumed: the kernel zeroes it after reading.
+int psb_norm_allreduce(const PsbFabric* fabric, float* local_sumsq, uint32_t* seq, float max_norm,
+                       float eps, float* coef_out, float* norm_out, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// K2f — bf16 GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed
+// shared-memory tiles:  Y[M,N] = X[M,K] · W[N,K]^T (+ bias), fp32 accumulate.
+// psb_gemm_bf16_tn: all operands local.
+// psb_gemm_allgather_bf16: W is row-sharded over the peers (rank r owns rows
+// [r*N/world, (r+1)*N/world)); B tiles are TMA-loaded straight from the owning
+// peer's replica over NVLink for the first M-tile and persisted into the local
+// replica by TMA stores, so the all-gather of the first layer overlaps its GEMM
+// tile by tile.  No counterpart in the reference (north-star item).
+// ---------------------------------------------------------------------------
+int psb_gemm_bf16_tn(const void* x, const void* w, const float* bias, void* y, int M, int N, int K,
+                     int out_dtype, psb_stream_t stream);
+typedef struct PsbGemmAG {
+  PsbFabric fabric;
+  void* w[PSB_MAX_PEERS];  // peer-mapped replicas of W [N,K] bf16 (full-size on every rank)
+  const void* x;           // [M,K] bf16, local
+  const float* bias;       // optional [N] fp32
+  void* y;                 // [M,N]
+  int32_t M, N, K;
+  int32_t out_dtype;       // PSB_BF16 / PSB_F32
+  int32_t bucket;          // version flags of this bucket gate the remote loads
+  const uint32_t* epoch;
+  int32_t skip_wait;
+} PsbGemmAG;
+int psb_gemm_allgather_bf16(const PsbGemmAG* args, psb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif

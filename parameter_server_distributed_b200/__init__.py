@@ -1,0 +1,13 @@
+"""parameter_server_distributed_b200 — a B200-native parameter-server training framework.
+
+Capabilities of araju6/parameter-server-distributed (coordinator, parameter-server shards,
+workers, gRPC-compatible control plane, checkpoints) rebuilt Blackwell-first: shards live in
+HBM, one per GPU; gradient push is a fused reduce-scatter + optimizer kernel over NVLink
+peer memory, parameter pull an all-gather fused into the first tcgen05 GEMM.
+"""
+from . import _lib
+from .ops.native import OptimConfig
+from .trainer import Context, Trainer, init
+
+__version__ = "0.1.0"
+__all__ = ["OptimConfig", "Context", "Trainer", "init", "_lib"]

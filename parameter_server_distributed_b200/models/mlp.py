@@ -1,0 +1,62 @@
+"""Synthetic MLP — BASELINE.json config 2 ("synthetic MLP sync-SGD with 8 PS shards / 8
+workers").  The reference has no model at all: its only tensor is a fabricated
+``weight[10,10]`` (src/worker.cpp:346-353) with constant gradients (:316-320).
+
+The first Linear can run through the fused all-gather + tcgen05 GEMM (K2f) when the
+parameter server is in pull mode; every other GEMM is a plain library call.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+@dataclass
+class MLPConfig:
+    d_in: int = 4096
+    hidden: Sequence[int] = (8192, 8192)
+    d_out: int = 1024
+    bias: bool = True
+
+    @property
+    def dims(self):
+        return [self.d_in, *self.hidden, self.d_out]
+
+    def num_params(self) -> int:
+        d = self.dims
+        return sum(d[i] * d[i + 1] + (d[i + 1] if self.bias else 0) for i in range(len(d) - 1))
+
+    def flops_per_sample(self) -> int:
+        d = self.dims
+        return 6 * sum(d[i] * d[i + 1] for i in range(len(d) - 1))
+
+
+class MLP(nn.Module):
+    def __init__(self, cfg: MLPConfig = MLPConfig()):
+        super().__init__()
+        self.cfg = cfg
+        d = cfg.dims
+        self.layers = nn.ModuleList(
+            [nn.Linear(d[i], d[i + 1], bias=cfg.bias) for i in range(len(d) - 1)])
+        self.first_linear_fn = None  # set by the trainer to route layer 0 through K2f
+
+    def first_weight_name(self) -> str:
+        return "layers.0.weight"
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        for i, layer in enumerate(self.layers):
+            if i == 0 and self.first_linear_fn is not None:
+                x = self.first_linear_fn(x, layer.weight, layer.bias)
+            else:
+                x = layer(x)
+            if i + 1 < len(self.layers):
+                x = F.gelu(x, approximate="tanh")
+        return x
+
+
+def mse_loss(out: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    return F.mse_loss(out.float(), target.float())

@@ -1,0 +1,211 @@
+"""ShardedParameterServer — worker + parameter-server shard of one rank.
+
+What the reference spreads over three processes and two gRPC hops per iteration
+(``pull -> compute -> push -> wait-for-sync``, src/worker.cpp:331-406, aggregation in
+src/parameter_server.cpp:18-91) happens here inside one process per GPU:
+
+* the model's parameters are views of the local bf16 replica ``P``;
+* backward hooks copy each finished bucket of gradients into the symmetric space ``G`` and
+  enqueue the fused push (K1) on a high-priority communication stream, so the push of
+  bucket *b* overlaps the backward of the layers in front of it;
+* K1 on rank *r* reduces slice *r* over all workers, updates the fp32 master shard and writes
+  the new bf16 slice into every replica (push-mode all-gather) or only locally (pull mode,
+  followed by K2 / the fused all-gather GEMM);
+* ``step()`` closes the iteration: leftover buckets, optional global-norm clipping, the
+  version wait that replaces the reference's CheckSyncStatus polling.
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+
+import torch
+
+from ..ops import native
+from ..ops.native import OptimConfig
+from .buckets import BucketPlan, ParamSlot, plan_buckets
+
+
+class ShardedParameterServer:
+    def __init__(self, named_params: Sequence[Tuple[str, torch.nn.Parameter]], optim: OptimConfig,
+                 fabric=None, *, world: Optional[int] = None, rank: Optional[int] = None,
+                 group=None, bucket_mb: float = 64.0, broadcast: bool = True,
+                 clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
+                 overlap: bool = True, push_grid: int = 0, sync_init: bool = True):
+        named_params = [(n, p) for n, p in named_params if p.requires_grad]
+        if not named_params:
+            raise ValueError("no trainable parameters")
+        self.named_params = named_params
+        dev = named_params[0][1].device
+        self.device = dev
+        self.is_cuda = dev.type == "cuda"
+        if self.is_cuda:
+            if fabric is None:
+                raise ValueError("CUDA parameters need a Fabric (symmetric heap)")
+            world, rank = fabric.world, fabric.rank
+        else:
+            world = 1 if world is None else world
+            rank = 0 if rank is None else rank
+        self.world, self.rank = world, rank
+        self.clip_norm = clip_norm
+        self.overlap = overlap and self.is_cuda
+        self.broadcast = broadcast
+        optim = OptimConfig(**{**optim.__dict__, "grad_scale": optim.grad_scale / world})
+        self.optim = optim
+
+        elem_bytes = 2
+        self.plan: BucketPlan = plan_buckets(
+            [(n, tuple(p.shape)) for n, p in named_params], world,
+            bucket_elems=max(1, int(bucket_mb * (1 << 20) / elem_bytes)), dedicated=dedicated)
+        if self.is_cuda:
+            from .device_backend import DeviceBackend
+            gdt = named_params[0][1].dtype
+            if gdt not in (torch.bfloat16, torch.float32):
+                raise TypeError(f"unsupported parameter dtype {gdt}")
+            if any(p.dtype != torch.bfloat16 for _, p in named_params):
+                raise TypeError("the CUDA backend keeps bf16 replicas: cast the model to bfloat16")
+            self.backend = DeviceBackend(fabric, self.plan, optim, grad_dtype=torch.bfloat16,
+                                         broadcast=broadcast, clip=clip_norm is not None,
+                                         push_grid=push_grid)
+            self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+        else:
+            from .host_backend import HostBackend
+            pdt = named_params[0][1].dtype
+            self.backend = HostBackend(self.plan, optim, rank, world, group, param_dtype=pdt,
+                                       grad_dtype=pdt, broadcast=broadcast,
+                                       clip=clip_norm is not None)
+            self.comm_stream = None
+        self.fabric = fabric
+
+        # ---- adopt the model: parameters become views of the replica
+        be = self.backend
+        self._params: Dict[str, torch.nn.Parameter] = dict(named_params)
+        with torch.no_grad():
+            for name, p in named_params:
+                slot = self.plan.slots[name]
+                bk = self.plan.buckets[slot.bucket]
+                view = be.param_flat[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
+                view.copy_(p.detach().reshape(-1))
+                p.data = view.view(p.shape)
+            for b, bk in enumerate(self.plan.buckets):
+                s = bk.slice_elems
+                be.shard_slice(be.master, b).copy_(
+                    be.param_bucket(b)[rank * s:(rank + 1) * s].to(torch.float32))
+        if sync_init and world > 1:
+            self._sync_replicas()
+
+        # ---- backward hooks
+        self._pending: List[List[Tuple[ParamSlot, torch.Tensor]]] = [[] for _ in self.plan.buckets]
+        self._flushed = [False] * len(self.plan.buckets)
+        self._events = ([torch.cuda.Event() for _ in self.plan.buckets] if self.is_cuda else None)
+        self._hooks = []
+        for name, p in named_params:
+            self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(name)))
+        self.steps_done = 0
+
+    # ------------------------------------------------------------------ setup helpers
+    def _sync_replicas(self) -> None:
+        """Make every replica the concatenation of the owners' slices (owners are
+        authoritative), so ranks agree even if their initialisation seeds differed."""
+        be = self.backend
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+            self.fabric.barrier(1)
+            for b in range(len(self.plan.buckets)):
+                be.pull(b, skip_wait=True)
+            self.fabric.barrier(1)
+            torch.cuda.synchronize(self.device)
+        else:
+            for b in range(len(self.plan.buckets)):
+                be.pull(b)
+
+    def _make_hook(self, name: str):
+        slot = self.plan.slots[name]
+
+        def hook(p: torch.nn.Parameter):
+            g = p.grad
+            p.grad = None
+            self._pending[slot.bucket].append((slot, g))
+            if len(self._pending[slot.bucket]) == len(self.plan.buckets[slot.bucket].slots):
+                self._flush(slot.bucket)
+
+        return hook
+
+    # ------------------------------------------------------------------ per-bucket push
+    def _stage(self, b: int) -> None:
+        """Copy the bucket's gradients into the symmetric space (zeros where none arrived)."""
+        be = self.backend
+        pend = self._pending[b]
+        bucket = be.grad_bucket(b)
+        if len(pend) < len(self.plan.buckets[b].slots):
+            bucket.zero_()
+        if self.is_cuda:
+            native.gather_to_bucket([g.contiguous() for _, g in pend], bucket,
+                                    [s.offset for s, _ in pend])
+        else:
+            for s, g in pend:
+                bucket[s.offset:s.offset + s.numel].copy_(g.reshape(-1))
+        self._pending[b] = []
+
+    def _flush(self, b: int) -> None:
+        self._stage(b)
+        self._flushed[b] = True
+        clip = self.clip_norm is not None
+        if not self.is_cuda:
+            self.backend.push(b, reduce_only=clip)
+            return
+        if self.overlap:
+            ev = self._events[b]
+            ev.record(torch.cuda.current_stream(self.device))
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                self.backend.push(b, reduce_only=clip)
+        else:
+            self.backend.push(b, reduce_only=clip)
+
+    # ------------------------------------------------------------------ end of iteration
+    def step(self) -> None:
+        """Finish the iteration: after this returns (stream-ordered on CUDA) the model's
+        parameters are the updated ones on every rank."""
+        be = self.backend
+        nb = len(self.plan.buckets)
+        for b in range(nb):
+            if not self._flushed[b]:
+                self._flush(b)
+        if self.is_cuda and self.overlap:
+            ctx = torch.cuda.stream(self.comm_stream)
+        else:
+            import contextlib
+            ctx = contextlib.nullcontext()
+        with ctx:
+            if self.clip_norm is not None:
+                be.norm_allreduce(self.clip_norm)
+                for b in range(nb):
+                    be.push(b, from_reduced=True, clip=True)
+            be.advance_step()
+            if not self.broadcast:
+                for b in range(nb):
+                    if not self.plan.buckets[b].dedicated or not self._fused_first_layer:
+                        be.pull(b)
+        if self.is_cuda:
+            cur = torch.cuda.current_stream(self.device)
+            if self.overlap:
+                cur.wait_stream(self.comm_stream)
+            if self.broadcast:
+                be.wait_versions()
+        self._flushed = [False] * nb
+        self.steps_done += 1
+
+    _fused_first_layer = False
+
+    # ------------------------------------------------------------------ introspection
+    def grad_norm(self) -> torch.Tensor:
+        return self.backend.grad_norm
+
+    def set_lr(self, lr: float) -> None:
+        self.optim = OptimConfig(**{**self.optim.__dict__, "lr": lr})
+        self.backend.set_optim(self.optim)
+
+    def close(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []

@@ -1,0 +1,176 @@
+"""Symmetric HBM heap + signal pads across the GPUs of one NVSwitch box.
+
+One process per GPU.  Every rank ``cudaMalloc``s one heap segment, exports a CUDA IPC
+handle, the handles are exchanged through the control plane (``torch.distributed`` object
+all-gather here; the coordinator's ``ExchangeHandles`` extension RPC for the C++ binaries)
+and every rank maps every peer's segment.  Sub-allocations are made with the same bump
+allocator on every rank, so a buffer has the same offset in every segment and
+``peer_ptr(r) = base[r] + offset`` — the addresses the fused kernels load from / store to
+over NVLink.
+
+Replaces the reference's NCCL clique (src/nccl_manager.cpp:28-85: one process driving all
+GPUs) and its per-iteration cudaMalloc/cudaFree of staging buffers (src/worker.cpp:420-443).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import torch
+
+from .. import _lib
+from .._lib import PsbFabric, check
+
+
+class _RawCuda:
+    """Adapter exposing a raw device allocation through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1",
+                                         "data": (ptr, False), "version": 3}
+
+
+def _wrap(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
+    return torch.as_tensor(_RawCuda(ptr, nbytes), device=device)
+
+
+@dataclass
+class SymBuffer:
+    """A sub-allocation present at the same offset in every rank's heap."""
+    fabric: "Fabric"
+    offset: int
+    nbytes: int
+
+    @property
+    def local(self) -> torch.Tensor:
+        """uint8 view of the local copy."""
+        return self.fabric.heap_u8[self.offset:self.offset + self.nbytes]
+
+    def view(self, dtype: torch.dtype) -> torch.Tensor:
+        return self.local.view(dtype)
+
+    def peer_ptr(self, r: int) -> int:
+        return self.fabric.heap_base[r] + self.offset
+
+    def peer_ptrs(self) -> List[int]:
+        return [self.peer_ptr(r) for r in range(self.fabric.world)]
+
+
+class Fabric:
+    """Peer-mapped heap and signal pad of one rank."""
+
+    def __init__(self, rank: int, world: int, device: torch.device, heap_bytes: int,
+                 exchange: Optional[Callable[[bytes], Sequence[bytes]]] = None,
+                 _local_bases: Optional[List[int]] = None):
+        if not 1 <= world <= _lib.MAX_PEERS:
+            raise ValueError(f"world size {world} outside [1, {_lib.MAX_PEERS}]")
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        self.lib = _lib.load()
+        self.heap_bytes = (int(heap_bytes) + self.pad_bytes() + (2 << 20) - 1) & ~((2 << 20) - 1)
+        self._opened: List[int] = []
+        self._owns = _local_bases is None
+        with torch.cuda.device(self.device):
+            if _local_bases is not None:
+                # in-process emulation: all "ranks" live on this device (tests on one GPU)
+                self.heap_base = list(_local_bases)
+            else:
+                p = C.c_void_p()
+                check(self.lib.psb_heap_alloc(self.heap_bytes, C.byref(p)), "psb_heap_alloc")
+                local = p.value
+                self.heap_base = [0] * world
+                self.heap_base[rank] = local
+                if world > 1:
+                    if exchange is None:
+                        raise ValueError("a multi-rank fabric needs an exchange function")
+                    handle = C.create_string_buffer(_lib.IPC_HANDLE_BYTES)
+                    check(self.lib.psb_ipc_export(local, handle), "psb_ipc_export")
+                    handles = exchange(bytes(handle.raw))
+                    for r in range(world):
+                        if r == rank:
+                            continue
+                        q = C.c_void_p()
+                        check(self.lib.psb_ipc_open(bytes(handles[r]), C.byref(q)),
+                              f"psb_ipc_open(peer {r})")
+                        self.heap_base[r] = q.value
+                        self._opened.append(q.value)
+        self.heap_u8 = _wrap(self.heap_base[rank], self.heap_bytes, self.device)
+        self._cursor = 0
+        self.pad = self.alloc(self.pad_bytes(), align=4096)
+        self._barrier_seq = torch.zeros(64, dtype=torch.int32, device=self.device)
+        self._cfab = PsbFabric()
+        self._cfab.rank, self._cfab.world = rank, world
+        for r in range(world):
+            self._cfab.pad[r] = self.pad.peer_ptr(r)
+
+    # ------------------------------------------------------------------ construction
+    @staticmethod
+    def pad_bytes() -> int:
+        return _lib.PAD_WORDS * 4
+
+    @classmethod
+    def from_process_group(cls, device: torch.device, heap_bytes: int, group=None) -> "Fabric":
+        """One rank per process; IPC handles travel through ``torch.distributed``."""
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            return cls(0, 1, device, heap_bytes)
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+
+        def exchange(h: bytes):
+            out = [None] * world
+            dist.all_gather_object(out, h, group=group)
+            return out
+
+        fab = cls(rank, world, device, heap_bytes, exchange)
+        dist.barrier(group=group)  # every peer has mapped every segment before first use
+        return fab
+
+    @classmethod
+    def local_group(cls, world: int, device: torch.device, heap_bytes: int) -> List["Fabric"]:
+        """``world`` emulated ranks inside this process on one GPU (kernel tests: the launches
+        of the ranks are serialised by the caller, never concurrent spinning kernels)."""
+        device = torch.device(device)
+        lib = _lib.load()
+        total = (int(heap_bytes) + cls.pad_bytes() + (2 << 20) - 1) & ~((2 << 20) - 1)
+        bases = []
+        with torch.cuda.device(device):
+            for _ in range(world):
+                p = C.c_void_p()
+                check(lib.psb_heap_alloc(total, C.byref(p)), "psb_heap_alloc")
+                bases.append(p.value)
+        fabs = [cls(r, world, device, heap_bytes, _local_bases=bases) for r in range(world)]
+        fabs[0]._group_bases = bases  # rank 0 frees them all
+        return fabs
+
+    # ------------------------------------------------------------------ allocation
+    def alloc(self, nbytes: int, align: int = 256) -> SymBuffer:
+        off = (self._cursor + align - 1) // align * align
+        if off + nbytes > self.heap_bytes:
+            raise MemoryError(f"symmetric heap exhausted: need {off + nbytes} of {self.heap_bytes} B")
+        self._cursor = off + nbytes
+        return SymBuffer(self, off, int(nbytes))
+
+    def c_fabric(self) -> PsbFabric:
+        return self._cfab
+
+    # ------------------------------------------------------------------ K9 helpers
+    def barrier(self, slot: int = 0) -> None:
+        """Device-side all-rank barrier on the current stream (no host involvement)."""
+        with torch.cuda.device(self.device):
+            check(self.lib.psb_device_barrier(C.byref(self._cfab), slot,
+                                              self._barrier_seq[slot:].data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream),
+                  "psb_device_barrier")
+
+    def close(self) -> None:
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            for p in self._opened:
+                self.lib.psb_ipc_close(p)
+            self._opened = []
+            if self._owns and self.heap_base[self.rank]:
+                self.lib.psb_heap_free(self.heap_base[self.rank])
+                self.heap_base[self.rank] = 0
+            for p in getattr(self, "_group_bases", []):
+                self.lib.psb_heap_free(p)
+            self._group_bases = []

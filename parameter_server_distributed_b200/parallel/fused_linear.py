@@ -1,0 +1,91 @@
+"""First-layer Linear through K2f: parameter pull (all-gather of the row-sharded weight)
+fused with the tcgen05 GEMM that consumes it.
+
+In pull mode the owner of each row-slice of ``W`` publishes only its own slice (K1 without
+broadcast).  The forward of the first layer then launches ONE kernel that pulls the remote
+slices over NVLink with bulk copies into the local replica while the tensor cores already
+work on the locally owned tiles.  Backward uses plain library GEMMs.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import _lib
+from .._lib import PsbGemmAG, check
+
+
+class FusedFirstLinear:
+    """Callable ``(x, weight, bias) -> y`` bound to one dedicated bucket of a parameter server."""
+
+    def __init__(self, ps, weight_name: str):
+        slot = ps.plan.slots[weight_name]
+        bk = ps.plan.buckets[slot.bucket]
+        if not bk.dedicated or slot.offset != 0:
+            raise ValueError(f"{weight_name} must live in a dedicated bucket")
+        if len(slot.shape) != 2:
+            raise ValueError("fused first layer needs a 2-D weight")
+        N, K = slot.shape
+        if bk.numel != N * K:
+            raise ValueError(f"{weight_name}: {N}x{K} is not divisible into {ps.world} row slices "
+                             "of 512-element granularity")
+        be = ps.backend
+        a = PsbGemmAG()
+        a.fabric = ps.fabric.c_fabric()
+        for r in range(ps.world):
+            a.w[r] = be.P.peer_ptr(r) + bk.base * 2
+        a.N, a.K = N, K
+        a.bucket = slot.bucket
+        a.epoch = be.epoch[slot.bucket:].data_ptr()
+        a.skip_wait = 0
+        self.args = a
+        self.ps = ps
+        self.device = ps.device
+        self.lib = _lib.load()
+        ps._fused_first_layer = True
+
+    def launch(self, x2d: torch.Tensor, bias_f32: Optional[torch.Tensor],
+               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+        a = self.args
+        M = x2d.shape[0]
+        y = torch.empty((M, a.N), dtype=out_dtype, device=x2d.device)
+        a.x = x2d.data_ptr()
+        a.bias = bias_f32.data_ptr() if bias_f32 is not None else None
+        a.y = y.data_ptr()
+        a.M = M
+        a.out_dtype = _lib.BF16 if out_dtype == torch.bfloat16 else _lib.F32
+        with torch.cuda.device(self.device):
+            check(self.lib.psb_gemm_allgather_bf16(
+                C.byref(a), torch.cuda.current_stream(self.device).cuda_stream),
+                "psb_gemm_allgather_bf16")
+        return y
+
+    def __call__(self, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+        return _FusedLinearFn.apply(x, weight, bias, self)
+
+
+class _FusedLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, op: FusedFirstLinear):
+        x2d = x.reshape(-1, x.shape[-1]).contiguous()
+        bias_f32 = bias.detach().float() if bias is not None else None
+        y = op.launch(x2d, bias_f32)
+        ctx.save_for_backward(x2d, weight)
+        ctx.has_bias = bias is not None
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2d, weight = ctx.saved_tensors
+        gy2d = gy.reshape(-1, gy.shape[-1])
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = (gy2d @ weight).view(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            gw = gy2d.t() @ x2d
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = gy2d.sum(0)
+        return gx, gw, gb, None

@@ -1,0 +1,140 @@
+"""Public training API: ``init()`` + ``Trainer``.
+
+``Trainer.step(*host_batch)`` is the call a user makes per iteration.  It is the whole
+reference iteration (``Worker::run_iteration``, src/worker.cpp:331-406: pull -> compute
+gradients -> push -> wait for sync) for one worker/shard pair: H2D copy of the batch from
+pinned host memory, forward, backward with bucket-wise fused pushes, the version wait that
+makes the updated parameters visible, and a D2H read of the loss.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import Callable, Iterable, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .ops.native import OptimConfig
+from .parallel.engine import ShardedParameterServer
+from .parallel.fabric import Fabric
+
+
+@dataclass
+class Context:
+    rank: int
+    world: int
+    local_rank: int
+    device: torch.device
+    fabric: Optional[Fabric]
+
+    def close(self) -> None:
+        if self.fabric is not None:
+            self.fabric.close()
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None) -> Context:
+    """Join the job described by RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* (torchrun) and
+    build the symmetric heap.  ``torch.distributed`` is used only as control plane (handle
+    exchange, host barriers); the data plane is peer memory."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    cuda = torch.cuda.is_available()
+    if cuda:
+        torch.cuda.set_device(local_rank)
+        device = torch.device("cuda", local_rank)
+    else:
+        device = torch.device("cpu")
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if cuda else "gloo"
+        kw = {"device_id": device} if (cuda and backend == "nccl") else {}
+        dist.init_process_group(backend, rank=rank, world_size=world, **kw)
+    fabric = Fabric.from_process_group(device, heap_bytes) if cuda else None
+    return Context(rank, world, local_rank, device, fabric)
+
+
+class LossHandle:
+    """Loss of one step, copied to pinned host memory asynchronously."""
+
+    def __init__(self, host: torch.Tensor, event):
+        self._host, self._event = host, event
+
+    def item(self) -> float:
+        if self._event is not None:
+            self._event.synchronize()
+        return float(self._host.item())
+
+
+class Trainer:
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, ctx: Context,
+                 optim: OptimConfig, *, mode: str = "sync", bucket_mb: float = 64.0,
+                 pull: str = "broadcast", clip_norm: Optional[float] = None,
+                 fused_first_layer: Optional[bool] = None, overlap: bool = True,
+                 staleness: int = 0, push_grid: int = 0):
+        """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
+        ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer)."""
+        if mode not in ("sync", "async", "ssp"):
+            raise ValueError(f"unknown mode {mode!r}")
+        self.model, self.loss_fn, self.ctx = model, loss_fn, ctx
+        self.device = ctx.device
+        dedicated = ()
+        first = getattr(model, "first_weight_name", None)
+        want_fused = (pull == "gather") if fused_first_layer is None else fused_first_layer
+        if want_fused and first is not None and ctx.device.type == "cuda":
+            dedicated = (first(),)
+        if mode == "sync":
+            self.ps = ShardedParameterServer(
+                list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
+                bucket_mb=bucket_mb, broadcast=(pull == "broadcast"), clip_norm=clip_norm,
+                dedicated=dedicated, overlap=overlap, push_grid=push_grid)
+        else:
+            from .parallel.async_engine import AsyncParameterServer
+            self.ps = AsyncParameterServer(
+                list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
+                bucket_mb=bucket_mb, staleness=(staleness if mode == "ssp" else None))
+        if dedicated and pull == "gather":
+            from .parallel.fused_linear import FusedFirstLinear
+            model.first_linear_fn = FusedFirstLinear(self.ps, dedicated[0])
+        self._dev_inputs = None
+        self._loss_ring = None
+        self._ring_i = 0
+        self.h2d_bytes = 0
+        self.d2h_bytes = 4
+
+    # ------------------------------------------------------------------ device-resident step
+    def step_device(self, *inputs: torch.Tensor) -> torch.Tensor:
+        """Forward + backward + push/pull on tensors already on the device; returns the loss
+        tensor (on device)."""
+        *xs, target = inputs
+        out = self.model(*xs)
+        loss = self.loss_fn(out, target)
+        loss.backward()
+        self.ps.step()
+        return loss.detach()
+
+    # ------------------------------------------------------------------ end-to-end step
+    def step(self, *host_inputs: torch.Tensor) -> LossHandle:
+        """End-to-end iteration from (pinned) host tensors; returns a handle on the loss."""
+        if self.device.type != "cuda":
+            loss = self.step_device(*host_inputs)
+            return LossHandle(loss.reshape(()).float(), None)
+        if self._dev_inputs is None:
+            self._dev_inputs = [torch.empty(t.shape, dtype=t.dtype, device=self.device)
+                                for t in host_inputs]
+            self._loss_ring = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(4)]
+            self.h2d_bytes = sum(t.numel() * t.element_size() for t in host_inputs)
+        for d, h in zip(self._dev_inputs, host_inputs):
+            d.copy_(h, non_blocking=True)
+        loss = self.step_device(*self._dev_inputs)
+        host = self._loss_ring[self._ring_i % len(self._loss_ring)]
+        self._ring_i += 1
+        host.copy_(loss.float(), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        return LossHandle(host, ev)

@@ -1,0 +1,53 @@
+"""Bucket plan: name -> (bucket, offset) table, alignment, ownership ranges."""
+import pytest
+
+from parameter_server_distributed_b200.parallel.buckets import (ALIGN_ELEMS, SLICE_QUANTUM,
+                                                                plan_buckets)
+
+
+def shapes():
+    return [("a.weight", (300, 70)), ("a.bias", (300,)), ("b.weight", (1000, 300)),
+            ("b.bias", (1000,)), ("c.weight", (10, 1000))]
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_plan_invariants(world):
+    plan = plan_buckets(shapes(), world, bucket_elems=200_000)
+    seen = set()
+    base = 0
+    for b in plan.buckets:
+        assert b.base == base
+        assert b.numel == b.slice_elems * world
+        assert b.slice_elems % SLICE_QUANTUM == 0
+        base += b.numel
+        end = 0
+        for s in b.slots:
+            assert s.offset % ALIGN_ELEMS == 0
+            assert s.offset >= end
+            end = s.offset + s.numel
+            seen.add(s.name)
+        assert end <= b.numel
+    assert seen == {n for n, _ in shapes()}
+    assert plan.total_elems == base and plan.shard_elems * world == base
+
+
+def test_reverse_order_and_dedicated():
+    plan = plan_buckets(shapes(), 2, bucket_elems=10**9, dedicated=["a.weight"])
+    # back-to-front: the last layer lands in bucket 0
+    assert plan.slots["c.weight"].bucket == 0
+    d = plan.buckets[plan.slots["a.weight"].bucket]
+    assert d.dedicated and len(d.slots) == 1 and plan.slots["a.weight"].offset == 0
+
+
+def test_owner_ranges_cover_tensor():
+    plan = plan_buckets(shapes(), 4, bucket_elems=10**9)
+    for slot in plan.slots.values():
+        pieces = plan.owner_ranges(slot)
+        assert pieces[0][1] == 0 and pieces[-1][2] == slot.numel
+        for (r0, a0, b0), (r1, a1, b1) in zip(pieces, pieces[1:]):
+            assert b0 == a1 and r1 == r0 + 1
+
+
+def test_duplicate_name_rejected():
+    with pytest.raises(ValueError):
+        plan_buckets([("w", (4,)), ("w", (4,))], 1)

@@ -1,0 +1,116 @@
+"""Engine on the host backend: equals torch.optim single-process; gloo world_size=2 equals
+data-parallel mean-gradient training (the reference's BSP semantics,
+/root/reference/src/parameter_server.cpp:49-60,83-90, with lr/momentum/Adam added)."""
+import copy
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from parameter_server_distributed_b200 import OptimConfig
+from parameter_server_distributed_b200.models import MLP, MLPConfig, mse_loss
+from parameter_server_distributed_b200.parallel.engine import ShardedParameterServer
+
+CFG = MLPConfig(d_in=32, hidden=(64, 48), d_out=8)
+
+
+def _torch_opt(kind, params):
+    return {"sgd": lambda: torch.optim.SGD(params, lr=0.01, weight_decay=0.01),
+            "momentum": lambda: torch.optim.SGD(params, lr=0.01, momentum=0.9, weight_decay=0.01),
+            "adam": lambda: torch.optim.Adam(params, lr=0.01, weight_decay=0.01),
+            "adamw": lambda: torch.optim.AdamW(params, lr=0.01, weight_decay=0.01)}[kind]()
+
+
+@pytest.mark.parametrize("kind", ["sgd", "momentum", "adam", "adamw"])
+def test_single_process_matches_torch(kind):
+    torch.manual_seed(0)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()),
+                                OptimConfig(kind=kind, lr=0.01, weight_decay=0.01), bucket_mb=0.005)
+    opt = _torch_opt(kind, list(ref.parameters()))
+    assert len(ps.plan.buckets) > 1
+    for _ in range(4):
+        x, y = torch.randn(16, 32), torch.randn(16, 8)
+        mse_loss(m(x), y).backward()
+        ps.step()
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        opt.step()
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+
+
+def test_clip_matches_torch():
+    torch.manual_seed(1)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind="sgd", lr=0.1),
+                                bucket_mb=0.005, clip_norm=0.05)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.1)
+    for _ in range(3):
+        x, y = torch.randn(16, 32), torch.randn(16, 8)
+        mse_loss(m(x), y).backward()
+        ps.step()
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        n = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.05)
+        opt.step()
+        assert abs(ps.grad_norm().item() - n.item()) < 1e-5
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, kind, broadcast, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind=kind, lr=0.01),
+                                world=world, rank=rank, bucket_mb=0.005, broadcast=broadcast)
+    opt = _torch_opt(kind, list(ref.parameters()))
+    for g in opt.param_groups:
+        g["weight_decay"] = 0.0
+    gen = torch.Generator().manual_seed(123)
+    for _ in range(3):
+        xs = torch.randn(world, 8, 32, generator=gen)
+        ys = torch.randn(world, 8, 8, generator=gen)
+        mse_loss(m(xs[rank]), ys[rank]).backward()
+        ps.step()
+        # oracle: mean over workers of the per-worker gradients
+        opt.zero_grad()
+        for w in range(world):
+            (mse_loss(ref(xs[w]), ys[w]) / world).backward()
+        opt.step()
+    err = max((a - b).abs().max().item() for a, b in zip(m.parameters(), ref.parameters()))
+    q.put((rank, err))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("kind,broadcast", [("sgd", True), ("adam", True), ("momentum", False)])
+def test_gloo_two_workers_match_mean_gradient(kind, broadcast):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, kind, broadcast, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err in res:
+        assert err < 5e-6, (rank, err)
