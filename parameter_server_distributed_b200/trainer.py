@@ -120,21 +120,37 @@ class Trainer:
 
     # ------------------------------------------------------------------ end-to-end step
     def step(self, *host_inputs: torch.Tensor) -> LossHandle:
-        """End-to-end iteration from (pinned) host tensors; returns a handle on the loss."""
+        """End-to-end iteration from (pinned) host tensors; returns a handle on the loss.
+
+        The H2D copy of step i runs on a copy stream into one of two device buffer sets, so it
+        overlaps the tail of step i-1; the loss goes back through a pinned ring."""
         if self.device.type != "cuda":
             loss = self.step_device(*host_inputs)
             return LossHandle(loss.reshape(()).float(), None)
         if self._dev_inputs is None:
-            self._dev_inputs = [torch.empty(t.shape, dtype=t.dtype, device=self.device)
-                                for t in host_inputs]
+            self._dev_inputs = [[torch.empty(t.shape, dtype=t.dtype, device=self.device)
+                                 for t in host_inputs] for _ in range(2)]
+            self._consumed = [None, None]
+            self._copy_stream = torch.cuda.Stream(device=self.device)
             self._loss_ring = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(4)]
             self.h2d_bytes = sum(t.numel() * t.element_size() for t in host_inputs)
-        for d, h in zip(self._dev_inputs, host_inputs):
-            d.copy_(h, non_blocking=True)
-        loss = self.step_device(*self._dev_inputs)
+        slot = self._ring_i & 1
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self._copy_stream):
+            if self._consumed[slot] is not None:
+                self._copy_stream.wait_event(self._consumed[slot])  # step i-2 is done with it
+            for d, h in zip(self._dev_inputs[slot], host_inputs):
+                d.copy_(h, non_blocking=True)
+            copied = torch.cuda.Event()
+            copied.record(self._copy_stream)
+        cur.wait_event(copied)
+        loss = self.step_device(*self._dev_inputs[slot])
+        done = torch.cuda.Event()
+        done.record(cur)
+        self._consumed[slot] = done
         host = self._loss_ring[self._ring_i % len(self._loss_ring)]
         self._ring_i += 1
         host.copy_(loss.float(), non_blocking=True)
         ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(self.device))
+        ev.record(cur)
         return LossHandle(host, ev)

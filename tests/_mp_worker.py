@@ -1,0 +1,113 @@
+"""Multi-GPU worker script (one rank per GPU, launched by torch.distributed.run from
+test_multigpu.py).  Checks the real cross-rank protocol of K1/K2/K2f over NVLink peer memory
+against NCCL collectives + PyTorch fp32 math.  Prints 'MP_OK <rank>' on success."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+import parameter_server_distributed_b200 as psd
+from parameter_server_distributed_b200 import OptimConfig
+from parameter_server_distributed_b200.models import MLP, MLPConfig, mse_loss
+from parameter_server_distributed_b200.ops import reference
+
+
+def check_training(ctx, pull, kind, clip):
+    """N workers through the fused push/pull == single-process training on the mean gradient."""
+    torch.manual_seed(0)
+    cfg = MLPConfig(d_in=512, hidden=(1024, 768), d_out=256)
+    model = MLP(cfg).to(ctx.device, torch.bfloat16)
+    ref = MLP(cfg).to(ctx.device, torch.float32)
+    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    optim = OptimConfig(kind=kind, lr=1e-2 if kind == "sgd" else 1e-3)
+    tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip)
+    masters = {n: p.detach().clone() for n, p in ref.named_parameters()}
+    m = {n: torch.zeros_like(p) for n, p in masters.items()}
+    v = {n: torch.zeros_like(p) for n, p in masters.items()}
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    for it in range(4):
+        xs = torch.randn(ctx.world, 256, 512, generator=gen).to(torch.bfloat16)
+        ys = torch.randn(ctx.world, 256, 256, generator=gen).to(torch.bfloat16)
+        loss = tr.step(xs[ctx.rank].pin_memory(), ys[ctx.rank].pin_memory()).item()
+        # oracle: bf16 model copy with the reference weights, gradient of every worker's batch
+        grads = {n: torch.zeros_like(p) for n, p in masters.items()}
+        omodel = MLP(cfg).to(ctx.device, torch.bfloat16)
+        omodel.load_state_dict({k: masters[k].to(torch.bfloat16) for k in masters})
+        for w in range(ctx.world):
+            omodel.zero_grad()
+            mse_loss(omodel(xs[w].to(ctx.device)), ys[w].to(ctx.device)).backward()
+            for n, p in omodel.named_parameters():
+                grads[n] += p.grad.float()  # bf16 grads summed in fp32, like K1
+        tot = sum(((g / ctx.world) ** 2).sum() for g in grads.values()).item()
+        coef = reference.clip_coef(tot, clip) if clip else 1.0
+        rcfg = OptimConfig(**{**optim.__dict__, "grad_scale": 1.0 / ctx.world})
+        for n in masters:
+            reference.optim_step(rcfg, masters[n].view(-1), grads[n].view(-1), m[n].view(-1),
+                                 v[n].view(-1), clip_coef=coef, step=it)
+        torch.cuda.synchronize()
+        for n, p in model.named_parameters():
+            exp = masters[n].to(torch.bfloat16).float()
+            err = (p.float() - exp).abs().max().item()
+            assert err <= 2e-2 * (exp.abs().max().item() + 1e-3), (pull, kind, it, n, err)
+        if clip:
+            assert abs(tr.ps.grad_norm().item() - tot ** 0.5) < 2e-2 * tot ** 0.5
+    # all ranks hold identical replicas
+    flat = tr.ps.backend.param_flat.clone()
+    ref0 = flat.clone()
+    dist.broadcast(ref0, 0)
+    assert torch.equal(flat, ref0), "replicas diverged"
+    tr.ps.close()
+
+
+def check_fused_gemm(ctx):
+    import ctypes as C
+    from parameter_server_distributed_b200 import _lib
+    world, rank = ctx.world, ctx.rank
+    M, K = 1024, 1024
+    N = 256 * world * 2
+    buf = ctx.fabric.alloc(N * K * 2, align=4096)
+    torch.manual_seed(11)
+    w_full = (torch.randn(N, K, device=ctx.device) * 0.5).to(torch.bfloat16)
+    rows = N // world
+    t = buf.view(torch.bfloat16).view(N, K)
+    t.zero_()
+    t[rank * rows:(rank + 1) * rows].copy_(w_full[rank * rows:(rank + 1) * rows])
+    torch.cuda.synchronize()
+    dist.barrier()
+    x = (torch.randn(M, K, device=ctx.device) * 0.5).to(torch.bfloat16)
+    y = torch.empty(M, N, dtype=torch.bfloat16, device=ctx.device)
+    a = _lib.PsbGemmAG()
+    a.fabric = ctx.fabric.c_fabric()
+    for q in range(world):
+        a.w[q] = buf.peer_ptr(q)
+    a.x, a.bias, a.y = x.data_ptr(), None, y.data_ptr()
+    a.M, a.N, a.K = M, N, K
+    a.out_dtype, a.bucket, a.epoch, a.skip_wait = _lib.BF16, 0, None, 1
+    _lib.check(_lib.load().psb_gemm_allgather_bf16(C.byref(a),
+                                                   torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    exp = x.float() @ w_full.float().t()
+    err = (y.float() - exp).abs().max().item() / exp.abs().max().item()
+    assert err < 1.5e-2, err
+    assert torch.equal(t, w_full), "gathered weight differs"
+    dist.barrier()
+
+
+def main():
+    ctx = psd.init(heap_bytes=256 << 20)
+    assert ctx.world >= 2
+    check_fused_gemm(ctx)
+    for pull, kind, clip in [("broadcast", "sgd", None), ("broadcast", "adamw", 0.5),
+                             ("gather", "momentum", None), ("gather", "adam", None)]:
+        check_training(ctx, pull, kind, clip)
+        dist.barrier()
+    print(f"MP_OK {ctx.rank}", flush=True)
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
