@@ -51,8 +51,14 @@ def check_training(ctx, pull, kind, clip):
         torch.cuda.synchronize()
         for n, p in model.named_parameters():
             exp = masters[n].to(torch.bfloat16).float()
-            err = (p.float() - exp).abs().max().item()
-            assert err <= 2e-2 * (exp.abs().max().item() + 1e-3), (pull, kind, it, n, err)
+            diff = (p.float() - exp).abs()
+            err = diff.max().item()
+            tol = 2e-2 * (exp.abs().max().item() + 1e-3)
+            if kind in ("adam", "adamw"):
+                # sign(g) decides an lr-sized move: bf16 noise on near-zero gradients flips it
+                tol += 2.2 * optim.lr * (it + 1)
+                assert diff.mean().item() <= 0.3 * optim.lr * (it + 1), (pull, kind, it, n)
+            assert err <= tol, (pull, kind, it, n, err, tol)
         if clip:
             assert abs(tr.ps.grad_norm().item() - tot ** 0.5) < 2e-2 * tot ** 0.5
     # all ranks hold identical replicas
