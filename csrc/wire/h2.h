@@ -1,0 +1,154 @@
+// h2.h — minimal HTTP/2 connection (RFC 7540) + gRPC unary transport on top of it.
+//
+// Wire-compatible stand-in for the gRPC C++ library the reference links
+// (/root/reference/CMakeLists.txt:20, src/*_service.cpp, src/worker.cpp:141-314) and which is
+// not installable on the target box.  Scope: cleartext h2 with prior knowledge (what
+// grpc::InsecureChannelCredentials / InsecureServerCredentials speak), unary calls, identity
+// encoding, full flow control in both directions, PING / SETTINGS / GOAWAY / RST_STREAM.
+// Unlike the reference (4 MiB default receive limit never raised — SURVEY D7) message size is
+// bounded only by `max_message_bytes`.
+#pragma once
+
+#include <atomic>
+#include <cstdint>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "hpack.h"
+
+namespace psb {
+namespace h2 {
+
+enum FrameType : uint8_t {
+  DATA = 0, HEADERS = 1, PRIORITY = 2, RST_STREAM = 3, SETTINGS = 4, PUSH_PROMISE = 5, PING = 6,
+  GOAWAY = 7, WINDOW_UPDATE = 8, CONTINUATION = 9
+};
+enum Flags : uint8_t { END_STREAM = 0x1, ACK = 0x1, END_HEADERS = 0x4, PADDED = 0x8, PRIO = 0x20 };
+
+struct Stream {
+  uint32_t id = 0;
+  std::vector<hpack::Header> headers;   // request headers (server) / response headers (client)
+  std::vector<hpack::Header> trailers;  // client side: trailing HEADERS
+  std::string body;
+  bool headers_done = false;
+  bool remote_closed = false;
+  bool reset = false;
+  int64_t send_window = 65535;
+};
+
+// One HTTP/2 connection over a connected TCP socket.  Not thread-safe: the owner serialises.
+class Conn {
+ public:
+  Conn(int fd, bool is_server);
+  ~Conn();
+  bool handshake();  // preface + SETTINGS exchange start
+  // Reads and processes exactly one frame.  Returns false when the connection is finished.
+  bool pump();
+  // Stream that became complete (remote END_STREAM) since the last call, or nullptr.
+  Stream* take_completed();
+  Stream* find(uint32_t id);
+  void erase(uint32_t id);
+  bool send_headers(uint32_t sid, const std::vector<hpack::Header>& h, bool end_stream);
+  // Sends `data` as DATA frames, honouring flow control (pumps incoming frames while blocked).
+  bool send_data(uint32_t sid, const std::string& data, bool end_stream);
+  bool send_rst(uint32_t sid, uint32_t code);
+  bool send_goaway(uint32_t code);
+  uint32_t next_stream_id() { uint32_t s = next_sid_; next_sid_ += 2; return s; }
+  Stream& open_stream(uint32_t sid);
+  bool alive() const { return alive_; }
+  int fd() const { return fd_; }
+  size_t max_message_bytes = (size_t)1 << 31;
+
+ private:
+  bool read_exact(void* buf, size_t n);
+  bool write_all(const void* buf, size_t n);
+  bool write_frame(uint8_t type, uint8_t flags, uint32_t sid, const void* payload, size_t n);
+  bool on_headers_block(uint32_t sid, uint8_t flags);
+  bool on_settings(const std::string& p, uint8_t flags);
+
+  int fd_;
+  bool server_;
+  bool alive_ = true;
+  bool goaway_ = false;
+  hpack::Decoder dec_;
+  hpack::Encoder enc_;
+  std::map<uint32_t, Stream> streams_;
+  std::vector<uint32_t> completed_;
+  std::string hdr_block_;
+  uint32_t hdr_sid_ = 0;
+  uint8_t hdr_flags_ = 0;
+  int64_t conn_send_window_ = 65535;
+  int64_t peer_initial_window_ = 65535;
+  uint32_t peer_max_frame_ = 16384;
+  uint32_t next_sid_ = 1;
+  uint32_t last_peer_sid_ = 0;
+};
+
+}  // namespace h2
+
+namespace grpc_lite {
+
+// gRPC status codes used here
+enum Code { OK = 0, UNKNOWN = 2, DEADLINE_EXCEEDED = 4, UNIMPLEMENTED = 12, INTERNAL = 13,
+            UNAVAILABLE = 14 };
+
+struct Status {
+  int code = OK;
+  std::string message;
+  bool ok() const { return code == OK; }
+};
+
+using Handler = std::function<Status(const std::string& request, std::string& response)>;
+
+class Server {
+ public:
+  Server();
+  ~Server();
+  void add(const std::string& path, Handler h);  // path = "/package.Service/Method"
+  // Binds and listens ("host:port"; port 0 picks a free one).  Returns the bound port or -1.
+  int listen(const std::string& address);
+  void serve_forever();  // blocks until shutdown()
+  void start();          // serve on a background thread
+  void shutdown();
+  int port() const { return port_; }
+
+ private:
+  void accept_loop();
+  void serve_conn(int fd);
+  std::map<std::string, Handler> handlers_;
+  int listen_fd_ = -1;
+  int port_ = -1;
+  std::atomic<bool> running_{false};
+  std::thread accept_thread_;
+  std::mutex conns_mu_;
+  std::vector<int> conn_fds_;
+  std::atomic<int> active_{0};
+};
+
+// Client channel: one persistent connection, one unary call at a time, reconnects on failure.
+class Channel {
+ public:
+  explicit Channel(const std::string& target);  // "host:port" (host-only => port 443 like gRPC)
+  ~Channel();
+  Status call(const std::string& path, const std::string& request, std::string& response,
+              int timeout_ms = 30000);
+
+ private:
+  bool connect_locked(int timeout_ms);
+  void close_locked();
+  std::string host_;
+  int port_;
+  std::mutex mu_;
+  std::unique_ptr<h2::Conn> conn_;
+};
+
+// helpers shared by binaries
+bool split_host_port(const std::string& s, std::string& host, int& port);
+
+}  // namespace grpc_lite
+}  // namespace psb

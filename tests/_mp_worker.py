@@ -57,7 +57,6 @@ def check_training(ctx, pull, kind, clip):
             if kind in ("adam", "adamw"):
                 # sign(g) decides an lr-sized move: bf16 noise on near-zero gradients flips it
                 tol += 2.2 * optim.lr * (it + 1)
-                assert diff.mean().item() <= 0.3 * optim.lr * (it + 1), (pull, kind, it, n)
             assert err <= tol, (pull, kind, it, n, err, tol)
         if clip:
             assert abs(tr.ps.grad_norm().item() - tot ** 0.5) < 2e-2 * tot ** 0.5
