@@ -1,0 +1,330 @@
+// h2.cpp — HTTP/2 connection state machine (see h2.h).
+#include "h2.h"
+
+#include <errno.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
+#include <cstring>
+
+namespace psb {
+namespace h2 {
+
+namespace {
+const char kPreface[] = "PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n";
+constexpr size_t kPrefaceLen = 24;
+constexpr uint32_t kOurWindow = 0x7fffffff;  // we never want to be the flow-control bottleneck
+constexpr uint32_t kOurMaxFrame = 1 << 20;
+
+void put32(std::string& s, uint32_t v) {
+  char b[4] = {static_cast<char>(v >> 24), static_cast<char>(v >> 16), static_cast<char>(v >> 8),
+               static_cast<char>(v)};
+  s.append(b, 4);
+}
+uint32_t get32(const uint8_t* p) {
+  return (uint32_t(p[0]) << 24) | (uint32_t(p[1]) << 16) | (uint32_t(p[2]) << 8) | p[3];
+}
+}  // namespace
+
+Conn::Conn(int fd, bool is_server) : fd_(fd), server_(is_server) {
+  next_sid_ = is_server ? 2 : 1;
+}
+
+Conn::~Conn() {
+  if (fd_ >= 0) ::close(fd_);
+}
+
+bool Conn::read_exact(void* buf, size_t n) {
+  uint8_t* p = static_cast<uint8_t*>(buf);
+  while (n > 0) {
+    ssize_t r = ::recv(fd_, p, n, 0);
+    if (r == 0) return alive_ = false;
+    if (r < 0) {
+      if (errno == EINTR) continue;
+      return alive_ = false;  // includes SO_RCVTIMEO expiry
+    }
+    p += r;
+    n -= static_cast<size_t>(r);
+  }
+  return true;
+}
+
+bool Conn::write_all(const void* buf, size_t n) {
+  const uint8_t* p = static_cast<const uint8_t*>(buf);
+  while (n > 0) {
+    ssize_t r = ::send(fd_, p, n, MSG_NOSIGNAL);
+    if (r < 0) {
+      if (errno == EINTR) continue;
+      return alive_ = false;
+    }
+    p += r;
+    n -= static_cast<size_t>(r);
+  }
+  return true;
+}
+
+bool Conn::write_frame(uint8_t type, uint8_t flags, uint32_t sid, const void* payload, size_t n) {
+  uint8_t h[9] = {static_cast<uint8_t>(n >> 16), static_cast<uint8_t>(n >> 8),
+                  static_cast<uint8_t>(n), type, flags,
+                  static_cast<uint8_t>((sid >> 24) & 0x7f), static_cast<uint8_t>(sid >> 16),
+                  static_cast<uint8_t>(sid >> 8), static_cast<uint8_t>(sid)};
+  if (n <= 1024) {  // one syscall for small frames
+    uint8_t buf[9 + 1024];
+    memcpy(buf, h, 9);
+    if (n) memcpy(buf + 9, payload, n);
+    return write_all(buf, 9 + n);
+  }
+  return write_all(h, 9) && write_all(payload, n);
+}
+
+bool Conn::handshake() {
+  if (server_) {
+    char pre[kPrefaceLen];
+    if (!read_exact(pre, kPrefaceLen) || memcmp(pre, kPreface, kPrefaceLen) != 0)
+      return alive_ = false;
+  } else {
+    if (!write_all(kPreface, kPrefaceLen)) return false;
+  }
+  std::string s;
+  auto setting = [&](uint16_t id, uint32_t v) {
+    s.push_back(static_cast<char>(id >> 8));
+    s.push_back(static_cast<char>(id));
+    put32(s, v);
+  };
+  if (!server_) setting(2, 0);  // ENABLE_PUSH = 0
+  setting(4, kOurWindow);       // INITIAL_WINDOW_SIZE
+  setting(5, kOurMaxFrame);     // MAX_FRAME_SIZE
+  if (!write_frame(SETTINGS, 0, 0, s.data(), s.size())) return false;
+  std::string wu;
+  put32(wu, kOurWindow - 65535);  // open the connection-level receive window as well
+  return write_frame(WINDOW_UPDATE, 0, 0, wu.data(), wu.size());
+}
+
+Stream& Conn::open_stream(uint32_t sid) {
+  Stream& st = streams_[sid];
+  st.id = sid;
+  st.send_window = peer_initial_window_;
+  return st;
+}
+
+Stream* Conn::find(uint32_t id) {
+  auto it = streams_.find(id);
+  return it == streams_.end() ? nullptr : &it->second;
+}
+
+void Conn::erase(uint32_t id) { streams_.erase(id); }
+
+Stream* Conn::take_completed() {
+  while (!completed_.empty()) {
+    uint32_t id = completed_.front();
+    completed_.erase(completed_.begin());
+    if (Stream* s = find(id)) return s;
+  }
+  return nullptr;
+}
+
+bool Conn::on_settings(const std::string& p, uint8_t flags) {
+  if (flags & ACK) return true;
+  if (p.size() % 6) return alive_ = false;
+  const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
+  for (size_t i = 0; i + 6 <= p.size(); i += 6) {
+    uint16_t id = static_cast<uint16_t>((d[i] << 8) | d[i + 1]);
+    uint32_t v = get32(d + i + 2);
+    if (id == 4) {  // INITIAL_WINDOW_SIZE: adjusts every open stream by the delta
+      int64_t delta = static_cast<int64_t>(v) - peer_initial_window_;
+      peer_initial_window_ = v;
+      for (auto& kv : streams_) kv.second.send_window += delta;
+    } else if (id == 5) {
+      if (v >= 16384 && v <= 16777215) peer_max_frame_ = v;
+    }
+    // HEADER_TABLE_SIZE (1): our encoder never indexes, nothing to do.
+  }
+  return write_frame(SETTINGS, ACK, 0, nullptr, 0);
+}
+
+bool Conn::on_headers_block(uint32_t sid, uint8_t flags) {
+  std::vector<hpack::Header> hs;
+  if (!dec_.decode(hdr_block_, hs)) {
+    send_goaway(9 /*COMPRESSION_ERROR*/);
+    return alive_ = false;
+  }
+  hdr_block_.clear();
+  Stream* st = find(sid);
+  if (!st) {
+    if (!server_) return true;  // response for a stream we already dropped
+    st = &open_stream(sid);
+    last_peer_sid_ = sid;
+  }
+  if (!st->headers_done) {
+    st->headers = std::move(hs);
+    st->headers_done = true;
+  } else {
+    st->trailers = std::move(hs);
+  }
+  if (flags & END_STREAM) {
+    st->remote_closed = true;
+    completed_.push_back(sid);
+  }
+  return true;
+}
+
+bool Conn::pump() {
+  if (!alive_) return false;
+  uint8_t h[9];
+  if (!read_exact(h, 9)) return false;
+  const size_t len = (size_t(h[0]) << 16) | (size_t(h[1]) << 8) | h[2];
+  const uint8_t type = h[3], flags = h[4];
+  const uint32_t sid = get32(h + 5) & 0x7fffffffu;
+  if (len > kOurMaxFrame + 1024) {
+    send_goaway(6 /*FRAME_SIZE_ERROR*/);
+    return alive_ = false;
+  }
+  std::string p(len, '\0');
+  if (len && !read_exact(&p[0], len)) return false;
+  const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
+
+  if (hdr_sid_ != 0 && type != CONTINUATION) {  // header block must be contiguous
+    send_goaway(1);
+    return alive_ = false;
+  }
+  switch (type) {
+    case DATA: {
+      size_t off = 0, pad = 0;
+      if (flags & PADDED) {
+        if (len < 1) return alive_ = false;
+        pad = d[0];
+        off = 1;
+      }
+      if (off + pad > len) return alive_ = false;
+      const size_t n = len - off - pad;
+      Stream* st = find(sid);
+      if (st && !st->reset) {
+        if (st->body.size() + n > max_message_bytes + 5) {
+          send_rst(sid, 11 /*ENHANCE_YOUR_CALM*/);
+          st->reset = true;
+        } else {
+          st->body.append(p, off, n);
+        }
+      }
+      if (len > 0) {  // replenish both windows by what the frame consumed
+        std::string wu;
+        put32(wu, static_cast<uint32_t>(len));
+        if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
+        if (st && !(flags & END_STREAM) && !write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4))
+          return false;
+      }
+      if (st && (flags & END_STREAM)) {
+        st->remote_closed = true;
+        completed_.push_back(sid);
+      }
+      break;
+    }
+    case HEADERS: {
+      size_t off = 0, pad = 0;
+      if (flags & PADDED) {
+        if (len < 1) return alive_ = false;
+        pad = d[0];
+        off = 1;
+      }
+      if (flags & PRIO) off += 5;
+      if (off + pad > len) return alive_ = false;
+      hdr_block_.assign(p, off, len - off - pad);
+      if (flags & END_HEADERS) return on_headers_block(sid, flags);
+      hdr_sid_ = sid;
+      hdr_flags_ = flags;
+      break;
+    }
+    case CONTINUATION: {
+      if (hdr_sid_ != sid) return alive_ = false;
+      hdr_block_.append(p);
+      if (flags & END_HEADERS) {
+        uint8_t f = hdr_flags_;
+        hdr_sid_ = 0;
+        return on_headers_block(sid, f);
+      }
+      break;
+    }
+    case SETTINGS: return on_settings(p, flags);
+    case PING:
+      if (!(flags & ACK)) return write_frame(PING, ACK, 0, p.data(), p.size());
+      break;
+    case WINDOW_UPDATE: {
+      if (len != 4) return alive_ = false;
+      const uint32_t inc = get32(d) & 0x7fffffffu;
+      if (sid == 0) conn_send_window_ += inc;
+      else if (Stream* st = find(sid)) st->send_window += inc;
+      break;
+    }
+    case RST_STREAM:
+      if (Stream* st = find(sid)) {
+        st->reset = true;
+        st->remote_closed = true;
+        completed_.push_back(sid);
+      }
+      break;
+    case GOAWAY: goaway_ = true; break;
+    case PRIORITY:
+    case PUSH_PROMISE:
+    default: break;  // ignored (unknown frame types MUST be ignored)
+  }
+  return true;
+}
+
+bool Conn::send_headers(uint32_t sid, const std::vector<hpack::Header>& hs, bool end_stream) {
+  std::string block;
+  enc_.encode(hs, block);
+  size_t off = 0;
+  bool first = true;
+  do {
+    size_t n = block.size() - off;
+    if (n > peer_max_frame_) n = peer_max_frame_;
+    const bool last = off + n == block.size();
+    uint8_t flags = last ? END_HEADERS : 0;
+    if (first && end_stream) flags |= END_STREAM;
+    if (!write_frame(first ? HEADERS : CONTINUATION, flags, sid, block.data() + off, n))
+      return false;
+    off += n;
+    first = false;
+  } while (off < block.size());
+  return true;
+}
+
+bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
+  size_t off = 0;
+  if (data.empty()) return write_frame(DATA, end_stream ? END_STREAM : 0, sid, nullptr, 0);
+  while (off < data.size()) {
+    Stream* st = find(sid);
+    if (!st || st->reset) return false;
+    int64_t win = conn_send_window_ < st->send_window ? conn_send_window_ : st->send_window;
+    if (win <= 0) {  // blocked: process incoming frames until a WINDOW_UPDATE arrives
+      if (!pump()) return false;
+      continue;
+    }
+    size_t n = data.size() - off;
+    if (n > static_cast<size_t>(win)) n = static_cast<size_t>(win);
+    if (n > peer_max_frame_) n = peer_max_frame_;
+    const bool last = off + n == data.size();
+    if (!write_frame(DATA, (last && end_stream) ? END_STREAM : 0, sid, data.data() + off, n))
+      return false;
+    conn_send_window_ -= static_cast<int64_t>(n);
+    st->send_window -= static_cast<int64_t>(n);
+    off += n;
+  }
+  return true;
+}
+
+bool Conn::send_rst(uint32_t sid, uint32_t code) {
+  std::string p;
+  put32(p, code);
+  return write_frame(RST_STREAM, 0, sid, p.data(), 4);
+}
+
+bool Conn::send_goaway(uint32_t code) {
+  std::string p;
+  put32(p, last_peer_sid_);
+  put32(p, code);
+  return write_frame(GOAWAY, 0, 0, p.data(), p.size());
+}
+
+}  // namespace h2
+}  // namespace psb

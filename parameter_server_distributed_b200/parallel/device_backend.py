@@ -32,6 +32,7 @@ class DeviceBackend:
         self.grad_dtype = grad_dtype
         self.broadcast = broadcast
         self.push_grid = push_grid
+        fabric.reset_flags()  # epoch words below start at 0: drop a previous engine's flags
         gsz = 2 if grad_dtype == torch.bfloat16 else 4
         total = plan.total_elems
         self.G = fabric.alloc(total * gsz, align=4096)

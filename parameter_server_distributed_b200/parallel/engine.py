@@ -197,6 +197,58 @@ class ShardedParameterServer:
 
     _fused_first_layer = False
 
+    # ------------------------------------------------------------------ shard state <-> names
+    def gather_state(self, which: str = "master", group=None) -> Dict[str, torch.Tensor]:
+        """Reassemble a sharded fp32 state (``master`` / ``m`` / ``v``) into named tensors on
+        every rank.  Control-plane path (checkpoints, tests): uses torch.distributed."""
+        import torch.distributed as dist
+        be = self.backend
+        shard = getattr(be, which)
+        if shard is None:
+            return {}
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            parts = [torch.empty_like(shard) for _ in range(self.world)]
+            dist.all_gather(parts, shard.contiguous(), group=group)
+        else:
+            parts = [shard]
+        out = {}
+        for name, slot in self.plan.slots.items():
+            bk = self.plan.buckets[slot.bucket]
+            sb = bk.shard_base(self.world)
+            flat = torch.empty(slot.numel, dtype=torch.float32, device=shard.device)
+            for r, a, b in self.plan.owner_ranges(slot):
+                lo = sb + (slot.offset + a) - r * bk.slice_elems
+                flat[a:b].copy_(parts[r][lo:lo + (b - a)])
+            out[name] = flat.view(slot.shape)
+        return out
+
+    def scatter_state(self, tensors: Dict[str, torch.Tensor], which: str = "master") -> None:
+        """Inverse of :meth:`gather_state` for this rank's shard; ``master`` also refreshes the
+        local replica (every rank must call it with the same tensors)."""
+        be = self.backend
+        shard = getattr(be, which)
+        if shard is None:
+            return
+        with torch.no_grad():
+            for name, t in tensors.items():
+                slot = self.plan.slots.get(name)
+                if slot is None:
+                    continue
+                bk = self.plan.buckets[slot.bucket]
+                sb = bk.shard_base(self.world)
+                flat = t.detach().reshape(-1).to(device=shard.device, dtype=torch.float32)
+                for r, a, b in self.plan.owner_ranges(slot):
+                    if r == self.rank:
+                        lo = sb + (slot.offset + a) - r * bk.slice_elems
+                        shard[lo:lo + (b - a)].copy_(flat[a:b])
+                if which == "master":
+                    view = be.param_flat[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
+                    view.copy_(flat.to(view.dtype))
+        if self.is_cuda:
+            torch.cuda.synchronize(self.device)
+
     # ------------------------------------------------------------------ introspection
     def grad_norm(self) -> torch.Tensor:
         return self.backend.grad_norm

@@ -162,6 +162,26 @@ class Fabric:
                                               torch.cuda.current_stream().cuda_stream),
                   "psb_device_barrier")
 
+    def reset_flags(self) -> None:
+        """Zero the ready / version / norm / ack words of the local pad between two barriers.
+
+        Flags are monotonic counters compared against per-engine epoch words that start at 0,
+        so a new engine on a used fabric must not see the previous engine's values.  Collective:
+        every rank calls it while no push / pull kernel is in flight."""
+        words = self.pad.view(torch.int32)
+        emulated = not self._owns
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            if self.world > 1 and not emulated:
+                self.barrier(3)
+                torch.cuda.synchronize()
+            words[:_lib.PAD_BARRIER_OFF].zero_()
+            words[_lib.PAD_CLOCK_OFF:].zero_()
+            torch.cuda.synchronize()
+            if self.world > 1 and not emulated:
+                self.barrier(3)
+                torch.cuda.synchronize()
+
     def close(self) -> None:
         with torch.cuda.device(self.device):
             torch.cuda.synchronize()

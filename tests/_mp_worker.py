@@ -17,26 +17,24 @@ from parameter_server_distributed_b200.ops import reference
 
 
 def check_training(ctx, pull, kind, clip):
-    """N workers through the fused push/pull == single-process training on the mean gradient."""
+    """Every iteration is checked as ONE step from the engine's actual state: N workers through
+    the fused push/pull == fp32 PyTorch update with the mean of the workers' gradients."""
     torch.manual_seed(0)
     cfg = MLPConfig(d_in=512, hidden=(1024, 768), d_out=256)
     model = MLP(cfg).to(ctx.device, torch.bfloat16)
-    ref = MLP(cfg).to(ctx.device, torch.float32)
-    ref.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
     optim = OptimConfig(kind=kind, lr=1e-2 if kind == "sgd" else 1e-3)
     tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip)
-    masters = {n: p.detach().clone() for n, p in ref.named_parameters()}
-    m = {n: torch.zeros_like(p) for n, p in masters.items()}
-    v = {n: torch.zeros_like(p) for n, p in masters.items()}
+    omodel = MLP(cfg).to(ctx.device, torch.bfloat16)
     gen = torch.Generator(device="cpu").manual_seed(5)
     for it in range(4):
+        masters = tr.ps.gather_state("master")
+        m = tr.ps.gather_state("m") or {n: torch.zeros_like(p) for n, p in masters.items()}
+        v = tr.ps.gather_state("v") or {n: torch.zeros_like(p) for n, p in masters.items()}
+        omodel.load_state_dict({k: p.detach().clone() for k, p in model.state_dict().items()})
         xs = torch.randn(ctx.world, 256, 512, generator=gen).to(torch.bfloat16)
         ys = torch.randn(ctx.world, 256, 256, generator=gen).to(torch.bfloat16)
-        loss = tr.step(xs[ctx.rank].pin_memory(), ys[ctx.rank].pin_memory()).item()
-        # oracle: bf16 model copy with the reference weights, gradient of every worker's batch
+        tr.step(xs[ctx.rank].pin_memory(), ys[ctx.rank].pin_memory()).item()
         grads = {n: torch.zeros_like(p) for n, p in masters.items()}
-        omodel = MLP(cfg).to(ctx.device, torch.bfloat16)
-        omodel.load_state_dict({k: masters[k].to(torch.bfloat16) for k in masters})
         for w in range(ctx.world):
             omodel.zero_grad()
             mse_loss(omodel(xs[w].to(ctx.device)), ys[w].to(ctx.device)).backward()
@@ -48,18 +46,25 @@ def check_training(ctx, pull, kind, clip):
         for n in masters:
             reference.optim_step(rcfg, masters[n].view(-1), grads[n].view(-1), m[n].view(-1),
                                  v[n].view(-1), clip_coef=coef, step=it)
+        if pull == "gather":
+            # the first-layer weight is gathered lazily by the fused GEMM of the next forward
+            with torch.no_grad():
+                model(xs[ctx.rank].to(ctx.device))
         torch.cuda.synchronize()
+        new_masters = tr.ps.gather_state("master")
         for n, p in model.named_parameters():
             exp = masters[n].to(torch.bfloat16).float()
             diff = (p.float() - exp).abs()
-            err = diff.max().item()
-            tol = 2e-2 * (exp.abs().max().item() + 1e-3)
+            tol = 1e-2 * (exp.abs().max().item() + 1e-3)
             if kind in ("adam", "adamw"):
                 # sign(g) decides an lr-sized move: bf16 noise on near-zero gradients flips it
-                tol += 2.2 * optim.lr * (it + 1)
-            assert err <= tol, (pull, kind, it, n, err, tol)
+                tol += 2.2 * optim.lr
+            assert diff.max().item() <= tol, (pull, kind, it, n, diff.max().item(), tol)
+            assert torch.equal(p.detach(), new_masters[n].to(torch.bfloat16)), \
+                ("replica != master", pull, kind, it, n)
         if clip:
-            assert abs(tr.ps.grad_norm().item() - tot ** 0.5) < 2e-2 * tot ** 0.5
+            got = tr.ps.grad_norm().item()
+            assert abs(got - tot ** 0.5) < 2e-2 * tot ** 0.5, (it, got, tot ** 0.5)
     # all ranks hold identical replicas
     flat = tr.ps.backend.param_flat.clone()
     ref0 = flat.clone()
