@@ -1,0 +1,301 @@
+// ps_core.cpp — see ps_core.h.
+#include "ps_core.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+
+#include "ps_device.h"
+
+namespace psb {
+
+ParameterServerCore::ParameterServerCore(int total_workers, const PsOptions& opt)
+    : total_workers_(total_workers), opt_(opt) {
+  if (opt_.device >= 0) dev_ = DeviceShard::create(opt_);  // nullptr if CUDA is unavailable
+}
+
+ParameterServerCore::~ParameterServerCore() { delete dev_; }
+
+void ParameterServerCore::initialize_parameters(const std::vector<HostTensor>& initial) {
+  std::lock_guard<std::mutex> lk(mu_);
+  params_ = initial;
+  m_.assign(params_.size(), {});
+  v_.assign(params_.size(), {});
+  if (dev_) dev_->upload(params_);
+  version_++;
+}
+
+bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration,
+                                            const std::vector<HostTensor>& grads) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (iteration > current_iteration_.load()) current_iteration_.store(iteration);
+
+  if (opt_.mode != PsMode::kSync) {
+    // async / SSP: apply this worker's contribution at once, scaled like one share of the mean
+    const float share = 1.0f / static_cast<float>(std::max(1, total_workers_.load()));
+    std::vector<HostTensor> scaled = grads;
+    for (auto& t : scaled)
+      for (auto& x : t.data) x *= share;
+    apply_locked(scaled);
+    clocks_[worker_id] = std::max(clocks_.count(worker_id) ? clocks_[worker_id] : -1, iteration);
+    IterState& st = iters_[iteration];
+    st.seen[worker_id] = true;
+    st.aggregated = true;
+    return true;
+  }
+
+  IterState& st = iters_[iteration];
+  if (st.aggregated) return true;  // idempotent retry after completion
+  st.staged[worker_id] = grads;    // a re-push from the same worker overwrites its slot
+  st.seen[worker_id] = true;
+  const size_t count = st.staged.size();
+  if (count < static_cast<size_t>(std::max(1, total_workers_.load()))) return false;
+
+  // names / shapes / dtypes come from the completing push; shorter contributions are truncated
+  std::vector<HostTensor> mean(grads.size());
+  for (size_t i = 0; i < grads.size(); ++i) {
+    HostTensor& a = mean[i];
+    a.name = grads[i].name;
+    a.shape = grads[i].shape;
+    a.dtype = grads[i].dtype;
+    const size_t n = grads[i].data.size();
+    a.data.assign(n, 0.0f);
+    for (const auto& kv : st.staged) {  // ascending worker id: deterministic summation order
+      if (i >= kv.second.size()) continue;
+      const std::vector<float>& g = kv.second[i].data;
+      const size_t lim = std::min(n, g.size());
+      for (size_t j = 0; j < lim; ++j) a.data[j] += g[j];
+    }
+    const float div = static_cast<float>(count);
+    for (size_t j = 0; j < n; ++j) a.data[j] /= div;
+  }
+  apply_locked(mean);
+  st.aggregated = true;
+  st.staged.clear();  // the reference keeps every copy forever
+  while (static_cast<int>(iters_.size()) > opt_.keep_iterations) iters_.erase(iters_.begin());
+  return true;
+}
+
+void ParameterServerCore::apply_locked(const std::vector<HostTensor>& g) {
+  if (params_.empty()) {  // bootstrap: the first aggregate becomes the model
+    params_ = g;
+    m_.assign(params_.size(), {});
+    v_.assign(params_.size(), {});
+    if (dev_) dev_->upload(params_);
+    version_++;
+    return;
+  }
+  ++opt_step_;
+  for (size_t i = 0; i < g.size() && i < params_.size(); ++i) {
+    if (g[i].name != params_[i].name || g[i].shape != params_[i].shape) continue;  // positional
+    update_tensor(i, g[i].data);
+  }
+  version_++;
+}
+
+void ParameterServerCore::update_tensor(size_t idx, const std::vector<float>& g) {
+  std::vector<float>& p = params_[idx].data;
+  const size_t n = std::min(p.size(), g.size());
+  if (dev_ && dev_->update(idx, g.data(), n, opt_step_)) return;
+  const std::string& kind = opt_.optimizer;
+  const float lr = opt_.lr, wd = opt_.weight_decay;
+  if (kind == "sgd") {
+    if (lr == 1.0f && wd == 0.0f) {
+      for (size_t j = 0; j < n; ++j) p[j] -= g[j];  // the reference's exact expression
+    } else {
+      for (size_t j = 0; j < n; ++j) p[j] -= lr * (g[j] + wd * p[j]);
+    }
+    return;
+  }
+  if (m_[idx].size() != p.size()) m_[idx].assign(p.size(), 0.0f);
+  std::vector<float>& m = m_[idx];
+  if (kind == "momentum") {
+    for (size_t j = 0; j < n; ++j) {
+      m[j] = opt_.momentum * m[j] + (g[j] + wd * p[j]);
+      p[j] -= lr * m[j];
+    }
+    return;
+  }
+  if (v_[idx].size() != p.size()) v_[idx].assign(p.size(), 0.0f);
+  std::vector<float>& v = v_[idx];
+  const bool decoupled = kind == "adamw";
+  const float b1 = opt_.beta1, b2 = opt_.beta2;
+  const float bias1 = 1.0f - std::pow(b1, static_cast<float>(opt_step_));
+  const float bias2 = 1.0f - std::pow(b2, static_cast<float>(opt_step_));
+  for (size_t j = 0; j < n; ++j) {
+    float gj = g[j];
+    if (decoupled) p[j] *= 1.0f - lr * wd;
+    else gj += wd * p[j];
+    m[j] = b1 * m[j] + (1.0f - b1) * gj;
+    v[j] = b2 * v[j] + (1.0f - b2) * gj * gj;
+    const float denom = std::sqrt(v[j]) / std::sqrt(bias2) + opt_.eps;
+    p[j] -= (lr / bias1) * (m[j] / denom);
+  }
+}
+
+std::vector<HostTensor> ParameterServerCore::serve_parameters(int32_t /*iteration*/) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (dev_) dev_->download(params_);
+  return params_;
+}
+
+bool ParameterServerCore::check_sync_status(int32_t iteration, int32_t& workers_received) {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto it = iters_.find(iteration);
+  if (it == iters_.end()) {
+    workers_received = 0;
+    return false;
+  }
+  workers_received = static_cast<int32_t>(it->second.seen.size());
+  return it->second.aggregated;
+}
+
+bool ParameterServerCore::staleness_ok(int32_t /*worker_id*/, int32_t iteration) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (opt_.mode == PsMode::kAsync) return true;
+  if (opt_.mode == PsMode::kSync) {
+    auto it = iters_.find(iteration);
+    return it != iters_.end() && it->second.aggregated;
+  }
+  int32_t slowest = -1;  // a worker that never pushed has completed nothing
+  if (static_cast<int>(clocks_.size()) >= total_workers_.load()) {
+    slowest = INT32_MAX;
+    for (const auto& kv : clocks_) slowest = std::min(slowest, kv.second);
+  }
+  return iteration - (slowest + 1) <= opt_.staleness;
+}
+
+// ---- checkpoints: SURVEY App. B (raw little-endian structs, size_t = 8 bytes, no padding) ----
+bool ParameterServerCore::write_file(int32_t epoch, const std::string& path) {
+  const std::string tmp = path + ".tmp";
+  {
+    std::ofstream f(tmp, std::ios::binary | std::ios::trunc);
+    if (!f.is_open()) return false;
+    const int32_t iter = current_iteration_.load();
+    f.write(reinterpret_cast<const char*>(&epoch), 4);
+    f.write(reinterpret_cast<const char*>(&iter), 4);
+    const uint64_t nt = params_.size();
+    f.write(reinterpret_cast<const char*>(&nt), 8);
+    for (const auto& t : params_) {
+      const uint64_t nl = t.name.size(), nd = t.shape.size(), ne = t.data.size();
+      f.write(reinterpret_cast<const char*>(&nl), 8);
+      f.write(t.name.data(), static_cast<std::streamsize>(nl));
+      f.write(reinterpret_cast<const char*>(&nd), 8);
+      f.write(reinterpret_cast<const char*>(t.shape.data()), static_cast<std::streamsize>(nd * 4));
+      f.write(reinterpret_cast<const char*>(&t.dtype), 4);
+      f.write(reinterpret_cast<const char*>(&ne), 8);
+      f.write(reinterpret_cast<const char*>(t.data.data()), static_cast<std::streamsize>(ne * 4));
+    }
+    f.flush();
+    if (!f.good()) return false;
+  }
+  return std::rename(tmp.c_str(), path.c_str()) == 0;  // atomic publish (reference writes in place)
+}
+
+bool ParameterServerCore::save_checkpoint(int32_t epoch, const std::string& path) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (dev_) dev_->download(params_);
+  if (!write_file(epoch, path)) return false;
+  // sidecar: optimizer state and mode, so the base file stays loadable by the reference
+  bool has_state = false;
+  for (const auto& m : m_) has_state |= !m.empty();
+  const std::string side = path + ".psb";
+  if (!has_state && opt_step_ == 0) {
+    std::remove(side.c_str());
+    return true;
+  }
+  std::ofstream f(side + ".tmp", std::ios::binary | std::ios::trunc);
+  if (!f.is_open()) return true;  // the parameters are safe; the sidecar is best effort
+  const char magic[4] = {'P', 'S', 'B', 'S'};
+  const uint32_t ver = 1;
+  f.write(magic, 4);
+  f.write(reinterpret_cast<const char*>(&ver), 4);
+  f.write(reinterpret_cast<const char*>(&opt_step_), 8);
+  const uint64_t nk = opt_.optimizer.size(), nt = params_.size();
+  f.write(reinterpret_cast<const char*>(&nk), 8);
+  f.write(opt_.optimizer.data(), static_cast<std::streamsize>(nk));
+  f.write(reinterpret_cast<const char*>(&nt), 8);
+  for (size_t i = 0; i < params_.size(); ++i) {
+    for (const std::vector<float>* s : {&m_[i], &v_[i]}) {
+      const uint64_t n = s->size();
+      f.write(reinterpret_cast<const char*>(&n), 8);
+      f.write(reinterpret_cast<const char*>(s->data()), static_cast<std::streamsize>(n * 4));
+    }
+  }
+  f.close();
+  std::rename((side + ".tmp").c_str(), side.c_str());
+  return true;
+}
+
+bool ParameterServerCore::load_checkpoint(const std::string& path, int32_t& epoch) {
+  std::lock_guard<std::mutex> lk(mu_);
+  std::ifstream f(path, std::ios::binary);
+  if (!f.is_open()) return false;
+  int32_t iter = 0;
+  uint64_t nt = 0;
+  f.read(reinterpret_cast<char*>(&epoch), 4);
+  f.read(reinterpret_cast<char*>(&iter), 4);
+  f.read(reinterpret_cast<char*>(&nt), 8);
+  if (!f.good() || nt > (1u << 24)) return false;
+  std::vector<HostTensor> loaded;
+  loaded.reserve(nt);
+  for (uint64_t i = 0; i < nt; ++i) {
+    HostTensor t;
+    uint64_t nl = 0, nd = 0, ne = 0;
+    f.read(reinterpret_cast<char*>(&nl), 8);
+    if (!f.good() || nl > (1u << 20)) return false;
+    t.name.resize(nl);
+    f.read(&t.name[0], static_cast<std::streamsize>(nl));
+    f.read(reinterpret_cast<char*>(&nd), 8);
+    if (!f.good() || nd > 64) return false;
+    t.shape.resize(nd);
+    f.read(reinterpret_cast<char*>(t.shape.data()), static_cast<std::streamsize>(nd * 4));
+    f.read(reinterpret_cast<char*>(&t.dtype), 4);
+    f.read(reinterpret_cast<char*>(&ne), 8);
+    if (!f.good() || ne > (1ull << 36)) return false;
+    t.data.resize(ne);
+    f.read(reinterpret_cast<char*>(t.data.data()), static_cast<std::streamsize>(ne * 4));
+    if (!f.good()) return false;  // truncated file (the reference would load garbage)
+    loaded.push_back(std::move(t));
+  }
+  params_ = std::move(loaded);
+  current_iteration_.store(iter);
+  m_.assign(params_.size(), {});
+  v_.assign(params_.size(), {});
+  opt_step_ = 0;
+  std::ifstream s(path + ".psb", std::ios::binary);
+  if (s.is_open()) {
+    char magic[4];
+    uint32_t ver = 0;
+    uint64_t nk = 0, n2 = 0;
+    int64_t step = 0;
+    s.read(magic, 4);
+    s.read(reinterpret_cast<char*>(&ver), 4);
+    s.read(reinterpret_cast<char*>(&step), 8);
+    s.read(reinterpret_cast<char*>(&nk), 8);
+    if (s.good() && memcmp(magic, "PSBS", 4) == 0 && ver == 1 && nk < 64) {
+      std::string kind(nk, '\0');
+      s.read(&kind[0], static_cast<std::streamsize>(nk));
+      s.read(reinterpret_cast<char*>(&n2), 8);
+      if (s.good() && n2 == params_.size() && kind == opt_.optimizer) {
+        opt_step_ = step;
+        for (size_t i = 0; i < params_.size() && s.good(); ++i) {
+          for (std::vector<float>* st : {&m_[i], &v_[i]}) {
+            uint64_t n = 0;
+            s.read(reinterpret_cast<char*>(&n), 8);
+            if (!s.good() || n > (1ull << 36)) break;
+            st->resize(n);
+            s.read(reinterpret_cast<char*>(st->data()), static_cast<std::streamsize>(n * 4));
+          }
+        }
+      }
+    }
+  }
+  if (dev_) dev_->upload(params_);
+  version_++;
+  return true;
+}
+
+}  // namespace psb

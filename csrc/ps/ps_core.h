@@ -1,0 +1,90 @@
+// ps_core.h — host-side parameter-server shard: staging, aggregation, update, checkpoints.
+//
+// Compat mode reproduces the reference's ParameterServerCore bit for bit
+// (/root/reference/include/parameter_server.h:17-54, src/parameter_server.cpp:18-188):
+// per-iteration staging by worker id, completion when #distinct pushers >= total_workers,
+// element-wise mean, `p -= mean` (lr = 1), bootstrap-from-first-gradient,
+// idempotent re-push, positional name+shape matching, App. B checkpoint bytes.
+// Beyond the reference: lr / momentum / Adam(W) server updates, async and bounded-staleness
+// (SSP) modes with versioned parameters, bounded memory (staged gradients are dropped after
+// aggregation — fixes D5), atomic checkpoint writes plus a sidecar for optimizer state, one
+// mutex discipline (fixes the races of D6), optional HBM residency through libpsb_kernels.
+#pragma once
+
+#include <atomic>
+#include <cstdint>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace psb {
+
+struct HostTensor {
+  std::string name;
+  std::vector<int32_t> shape;
+  std::vector<float> data;
+  int32_t dtype = 0;
+};
+
+enum class PsMode { kSync, kAsync, kSsp };
+
+struct PsOptions {
+  PsMode mode = PsMode::kSync;
+  int staleness = 0;            // SSP bound s: a worker may run at most s clocks ahead
+  std::string optimizer = "sgd";  // sgd | momentum | adam | adamw
+  float lr = 1.0f;              // compat default: p -= mean(g)
+  float momentum = 0.9f;
+  float beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;
+  float weight_decay = 0.0f;
+  int keep_iterations = 1024;   // iteration states retained for status queries
+  int device = -1;              // >= 0: keep master weights in HBM and update with K3
+};
+
+class DeviceShard;  // ps_device.cpp (dlopen of libpsb_kernels.so)
+
+class ParameterServerCore {
+ public:
+  explicit ParameterServerCore(int total_workers, const PsOptions& opt = PsOptions());
+  ~ParameterServerCore();
+
+  void initialize_parameters(const std::vector<HostTensor>& initial);
+  // Returns true when `iteration` is (now or already) aggregated.
+  bool receive_gradients(int32_t worker_id, int32_t iteration, const std::vector<HostTensor>& grads);
+  std::vector<HostTensor> serve_parameters(int32_t iteration);
+  bool check_sync_status(int32_t iteration, int32_t& workers_received);
+  // SSP / async: is a worker allowed to start clock `iteration`?
+  bool staleness_ok(int32_t worker_id, int32_t iteration);
+  bool save_checkpoint(int32_t epoch, const std::string& path);
+  bool load_checkpoint(const std::string& path, int32_t& epoch);
+
+  int get_total_workers() const { return total_workers_.load(); }
+  void set_total_workers(int n) { total_workers_.store(n); }  // eviction shrinks the barrier
+  int32_t get_current_iteration() const { return current_iteration_.load(); }
+  int64_t version() const { return version_.load(); }
+  const PsOptions& options() const { return opt_; }
+
+ private:
+  void apply_locked(const std::vector<HostTensor>& mean_grads);
+  void update_tensor(size_t idx, const std::vector<float>& g);
+  bool write_file(int32_t epoch, const std::string& path);
+
+  std::atomic<int> total_workers_;
+  PsOptions opt_;
+  std::mutex mu_;  // guards everything below (single lock: no ordering hazards)
+  std::vector<HostTensor> params_;
+  std::vector<std::vector<float>> m_, v_;
+  int64_t opt_step_ = 0;
+  struct IterState {
+    std::map<int32_t, std::vector<HostTensor>> staged;  // ordered by worker id: fixed sum order
+    std::map<int32_t, bool> seen;
+    bool aggregated = false;
+  };
+  std::map<int32_t, IterState> iters_;
+  std::map<int32_t, int32_t> clocks_;  // async / ssp: last clock pushed per worker
+  std::atomic<int32_t> current_iteration_{0};
+  std::atomic<int64_t> version_{0};
+  DeviceShard* dev_ = nullptr;
+};
+
+}  // namespace psb
