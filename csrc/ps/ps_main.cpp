@@ -1,0 +1,61 @@
+// parameter_server — argv-compatible with the reference binary
+// (/root/reference/src/parameter_main.cpp:5-22):
+//   parameter_server [listen=0.0.0.0:50051] [total_workers=2] [checkpoint_interval=10]
+// Extensions are trailing --key=value flags or PSB_* environment variables:
+//   --mode=sync|async|ssp  --staleness=N  --optimizer=sgd|momentum|adam|adamw  --lr=F
+//   --momentum=F --beta1=F --beta2=F --eps=F --weight-decay=F  --device=N (HBM-resident shard)
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "ps_service.h"
+
+static bool flag(const std::string& arg, const char* key, std::string& val) {
+  const std::string pre = std::string("--") + key + "=";
+  if (arg.compare(0, pre.size(), pre) != 0) return false;
+  val = arg.substr(pre.size());
+  return true;
+}
+
+int main(int argc, char** argv) {
+  std::string listen = "0.0.0.0:50051";
+  int total_workers = 2, checkpoint_interval = 10;
+  psb::PsOptions opt;
+  auto env = [](const char* k) -> const char* { return std::getenv(k); };
+  if (const char* e = env("PSB_MODE")) {
+    std::string m = e;
+    opt.mode = m == "async" ? psb::PsMode::kAsync : m == "ssp" ? psb::PsMode::kSsp
+                                                               : psb::PsMode::kSync;
+  }
+  if (const char* e = env("PSB_STALENESS")) opt.staleness = std::atoi(e);
+  if (const char* e = env("PSB_OPTIMIZER")) opt.optimizer = e;
+  if (const char* e = env("PSB_LR")) opt.lr = std::strtof(e, nullptr);
+  if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
+  std::vector<std::string> pos;
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i], v;
+    if (flag(a, "mode", v)) {
+      opt.mode = v == "async" ? psb::PsMode::kAsync : v == "ssp" ? psb::PsMode::kSsp
+                                                                 : psb::PsMode::kSync;
+    } else if (flag(a, "staleness", v)) opt.staleness = std::atoi(v.c_str());
+    else if (flag(a, "optimizer", v)) opt.optimizer = v;
+    else if (flag(a, "lr", v)) opt.lr = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "momentum", v)) opt.momentum = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "beta1", v)) opt.beta1 = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "beta2", v)) opt.beta2 = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "eps", v)) opt.eps = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "weight-decay", v)) opt.weight_decay = std::strtof(v.c_str(), nullptr);
+    else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
+    else if (a.rfind("--", 0) == 0) {
+      std::cerr << "unknown flag " << a << std::endl;
+      return 2;
+    } else pos.push_back(a);
+  }
+  if (pos.size() > 0) listen = pos[0];
+  if (pos.size() > 1) total_workers = std::stoi(pos[1]);
+  if (pos.size() > 2) checkpoint_interval = std::stoi(pos[2]);
+  psb::run_server(listen, total_workers, checkpoint_interval, opt);
+  return 0;
+}

@@ -1,0 +1,167 @@
+// ps_service.cpp — see ps_service.h.
+#include "ps_service.h"
+
+#include <chrono>
+#include <cstdlib>
+#include <iostream>
+#include <sstream>
+
+#include "../wire/pb.h"
+
+namespace psb {
+
+using grpc_lite::Status;
+
+namespace {
+HostTensor from_pb(pb::Tensor&& t) {
+  HostTensor h;
+  h.name = std::move(t.name);
+  h.shape = std::move(t.shape);
+  h.data = std::move(t.data);
+  h.dtype = t.dtype;
+  return h;
+}
+pb::Tensor to_pb(HostTensor&& h) {
+  pb::Tensor t;
+  t.name = std::move(h.name);
+  t.shape = std::move(h.shape);
+  t.data = std::move(h.data);
+  t.dtype = h.dtype;
+  return t;
+}
+}  // namespace
+
+ParameterServerService::ParameterServerService(int total_workers, int checkpoint_interval,
+                                               const PsOptions& opt, int checkpoint_scan_ms)
+    : core_(total_workers, opt), checkpoint_interval_(checkpoint_interval),
+      scan_ms_(checkpoint_scan_ms) {
+  const std::string base = "/parameter_server.ParameterServer/";
+  server_.add(base + "ReceiveGradients", [this](const std::string& req, std::string& resp) {
+    pb::GradientUpdate in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed GradientUpdate"};
+    std::vector<HostTensor> grads;
+    grads.reserve(in.gradients.size());
+    for (auto& t : in.gradients) grads.push_back(from_pb(std::move(t)));  // one move, no copies
+    pb::PushResponse out;
+    out.aggregation_complete = core_.receive_gradients(in.worker_id, in.iteration, grads);
+    out.success = true;
+    out.message = "gradients received";
+    out.iteration = in.iteration;
+    core_.check_sync_status(in.iteration, out.workers_received);
+    out.total_workers = core_.get_total_workers();
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(base + "ServeParameters", [this](const std::string& req, std::string& resp) {
+    pb::PullRequest in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed PullRequest"};
+    pb::ParameterUpdate out;
+    out.iteration = in.iteration;
+    if (core_.options().mode == PsMode::kSync) {
+      int32_t received = 0;
+      out.ready = core_.check_sync_status(in.iteration, received);
+    } else {
+      out.ready = core_.staleness_ok(in.worker_id, in.iteration);
+    }
+    for (auto& t : core_.serve_parameters(in.iteration)) out.parameters.push_back(to_pb(std::move(t)));
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(base + "CheckSyncStatus", [this](const std::string& req, std::string& resp) {
+    pb::SyncStatusRequest in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SyncStatusRequest"};
+    pb::SyncStatusResponse out;
+    out.iteration = in.iteration;
+    out.ready = core_.check_sync_status(in.iteration, out.workers_received);
+    out.total_workers = core_.get_total_workers();
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(base + "SaveCheckpoint", [this](const std::string& req, std::string& resp) {
+    pb::SaveCheckpointRequest in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SaveCheckpointRequest"};
+    std::string path = in.path;
+    if (path.empty()) path = "checkpoint_epoch_" + std::to_string(in.epoch) + ".ckpt";
+    pb::SaveCheckpointResponse out;
+    out.success = core_.save_checkpoint(in.epoch, path);
+    if (out.success) {
+      out.message = "checkpoint saved";
+      out.checkpoint_path = path;
+    } else {
+      out.message = "failed to save checkpoint";
+    }
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(base + "LoadCheckpoint", [this](const std::string& req, std::string& resp) {
+    pb::LoadCheckpointRequest in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed LoadCheckpointRequest"};
+    pb::LoadCheckpointResponse out;
+    int32_t epoch = 0;
+    out.success = core_.load_checkpoint(in.path, epoch);
+    if (out.success) {
+      out.message = "checkpoint loaded";
+      out.epoch = epoch;
+      for (auto& t : core_.serve_parameters(0)) out.parameters.push_back(to_pb(std::move(t)));
+    } else {
+      out.message = "failed to load checkpoint";
+    }
+    resp = out.encode();
+    return Status{};
+  });
+  if (checkpoint_interval_ > 0)
+    checkpoint_thread_ = std::thread(&ParameterServerService::periodic_checkpoint, this);
+}
+
+ParameterServerService::~ParameterServerService() { shutdown(); }
+
+// Same policy as the reference (src/parameter_server_service.cpp:150-169): every scan,
+// epoch = current_iteration / interval; save when a new epoch started and iteration > 0.
+void ParameterServerService::periodic_checkpoint() {
+  int32_t last_epoch = -1;
+  int waited = 0;
+  while (running_) {
+    std::this_thread::sleep_for(std::chrono::milliseconds(50));
+    waited += 50;
+    if (waited < scan_ms_) continue;
+    waited = 0;
+    const int32_t iter = core_.get_current_iteration();
+    const int32_t epoch = iter / checkpoint_interval_;
+    if (epoch > last_epoch && iter > 0) {
+      const std::string path = "checkpoint_epoch_" + std::to_string(epoch) + ".ckpt";
+      if (core_.save_checkpoint(epoch, path)) {
+        last_epoch = epoch;
+        std::cout << "saved checkpoint: " << path << " (epoch " << epoch << ")" << std::endl;
+      }
+    }
+  }
+}
+
+int ParameterServerService::listen(const std::string& address) { return server_.listen(address); }
+void ParameterServerService::serve_forever() { server_.serve_forever(); }
+void ParameterServerService::start() { server_.start(); }
+
+void ParameterServerService::shutdown() {
+  if (running_.exchange(false)) {
+    server_.shutdown();
+    if (checkpoint_thread_.joinable()) checkpoint_thread_.join();
+  }
+}
+
+void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
+                const PsOptions& opt) {
+  int scan_ms = 5000;
+  if (const char* e = std::getenv("PSB_CHECKPOINT_SCAN_MS")) scan_ms = std::atoi(e);
+  ParameterServerService svc(total_workers, checkpoint_interval, opt, scan_ms);
+  if (svc.listen(server_address) < 0) {
+    std::cerr << "parameter server failed to listen on " << server_address << std::endl;
+    std::exit(1);
+  }
+  std::cout << "parameter server listening on " << server_address << std::endl;
+  if (checkpoint_interval > 0)
+    std::cout << "periodic checkpointing every " << checkpoint_interval << " iterations"
+              << std::endl;
+  svc.serve_forever();
+}
+
+}  // namespace psb

@@ -1,0 +1,40 @@
+// ps_service.h — gRPC adapter of ParameterServerCore + periodic checkpoint thread.
+// Counterpart of /root/reference/src/parameter_server_service.cpp:15-191.
+#pragma once
+
+#include <atomic>
+#include <string>
+#include <thread>
+
+#include "../wire/h2.h"
+#include "ps_core.h"
+
+namespace psb {
+
+class ParameterServerService {
+ public:
+  ParameterServerService(int total_workers, int checkpoint_interval, const PsOptions& opt,
+                         int checkpoint_scan_ms = 5000);
+  ~ParameterServerService();
+  int listen(const std::string& address);
+  void serve_forever();
+  void start();
+  void shutdown();
+  ParameterServerCore& core() { return core_; }
+
+ private:
+  void periodic_checkpoint();
+  ParameterServerCore core_;
+  grpc_lite::Server server_;
+  int checkpoint_interval_;
+  int scan_ms_;
+  std::thread checkpoint_thread_;
+  std::atomic<bool> running_{true};
+};
+
+// Blocking entry point with the reference's signature and log lines
+// (include/parameter_server_service.h:5, src/parameter_server_service.cpp:177-191).
+void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
+                const PsOptions& opt = PsOptions());
+
+}  // namespace psb

@@ -196,52 +196,68 @@ void Server::accept_loop() {
 }
 
 void Server::serve_conn(int fd) {
-  h2::Conn conn(fd, /*is_server=*/true);
-  if (!conn.handshake()) return;
-  while (running_ && conn.pump()) {
-    while (h2::Stream* st = conn.take_completed()) {
-      const uint32_t sid = st->id;
-      if (st->reset) {
-        conn.erase(sid);
+  // The reader (this thread) only pumps frames; every completed request runs on its own
+  // handler thread so RPCs multiplexed on one connection (gRPC shares connections between
+  // channels of a process) never wait for each other — e.g. two Barrier calls.
+  auto conn = std::make_shared<h2::Conn>(fd, /*is_server=*/true, /*threaded=*/true);
+  if (!conn->handshake()) return;
+  auto inflight = std::make_shared<std::atomic<int>>(0);
+  while (running_ && conn->pump()) {
+    h2::Stream req;
+    while (conn->take_completed(req)) {
+      if (req.reset) {
+        conn->erase(req.id);
         continue;
       }
-      const std::string* path = find_header(st->headers, ":path");
-      const std::string* ctype = find_header(st->headers, "content-type");
-      Status status;
-      std::string response;
-      if (!path || !ctype || ctype->rfind("application/grpc", 0) != 0) {
-        status = {UNKNOWN, "not a gRPC request"};
-      } else {
-        auto it = handlers_.find(*path);
-        std::string request, err;
-        if (it == handlers_.end()) status = {UNIMPLEMENTED, "unknown method " + *path};
-        else if (!unframe_message(st->body, request, err)) status = {INTERNAL, err};
-        else {
-          try {
-            status = it->second(request, response);
-          } catch (const std::exception& e) {
-            status = {INTERNAL, e.what()};
+      auto st = std::make_shared<h2::Stream>(std::move(req));
+      req = h2::Stream();
+      (*inflight)++;
+      std::thread([this, conn, st, inflight] {
+        const uint32_t sid = st->id;
+        const std::string* path = find_header(st->headers, ":path");
+        const std::string* ctype = find_header(st->headers, "content-type");
+        Status status;
+        std::string response;
+        if (!path || !ctype || ctype->rfind("application/grpc", 0) != 0) {
+          status = {UNKNOWN, "not a gRPC request"};
+        } else {
+          auto it = handlers_.find(*path);
+          std::string request, err;
+          if (it == handlers_.end()) status = {UNIMPLEMENTED, "unknown method " + *path};
+          else if (!unframe_message(st->body, request, err)) status = {INTERNAL, err};
+          else {
+            try {
+              status = it->second(request, response);
+            } catch (const std::exception& e) {
+              status = {INTERNAL, e.what()};
+            }
           }
         }
-      }
-      std::vector<hpack::Header> trailers = {{"grpc-status", std::to_string(status.code)}};
-      if (!status.message.empty())
-        trailers.push_back({"grpc-message", percent_encode(status.message)});
-      bool ok;
-      if (status.ok()) {
-        ok = conn.send_headers(sid, {{":status", "200"}, {"content-type", "application/grpc"}},
-                               false) &&
-             conn.send_data(sid, frame_message(response), false) &&
-             conn.send_headers(sid, trailers, true);
-      } else {  // trailers-only response
-        std::vector<hpack::Header> hs = {{":status", "200"}, {"content-type", "application/grpc"}};
-        hs.insert(hs.end(), trailers.begin(), trailers.end());
-        ok = conn.send_headers(sid, hs, true);
-      }
-      conn.erase(sid);
-      if (!ok) return;
+        std::vector<hpack::Header> trailers = {{"grpc-status", std::to_string(status.code)}};
+        if (!status.message.empty())
+          trailers.push_back({"grpc-message", percent_encode(status.message)});
+        bool ok;
+        if (status.ok()) {
+          ok = conn->send_headers(sid, {{":status", "200"}, {"content-type", "application/grpc"}},
+                                  false) &&
+               conn->send_data(sid, frame_message(response), false) &&
+               conn->send_headers(sid, trailers, true);
+        } else {  // trailers-only response
+          std::vector<hpack::Header> hs = {{":status", "200"},
+                                           {"content-type", "application/grpc"}};
+          hs.insert(hs.end(), trailers.begin(), trailers.end());
+          ok = conn->send_headers(sid, hs, true);
+        }
+        conn->erase(sid);
+        if (!ok) conn->mark_dead();
+        (*inflight)--;
+      }).detach();
     }
   }
+  conn->mark_dead();
+  ::shutdown(fd, SHUT_RDWR);  // wakes handler threads blocked in send()
+  for (int i = 0; i < 1000 && inflight->load() > 0; ++i)
+    std::this_thread::sleep_for(std::chrono::milliseconds(5));
 }
 
 // ------------------------------------------------------------------------------ Channel
@@ -306,15 +322,17 @@ Status Channel::call(const std::string& path, const std::string& request, std::s
         {"user-agent", "psb-grpc-lite/0.1"}};
     bool sent = c.send_headers(sid, hs, false) && c.send_data(sid, frame_message(request), true);
     bool done = false;
-    h2::Stream* st = nullptr;
+    h2::Stream got, tmp;
+    h2::Stream* st = &got;
     while (sent && !done && c.pump()) {
-      while (h2::Stream* s = c.take_completed()) {
-        if (s->id == sid) {
-          st = s;
+      while (c.take_completed(tmp)) {
+        if (tmp.id == sid) {
+          got = std::move(tmp);
           done = true;
         } else {
-          c.erase(s->id);
+          c.erase(tmp.id);
         }
+        tmp = h2::Stream();
       }
     }
     if (!done) {

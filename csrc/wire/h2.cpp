@@ -26,8 +26,14 @@ uint32_t get32(const uint8_t* p) {
 }
 }  // namespace
 
-Conn::Conn(int fd, bool is_server) : fd_(fd), server_(is_server) {
+Conn::Conn(int fd, bool is_server, bool threaded)
+    : fd_(fd), server_(is_server), threaded_(threaded) {
   next_sid_ = is_server ? 2 : 1;
+}
+
+void Conn::mark_dead() {
+  alive_ = false;
+  window_cv_.notify_all();
 }
 
 Conn::~Conn() {
@@ -38,10 +44,11 @@ bool Conn::read_exact(void* buf, size_t n) {
   uint8_t* p = static_cast<uint8_t*>(buf);
   while (n > 0) {
     ssize_t r = ::recv(fd_, p, n, 0);
-    if (r == 0) return alive_ = false;
+    if (r == 0) { mark_dead(); return false; }
     if (r < 0) {
       if (errno == EINTR) continue;
-      return alive_ = false;  // includes SO_RCVTIMEO expiry
+      mark_dead();  // includes SO_RCVTIMEO expiry
+      return false;
     }
     p += r;
     n -= static_cast<size_t>(r);
@@ -55,7 +62,8 @@ bool Conn::write_all(const void* buf, size_t n) {
     ssize_t r = ::send(fd_, p, n, MSG_NOSIGNAL);
     if (r < 0) {
       if (errno == EINTR) continue;
-      return alive_ = false;
+      mark_dead();
+      return false;
     }
     p += r;
     n -= static_cast<size_t>(r);
@@ -64,6 +72,12 @@ bool Conn::write_all(const void* buf, size_t n) {
 }
 
 bool Conn::write_frame(uint8_t type, uint8_t flags, uint32_t sid, const void* payload, size_t n) {
+  std::lock_guard<std::mutex> wl(write_mu_);
+  return write_frame_locked(type, flags, sid, payload, n);
+}
+
+bool Conn::write_frame_locked(uint8_t type, uint8_t flags, uint32_t sid, const void* payload,
+                              size_t n) {
   uint8_t h[9] = {static_cast<uint8_t>(n >> 16), static_cast<uint8_t>(n >> 8),
                   static_cast<uint8_t>(n), type, flags,
                   static_cast<uint8_t>((sid >> 24) & 0x7f), static_cast<uint8_t>(sid >> 16),
@@ -80,8 +94,10 @@ bool Conn::write_frame(uint8_t type, uint8_t flags, uint32_t sid, const void* pa
 bool Conn::handshake() {
   if (server_) {
     char pre[kPrefaceLen];
-    if (!read_exact(pre, kPrefaceLen) || memcmp(pre, kPreface, kPrefaceLen) != 0)
-      return alive_ = false;
+    if (!read_exact(pre, kPrefaceLen) || memcmp(pre, kPreface, kPrefaceLen) != 0) {
+      mark_dead();
+      return false;
+    }
   } else {
     if (!write_all(kPreface, kPrefaceLen)) return false;
   }
@@ -100,11 +116,11 @@ bool Conn::handshake() {
   return write_frame(WINDOW_UPDATE, 0, 0, wu.data(), wu.size());
 }
 
-Stream& Conn::open_stream(uint32_t sid) {
+void Conn::open_stream(uint32_t sid) {
+  std::lock_guard<std::mutex> lk(state_mu_);
   Stream& st = streams_[sid];
   st.id = sid;
   st.send_window = peer_initial_window_;
-  return st;
 }
 
 Stream* Conn::find(uint32_t id) {
@@ -112,20 +128,38 @@ Stream* Conn::find(uint32_t id) {
   return it == streams_.end() ? nullptr : &it->second;
 }
 
-void Conn::erase(uint32_t id) { streams_.erase(id); }
+void Conn::erase(uint32_t id) {
+  std::lock_guard<std::mutex> lk(state_mu_);
+  streams_.erase(id);
+}
 
-Stream* Conn::take_completed() {
+bool Conn::take_completed(Stream& out) {
+  std::lock_guard<std::mutex> lk(state_mu_);
   while (!completed_.empty()) {
     uint32_t id = completed_.front();
     completed_.erase(completed_.begin());
-    if (Stream* s = find(id)) return s;
+    if (Stream* s = find(id)) {
+      out.id = s->id;
+      out.headers = std::move(s->headers);
+      out.trailers = std::move(s->trailers);
+      out.body = std::move(s->body);
+      out.reset = s->reset;
+      out.remote_closed = s->remote_closed;
+      return true;
+    }
   }
-  return nullptr;
+  return false;
 }
 
+bool Conn::fail() {
+  mark_dead();
+  return false;
+}
+
+// state_mu_ held by the caller (pump)
 bool Conn::on_settings(const std::string& p, uint8_t flags) {
   if (flags & ACK) return true;
-  if (p.size() % 6) return alive_ = false;
+  if (p.size() % 6) return fail();
   const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
   for (size_t i = 0; i + 6 <= p.size(); i += 6) {
     uint16_t id = static_cast<uint16_t>((d[i] << 8) | d[i + 1]);
@@ -134,6 +168,7 @@ bool Conn::on_settings(const std::string& p, uint8_t flags) {
       int64_t delta = static_cast<int64_t>(v) - peer_initial_window_;
       peer_initial_window_ = v;
       for (auto& kv : streams_) kv.second.send_window += delta;
+      window_cv_.notify_all();
     } else if (id == 5) {
       if (v >= 16384 && v <= 16777215) peer_max_frame_ = v;
     }
@@ -142,17 +177,20 @@ bool Conn::on_settings(const std::string& p, uint8_t flags) {
   return write_frame(SETTINGS, ACK, 0, nullptr, 0);
 }
 
+// state_mu_ held by the caller (pump)
 bool Conn::on_headers_block(uint32_t sid, uint8_t flags) {
   std::vector<hpack::Header> hs;
   if (!dec_.decode(hdr_block_, hs)) {
     send_goaway(9 /*COMPRESSION_ERROR*/);
-    return alive_ = false;
+    return fail();
   }
   hdr_block_.clear();
   Stream* st = find(sid);
   if (!st) {
     if (!server_) return true;  // response for a stream we already dropped
-    st = &open_stream(sid);
+    st = &streams_[sid];
+    st->id = sid;
+    st->send_window = peer_initial_window_;
     last_peer_sid_ = sid;
   }
   if (!st->headers_done) {
@@ -177,25 +215,26 @@ bool Conn::pump() {
   const uint32_t sid = get32(h + 5) & 0x7fffffffu;
   if (len > kOurMaxFrame + 1024) {
     send_goaway(6 /*FRAME_SIZE_ERROR*/);
-    return alive_ = false;
+    return fail();
   }
   std::string p(len, '\0');
   if (len && !read_exact(&p[0], len)) return false;
   const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
 
+  std::lock_guard<std::mutex> lk(state_mu_);
   if (hdr_sid_ != 0 && type != CONTINUATION) {  // header block must be contiguous
     send_goaway(1);
-    return alive_ = false;
+    return fail();
   }
   switch (type) {
     case DATA: {
       size_t off = 0, pad = 0;
       if (flags & PADDED) {
-        if (len < 1) return alive_ = false;
+        if (len < 1) return fail();
         pad = d[0];
         off = 1;
       }
-      if (off + pad > len) return alive_ = false;
+      if (off + pad > len) return fail();
       const size_t n = len - off - pad;
       Stream* st = find(sid);
       if (st && !st->reset) {
@@ -222,12 +261,12 @@ bool Conn::pump() {
     case HEADERS: {
       size_t off = 0, pad = 0;
       if (flags & PADDED) {
-        if (len < 1) return alive_ = false;
+        if (len < 1) return fail();
         pad = d[0];
         off = 1;
       }
       if (flags & PRIO) off += 5;
-      if (off + pad > len) return alive_ = false;
+      if (off + pad > len) return fail();
       hdr_block_.assign(p, off, len - off - pad);
       if (flags & END_HEADERS) return on_headers_block(sid, flags);
       hdr_sid_ = sid;
@@ -235,7 +274,7 @@ bool Conn::pump() {
       break;
     }
     case CONTINUATION: {
-      if (hdr_sid_ != sid) return alive_ = false;
+      if (hdr_sid_ != sid) return fail();
       hdr_block_.append(p);
       if (flags & END_HEADERS) {
         uint8_t f = hdr_flags_;
@@ -249,10 +288,11 @@ bool Conn::pump() {
       if (!(flags & ACK)) return write_frame(PING, ACK, 0, p.data(), p.size());
       break;
     case WINDOW_UPDATE: {
-      if (len != 4) return alive_ = false;
+      if (len != 4) return fail();
       const uint32_t inc = get32(d) & 0x7fffffffu;
       if (sid == 0) conn_send_window_ += inc;
       else if (Stream* st = find(sid)) st->send_window += inc;
+      window_cv_.notify_all();
       break;
     }
     case RST_STREAM:
@@ -260,6 +300,7 @@ bool Conn::pump() {
         st->reset = true;
         st->remote_closed = true;
         completed_.push_back(sid);
+        window_cv_.notify_all();
       }
       break;
     case GOAWAY: goaway_ = true; break;
@@ -272,16 +313,22 @@ bool Conn::pump() {
 
 bool Conn::send_headers(uint32_t sid, const std::vector<hpack::Header>& hs, bool end_stream) {
   std::string block;
-  enc_.encode(hs, block);
+  enc_.encode(hs, block);  // stateless encoder (no dynamic table): safe from any thread
+  uint32_t max_frame;
+  {
+    std::lock_guard<std::mutex> lk(state_mu_);
+    max_frame = peer_max_frame_;
+  }
+  std::lock_guard<std::mutex> wl(write_mu_);  // HEADERS + CONTINUATION must not be interleaved
   size_t off = 0;
   bool first = true;
   do {
     size_t n = block.size() - off;
-    if (n > peer_max_frame_) n = peer_max_frame_;
+    if (n > max_frame) n = max_frame;
     const bool last = off + n == block.size();
     uint8_t flags = last ? END_HEADERS : 0;
     if (first && end_stream) flags |= END_STREAM;
-    if (!write_frame(first ? HEADERS : CONTINUATION, flags, sid, block.data() + off, n))
+    if (!write_frame_locked(first ? HEADERS : CONTINUATION, flags, sid, block.data() + off, n))
       return false;
     off += n;
     first = false;
@@ -293,21 +340,35 @@ bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
   size_t off = 0;
   if (data.empty()) return write_frame(DATA, end_stream ? END_STREAM : 0, sid, nullptr, 0);
   while (off < data.size()) {
-    Stream* st = find(sid);
-    if (!st || st->reset) return false;
-    int64_t win = conn_send_window_ < st->send_window ? conn_send_window_ : st->send_window;
-    if (win <= 0) {  // blocked: process incoming frames until a WINDOW_UPDATE arrives
-      if (!pump()) return false;
-      continue;
+    size_t n = 0;
+    {
+      std::unique_lock<std::mutex> lk(state_mu_);
+      while (true) {
+        if (!alive_) return false;
+        Stream* st = find(sid);
+        if (!st || st->reset) return false;
+        int64_t win = conn_send_window_ < st->send_window ? conn_send_window_ : st->send_window;
+        if (win > 0) {
+          n = data.size() - off;
+          if (n > static_cast<size_t>(win)) n = static_cast<size_t>(win);
+          if (n > peer_max_frame_) n = peer_max_frame_;
+          conn_send_window_ -= static_cast<int64_t>(n);
+          st->send_window -= static_cast<int64_t>(n);
+          break;
+        }
+        // blocked on flow control until a WINDOW_UPDATE is processed
+        if (threaded_) {
+          window_cv_.wait(lk);
+        } else {
+          lk.unlock();
+          if (!pump()) return false;
+          lk.lock();
+        }
+      }
     }
-    size_t n = data.size() - off;
-    if (n > static_cast<size_t>(win)) n = static_cast<size_t>(win);
-    if (n > peer_max_frame_) n = peer_max_frame_;
     const bool last = off + n == data.size();
     if (!write_frame(DATA, (last && end_stream) ? END_STREAM : 0, sid, data.data() + off, n))
       return false;
-    conn_send_window_ -= static_cast<int64_t>(n);
-    st->send_window -= static_cast<int64_t>(n);
     off += n;
   }
   return true;

@@ -10,6 +10,7 @@
 #pragma once
 
 #include <atomic>
+#include <condition_variable>
 #include <cstdint>
 #include <functional>
 #include <map>
@@ -41,17 +42,21 @@ struct Stream {
   int64_t send_window = 65535;
 };
 
-// One HTTP/2 connection over a connected TCP socket.  Not thread-safe: the owner serialises.
+// One HTTP/2 connection over a connected TCP socket.
+// Threading: exactly one thread calls pump() (the reader).  In `threaded` mode other threads may
+// call send_headers / send_data / erase concurrently (the server runs one handler thread per
+// request so RPCs multiplexed on one connection do not serialise); a sender blocked on flow
+// control then waits for the reader to process WINDOW_UPDATE.  In non-threaded mode (client
+// channel) the single owner thread pumps frames itself while blocked.
 class Conn {
  public:
-  Conn(int fd, bool is_server);
+  Conn(int fd, bool is_server, bool threaded = false);
   ~Conn();
   bool handshake();  // preface + SETTINGS exchange start
   // Reads and processes exactly one frame.  Returns false when the connection is finished.
   bool pump();
-  // Stream that became complete (remote END_STREAM) since the last call, or nullptr.
-  Stream* take_completed();
-  Stream* find(uint32_t id);
+  // Copy of a stream that became complete (remote END_STREAM) since the last call; false if none.
+  bool take_completed(Stream& out);
   void erase(uint32_t id);
   bool send_headers(uint32_t sid, const std::vector<hpack::Header>& h, bool end_stream);
   // Sends `data` as DATA frames, honouring flow control (pumps incoming frames while blocked).
@@ -59,8 +64,9 @@ class Conn {
   bool send_rst(uint32_t sid, uint32_t code);
   bool send_goaway(uint32_t code);
   uint32_t next_stream_id() { uint32_t s = next_sid_; next_sid_ += 2; return s; }
-  Stream& open_stream(uint32_t sid);
-  bool alive() const { return alive_; }
+  void open_stream(uint32_t sid);
+  bool alive() const { return alive_.load(); }
+  void mark_dead();
   int fd() const { return fd_; }
   size_t max_message_bytes = (size_t)1 << 31;
 
@@ -68,13 +74,21 @@ class Conn {
   bool read_exact(void* buf, size_t n);
   bool write_all(const void* buf, size_t n);
   bool write_frame(uint8_t type, uint8_t flags, uint32_t sid, const void* payload, size_t n);
+  bool write_frame_locked(uint8_t type, uint8_t flags, uint32_t sid, const void* payload,
+                          size_t n);  // write_mu_ held
+  bool fail();
   bool on_headers_block(uint32_t sid, uint8_t flags);
   bool on_settings(const std::string& p, uint8_t flags);
+  Stream* find(uint32_t id);  // state_mu_ held
 
   int fd_;
   bool server_;
-  bool alive_ = true;
+  bool threaded_;
+  std::atomic<bool> alive_{true};
   bool goaway_ = false;
+  std::mutex state_mu_;   // streams_, windows, completed_ (lock order: state_mu_ -> write_mu_)
+  std::mutex write_mu_;   // socket writes; a header block is written under one hold
+  std::condition_variable window_cv_;
   hpack::Decoder dec_;
   hpack::Encoder enc_;
   std::map<uint32_t, Stream> streams_;

@@ -1,0 +1,369 @@
+// worker.cpp — see worker.h.  Reference counterpart: /root/reference/src/worker.cpp:69-406.
+#include "worker.h"
+
+#include <dlfcn.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdlib>
+#include <iostream>
+
+#include "../../include/psb_kernels.h"
+#include "../wire/pb.h"
+
+namespace psb {
+
+using grpc_lite::Channel;
+using grpc_lite::Status;
+
+namespace {
+pb::Tensor to_pb(const TensorLite& t) {
+  pb::Tensor p;
+  p.name = t.name, p.shape = t.shape, p.data = t.data, p.dtype = t.dtype;
+  return p;
+}
+TensorLite from_pb(pb::Tensor&& p) {
+  TensorLite t;
+  t.name = std::move(p.name), t.shape = std::move(p.shape), t.data = std::move(p.data);
+  t.dtype = p.dtype;
+  return t;
+}
+void sleep_ms(int ms) { std::this_thread::sleep_for(std::chrono::milliseconds(ms)); }
+}  // namespace
+
+// Synthetic gradients on the GPU (kernel K7), through dlopen like the PS device shard.
+struct Worker::DeviceFill {
+  void* lib = nullptr;
+  decltype(&psb_set_device) set_device = nullptr;
+  decltype(&psb_heap_alloc) heap_alloc = nullptr;
+  decltype(&psb_heap_free) heap_free = nullptr;
+  decltype(&psb_fill_f32) fill = nullptr;
+  decltype(&psb_memcpy_d2h) d2h = nullptr;
+  decltype(&psb_stream_sync) sync = nullptr;
+  int device = 0;
+  float* buf = nullptr;
+  size_t cap = 0;
+
+  static DeviceFill* create(int device) {
+    std::string path = "libpsb_kernels.so";
+    if (const char* e = std::getenv("PSB_KERNELS_LIB")) path = e;
+    else {
+      char exe[4096];
+      ssize_t n = readlink("/proc/self/exe", exe, sizeof(exe) - 1);
+      if (n > 0) {
+        exe[n] = 0;
+        std::string p(exe);
+        size_t cut = p.rfind("/build/bin/");
+        if (cut != std::string::npos)
+          path = p.substr(0, cut) + "/parameter_server_distributed_b200/_native/libpsb_kernels.so";
+      }
+    }
+    void* lib = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (!lib) return nullptr;
+    auto* d = new DeviceFill;
+    d->lib = lib;
+    d->device = device;
+#define PSB_SYM(field, name) d->field = reinterpret_cast<decltype(d->field)>(dlsym(lib, #name))
+    PSB_SYM(set_device, psb_set_device);
+    PSB_SYM(heap_alloc, psb_heap_alloc);
+    PSB_SYM(heap_free, psb_heap_free);
+    PSB_SYM(fill, psb_fill_f32);
+    PSB_SYM(d2h, psb_memcpy_d2h);
+    PSB_SYM(sync, psb_stream_sync);
+#undef PSB_SYM
+    if (!d->fill || d->set_device(device) != 0) {
+      dlclose(lib);
+      delete d;
+      return nullptr;
+    }
+    return d;
+  }
+  bool run(std::vector<float>& out, float value) {
+    if (out.empty()) return true;
+    set_device(device);
+    if (out.size() > cap) {
+      if (buf) heap_free(buf);
+      void* p = nullptr;
+      if (heap_alloc(out.size() * sizeof(float), &p) != 0) return false;
+      buf = static_cast<float*>(p);
+      cap = out.size();
+    }
+    return fill(buf, out.size(), value, nullptr) == 0 &&
+           d2h(out.data(), buf, out.size() * sizeof(float), nullptr) == 0 && sync(nullptr) == 0;
+  }
+  ~DeviceFill() {
+    if (buf) heap_free(buf);
+    if (lib) dlclose(lib);
+  }
+};
+
+Worker::Worker(int worker_id, const std::string& coordinator_address,
+               const std::string& worker_address, int32_t worker_port, const WorkerOptions& opt)
+    : worker_id_(worker_id), coordinator_address_(coordinator_address),
+      worker_address_(worker_address), worker_port_(worker_port), opt_(opt) {
+  coord_.reset(new Channel(coordinator_address_));
+  coord_hb_.reset(new Channel(coordinator_address_));
+  if (opt_.device >= 0) {
+    dev_ = DeviceFill::create(opt_.device);
+    if (!dev_) std::cerr << "worker " << worker_id_ << ": GPU fill unavailable, using host" << std::endl;
+  }
+  heartbeat_thread_ = std::thread(&Worker::heartbeat_loop, this);
+}
+
+Worker::~Worker() {
+  {
+    std::lock_guard<std::mutex> lk(hb_mu_);
+    running_ = false;
+  }
+  hb_cv_.notify_all();
+  if (heartbeat_thread_.joinable()) heartbeat_thread_.join();
+  delete dev_;
+}
+
+bool Worker::initialize() {
+  if (initialized_) return true;
+  if (!discover_parameter_server()) return false;
+  if (!register_with_coordinator()) return false;
+  initialized_ = true;
+  current_status_ = pb::IDLE;
+  return true;
+}
+
+bool Worker::reconnect() {
+  initialized_ = false;
+  coord_.reset(new Channel(coordinator_address_));
+  ps_.reset();
+  return initialize();
+}
+
+// exponential back-off 100 * 2^k ms, 5 tries (reference: src/worker.cpp:129-139)
+bool Worker::query_with_retry(const std::function<bool()>& query, int max_retries) {
+  for (int attempt = 0; attempt < max_retries; ++attempt) {
+    if (query()) return true;
+    if (attempt + 1 < max_retries) sleep_ms(static_cast<int>(std::pow(2, attempt) * 100));
+  }
+  return false;
+}
+
+bool Worker::discover_parameter_server() {
+  return query_with_retry([this]() {
+    std::string resp;
+    Status s = coord_->call("/coordinator.Coordinator/GetParameterServerAddress",
+                            pb::GetPSAddressRequest().encode(), resp, 5000);
+    pb::GetPSAddressResponse out;
+    if (!s.ok() || !out.decode(resp)) return false;
+    ps_port_hint_ = out.port;
+    // tolerate an address that already carries a port ("localhost:50051" + 50051)
+    std::string host;
+    int port = 0;
+    if (grpc_lite::split_host_port(out.address, host, port)) ps_address_ = out.address;
+    else ps_address_ = out.address + ":" + std::to_string(out.port);
+    return true;
+  });
+}
+
+bool Worker::register_with_coordinator() {
+  return query_with_retry([this]() {
+    pb::WorkerInfo req;
+    req.worker_id = worker_id_;
+    req.address = worker_address_.empty() ? "localhost" : worker_address_;
+    req.port = worker_port_;
+    req.hostname = "worker-" + std::to_string(worker_id_);
+    std::string resp;
+    Status s = coord_->call("/coordinator.Coordinator/RegisterWorker", req.encode(), resp, 5000);
+    pb::RegisterResponse out;
+    if (!s.ok() || !out.decode(resp) || !out.success) return false;
+    if (!out.parameter_server_address.empty()) {
+      std::string host;
+      int port = 0;
+      if (grpc_lite::split_host_port(out.parameter_server_address, host, port)) {
+        ps_address_ = out.parameter_server_address;
+      } else if (ps_port_hint_ > 0) {
+        // host-only answer (what the reference coordinator sends): keep the discovered port
+        ps_address_ = out.parameter_server_address + ":" + std::to_string(ps_port_hint_);
+      }
+    }
+    return true;
+  });
+}
+
+std::vector<std::string> Worker::discover_peer_workers() {
+  std::vector<std::string> peers;
+  query_with_retry([this, &peers]() {
+    std::string resp;
+    Status s = coord_->call("/coordinator.Coordinator/ListWorkers",
+                            pb::ListWorkersRequest().encode(), resp, 5000);
+    pb::ListWorkersResponse out;
+    if (!s.ok() || !out.decode(resp)) return false;
+    peers.clear();
+    for (const auto& w : out.workers)
+      if (w.worker_id != worker_id_) peers.push_back(w.address + ":" + std::to_string(w.port));
+    return true;
+  });
+  return peers;
+}
+
+void Worker::send_heartbeat() {
+  if (!initialized_) return;
+  pb::HeartbeatRequest req;
+  req.worker_id = worker_id_;
+  req.status = current_status_.load();
+  std::string resp;
+  Status s = coord_hb_->call("/coordinator.Coordinator/Heartbeat", req.encode(), resp, 3000);
+  pb::HeartbeatResponse out;
+  if (s.ok() && out.decode(resp) && !out.success) {
+    // the coordinator evicted us (e.g. after a stall): announce ourselves again
+    pb::WorkerInfo info;
+    info.worker_id = worker_id_;
+    info.address = worker_address_.empty() ? "localhost" : worker_address_;
+    info.port = worker_port_;
+    info.hostname = "worker-" + std::to_string(worker_id_);
+    coord_hb_->call("/coordinator.Coordinator/RegisterWorker", info.encode(), resp, 3000);
+  }
+}
+
+void Worker::heartbeat_loop() {
+  std::unique_lock<std::mutex> lk(hb_mu_);
+  while (running_) {
+    hb_cv_.wait_for(lk, std::chrono::milliseconds(opt_.heartbeat_ms));
+    if (!running_) break;
+    lk.unlock();
+    send_heartbeat();
+    lk.lock();
+  }
+}
+
+grpc_lite::Channel& Worker::ps_channel() {
+  if (!ps_ || ps_channel_target_ != ps_address_) {
+    ps_.reset(new Channel(ps_address_));
+    ps_channel_target_ = ps_address_;
+  }
+  return *ps_;
+}
+
+std::vector<TensorLite> Worker::pull_parameters(int iteration, bool* ready) {
+  pb::PullRequest req;
+  req.worker_id = worker_id_;
+  req.iteration = iteration;
+  std::string resp;
+  Status s = ps_channel().call("/parameter_server.ParameterServer/ServeParameters", req.encode(),
+                               resp, 30000);
+  pb::ParameterUpdate out;
+  if (!s.ok() || !out.decode(resp)) return {};
+  if (ready) *ready = out.ready;
+  std::vector<TensorLite> params;
+  params.reserve(out.parameters.size());
+  for (auto& t : out.parameters) params.push_back(from_pb(std::move(t)));
+  return params;
+}
+
+bool Worker::push_gradients(int iteration, const std::vector<TensorLite>& grads,
+                            int& workers_received, int& total_workers) {
+  pb::GradientUpdate req;
+  req.worker_id = worker_id_;
+  req.iteration = iteration;
+  req.gradients.reserve(grads.size());
+  for (const auto& g : grads) req.gradients.push_back(to_pb(g));
+  std::string resp;
+  Status s = ps_channel().call("/parameter_server.ParameterServer/ReceiveGradients", req.encode(),
+                               resp, 30000);
+  pb::PushResponse out;
+  last_push_ok_ = s.ok() && out.decode(resp);
+  if (!last_push_ok_) return false;
+  workers_received = out.workers_received;
+  total_workers = out.total_workers;
+  return out.aggregation_complete;
+}
+
+bool Worker::check_sync_ready(int iteration, int& workers_received, int& total_workers) {
+  pb::SyncStatusRequest req;
+  req.iteration = iteration;
+  std::string resp;
+  Status s = ps_channel().call("/parameter_server.ParameterServer/CheckSyncStatus", req.encode(),
+                               resp, 5000);
+  pb::SyncStatusResponse out;
+  if (!s.ok() || !out.decode(resp)) return false;
+  workers_received = out.workers_received;
+  total_workers = out.total_workers;
+  return out.ready;
+}
+
+bool Worker::load_checkpoint_from_server(const std::string& checkpoint_path, int32_t& epoch) {
+  if (!initialized_ && ps_address_.empty() && !discover_parameter_server()) return false;
+  pb::LoadCheckpointRequest req;
+  req.path = checkpoint_path;
+  std::string resp;
+  Status s = ps_channel().call("/parameter_server.ParameterServer/LoadCheckpoint", req.encode(),
+                               resp, 60000);
+  pb::LoadCheckpointResponse out;
+  if (!s.ok() || !out.decode(resp) || !out.success) return false;
+  epoch = out.epoch;  // the parameters now live in the server; the next pull returns them
+  return true;
+}
+
+std::vector<TensorLite> Worker::compute_gradients(const std::vector<TensorLite>& params) {
+  if (grad_fn_) return grad_fn_(params);
+  std::vector<TensorLite> grads = params;
+  for (auto& t : grads) {
+    if (dev_ && dev_->run(t.data, opt_.synthetic_grad)) continue;
+    for (auto& v : t.data) v = opt_.synthetic_grad;
+  }
+  return grads;
+}
+
+bool Worker::run_iteration(int iteration) {
+  current_status_ = pb::TRAINING;
+  for (int attempt = 0; attempt < opt_.max_retries; ++attempt) {
+    bool ready = true;
+    std::vector<TensorLite> params = pull_parameters(iteration, &ready);
+    if (opt_.mode == "ssp") {
+      // bounded staleness: wait until the slowest worker is within the bound
+      const auto deadline = std::chrono::steady_clock::now() +
+                            std::chrono::milliseconds(opt_.sync_timeout_ms);
+      int backoff = 1;
+      while (!ready && std::chrono::steady_clock::now() < deadline) {
+        sleep_ms(backoff);
+        backoff = std::min(backoff * 2, 50);
+        params = pull_parameters(iteration, &ready);
+      }
+    }
+    if (params.empty()) {
+      // empty server: same fabricated model as the reference (src/worker.cpp:346-353)
+      TensorLite w;
+      w.name = "weight";
+      w.shape = {10, 10};
+      w.dtype = 0;
+      w.data.assign(100, 0.0f);
+      params.push_back(std::move(w));
+    }
+    std::vector<TensorLite> grads = compute_gradients(params);
+    int received = 0, total = 0;
+    bool complete = push_gradients(iteration, grads, received, total);
+    if (complete) {
+      current_status_ = pb::IDLE;
+      return true;
+    }
+    if (!last_push_ok_) {  // transport failure: back off and try the whole step again
+      if (attempt + 1 < opt_.max_retries) sleep_ms(500);
+      continue;
+    }
+    // not the last pusher: poll the barrier with a short adaptive back-off
+    const auto deadline =
+        std::chrono::steady_clock::now() + std::chrono::milliseconds(opt_.sync_timeout_ms);
+    int backoff = 1;
+    while (std::chrono::steady_clock::now() < deadline) {
+      if (check_sync_ready(iteration, received, total)) {
+        current_status_ = pb::IDLE;
+        return true;
+      }
+      sleep_ms(backoff);
+      backoff = std::min(backoff * 2, 50);
+    }
+    break;  // the barrier did not open in time: give up on this iteration like the reference
+  }
+  current_status_ = pb::IDLE;
+  return false;
+}
+
+}  // namespace psb

@@ -1,0 +1,71 @@
+// worker_main — argv-compatible with the reference binary
+// (/root/reference/src/worker_main.cpp:5-45):
+//   worker_main [coordinator=localhost:50052] [worker_id=0] [iterations=1] [worker_addr=""]
+//               [worker_port=0] [checkpoint_path=""]
+// Extensions: --mode=sync|async|ssp  --device=N  --heartbeat-ms=N  --sync-timeout-ms=N
+// (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS).
+#include <cstdlib>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "worker.h"
+
+static bool flag(const std::string& arg, const char* key, std::string& val) {
+  const std::string pre = std::string("--") + key + "=";
+  if (arg.compare(0, pre.size(), pre) != 0) return false;
+  val = arg.substr(pre.size());
+  return true;
+}
+
+int main(int argc, char** argv) {
+  std::string coordinator_addr = "localhost:50052";
+  int worker_id = 0, iterations = 1;
+  std::string worker_addr, checkpoint_path;
+  int32_t worker_port = 0;
+  psb::WorkerOptions opt;
+  if (const char* e = std::getenv("PSB_MODE")) opt.mode = e;
+  if (const char* e = std::getenv("PSB_DEVICE")) opt.device = std::atoi(e);
+  if (const char* e = std::getenv("PSB_HEARTBEAT_MS")) opt.heartbeat_ms = std::atoi(e);
+  if (const char* e = std::getenv("PSB_SYNC_TIMEOUT_MS")) opt.sync_timeout_ms = std::atoi(e);
+  std::vector<std::string> pos;
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i], v;
+    if (flag(a, "mode", v)) opt.mode = v;
+    else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
+    else if (flag(a, "heartbeat-ms", v)) opt.heartbeat_ms = std::atoi(v.c_str());
+    else if (flag(a, "sync-timeout-ms", v)) opt.sync_timeout_ms = std::atoi(v.c_str());
+    else if (a.rfind("--", 0) == 0 && a.size() > 2) {
+      std::cerr << "unknown flag " << a << std::endl;
+      return 2;
+    } else pos.push_back(a);
+  }
+  if (pos.size() > 0) coordinator_addr = pos[0];
+  if (pos.size() > 1) worker_id = std::stoi(pos[1]);
+  if (pos.size() > 2) iterations = std::stoi(pos[2]);
+  if (pos.size() > 3) worker_addr = pos[3];
+  if (pos.size() > 4) worker_port = std::stoi(pos[4]);
+  if (pos.size() > 5) checkpoint_path = pos[5];
+
+  psb::Worker w(worker_id, coordinator_addr, worker_addr, worker_port, opt);
+  if (!w.initialize()) {
+    std::cerr << "worker " << worker_id << " failed to initialize" << std::endl;
+    return 1;
+  }
+  if (!checkpoint_path.empty()) {
+    int32_t epoch = 0;
+    if (w.load_checkpoint_from_server(checkpoint_path, epoch)) {
+      std::cout << "worker " << worker_id << " loaded checkpoint from " << checkpoint_path
+                << " (epoch " << epoch << ")" << std::endl;
+    } else {
+      std::cerr << "worker " << worker_id << " failed to load checkpoint from " << checkpoint_path
+                << std::endl;  // continue from scratch, like the reference
+    }
+  }
+  for (int it = 0; it < iterations; ++it) {
+    bool done = w.run_iteration(it);
+    std::cout << "worker " << worker_id << " iter " << it << " done=" << (done ? "true" : "false")
+              << std::endl;
+  }
+  return 0;
+}

@@ -20,7 +20,8 @@ def _setup(world, kind, clip=False, broadcast=True, shapes=None):
     shapes = shapes or [("w0", (257, 130)), ("b0", (257,)), ("w1", (1000, 257))]
     plan = plan_buckets(shapes, world, bucket_elems=200_000)
     fabs = Fabric.local_group(world, DEV, heap_bytes=plan.total_elems * 4 + (8 << 20))
-    cfg = OptimConfig(kind=kind, lr=0.05, weight_decay=0.01, grad_scale=1.0 / world)
+    cfg = OptimConfig(kind=kind, lr=0.05 if kind in ("sgd", "momentum") else 0.002,
+                      weight_decay=0.01, grad_scale=1.0 / world)
     bes = [DeviceBackend(f, plan, cfg, broadcast=broadcast, clip=clip) for f in fabs]
     return plan, fabs, cfg, bes
 

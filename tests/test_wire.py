@@ -1,0 +1,137 @@
+"""T0: the hand-written proto3 codec (csrc/wire/pb.h) against the protobuf runtime built from
+proto/*.proto — golden bytes of SURVEY.md App. A, every message of both reference services and
+the extension service, unpacked repeated scalars, unknown fields, negative int32."""
+import struct
+import subprocess
+
+import pytest
+
+from parameter_server_distributed_b200.control import protos
+from tests._native import ensure_binaries
+
+BIN = ensure_binaries()
+
+
+def roundtrip(name: str, data: bytes) -> bytes:
+    r = subprocess.run([f"{BIN}/psb_pbtool", name], input=data, capture_output=True, timeout=30)
+    assert r.returncode == 0, (name, r.returncode)
+    return r.stdout
+
+
+def test_golden_bytes_gradient_update():
+    T, G = protos.msg("parameter_server.Tensor"), protos.msg("parameter_server.GradientUpdate")
+    g = G(worker_id=1, iteration=2,
+          gradients=[T(name="weight", shape=[10, 10], data=[0.01, 0.01], dtype=0)])
+    golden = bytes.fromhex("080110021a160a0677656967687412020a0a1a080ad7233c0ad7233c")
+    assert g.SerializeToString() == golden
+    assert roundtrip("parameter_server.GradientUpdate", golden) == golden
+
+
+def test_golden_bytes_worker_info_and_push_response():
+    W = protos.msg("coordinator.WorkerInfo")
+    w = W(worker_id=0, address="localhost", port=0, hostname="worker-0")
+    golden = bytes.fromhex("12096c6f63616c686f7374" "2208776f726b65722d30")
+    assert w.SerializeToString() == golden
+    assert roundtrip("coordinator.WorkerInfo", golden) == golden
+    P = protos.msg("parameter_server.PushResponse")
+    p = P(success=True, message="gradients received", iteration=3, aggregation_complete=True,
+          workers_received=2, total_workers=2)
+    golden = bytes.fromhex("08011212") + b"gradients received" + bytes.fromhex("180320012802" "3002")
+    assert p.SerializeToString() == golden
+    assert roundtrip("parameter_server.PushResponse", golden) == golden
+
+
+def _samples():
+    m = protos.msg
+    T = m("parameter_server.Tensor")
+    t1 = T(name="w", shape=[3, 2], data=[1.5, -2.25, 0.0, 3e-8, 1e30, -0.0], dtype=1)
+    t2 = T(name="", shape=[], data=[], dtype=0)
+    W = m("coordinator.WorkerInfo")
+    return [
+        ("coordinator.WorkerInfo", W(worker_id=-7, address="10.0.0.1", port=65535, hostname="h")),
+        ("coordinator.RegisterResponse", m("coordinator.RegisterResponse")(
+            success=True, message="worker registered", parameter_server_address="ps:50051",
+            total_workers=3)),
+        ("coordinator.HeartbeatRequest", m("coordinator.HeartbeatRequest")(worker_id=4, status=1)),
+        ("coordinator.HeartbeatResponse", m("coordinator.HeartbeatResponse")(
+            success=True, timestamp=1793994981)),
+        ("coordinator.ListWorkersRequest", m("coordinator.ListWorkersRequest")()),
+        ("coordinator.ListWorkersResponse", m("coordinator.ListWorkersResponse")(
+            workers=[W(worker_id=0, address="a"), W(worker_id=1, port=9), W()], total_workers=3)),
+        ("coordinator.GetPSAddressRequest", m("coordinator.GetPSAddressRequest")()),
+        ("coordinator.GetPSAddressResponse", m("coordinator.GetPSAddressResponse")(
+            address="localhost", port=50051)),
+        ("parameter_server.Tensor", t1),
+        ("parameter_server.GradientUpdate", m("parameter_server.GradientUpdate")(
+            worker_id=2, iteration=2147483647, gradients=[t1, t2])),
+        ("parameter_server.PushResponse", m("parameter_server.PushResponse")(
+            success=True, message="gradients received", iteration=-1)),
+        ("parameter_server.PullRequest", m("parameter_server.PullRequest")(worker_id=1, iteration=9)),
+        ("parameter_server.ParameterUpdate", m("parameter_server.ParameterUpdate")(
+            iteration=5, parameters=[t1], ready=True)),
+        ("parameter_server.SyncStatusRequest", m("parameter_server.SyncStatusRequest")(iteration=3)),
+        ("parameter_server.SyncStatusResponse", m("parameter_server.SyncStatusResponse")(
+            iteration=3, ready=True, workers_received=2, total_workers=2)),
+        ("parameter_server.SaveCheckpointRequest", m("parameter_server.SaveCheckpointRequest")(
+            epoch=2, path="/tmp/x.ckpt")),
+        ("parameter_server.SaveCheckpointResponse", m("parameter_server.SaveCheckpointResponse")(
+            success=True, message="checkpoint saved", checkpoint_path="/tmp/x.ckpt")),
+        ("parameter_server.LoadCheckpointRequest", m("parameter_server.LoadCheckpointRequest")(
+            path="c.ckpt")),
+        ("parameter_server.LoadCheckpointResponse", m("parameter_server.LoadCheckpointResponse")(
+            success=True, message="checkpoint loaded", epoch=1, parameters=[t1, t2])),
+        ("psb.ShardInfo", m("psb.ShardInfo")(shard_id=3, address="127.0.0.1:6000", device=4)),
+        ("psb.ShardMapResponse", m("psb.ShardMapResponse")(
+            shards=[m("psb.ShardInfo")(shard_id=1, address="x")], total_workers=8)),
+        ("psb.BarrierRequest", m("psb.BarrierRequest")(
+            name="step", worker_id=1, generation=7, expected=8, timeout_ms=1 << 40)),
+        ("psb.BarrierResponse", m("psb.BarrierResponse")(released=True, arrived=8)),
+        ("psb.ClockRequest", m("psb.ClockRequest")(worker_id=1, clock=12)),
+        ("psb.ClockResponse", m("psb.ClockResponse")(min_clock=10)),
+        ("psb.HandleBlob", m("psb.HandleBlob")(key="heap", rank=2, blob=bytes(range(64)))),
+        ("psb.HandleQuery", m("psb.HandleQuery")(key="heap")),
+        ("psb.HandleList", m("psb.HandleList")(
+            handles=[m("psb.HandleBlob")(key="k", rank=1, blob=b"\x00\xff")])),
+        ("psb.Ack", m("psb.Ack")(success=True)),
+    ]
+
+
+@pytest.mark.parametrize("name,message", _samples(), ids=[n for n, _ in _samples()])
+def test_roundtrip_equals_runtime(name, message):
+    data = message.SerializeToString()
+    out = roundtrip(name, data)
+    assert out == data  # canonical field order + packed encoding, byte for byte
+    assert protos.msg(name).FromString(out) == message
+
+
+def varint(v):
+    out = bytearray()
+    while v >= 0x80:
+        out.append((v & 0x7f) | 0x80)
+        v >>= 7
+    out.append(v)
+    return bytes(out)
+
+
+def test_decoder_accepts_unpacked_and_unknown_fields():
+    # Tensor with shape as two unpacked varints (tag 0x10), data as unpacked fixed32 (tag 0x1d),
+    # an unknown varint field 15, an unknown length-delimited field 14 and an unknown fixed64.
+    raw = (b"\x0a\x01w" + b"\x10\x02" + b"\x10\x03" + b"\x1d" + struct.pack("<f", 1.5) +
+           b"\x1d" + struct.pack("<f", -2.0) + b"\x78\x2a" + b"\x72\x03abc" +
+           b"\x69" + b"\x00" * 8 + b"\x20\x01")
+    out = roundtrip("parameter_server.Tensor", raw)
+    t = protos.msg("parameter_server.Tensor").FromString(out)
+    assert t.name == "w" and list(t.shape) == [2, 3] and list(t.data) == [1.5, -2.0] and t.dtype == 1
+
+
+def test_negative_int32_is_ten_byte_varint():
+    P = protos.msg("parameter_server.PullRequest")
+    data = P(worker_id=-1, iteration=-2147483648).SerializeToString()
+    assert len(data) == 2 * 11
+    assert roundtrip("parameter_server.PullRequest", data) == data
+
+
+def test_malformed_input_is_rejected():
+    r = subprocess.run([f"{BIN}/psb_pbtool", "parameter_server.Tensor"], input=b"\x0a\x05ab",
+                       capture_output=True)
+    assert r.returncode == 3
