@@ -1,0 +1,160 @@
+"""T3 / T6 / T7 on the CPU binaries: the test_local.sh flow with assertions (BASELINE.json
+config 1), server-side optimizers and async / SSP modes through the unchanged wire schema,
+periodic checkpoints, resume from a checkpoint, and a missing worker."""
+import os
+import random
+import subprocess
+import time
+
+import grpc
+import numpy as np
+import pytest
+import torch
+
+from parameter_server_distributed_b200.control import protos
+from tests._native import BIN, ROOT, Proc, ensure_binaries, free_port, wait_port
+
+ensure_binaries()
+M = protos.msg
+T = lambda name, data: M("parameter_server.Tensor")(name=name, shape=[len(data)], data=data)
+
+
+def _stub(port):
+    return protos.Stub(grpc.insecure_channel(f"127.0.0.1:{port}"), "parameter_server.ParameterServer")
+
+
+def test_selftest_binary():
+    r = subprocess.run([f"{BIN}/psb_selftest"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "psb_selftest ok" in r.stdout, r.stderr
+
+
+def test_test_local_script(tmp_path):
+    env = dict(os.environ, COORD_PORT=str(free_port()), PS_PORT=str(free_port()),
+               LOG_DIR=str(tmp_path))
+    r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "test_local.sh")], env=env,
+                       capture_output=True, text=True, timeout=180)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "PASS: test_local (10 x done=true)" in r.stdout
+    assert "final weight = -0.0300, checkpoint = 458 bytes" in r.stdout
+
+
+@pytest.mark.parametrize("kind", ["momentum", "adam", "adamw"])
+def test_server_side_optimizers_match_torch(tmp_path, kind):
+    port = free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "2", "0", f"--optimizer={kind}",
+               "--lr=0.05", "--weight-decay=0.01"], str(tmp_path), str(tmp_path / "ps.log"))
+    try:
+        assert wait_port(port)
+        stub = _stub(port)
+        rng = np.random.default_rng(0)
+        w0 = rng.standard_normal(64).astype(np.float32)
+        # bootstrap: the first aggregate becomes the model
+        for wid in (0, 1):
+            stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+                worker_id=wid, iteration=0, gradients=[T("w", w0.tolist())]), timeout=5)
+        p = torch.nn.Parameter(torch.tensor(w0))
+        opt = {"momentum": lambda: torch.optim.SGD([p], lr=0.05, momentum=0.9, weight_decay=0.01),
+               "adam": lambda: torch.optim.Adam([p], lr=0.05, weight_decay=0.01),
+               "adamw": lambda: torch.optim.AdamW([p], lr=0.05, weight_decay=0.01)}[kind]()
+        for it in range(1, 5):
+            g0 = rng.standard_normal(64).astype(np.float32)
+            g1 = rng.standard_normal(64).astype(np.float32)
+            stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+                worker_id=0, iteration=it, gradients=[T("w", g0.tolist())]), timeout=5)
+            r = stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+                worker_id=1, iteration=it, gradients=[T("w", g1.tolist())]), timeout=5)
+            assert r.aggregation_complete
+            p.grad = torch.tensor((g0 + g1) / np.float32(2))
+            opt.step()
+        got = np.array(stub.ServeParameters(M("parameter_server.PullRequest")(), timeout=5)
+                       .parameters[0].data, dtype=np.float32)
+        assert np.allclose(got, p.detach().numpy(), atol=2e-5, rtol=1e-4)
+        # optimizer state survives a checkpoint through the sidecar file
+        assert stub.SaveCheckpoint(M("parameter_server.SaveCheckpointRequest")(
+            epoch=1, path="opt.ckpt"), timeout=5).success
+        assert (tmp_path / "opt.ckpt.psb").exists()
+        assert stub.LoadCheckpoint(M("parameter_server.LoadCheckpointRequest")(path="opt.ckpt"),
+                                   timeout=5).success
+    finally:
+        ps.stop()
+
+
+def test_async_mode_applies_each_push_and_ssp_bounds_staleness(tmp_path):
+    port = free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "2", "0", "--mode=ssp",
+               "--staleness=1"], str(tmp_path), str(tmp_path / "ps.log"))
+    try:
+        assert wait_port(port)
+        stub = _stub(port)
+        push = lambda wid, it, v: stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+            worker_id=wid, iteration=it, gradients=[T("w", [v] * 8)]), timeout=5)
+        pull = lambda wid, it: stub.ServeParameters(M("parameter_server.PullRequest")(
+            worker_id=wid, iteration=it), timeout=5)
+        assert push(0, 0, 1.0).aggregation_complete       # bootstrap: params = share of the push
+        w = np.array(pull(0, 1).parameters[0].data)
+        assert np.allclose(w, 0.5)                         # 1.0 / total_workers
+        assert push(0, 1, 0.2).aggregation_complete        # applied at once: no barrier
+        assert np.allclose(np.array(pull(0, 1).parameters[0].data), 0.5 - 0.1)
+        # worker 1 never pushed: it has completed 0 clocks, so clock 2 of worker 0 is 2 ahead
+        assert pull(0, 1).ready            # 1 - 0 <= 1
+        assert not pull(0, 2).ready        # 2 - 0 >  1
+        push(1, 0, 0.0)
+        assert pull(0, 2).ready            # slowest finished clock 0 -> 2 - 1 <= 1
+        assert not pull(0, 3).ready
+    finally:
+        ps.stop()
+
+
+def test_periodic_checkpoint_and_resume(tmp_path):
+    ps_port, co_port = free_port(), free_port()
+    env = {"PSB_CHECKPOINT_SCAN_MS": "100"}
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "1", "2"], str(tmp_path),
+              str(tmp_path / "ps.log"), env=env)
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "5"],
+                           capture_output=True, text=True, timeout=60, cwd=tmp_path)
+        assert w.stdout.count("done=true") == 5
+        time.sleep(0.5)
+        out = ps.output()
+        assert "periodic checkpointing every 2 iterations" in out
+        assert "saved checkpoint: checkpoint_epoch_2.ckpt (epoch 2)" in out  # iteration 4 / 2
+        ps.stop()
+        # a fresh server resumes from the file when a worker passes it as argv[6]
+        ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "1", "0"], str(tmp_path),
+                  str(tmp_path / "ps2.log"))
+        assert wait_port(ps_port)
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "1", "", "0",
+                            "checkpoint_epoch_2.ckpt"], capture_output=True, text=True, timeout=60,
+                           cwd=tmp_path)
+        assert "worker 0 loaded checkpoint from checkpoint_epoch_2.ckpt (epoch 2)" in w.stdout
+        got = _stub(ps_port).ServeParameters(M("parameter_server.PullRequest")(), timeout=5)
+        # -0.03 after 5 iterations, minus one more 0.01 step
+        assert np.allclose(np.array(got.parameters[0].data), -0.04, atol=1e-6)
+    finally:
+        ps.stop()
+        co.stop()
+
+
+def test_missing_worker_times_out_with_done_false(tmp_path):
+    ps_port, co_port = free_port(), free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0"], str(tmp_path),
+              str(tmp_path / "ps.log"))
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        t0 = time.time()
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "1",
+                            "--sync-timeout-ms=400"], capture_output=True, text=True, timeout=60)
+        assert "worker 0 iter 0 done=false" in w.stdout and w.returncode == 0
+        assert time.time() - t0 < 10
+        # no coordinator at all -> exit code 1 and the reference's stderr line
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{free_port()}", "5", "1"],
+                           capture_output=True, text=True, timeout=60)
+        assert w.returncode == 1 and "worker 5 failed to initialize" in w.stderr
+    finally:
+        ps.stop()
+        co.stop()
