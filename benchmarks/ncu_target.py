@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""Short single-GPU program that launches each hand-written kernel a few times: the target of
+`ncu --set full` captures (profiles/).  Run plainly first; never take timings from a profiled
+run."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+
+from parameter_server_distributed_b200 import OptimConfig
+from parameter_server_distributed_b200.ops import native
+from parameter_server_distributed_b200.parallel.buckets import plan_buckets
+from parameter_server_distributed_b200.parallel.device_backend import DeviceBackend
+from parameter_server_distributed_b200.parallel.fabric import Fabric
+
+DEV = torch.device("cuda:0")
+torch.cuda.set_device(DEV)
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+
+# K2f: tcgen05 GEMM (first MLP layer shape of bench.py: M=4096 tokens, N=8192, K=4096)
+x = (torch.randn(4096, 4096, device=DEV) * 0.1).to(torch.bfloat16)
+w = (torch.randn(8192, 4096, device=DEV) * 0.1).to(torch.bfloat16)
+y = torch.empty(4096, 8192, dtype=torch.bfloat16, device=DEV)
+for _ in range(reps):
+    native.gemm_bf16(x, w, out=y)
+
+# K3: AdamW on a 64M-element shard
+n = 64 << 20
+master = torch.randn(n, device=DEV)
+m = torch.zeros(n, device=DEV)
+v = torch.zeros(n, device=DEV)
+g = torch.randn(n, device=DEV).to(torch.bfloat16)
+out = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+cfg = OptimConfig(kind="adamw", lr=1e-3)
+for _ in range(reps):
+    native.optim_step(cfg, master, g, m, v, out)
+
+# K1: fused push on one rank (reduce over 1 peer + AdamW + replica store), 64M-element bucket
+plan = plan_buckets([("vec", (n,))], 1, bucket_elems=1 << 62)
+fab = Fabric(0, 1, DEV, plan.total_elems * 4 + (8 << 20))
+be = DeviceBackend(fab, plan, OptimConfig(kind="adamw", lr=1e-3))
+be.grad_flat.normal_()
+for _ in range(reps):
+    be.push(0)
+
+# K4 / K6
+for _ in range(reps):
+    native.sumsq(g)
+bucket = torch.empty(n, dtype=torch.bfloat16, device=DEV)
+srcs = [g[i * (n // 8):(i + 1) * (n // 8)] for i in range(8)]
+for _ in range(reps):
+    native.gather_to_bucket(srcs, bucket, [i * (n // 8) for i in range(8)])
+torch.cuda.synchronize()
+print("ncu_target ok")

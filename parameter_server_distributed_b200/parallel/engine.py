@@ -79,13 +79,23 @@ class ShardedParameterServer:
         # ---- adopt the model: parameters become views of the replica
         be = self.backend
         self._params: Dict[str, torch.nn.Parameter] = dict(named_params)
+        # 4-D weights kept in channels-last order (cuDNN's preferred layout) stay that way:
+        # the flat space stores them NHWC and the parameter is a permuted view of it
+        self._nhwc = {name for name, p in named_params
+                      if p.dim() == 4 and not p.is_contiguous()
+                      and p.is_contiguous(memory_format=torch.channels_last)}
         with torch.no_grad():
             for name, p in named_params:
                 slot = self.plan.slots[name]
                 bk = self.plan.buckets[slot.bucket]
                 view = be.param_flat[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
-                view.copy_(p.detach().reshape(-1))
-                p.data = view.view(p.shape)
+                if name in self._nhwc:
+                    n, c, h, w = p.shape
+                    view.copy_(p.detach().permute(0, 2, 3, 1).reshape(-1))
+                    p.data = view.view(n, h, w, c).permute(0, 3, 1, 2)
+                else:
+                    view.copy_(p.detach().reshape(-1))
+                    p.data = view.view(p.shape)
             for b, bk in enumerate(self.plan.buckets):
                 s = bk.slice_elems
                 be.shard_slice(be.master, b).copy_(
@@ -139,12 +149,18 @@ class ShardedParameterServer:
         if len(pend) < len(self.plan.buckets[b].slots):
             bucket.zero_()
         if self.is_cuda:
-            native.gather_to_bucket([g.contiguous() for _, g in pend], bucket,
+            native.gather_to_bucket([self._flat_grad(s, g) for s, g in pend], bucket,
                                     [s.offset for s, _ in pend])
         else:
             for s, g in pend:
-                bucket[s.offset:s.offset + s.numel].copy_(g.reshape(-1))
+                bucket[s.offset:s.offset + s.numel].copy_(self._flat_grad(s, g).reshape(-1))
         self._pending[b] = []
+
+    def _flat_grad(self, slot: ParamSlot, g: torch.Tensor) -> torch.Tensor:
+        """Gradient in the element order of the flat space (NHWC for channels-last weights)."""
+        if slot.name in self._nhwc:
+            return g.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+        return g.contiguous()
 
     def _flush(self, b: int) -> None:
         self._stage(b)
@@ -221,7 +237,11 @@ class ShardedParameterServer:
             for r, a, b in self.plan.owner_ranges(slot):
                 lo = sb + (slot.offset + a) - r * bk.slice_elems
                 flat[a:b].copy_(parts[r][lo:lo + (b - a)])
-            out[name] = flat.view(slot.shape)
+            if name in self._nhwc:
+                n, c, h, w = slot.shape
+                out[name] = flat.view(n, h, w, c).permute(0, 3, 1, 2)
+            else:
+                out[name] = flat.view(slot.shape)
         return out
 
     def scatter_state(self, tensors: Dict[str, torch.Tensor], which: str = "master") -> None:
@@ -238,7 +258,10 @@ class ShardedParameterServer:
                     continue
                 bk = self.plan.buckets[slot.bucket]
                 sb = bk.shard_base(self.world)
-                flat = t.detach().reshape(-1).to(device=shard.device, dtype=torch.float32)
+                t = t.detach()
+                if name in self._nhwc:
+                    t = t.permute(0, 2, 3, 1)
+                flat = t.reshape(-1).to(device=shard.device, dtype=torch.float32)
                 for r, a, b in self.plan.owner_ranges(slot):
                     if r == self.rank:
                         lo = sb + (slot.offset + a) - r * bk.slice_elems

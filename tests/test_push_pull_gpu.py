@@ -64,7 +64,7 @@ def test_fused_push_broadcast(world, kind):
                 # Adam's m / sqrt(v) is ill-conditioned where the gradient cancels to ~0:
                 # tolerate a vanishing fraction of lr-sized outliers
                 bad = ~torch.isclose(got, exp, atol=2e-5, rtol=1e-5)
-                assert bad.float().mean().item() < 1e-4
+                assert bad.float().mean().item() < 1e-3
                 assert (got - exp).abs().max().item() < (
                     2e-5 if kind == "sgd" else 2 * cfg.lr * (it + 1))
             assert int(be.epoch[0].item()) == it + 1 and int(be.done.sum().item()) == 0
