@@ -434,3 +434,80 @@ int psb_clip_coef(const float* sumsq_parts, int n_parts, float max_norm, float e
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// psb_sumsq_noalloc — Σx² for callers that cannot allocate device memory.
+//
+// Same two-phase reduction as psb_sumsq, but the per-block partial sums go to the file-scope
+// array below instead of a caller-provided buffer.  Every GPU that loads this library keeps
+// the array (PSB_SUMSQ_NOALLOC_SLOTS floats = 4 KB) until the process exits.
+//
+// In host code `g_sumsq_noalloc_scratch` is only a host-side stand-in for the symbol, not a
+// device address; the address the kernels receive is looked up once per device with
+// cudaGetSymbolAddress while that device is current (noalloc_scratch_for_current_device).
+// ---------------------------------------------------------------------------------------
+namespace psb {
+
+static __device__ __align__(256) float g_sumsq_noalloc_scratch[PSB_SUMSQ_NOALLOC_SLOTS];
+
+constexpr int kMaxDevices = 64;
+static float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+static std::atomic<bool> g_noalloc_ready[kMaxDevices];
+
+// Returns the device address of the scratch array on the current device (set-up on first use).
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  PSB_CUDA_OK(cudaGetDevice(&dev));
+  PSB_REQUIRE(dev >= 0 && dev < kMaxDevices, PSB_ERANGE,
+              "psb_sumsq_noalloc: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  if (!g_noalloc_ready[dev].load(std::memory_order_acquire)) {
+    float* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_sumsq_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("psb_sumsq_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : PSB_EINVAL;
+    }
+    g_noalloc_ptr[dev] = ptr;  // racing first calls store the same value
+    g_noalloc_ready[dev].store(true, std::memory_order_release);
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace psb
+
+extern "C" int psb_sumsq_noalloc(const void* x, int dtype, size_t n, float* out,
+                                 psb_stream_t stream) {
+  PSB_REQUIRE(x && out, PSB_EINVAL, "psb_sumsq_noalloc: null argument");
+  PSB_REQUIRE(((uintptr_t)x & 15) == 0, PSB_EINVAL,
+              "psb_sumsq_noalloc: input must be 16-byte aligned");
+  PSB_REQUIRE(dtype == PSB_BF16 || dtype == PSB_F32, PSB_EINVAL,
+              "psb_sumsq_noalloc: bad dtype %d", dtype);
+  PSB_REQUIRE(n <= (size_t)PSB_SUMSQ_NOALLOC_MAX_ELEMS, PSB_ERANGE,
+              "psb_sumsq_noalloc: n = %llu exceeds PSB_SUMSQ_NOALLOC_MAX_ELEMS = %llu (the static "
+              "scratch holds %d partial sums of at most %d elements each); use psb_sumsq with "
+              "caller-provided scratch for larger inputs",
+              (unsigned long long)n, (unsigned long long)PSB_SUMSQ_NOALLOC_MAX_ELEMS,
+              PSB_SUMSQ_NOALLOC_SLOTS, PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT);
+  float* scratch = nullptr;
+  if (int rc = psb::noalloc_scratch_for_current_device(&scratch)) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // one block (= one partial slot) per PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT elements at most, and
+  // never more blocks than the regular entry point would launch
+  size_t by_span = (n + PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT - 1) / PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT;
+  int blocks = psb::grid_for(n / 8 + 1, psb::kSumsqThreads, 4);
+  if (blocks > PSB_SUMSQ_NOALLOC_SLOTS) blocks = PSB_SUMSQ_NOALLOC_SLOTS;
+  if ((size_t)blocks < by_span) blocks = (int)by_span;  // by_span <= SLOTS by the check above
+  // Every slot in [0, blocks) is overwritten by the first kernel and only those are read by the
+  // second, so nothing in the shared array has to start at zero.
+  if (dtype == PSB_BF16) {
+    psb::sumsq_partial_kernel<PSB_BF16><<<blocks, psb::kSumsqThreads, 0, s>>>(x, n, scratch);
+  } else {
+    psb::sumsq_partial_kernel<PSB_F32><<<blocks, psb::kSumsqThreads, 0, s>>>(x, n, scratch);
+  }
+  PSB_LAUNCH_OK("sumsq_noalloc_partial");
+  psb::sumsq_final_kernel<<<1, 256, 0, s>>>(scratch, blocks, out);
+  PSB_LAUNCH_OK("sumsq_noalloc_final");
+  return 0;
+}

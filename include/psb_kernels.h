@@ -111,6 +111,35 @@ int psb_sumsq(const void* x, int dtype, size_t n, float* partials, float* out, p
 int psb_clip_coef(const float* sumsq_parts, int n_parts, float max_norm, float eps, float* coef_out,
                   float* norm_out, psb_stream_t stream);
 
+// psb_sumsq_noalloc — Σx² without any caller-provided or freshly allocated scratch.
+// No counterpart in the reference (it has no device code and no gradient norm at all).
+//
+// Who needs it: code that is not allowed to allocate GPU memory at the point where it wants a
+// gradient norm — a service that hands this library a fixed, fully pre-carved memory pool; a
+// monitoring hook that runs while the framework's allocator is locked or already exhausted; a
+// plain C host program that only passes pointers it was given.  psb_sumsq asks such callers
+// for a scratch buffer they cannot make; this entry point brings its own.
+//
+// The partial sums live in ONE static device array per GPU: PSB_SUMSQ_NOALLOC_SLOTS floats
+// (4 KB), resident on every GPU that loads the library for the life of the process.  Each slot
+// covers at most PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT elements, so inputs longer than
+// PSB_SUMSQ_NOALLOC_MAX_ELEMS (2^31) are rejected with PSB_ERANGE and a message — use
+// psb_sumsq for those.  The function never calls cudaMalloc / cudaFree or any allocating
+// routine.
+//
+// First call on a device: looks up the array's device address (cudaGetSymbolAddress, with
+// that device current) and remembers it.  Make that first call during set-up, before any
+// stream capture begins.
+// Sharing: all calls on a GPU use the same array, which keeps whatever the last call left in
+// it.  Nothing needs to start at zero (each call overwrites every slot it later reads), but
+// two calls that overlap on the GPU — different streams, or different host threads without
+// ordering — race on it: serialise them on one stream or with events.
+// `x` must be 16-byte aligned; `out` receives one float; dtype is PSB_F32 or PSB_BF16.
+#define PSB_SUMSQ_NOALLOC_SLOTS 1024
+#define PSB_SUMSQ_NOALLOC_ELEMS_PER_SLOT (1 << 21)
+#define PSB_SUMSQ_NOALLOC_MAX_ELEMS (1ull << 31)
+int psb_sumsq_noalloc(const void* x, int dtype, size_t n, float* out, psb_stream_t stream);
+
 // ---------------------------------------------------------------------------
 // Fabric — symmetric heap over the GPUs of one NVSwitch box.  Replaces the
 // reference's per-iteration cudaMalloc + host staging (src/worker.cpp:416-444)
