@@ -66,6 +66,10 @@ def run(args, lib_path: str) -> int:
         return 0
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     from bench import model_config  # shapes only
+    if args.config not in ("mlp", "mlp-small"):
+        print(json.dumps({"impl": "reference", "unavailable":
+                          f"reference arm implements the flagship MLP config only, not {args.config}"}))
+        return 0
     cfg = model_config(args.config)
     n_gpus = min(args.gpus, torch.cuda.device_count())
 
@@ -108,7 +112,7 @@ def run(args, lib_path: str) -> int:
     pull_ptrs = (C.c_void_p * len(names))(*[b.ctypes.data for b in host_p])
     pull_sizes = (C.c_longlong * len(names))(*[b.size for b in host_p])
 
-    B = args.batch_per_gpu
+    B = args.batch_per_gpu or 4096
     gen = torch.Generator().manual_seed(100)
     hx = [torch.randn(B, cfg.d_in, generator=gen).to(torch.bfloat16).pin_memory() for _ in range(4)]
     hy = [torch.randn(B, cfg.d_out, generator=gen).to(torch.bfloat16).pin_memory() for _ in range(4)]

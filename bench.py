@@ -29,8 +29,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="mlp", choices=["mlp", "mlp-small"])
-    ap.add_argument("--batch-per-gpu", type=int, default=4096)
+    ap.add_argument("--config", default="mlp",
+                    choices=["mlp", "mlp-small", "gpt2m", "gpt2s", "resnet50"])
+    ap.add_argument("--batch-per-gpu", type=int, default=0,
+                    help="0 = config default (mlp 4096, gpt2 8 x 1024 tokens, resnet50 128)")
     ap.add_argument("--optimizer", default="sgd")
     ap.add_argument("--pull", default="broadcast", choices=["broadcast", "gather"])
     ap.add_argument("--bucket-mb", type=float, default=64.0)
@@ -44,6 +46,53 @@ def model_config(name):
     if name == "mlp-small":
         return MLPConfig(d_in=1024, hidden=(2048, 2048), d_out=512)
     return MLPConfig(d_in=4096, hidden=(8192, 8192), d_out=1024)
+
+
+class Workload:
+    """Model + loss + synthetic batch factory of one BASELINE.json config."""
+
+    def __init__(self, name, batch):
+        import torch
+        from parameter_server_distributed_b200 import models as M
+        self.name = name
+        self.seq_len = 1
+        self.memory_format = None
+        if name in ("mlp", "mlp-small"):
+            self.cfg = model_config(name)
+            self.batch = batch or 4096
+            self.build = lambda: M.MLP(self.cfg)
+            self.loss = M.mse_loss
+            self.nparams = self.cfg.num_params()
+            self.flops_per_sample = self.cfg.flops_per_sample()
+            self.label = f"MLP {'-'.join(map(str, self.cfg.dims))}"
+            self.make = lambda g: (torch.randn(self.batch, self.cfg.d_in, generator=g).to(torch.bfloat16),
+                                   torch.randn(self.batch, self.cfg.d_out, generator=g).to(torch.bfloat16))
+        elif name in ("gpt2m", "gpt2s"):
+            self.cfg = M.GPT2Config.medium() if name == "gpt2m" else M.GPT2Config.small()
+            self.batch = batch or 8
+            self.seq_len = self.cfg.n_positions
+            self.build = lambda: M.GPT2(self.cfg)
+            self.loss = M.lm_loss
+            self.nparams = self.cfg.num_params()
+            self.flops_per_sample = self.cfg.flops_per_token(self.seq_len) * self.seq_len
+            self.label = f"GPT-2 {'medium' if name == 'gpt2m' else 'small'}"
+
+            def make(g):
+                ids = torch.randint(0, self.cfg.vocab_size, (self.batch, self.seq_len + 1), generator=g)
+                return ids[:, :-1].contiguous(), ids[:, 1:].contiguous()
+            self.make = make
+        else:
+            self.batch = batch or 128
+            self.build = lambda: M.resnet50()
+            self.loss = M.ce_loss
+            self.nparams = 25_557_032
+            self.flops_per_sample = 3 * 2 * 4.09e9  # fwd 4.09 GMAC, bwd ~2x
+            self.label = "ResNet-50"
+            self.memory_format = torch.channels_last
+            self.make = lambda g: (
+                torch.randn(self.batch, 3, 224, 224, generator=g).to(torch.bfloat16)
+                .contiguous(memory_format=torch.channels_last),
+                torch.randint(0, 1000, (self.batch,), generator=g))
 
 
 def max_over_ranks(x: float, ctx) -> float:
@@ -69,30 +118,30 @@ def run_ours(args):
 
     import parameter_server_distributed_b200 as psd
     from parameter_server_distributed_b200 import _lib
-    from parameter_server_distributed_b200.models import MLP, mse_loss
     from parameter_server_distributed_b200.utils import ClockSampler
 
     if not torch.cuda.is_available():
         print(json.dumps({"error": "no CUDA device", "impl": "ours"}))
         return 1
-    cfg = model_config(args.config)
-    nparams = cfg.num_params()
-    ctx = psd.init(heap_bytes=nparams * 4 + (256 << 20))
+    wl = Workload(args.config, args.batch_per_gpu)
+    nparams = wl.nparams
+    ctx = psd.init(heap_bytes=nparams * 4 + (512 << 20))
     world = ctx.world
     if world != args.gpus and ctx.rank == 0:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)
     torch.manual_seed(1234)
-    model = MLP(cfg).to(ctx.device, torch.bfloat16)
+    model = wl.build().to(ctx.device, torch.bfloat16)
+    if wl.memory_format is not None:
+        model = model.to(memory_format=wl.memory_format)
     optim = psd.OptimConfig(kind=args.optimizer, lr=1e-3 if args.optimizer != "sgd" else 1e-2)
-    trainer = psd.Trainer(model, mse_loss, ctx, optim, pull=args.pull, bucket_mb=args.bucket_mb,
+    trainer = psd.Trainer(model, wl.loss, ctx, optim, pull=args.pull, bucket_mb=args.bucket_mb,
                           overlap=not args.no_overlap, push_grid=args.push_grid)
-    B = args.batch_per_gpu
+    B = wl.batch
     gen = torch.Generator().manual_seed(100 + ctx.rank)
     n_host = 4  # rotate a few distinct pinned batches
-    host_x = [torch.randn(B, cfg.d_in, generator=gen).to(torch.bfloat16).pin_memory()
-              for _ in range(n_host)]
-    host_y = [torch.randn(B, cfg.d_out, generator=gen).to(torch.bfloat16).pin_memory()
-              for _ in range(n_host)]
+    batches = [wl.make(gen) for _ in range(n_host)]
+    host_x = [b[0].pin_memory() for b in batches]
+    host_y = [b[1].pin_memory() for b in batches]
     dev_x = [t.to(ctx.device) for t in host_x]
     dev_y = [t.to(ctx.device) for t in host_y]
 
@@ -150,7 +199,7 @@ def run_ours(args):
     value = global_batch * args.steps / (dev_ms / 1e3)
     e2e_value = global_batch * args.steps / (e2e_ms / 1e3)
     if ctx.rank == 0:
-        flops = cfg.flops_per_sample() * global_batch * args.steps
+        flops = wl.flops_per_sample * global_batch * args.steps
         out = {
             "metric": "samples/sec (sync-SGD through the sharded parameter server)",
             "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
@@ -158,8 +207,8 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic (random batches, random-init weights)",
             "impl": "ours",
-            "config": {"model": f"MLP {'-'.join(map(str, cfg.dims))} ({nparams / 1e6:.1f}M params)",
-                       "global_batch": global_batch, "seq_len": 1,
+            "config": {"model": f"{wl.label} ({nparams / 1e6:.1f}M params)",
+                       "global_batch": global_batch, "seq_len": wl.seq_len,
                        "parallelism": f"dp{world} / {world} PS shards", "optimizer": args.optimizer,
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
                        "l2": "working set (weights+grads+state+activations > 1 GB) exceeds the "
