@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
   uint32_t* const my_pad = a.fabric.pad[rank];
   const uint32_t e = *reinterpret_cast<volatile const uint32_t*>(a.epoch) + 1u;
   const uint32_t mask = (flags & PSB_PUSH_MASKED) ? *a.peer_mask : 0xffffffffu;
+  if ((flags & PSB_PUSH_MASKED) && (mask & ((1u << world) - 1u)) == 0u) return;  // nothing pending
 
   // ---- 1. announce "my gradients of this bucket are complete", 2. wait for everyone's
   if (!(flags & (PSB_PUSH_NO_WAIT | PSB_PUSH_FROM_REDUCED))) {
@@ -115,7 +116,9 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
 #pragma unroll
         for (int w = 0; w < MAXW; ++w) {
           if (w < world && valid[u] && ((mask >> w) & 1u))
-            raw[u][w].load(a.grad[w], base + (i0 + u * stride) * 8);
+            raw[u][w].load(reinterpret_cast<const char*>(a.grad[w]) +
+                               (a.grad_off ? __ldg(a.grad_off + w) : 0ull),
+                           base + (i0 + u * stride) * 8);
         }
       }
 #pragma unroll
@@ -194,7 +197,8 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
     if (!(flags & PSB_PUSH_REDUCE_ONLY)) {
       if (threadIdx.x < world) {
         st_release_sys(
-            a.fabric.pad[threadIdx.x] + PSB_PAD_VERSION_OFF + a.bucket * PSB_MAX_PEERS + rank, e);
+            a.fabric.pad[threadIdx.x] + PSB_PAD_VERSION_OFF + a.bucket * PSB_MAX_PEERS + rank,
+            (flags & PSB_PUSH_SEQLOCK) ? 2u * e : e);
       }
       if (threadIdx.x == 0) *a.epoch = e;
     }
@@ -207,21 +211,56 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a) {
   const int rank = a.fabric.rank, world = a.fabric.world;
-  if (!a.skip_wait) {
+  const uint32_t* vpad = a.fabric.pad[rank] + PSB_PAD_VERSION_OFF + a.bucket * PSB_MAX_PEERS;
+  if (!a.skip_wait && !a.seqlock) {
     const uint32_t e = *a.epoch;
-    if (threadIdx.x < world)
-      wait_ge_sys(a.fabric.pad[rank] + PSB_PAD_VERSION_OFF + a.bucket * PSB_MAX_PEERS + threadIdx.x,
-                  e);
+    if (threadIdx.x < world) wait_ge_sys(vpad + threadIdx.x, e);
     __syncthreads();
   }
   if (world == 1) return;
   const size_t slice_vec = a.slice_bytes / 16;
-  const size_t chunks_per_slice = (slice_vec + 31) / 32;  // one warp-wide run = 32 x 16 B
-  const size_t total_chunks = chunks_per_slice * (size_t)(world - 1);
   const int lane = threadIdx.x & 31;
   const size_t warps = (size_t)gridDim.x * (blockDim.x >> 5);
   const size_t warp_id = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   constexpr int U = 4;
+  if (a.seqlock) {
+    // Async mode: owners rewrite their slices at any time.  Each CTA copies its share of one
+    // owner's slice between two reads of that owner's version word and repeats the share if
+    // the word was odd (update in flight) or changed meanwhile.
+    __shared__ uint32_t v0s, v1s;
+    const size_t chunks = (slice_vec + 31) / 32;
+    for (int ord = 0; ord < world - 1; ++ord) {
+      const int owner = (rank + 1 + ord) % world;
+      while (true) {
+        if (threadIdx.x == 0) {
+          uint32_t v;
+          while ((v = ld_acquire_sys(vpad + owner)) & 1u) __nanosleep(64);
+          v0s = v;
+        }
+        __syncthreads();
+        for (size_t c = warp_id; c < chunks; c += warps) {
+          const size_t vec = c * 32 + lane;
+          if (vec < slice_vec) {
+            const size_t off = (size_t)owner * a.slice_bytes + vec * 16;
+            st_stream_16(reinterpret_cast<char*>(a.param[rank]) + off,
+                         ld_stream_16(reinterpret_cast<const char*>(a.param[owner]) + off));
+          }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          fence_sys();
+          v1s = ld_acquire_sys(vpad + owner);
+        }
+        __syncthreads();
+        const bool stable = v1s == v0s;
+        __syncthreads();  // nobody may still be comparing when thread 0 rewrites v0s
+        if (stable) break;
+      }
+    }
+    return;
+  }
+  const size_t chunks_per_slice = (slice_vec + 31) / 32;  // one warp-wide run = 32 x 16 B
+  const size_t total_chunks = chunks_per_slice * (size_t)(world - 1);
   for (size_t c0 = warp_id; c0 < total_chunks; c0 += warps * U) {
     uint4 val[U];
     size_t off[U];
@@ -244,6 +283,82 @@ __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a)
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (ok[u]) st_stream_16(reinterpret_cast<char*>(a.param[rank]) + off[u], val[u]);
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// Async / SSP control kernels (tiny: one thread per (bucket, peer) or per bucket).
+// ------------------------------------------------------------------------------------
+__global__ void async_signal_kernel(PsbAsync a, uint32_t clock) {
+  const int rank = a.fabric.rank, world = a.fabric.world;
+  const int total = a.num_buckets * world;
+  __threadfence_system();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int b = i / world, r = i % world;
+    st_release_sys(a.fabric.pad[r] + PSB_PAD_READY_OFF + b * PSB_MAX_PEERS + rank, clock);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < world)
+    st_release_sys(a.fabric.pad[threadIdx.x] + PSB_PAD_CLOCK_OFF + rank, clock);
+}
+
+__global__ void pad_post_kernel(PsbFabric f, uint32_t word_base, uint32_t value) {
+  if (threadIdx.x < f.world) {
+    fence_sys();
+    st_release_sys(f.pad[threadIdx.x] + word_base + f.rank, value);
+  }
+}
+
+__global__ void async_plan_kernel(PsbAsync a) {
+  const int rank = a.fabric.rank, world = a.fabric.world;
+  const uint32_t* ready = a.fabric.pad[rank] + PSB_PAD_READY_OFF;
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < a.num_buckets;
+       b += gridDim.x * blockDim.x) {
+    uint32_t mask = 0;
+    for (int w = 0; w < world; ++w) {
+      const uint32_t rdy = ld_acquire_sys(ready + b * PSB_MAX_PEERS + w);
+      const uint32_t ap = a.applied[b * PSB_MAX_PEERS + w];
+      if ((int32_t)(rdy - ap) > 0) {  // oldest unapplied clock of this worker
+        const uint32_t clock = ap + 1u;
+        mask |= 1u << w;
+        a.grad_off[b * PSB_MAX_PEERS + w] = (uint64_t)(clock % (uint32_t)a.ring) * a.ring_stride_bytes;
+        a.applied[b * PSB_MAX_PEERS + w] = clock;
+      } else {
+        a.grad_off[b * PSB_MAX_PEERS + w] = 0;
+      }
+    }
+    a.masks[b] = mask;
+    if (mask) {  // seqlock: odd = "slice r of bucket b is being rewritten"
+      const uint32_t odd = 2u * a.epoch[b] + 1u;
+      for (int t = 0; t < world; ++t)
+        st_release_sys(a.fabric.pad[t] + PSB_PAD_VERSION_OFF + b * PSB_MAX_PEERS + rank, odd);
+    }
+  }
+}
+
+__global__ void async_ack_kernel(PsbAsync a) {
+  const int rank = a.fabric.rank, world = a.fabric.world;
+  const int total = a.num_buckets * world;
+  __threadfence_system();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int b = i / world, w = i % world;
+    st_release_sys(a.fabric.pad[w] + PSB_PAD_ACK_OFF + b * PSB_MAX_PEERS + rank,
+                   a.applied[b * PSB_MAX_PEERS + w]);
+  }
+}
+
+__global__ void async_gate_kernel(PsbAsync a, uint32_t clock, int staleness) {
+  const int rank = a.fabric.rank, world = a.fabric.world;
+  const uint32_t* ack = a.fabric.pad[rank] + PSB_PAD_ACK_OFF;
+  const uint32_t* clk = a.fabric.pad[rank] + PSB_PAD_CLOCK_OFF;
+  const int total = a.num_buckets * world;
+  if (clock > (uint32_t)a.ring) {  // the slot of `clock` last held clock - ring
+    const uint32_t need = clock - (uint32_t)a.ring;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+      wait_ge_sys(ack + (i / world) * PSB_MAX_PEERS + (i % world), need);
+  }
+  if (staleness >= 0 && blockIdx.x == 0 && threadIdx.x < world &&
+      clock > (uint32_t)staleness + 1u) {
+    wait_ge_sys(clk + threadIdx.x, clock - 1u - (uint32_t)staleness);
   }
 }
 
@@ -460,6 +575,55 @@ int psb_norm_allreduce(const PsbFabric* fabric, float* local_sumsq, uint32_t* se
   norm_allreduce_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
       *fabric, local_sumsq, seq, max_norm, eps, coef_out, norm_out);
   PSB_LAUNCH_OK("norm_allreduce");
+  return 0;
+}
+
+static int check_async(const PsbAsync* a, const char* who) {
+  PSB_REQUIRE(a, PSB_EINVAL, "%s: null args", who);
+  if (int rc = check_fabric(a->fabric, who)) return rc;
+  PSB_REQUIRE(a->num_buckets > 0 && a->num_buckets <= PSB_MAX_BUCKETS, PSB_ERANGE,
+              "%s: num_buckets %d outside (0, %d]", who, a->num_buckets, PSB_MAX_BUCKETS);
+  PSB_REQUIRE(a->ring >= 1 && a->ring <= 8, PSB_ERANGE, "%s: ring %d outside [1, 8]", who, a->ring);
+  PSB_REQUIRE(a->applied && a->masks && a->grad_off && a->epoch, PSB_EINVAL,
+              "%s: state arrays missing", who);
+  return 0;
+}
+
+int psb_async_signal(const PsbAsync* a, uint32_t clock, psb_stream_t stream) {
+  if (int rc = check_async(a, "psb_async_signal")) return rc;
+  async_signal_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*a, clock);
+  PSB_LAUNCH_OK("async_signal");
+  return 0;
+}
+
+int psb_async_plan(const PsbAsync* a, psb_stream_t stream) {
+  if (int rc = check_async(a, "psb_async_plan")) return rc;
+  async_plan_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(*a);
+  PSB_LAUNCH_OK("async_plan");
+  return 0;
+}
+
+int psb_async_ack(const PsbAsync* a, psb_stream_t stream) {
+  if (int rc = check_async(a, "psb_async_ack")) return rc;
+  async_ack_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*a);
+  PSB_LAUNCH_OK("async_ack");
+  return 0;
+}
+
+int psb_async_gate(const PsbAsync* a, uint32_t clock, int32_t staleness, psb_stream_t stream) {
+  if (int rc = check_async(a, "psb_async_gate")) return rc;
+  async_gate_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*a, clock, staleness);
+  PSB_LAUNCH_OK("async_gate");
+  return 0;
+}
+
+int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, psb_stream_t stream) {
+  PSB_REQUIRE(fabric, PSB_EINVAL, "psb_pad_post: null fabric");
+  if (int rc = check_fabric(*fabric, "psb_pad_post")) return rc;
+  PSB_REQUIRE(word_base + PSB_MAX_PEERS <= PSB_PAD_WORDS, PSB_ERANGE,
+              "psb_pad_post: word %u outside the pad", word_base);
+  pad_post_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*fabric, word_base, value);
+  PSB_LAUNCH_OK("pad_post");
   return 0;
 }
 

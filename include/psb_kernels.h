@@ -168,13 +168,15 @@ int psb_device_sync(void);
 //   clock  [PSB_MAX_PEERS]                    SSP clocks (one word per worker)
 //   norm   [2][PSB_MAX_PEERS] (64-bit words)   {seq, float bits} of per-shard Σg², double-buffered
 //   ack    [PSB_MAX_BUCKETS][PSB_MAX_PEERS]   async mode: owner r consumed worker's clock
+//   done   [PSB_MAX_PEERS]                    async mode: final clock of a worker that finished
 #define PSB_PAD_READY_OFF 0
 #define PSB_PAD_VERSION_OFF (PSB_MAX_BUCKETS * PSB_MAX_PEERS)
 #define PSB_PAD_BARRIER_OFF (2 * PSB_MAX_BUCKETS * PSB_MAX_PEERS)
 #define PSB_PAD_CLOCK_OFF (PSB_PAD_BARRIER_OFF + 64 * PSB_MAX_PEERS)
 #define PSB_PAD_NORM_OFF (PSB_PAD_CLOCK_OFF + PSB_MAX_PEERS)
 #define PSB_PAD_ACK_OFF (PSB_PAD_NORM_OFF + 4 * PSB_MAX_PEERS)
-#define PSB_PAD_WORDS (PSB_PAD_ACK_OFF + PSB_MAX_BUCKETS * PSB_MAX_PEERS)
+#define PSB_PAD_DONE_OFF (PSB_PAD_ACK_OFF + PSB_MAX_BUCKETS * PSB_MAX_PEERS)
+#define PSB_PAD_WORDS (PSB_PAD_DONE_OFF + PSB_MAX_PEERS)
 size_t psb_pad_bytes(void);
 
 typedef struct PsbFabric {
@@ -205,7 +207,10 @@ typedef struct PsbFabric {
 #define PSB_PUSH_NO_WAIT 2      // skip steps 1-2 (caller already synchronised; async single-pusher)
 #define PSB_PUSH_REDUCE_ONLY 4  // stop after the reduction: write fp32 sum to `reduced`, Σg² to norm pads
 #define PSB_PUSH_FROM_REDUCED 8 // skip the reduction: gradient comes from `reduced` (after clipping)
-#define PSB_PUSH_MASKED 16      // only sum peers whose bit is set in *peer_mask (async / SSP)
+#define PSB_PUSH_MASKED 16      // only sum peers whose bit is set in *peer_mask (async / SSP);
+                                // an empty mask makes the launch a no-op (nothing published)
+#define PSB_PUSH_SEQLOCK 32     // publish 2*epoch (even) instead of epoch: readers pair it with the
+                                // odd mark written by psb_async_plan before the update started
 
 typedef struct PsbPush {
   PsbFabric fabric;
@@ -227,6 +232,8 @@ typedef struct PsbPush {
   int32_t flags;
   int32_t grid;                     // CTAs (0 = auto)
   PsbOptim opt;
+  const uint64_t* grad_off;         // optional device array [world]: byte offset added to grad[w]
+                                    // (which slot of the worker's gradient ring to read)
 } PsbPush;
 int psb_push_fused(const PsbPush* args, psb_stream_t stream);
 
@@ -245,6 +252,7 @@ typedef struct PsbPull {
   const uint32_t* epoch;       // local device word of this bucket
   int32_t grid;
   int32_t skip_wait;
+  int32_t seqlock;             // async mode: copy each owner slice under a seqlock (retry on change)
 } PsbPull;
 int psb_pull_allgather(const PsbPull* args, psb_stream_t stream);
 
@@ -259,6 +267,38 @@ int psb_device_barrier(const PsbFabric* fabric, int slot, uint32_t* seq, psb_str
 // `local_sumsq` is consumed: the kernel zeroes it after reading.
 int psb_norm_allreduce(const PsbFabric* fabric, float* local_sumsq, uint32_t* seq, float max_norm,
                        float eps, float* coef_out, float* norm_out, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// Asynchronous / bounded-staleness mode (no counterpart in the reference, which is BSP only;
+// PullRequest.iteration / ParameterUpdate.ready are the wire carriers on the host path).
+// Every rank is a worker with its own clock and the owner of one slice per bucket.
+//   worker:  stages clock c into slot c % ring of its gradient ring, then psb_async_signal
+//            raises ready[b][w] = c on every owner's pad and publishes clock[w] = c
+//   owner:   psb_async_plan picks, per bucket, the workers with an unapplied clock (one clock
+//            per worker per call, in order), writes the peer mask + ring offsets, advances
+//            applied[b][w] and marks version[b][r] odd on every pad; K1 (MASKED | SEQLOCK)
+//            applies the picked gradients and publishes the even version; psb_async_ack tells
+//            each worker which of its clocks have been consumed (ring slot reusable)
+//   gate:    psb_async_gate blocks the stream until clock c may start: every owner consumed
+//            clock c - ring (slot free) and, with staleness >= 0, no worker is more than
+//            `staleness` clocks behind c - 1
+// ---------------------------------------------------------------------------
+typedef struct PsbAsync {
+  PsbFabric fabric;
+  int32_t num_buckets;
+  int32_t ring;                 // slots in the gradient ring
+  uint64_t ring_stride_bytes;   // bytes between two slots
+  uint32_t* applied;            // local [num_buckets][PSB_MAX_PEERS]: last applied clock per worker
+  uint32_t* masks;              // local [num_buckets]: peer mask chosen by the plan
+  uint64_t* grad_off;           // local [num_buckets][PSB_MAX_PEERS]: ring offsets chosen by the plan
+  const uint32_t* epoch;        // local [num_buckets]: K1 epoch words
+} PsbAsync;
+int psb_async_signal(const PsbAsync* a, uint32_t clock, psb_stream_t stream);
+int psb_async_plan(const PsbAsync* a, psb_stream_t stream);
+int psb_async_ack(const PsbAsync* a, psb_stream_t stream);
+int psb_async_gate(const PsbAsync* a, uint32_t clock, int32_t staleness, psb_stream_t stream);
+// store `value` into word [word_base + rank] of every rank's pad (release.sys)
+int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, psb_stream_t stream);
 
 // ---------------------------------------------------------------------------
 // K2f — bf16 GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed

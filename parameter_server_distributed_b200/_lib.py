@@ -23,6 +23,7 @@ PUSH_NO_WAIT = 2
 PUSH_REDUCE_ONLY = 4
 PUSH_FROM_REDUCED = 8
 PUSH_MASKED = 16
+PUSH_SEQLOCK = 32
 
 PAD_READY_OFF = 0
 PAD_VERSION_OFF = MAX_BUCKETS * MAX_PEERS
@@ -30,7 +31,8 @@ PAD_BARRIER_OFF = 2 * MAX_BUCKETS * MAX_PEERS
 PAD_CLOCK_OFF = PAD_BARRIER_OFF + 64 * MAX_PEERS
 PAD_NORM_OFF = PAD_CLOCK_OFF + MAX_PEERS
 PAD_ACK_OFF = PAD_NORM_OFF + 4 * MAX_PEERS
-PAD_WORDS = PAD_ACK_OFF + MAX_BUCKETS * MAX_PEERS
+PAD_DONE_OFF = PAD_ACK_OFF + MAX_BUCKETS * MAX_PEERS
+PAD_WORDS = PAD_DONE_OFF + MAX_PEERS
 
 
 class PsbOptim(C.Structure):
@@ -56,13 +58,19 @@ class PsbPush(C.Structure):
                 ("slice_elems", C.c_uint64), ("bucket", C.c_int32), ("grad_dtype", C.c_int32),
                 ("epoch", C.c_void_p), ("step", C.c_void_p), ("clip_coef", C.c_void_p),
                 ("peer_mask", C.c_void_p), ("done_counter", C.c_void_p), ("flags", C.c_int32),
-                ("grid", C.c_int32), ("opt", PsbOptim)]
+                ("grid", C.c_int32), ("opt", PsbOptim), ("grad_off", C.c_void_p)]
 
 
 class PsbPull(C.Structure):
     _fields_ = [("fabric", PsbFabric), ("param", C.c_void_p * MAX_PEERS),
                 ("slice_bytes", C.c_uint64), ("bucket", C.c_int32), ("epoch", C.c_void_p),
-                ("grid", C.c_int32), ("skip_wait", C.c_int32)]
+                ("grid", C.c_int32), ("skip_wait", C.c_int32), ("seqlock", C.c_int32)]
+
+
+class PsbAsync(C.Structure):
+    _fields_ = [("fabric", PsbFabric), ("num_buckets", C.c_int32), ("ring", C.c_int32),
+                ("ring_stride_bytes", C.c_uint64), ("applied", C.c_void_p), ("masks", C.c_void_p),
+                ("grad_off", C.c_void_p), ("epoch", C.c_void_p)]
 
 
 class PsbGemmAG(C.Structure):
@@ -120,6 +128,12 @@ def _declare(lib) -> None:
         "psb_wait_versions": (i32, [C.POINTER(PsbFabric), vp, i32, i32, vp]),
         "psb_device_barrier": (i32, [C.POINTER(PsbFabric), i32, vp, vp]),
         "psb_norm_allreduce": (i32, [C.POINTER(PsbFabric), vp, vp, f32, f32, vp, vp, vp]),
+        "psb_async_signal": (i32, [C.POINTER(PsbAsync), u32, vp]),
+        "psb_async_plan": (i32, [C.POINTER(PsbAsync), vp]),
+        "psb_async_ack": (i32, [C.POINTER(PsbAsync), vp]),
+        "psb_async_gate": (i32, [C.POINTER(PsbAsync), u32, i32, vp]),
+        "psb_pad_post": (i32, [C.POINTER(PsbFabric), u32, u32, vp]),
+        "psb_sumsq_noalloc": (i32, [vp, i32, sz, vp, vp]),
         "psb_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
         "psb_gemm_allgather_bf16": (i32, [C.POINTER(PsbGemmAG), vp]),
     }

@@ -22,7 +22,7 @@ from .fabric import Fabric
 class DeviceBackend:
     def __init__(self, fabric: Fabric, plan: BucketPlan, optim: OptimConfig,
                  grad_dtype: torch.dtype = torch.bfloat16, broadcast: bool = True,
-                 clip: bool = False, push_grid: int = 0):
+                 clip: bool = False, push_grid: int = 0, grad_ring: int = 1):
         if len(plan.buckets) > _lib.MAX_BUCKETS:
             raise ValueError(f"{len(plan.buckets)} buckets exceed MAX_BUCKETS={_lib.MAX_BUCKETS}")
         self.fabric, self.plan, self.optim = fabric, plan, optim
@@ -35,9 +35,11 @@ class DeviceBackend:
         fabric.reset_flags()  # epoch words below start at 0: drop a previous engine's flags
         gsz = 2 if grad_dtype == torch.bfloat16 else 4
         total = plan.total_elems
-        self.G = fabric.alloc(total * gsz, align=4096)
+        self.grad_ring = grad_ring
+        self.ring_stride_bytes = (total * gsz + 4095) // 4096 * 4096
+        self.G = fabric.alloc(self.ring_stride_bytes * grad_ring, align=4096)
         self.P = fabric.alloc(total * 2, align=4096)
-        self.grad_flat = self.G.view(grad_dtype)
+        self.grad_flat = self.G.view(grad_dtype)[:total]
         self.param_flat = self.P.view(torch.bfloat16)
         shard = plan.shard_elems
         dev = self.device
@@ -98,6 +100,12 @@ class DeviceBackend:
         a.skip_wait = 0
         return a
 
+    def grad_slot(self, k: int) -> torch.Tensor:
+        """Flat gradient space of ring slot ``k`` (async mode keeps ``grad_ring`` clocks alive)."""
+        gsz = 2 if self.grad_dtype == torch.bfloat16 else 4
+        lo = k * self.ring_stride_bytes // gsz
+        return self.G.view(self.grad_dtype)[lo:lo + self.plan.total_elems]
+
     def set_optim(self, optim: OptimConfig) -> None:
         """Change hyper-parameters (e.g. lr schedule); buffers stay."""
         self.optim = optim
@@ -123,10 +131,16 @@ class DeviceBackend:
         return torch.cuda.current_stream(self.device).cuda_stream
 
     def push(self, b: int, *, reduce_only: bool = False, from_reduced: bool = False,
-             no_wait: bool = False, masked: bool = False, clip: bool = False) -> None:
+             no_wait: bool = False, masked: bool = False, clip: bool = False,
+             seqlock: bool = False, mask_ptr: Optional[int] = None,
+             grad_off_ptr: Optional[int] = None) -> None:
         """K1 on the current stream."""
         a = self._push_args[b]
         flags = _lib.PUSH_BROADCAST if self.broadcast else 0
+        if seqlock:
+            flags |= _lib.PUSH_SEQLOCK
+        a.peer_mask = mask_ptr if mask_ptr is not None else self.peer_mask.data_ptr()
+        a.grad_off = grad_off_ptr
         if reduce_only:
             flags |= _lib.PUSH_REDUCE_ONLY
         if from_reduced:
@@ -140,10 +154,11 @@ class DeviceBackend:
         with torch.cuda.device(self.device):
             check(self.lib.psb_push_fused(C.byref(a), self._stream()), "psb_push_fused")
 
-    def pull(self, b: int, skip_wait: bool = False) -> None:
+    def pull(self, b: int, skip_wait: bool = False, seqlock: bool = False) -> None:
         """K2 on the current stream."""
         a = self._pull_args[b]
         a.skip_wait = int(skip_wait)
+        a.seqlock = int(seqlock)
         with torch.cuda.device(self.device):
             check(self.lib.psb_pull_allgather(C.byref(a), self._stream()), "psb_pull_allgather")
 

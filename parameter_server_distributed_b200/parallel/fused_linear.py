@@ -20,6 +20,15 @@ from .._lib import PsbGemmAG, check
 class FusedFirstLinear:
     """Callable ``(x, weight, bias) -> y`` bound to one dedicated bucket of a parameter server."""
 
+    @staticmethod
+    def supported(shape, world: int) -> bool:
+        """The fused kernel needs every 256-row N-tile to have exactly one owner and K to be a
+        multiple of 64; otherwise the layer is pulled by K2 like any other bucket."""
+        if len(shape) != 2:
+            return False
+        n, k = shape
+        return n % (256 * world) == 0 and k % 64 == 0 and (n * k) % (world * 512) == 0
+
     def __init__(self, ps, weight_name: str):
         slot = ps.plan.slots[weight_name]
         bk = ps.plan.buckets[slot.bucket]

@@ -87,7 +87,10 @@ class Trainer:
         first = getattr(model, "first_weight_name", None)
         want_fused = (pull == "gather") if fused_first_layer is None else fused_first_layer
         if want_fused and first is not None and ctx.device.type == "cuda":
-            dedicated = (first(),)
+            from .parallel.fused_linear import FusedFirstLinear
+            shape = tuple(dict(model.named_parameters())[first()].shape)
+            if FusedFirstLinear.supported(shape, ctx.world):
+                dedicated = (first(),)
         if mode == "sync":
             self.ps = ShardedParameterServer(
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,

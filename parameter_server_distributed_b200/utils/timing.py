@@ -71,6 +71,11 @@ class ClockSampler:
             self._lines.append(line.strip())
 
     def __exit__(self, *exc):
+        if self._proc is not None and not self._lines:
+            import time
+            end = time.time() + 3.0  # short regions: wait for at least one sample
+            while not self._lines and time.time() < end:
+                time.sleep(0.05)
         if self._proc is not None:
             self._proc.terminate()
             try:

@@ -16,11 +16,19 @@ from parameter_server_distributed_b200.models import MLP, MLPConfig, mse_loss
 from parameter_server_distributed_b200.ops import reference
 
 
+def _log(msg):
+    """Progress trace per rank (post-mortem of a hang): gpurun_out/mp_rank<r>.log if possible."""
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, f"mp_rank{os.environ.get('RANK', '0')}.log"), "a") as f:
+            f.write(msg + "\n")
+
+
 def check_training(ctx, pull, kind, clip):
     """Every iteration is checked as ONE step from the engine's actual state: N workers through
     the fused push/pull == fp32 PyTorch update with the mean of the workers' gradients."""
     torch.manual_seed(0)
-    cfg = MLPConfig(d_in=512, hidden=(1024, 768), d_out=256)
+    cfg = MLPConfig(d_in=512, hidden=(2048, 768), d_out=256)
     model = MLP(cfg).to(ctx.device, torch.bfloat16)
     optim = OptimConfig(kind=kind, lr=1e-2 if kind == "sgd" else 1e-3)
     tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip)
@@ -107,17 +115,89 @@ def check_fused_gemm(ctx):
     dist.barrier()
 
 
+class _Vec(torch.nn.Module):
+    def __init__(self, n):
+        super().__init__()
+        self.a = torch.nn.Parameter(torch.zeros(n))
+        self.b = torch.nn.Parameter(torch.zeros(n // 3))
+
+
+def check_async(ctx, staleness):
+    """Async / SSP on versioned shard buffers: every gradient is applied exactly once, the
+    staleness bound holds at every step, replicas agree after drain().  Rank 1 is a straggler."""
+    from parameter_server_distributed_b200 import _lib
+    from parameter_server_distributed_b200.parallel.async_engine import AsyncParameterServer
+    torch.manual_seed(3)
+    n, T, lr = 300_000, 12, 0.5
+    model = _Vec(n).to(ctx.device, torch.bfloat16)
+    ps = AsyncParameterServer(list(model.named_parameters()), OptimConfig(kind="sgd", lr=lr),
+                              ctx.fabric, bucket_mb=0.3, staleness=staleness)
+    assert len(ps.plan.buckets) >= 2
+    pad = ctx.fabric.pad.view(torch.int32)
+    total = {k: torch.zeros_like(p, dtype=torch.float32) for k, p in model.named_parameters()}
+    worst = 0
+    for c in range(1, T + 1):
+        if ctx.rank == 1 and c % 3 == 0:
+            torch.cuda._sleep(int(2e8))  # ~100 ms straggle on the device
+        loss = 0
+        for k, p in model.named_parameters():
+            # gradient of worker w at clock c: a constant pattern that is exact in bf16
+            coef = torch.full_like(p, float((ctx.rank + 1) * (c % 4 + 1)) / 64.0)
+            loss = loss + (p * coef).sum()
+        loss.backward()
+        ps.step()
+        _log(f"async s={staleness} clock {c} launched")
+        torch.cuda.synchronize()
+        _log(f"async s={staleness} clock {c} done")
+        clocks = pad[_lib.PAD_CLOCK_OFF:_lib.PAD_CLOCK_OFF + ctx.world]
+        lag = ps.clock - int(clocks.min().item())
+        worst = max(worst, lag)
+        if staleness is not None:
+            # clock c started only after everybody had published clock c - 1 - staleness
+            assert lag <= staleness + 1, (ctx.rank, c, lag, staleness)
+        assert lag <= ps.ring
+    ps.drain()
+    _log(f"async s={staleness} drained")
+    assert int(ps.applied_clocks().min().item()) == T and int(ps.applied_clocks().max().item()) == T
+    for k, p in model.named_parameters():
+        s_all = sum((w + 1) * (c % 4 + 1) for w in range(ctx.world) for c in range(1, T + 1)) / 64.0
+        exp = torch.full_like(p, -lr * s_all / ctx.world, dtype=torch.float32)
+        got = ps.gather_state("master")[k]
+        assert torch.allclose(got, exp, rtol=1e-5, atol=1e-5), (k, got.flatten()[:3], exp.flatten()[:3])
+        assert torch.equal(p.detach(), got.to(torch.bfloat16)), f"replica of {k} is not the master"
+    flat = ps.backend.param_flat.clone()
+    ref0 = flat.clone()
+    dist.broadcast(ref0, 0)
+    assert torch.equal(flat, ref0), "async replicas diverged after drain"
+    ps.close()
+    return worst
+
+
 def main():
     ctx = psd.init(heap_bytes=256 << 20)
     assert ctx.world >= 2
     check_fused_gemm(ctx)
+    _log("fused gemm ok")
     for pull, kind, clip in [("broadcast", "sgd", None), ("broadcast", "adamw", 0.5),
                              ("gather", "momentum", None), ("gather", "adam", None)]:
         check_training(ctx, pull, kind, clip)
         dist.barrier()
+        _log(f"training {pull} {kind} ok")
+    for st in (None, 1, 0):
+        worst = check_async(ctx, st)
+        dist.barrier()
+        if ctx.rank == 0:
+            print(f"async staleness={st}: worst observed lag {worst}", flush=True)
     print(f"MP_OK {ctx.rank}", flush=True)
     ctx.close()
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    except BaseException as e:  # one compact line per rank: torchrun's own traceback is noise
+        import traceback
+        tb = traceback.extract_tb(e.__traceback__)[-1]
+        print(f"MP_FAIL rank={os.environ.get('RANK')} {type(e).__name__}: {str(e)[:400]} "
+              f"({os.path.basename(tb.filename)}:{tb.lineno})", flush=True)
+        os._exit(1)

@@ -114,3 +114,27 @@ def test_gloo_two_workers_match_mean_gradient(kind, broadcast):
         assert p.exitcode == 0
     for rank, err in res:
         assert err < 5e-6, (rank, err)
+
+
+def test_async_engine_host_emulation_matches_sequential_application():
+    """Host emulation of the async mode: each worker's gradient is applied on its own, scaled by
+    1/N — for plain SGD that equals the synchronous mean update."""
+    from parameter_server_distributed_b200.parallel.async_engine import AsyncParameterServer
+    torch.manual_seed(2)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = AsyncParameterServer(list(m.named_parameters()), OptimConfig(kind="sgd", lr=0.05),
+                              bucket_mb=0.005, staleness=1)
+    assert ps.ring == 2 and ps.staleness == 1
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    for _ in range(3):
+        x, y = torch.randn(16, 32), torch.randn(16, 8)
+        mse_loss(m(x), y).backward()
+        ps.step()
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        opt.step()
+    assert ps.clock == 3
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)
+    ps.drain()  # no-op on the host

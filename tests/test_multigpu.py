@@ -17,6 +17,8 @@ def test_cross_rank_push_pull_and_fused_gemm():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", "29613",
            os.path.join(HERE, "_mp_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
     ok = r.stdout.count("MP_OK")
-    assert r.returncode == 0 and ok == n, f"rc={r.returncode} ok={ok}\n{r.stdout[-3000:]}\n{r.stderr[-3000:]}"
+    fails = [l for l in r.stdout.splitlines() if "MP_FAIL" in l]
+    assert r.returncode == 0 and ok == n, f"rc={r.returncode} ok={ok}\n" + "\n".join(fails[:8]) + \
+        f"\n{r.stderr[-1500:]}"
