@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--push-grid", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--push-tma", action="store_true",
+                    help="bulk-copy K1 variant (few SMs) instead of the register-path kernel")
     return ap.parse_args()
 
 
@@ -135,7 +137,8 @@ def run_ours(args):
         model = model.to(memory_format=wl.memory_format)
     optim = psd.OptimConfig(kind=args.optimizer, lr=1e-3 if args.optimizer != "sgd" else 1e-2)
     trainer = psd.Trainer(model, wl.loss, ctx, optim, pull=args.pull, bucket_mb=args.bucket_mb,
-                          overlap=not args.no_overlap, push_grid=args.push_grid)
+                          overlap=not args.no_overlap, push_grid=args.push_grid,
+                          push_tma=args.push_tma)
     B = wl.batch
     gen = torch.Generator().manual_seed(100 + ctx.rank)
     n_host = 4  # rotate a few distinct pinned batches

@@ -55,6 +55,8 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--optimizer", default="sgd")
     ap.add_argument("--grids", default="0")
+    ap.add_argument("--tma-grids", default="16,24,32,48",
+                    help="CTA counts of the bulk-copy K1 variant (empty = skip)")
     args = ap.parse_args()
     max_elems = int(args.max_mb * (1 << 20) / 2)
     ctx = psd.init(heap_bytes=max_elems * 4 + (64 << 20))
@@ -105,6 +107,14 @@ def main():
             ts = timed(ctx, lambda: be.push(0), args.iters)
             emit("K1 push+update+broadcast", ts, 2 * link_bytes)
             # pull mode: K1 (reduce-scatter + update) then K2 (all-gather)
+            if grid == 0 and args.tma_grids:
+                be.push_tma = True
+                for tg in [int(g) for g in args.tma_grids.split(",")]:
+                    be._push_args[0].grid = tg
+                    ts = timed(ctx, lambda: be.push(0), args.iters)
+                    emit(f"K1-TMA push+update+broadcast grid={tg}", ts, 2 * link_bytes)
+                be.push_tma = False
+                be._push_args[0].grid = grid
             be.broadcast = False
             ts = timed(ctx, lambda: be.push(0), args.iters)
             emit("K1 push+update (no broadcast)", ts, link_bytes)

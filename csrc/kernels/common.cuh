@@ -48,6 +48,9 @@ inline void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed);
 
 constexpr int kNumSMs = 148;  // B200
 
+// push_tma.cu
+int push_fused_tma_dispatch(const PsbPush& a, cudaStream_t s);
+
 // ---- memory-model primitives (system scope: visible across NVLink peers) ------
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

@@ -494,6 +494,8 @@ int psb_push_fused(const PsbPush* args, psb_stream_t stream) {
     for (int i = 0; i < a.fabric.world; ++i)
       PSB_REQUIRE(a.grad[i], PSB_EINVAL, "psb_push_fused: gradient buffer of peer %d is null", i);
 
+  if ((a.flags & PSB_PUSH_TMA) && !reduce_only && !from_reduced)
+    return push_fused_tma_dispatch(a, (cudaStream_t)stream);
   const size_t nvec = a.slice_elems / 8;
   int grid = a.grid;
   if (grid <= 0) {

@@ -209,6 +209,8 @@ typedef struct PsbFabric {
 #define PSB_PUSH_FROM_REDUCED 8 // skip the reduction: gradient comes from `reduced` (after clipping)
 #define PSB_PUSH_MASKED 16      // only sum peers whose bit is set in *peer_mask (async / SSP);
                                 // an empty mask makes the launch a no-op (nothing published)
+#define PSB_PUSH_TMA 64         // bulk-copy (cp.async.bulk) smem-ring variant: fills NVLink from ~24 SMs
+                                // instead of ~148, so backward kernels keep the other SMs
 #define PSB_PUSH_SEQLOCK 32     // publish 2*epoch (even) instead of epoch: readers pair it with the
                                 // odd mark written by psb_async_plan before the update started
 

@@ -24,6 +24,7 @@ PUSH_REDUCE_ONLY = 4
 PUSH_FROM_REDUCED = 8
 PUSH_MASKED = 16
 PUSH_SEQLOCK = 32
+PUSH_TMA = 64
 
 PAD_READY_OFF = 0
 PAD_VERSION_OFF = MAX_BUCKETS * MAX_PEERS

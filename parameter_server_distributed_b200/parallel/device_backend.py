@@ -22,7 +22,8 @@ from .fabric import Fabric
 class DeviceBackend:
     def __init__(self, fabric: Fabric, plan: BucketPlan, optim: OptimConfig,
                  grad_dtype: torch.dtype = torch.bfloat16, broadcast: bool = True,
-                 clip: bool = False, push_grid: int = 0, grad_ring: int = 1):
+                 clip: bool = False, push_grid: int = 0, grad_ring: int = 1,
+                 push_tma: bool = False):
         if len(plan.buckets) > _lib.MAX_BUCKETS:
             raise ValueError(f"{len(plan.buckets)} buckets exceed MAX_BUCKETS={_lib.MAX_BUCKETS}")
         self.fabric, self.plan, self.optim = fabric, plan, optim
@@ -32,6 +33,7 @@ class DeviceBackend:
         self.grad_dtype = grad_dtype
         self.broadcast = broadcast
         self.push_grid = push_grid
+        self.push_tma = push_tma
         fabric.reset_flags()  # epoch words below start at 0: drop a previous engine's flags
         gsz = 2 if grad_dtype == torch.bfloat16 else 4
         total = plan.total_elems
@@ -139,6 +141,8 @@ class DeviceBackend:
         flags = _lib.PUSH_BROADCAST if self.broadcast else 0
         if seqlock:
             flags |= _lib.PUSH_SEQLOCK
+        if self.push_tma:
+            flags |= _lib.PUSH_TMA
         a.peer_mask = mask_ptr if mask_ptr is not None else self.peer_mask.data_ptr()
         a.grad_off = grad_off_ptr
         if reduce_only:

@@ -31,7 +31,7 @@ class ShardedParameterServer:
                  group=None, bucket_mb: float = 64.0, broadcast: bool = True,
                  clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
-                 grad_ring: int = 1):
+                 grad_ring: int = 1, push_tma: bool = False):
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
         if not named_params:
             raise ValueError("no trainable parameters")
@@ -66,7 +66,8 @@ class ShardedParameterServer:
                 raise TypeError("the CUDA backend keeps bf16 replicas: cast the model to bfloat16")
             self.backend = DeviceBackend(fabric, self.plan, optim, grad_dtype=torch.bfloat16,
                                          broadcast=broadcast, clip=clip_norm is not None,
-                                         push_grid=push_grid, grad_ring=grad_ring)
+                                         push_grid=push_grid, grad_ring=grad_ring,
+                                         push_tma=push_tma)
             self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         else:
             from .host_backend import HostBackend

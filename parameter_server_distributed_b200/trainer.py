@@ -76,7 +76,7 @@ class Trainer:
                  optim: OptimConfig, *, mode: str = "sync", bucket_mb: float = 64.0,
                  pull: str = "broadcast", clip_norm: Optional[float] = None,
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
-                 staleness: int = 0, push_grid: int = 0):
+                 staleness: int = 0, push_grid: int = 0, push_tma: bool = False):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer)."""
         if mode not in ("sync", "async", "ssp"):
@@ -95,7 +95,8 @@ class Trainer:
             self.ps = ShardedParameterServer(
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
                 bucket_mb=bucket_mb, broadcast=(pull == "broadcast"), clip_norm=clip_norm,
-                dedicated=dedicated, overlap=overlap, push_grid=push_grid)
+                dedicated=dedicated, overlap=overlap, push_grid=push_grid,
+                push_tma=push_tma)
         else:
             from .parallel.async_engine import AsyncParameterServer
             self.ps = AsyncParameterServer(

@@ -24,14 +24,15 @@ def _log(msg):
             f.write(msg + "\n")
 
 
-def check_training(ctx, pull, kind, clip):
+def check_training(ctx, pull, kind, clip, tma=False):
     """Every iteration is checked as ONE step from the engine's actual state: N workers through
     the fused push/pull == fp32 PyTorch update with the mean of the workers' gradients."""
     torch.manual_seed(0)
     cfg = MLPConfig(d_in=512, hidden=(2048, 768), d_out=256)
     model = MLP(cfg).to(ctx.device, torch.bfloat16)
     optim = OptimConfig(kind=kind, lr=1e-2 if kind == "sgd" else 1e-3)
-    tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip)
+    tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip,
+                     push_tma=tma)
     omodel = MLP(cfg).to(ctx.device, torch.bfloat16)
     gen = torch.Generator(device="cpu").manual_seed(5)
     for it in range(4):
@@ -178,11 +179,12 @@ def main():
     assert ctx.world >= 2
     check_fused_gemm(ctx)
     _log("fused gemm ok")
-    for pull, kind, clip in [("broadcast", "sgd", None), ("broadcast", "adamw", 0.5),
-                             ("gather", "momentum", None), ("gather", "adam", None)]:
-        check_training(ctx, pull, kind, clip)
+    for pull, kind, clip, tma in [("broadcast", "sgd", None, False), ("broadcast", "adamw", 0.5, False),
+                                  ("gather", "momentum", None, False), ("gather", "adam", None, False),
+                                  ("broadcast", "sgd", None, True), ("gather", "adamw", None, True)]:
+        check_training(ctx, pull, kind, clip, tma)
         dist.barrier()
-        _log(f"training {pull} {kind} ok")
+        _log(f"training {pull} {kind} tma={tma} ok")
     for st in (None, 1, 0):
         worst = check_async(ctx, st)
         dist.barrier()

@@ -16,21 +16,22 @@ pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda:0")
 
 
-def _setup(world, kind, clip=False, broadcast=True, shapes=None):
+def _setup(world, kind, clip=False, broadcast=True, shapes=None, tma=False):
     shapes = shapes or [("w0", (257, 130)), ("b0", (257,)), ("w1", (1000, 257))]
     plan = plan_buckets(shapes, world, bucket_elems=200_000)
     fabs = Fabric.local_group(world, DEV, heap_bytes=plan.total_elems * 4 + (8 << 20))
     cfg = OptimConfig(kind=kind, lr=0.05 if kind in ("sgd", "momentum") else 0.002,
                       weight_decay=0.01, grad_scale=1.0 / world)
-    bes = [DeviceBackend(f, plan, cfg, broadcast=broadcast, clip=clip) for f in fabs]
+    bes = [DeviceBackend(f, plan, cfg, broadcast=broadcast, clip=clip, push_tma=tma) for f in fabs]
     return plan, fabs, cfg, bes
 
 
 @pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
 @pytest.mark.parametrize("kind", ["sgd", "adam"])
-def test_fused_push_broadcast(world, kind):
+@pytest.mark.parametrize("tma", [False, True], ids=["ldg", "tma"])
+def test_fused_push_broadcast(world, kind, tma):
     torch.manual_seed(world)
-    plan, fabs, cfg, bes = _setup(world, kind)
+    plan, fabs, cfg, bes = _setup(world, kind, tma=tma)
     total, shard = plan.total_elems, plan.shard_elems
     init = torch.randn(total, device=DEV).to(torch.bfloat16)
     ref_master = init.float().clone()
