@@ -12,7 +12,7 @@ sys.path.insert(0, ROOT)
 
 import torch
 
-from parameter_server_distributed_b200 import OptimConfig
+from parameter_server_distributed_b200 import OptimConfig, _lib
 from parameter_server_distributed_b200.ops import native
 from parameter_server_distributed_b200.utils import cuda_time_ms
 
@@ -63,8 +63,11 @@ def bench_gemm():
         w = (torch.randn(N, K, device=DEV) * 0.1).to(torch.bfloat16)
         y = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
         fl = 2.0 * M * N * K
-        ms = cuda_time_ms(lambda: native.gemm_bf16(x, w, out=y), device=DEV)
-        report(f"K2f tcgen05 gemm {M}x{N}x{K}", ms, flops=fl)
+        for variant, label in ((1, "cta_group::2"), (0, "cta_group::1")):
+            _lib.check(_lib.load().psb_gemm_select(variant))
+            ms = cuda_time_ms(lambda: native.gemm_bf16(x, w, out=y), device=DEV)
+            report(f"K2f tcgen05 gemm {label} {M}x{N}x{K}", ms, flops=fl)
+        _lib.check(_lib.load().psb_gemm_select(1))
         ms = cuda_time_ms(lambda: torch.matmul(x, w.t(), out=y), device=DEV)
         report(f"cuBLAS torch.matmul {M}x{N}x{K}", ms, flops=fl)
 

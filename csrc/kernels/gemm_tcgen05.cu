@@ -22,6 +22,7 @@
 // (src/parameter_server.cpp:93-97) and it has no GEMM at all.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -484,6 +485,28 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return 0;
 }
 
+}  // namespace gemm
+
+// gemm_tcgen05_2cta.cu
+int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M, int N, int K,
+                 int out_dtype, int fused, int gather_ctas, int rank, int world,
+                 const char* const* w_peer, char* w_local, uint32_t* tile_flags,
+                 const uint32_t* version_pad, const uint32_t* epoch, int skip_wait, cudaStream_t s);
+
+namespace gemm {
+
+// 0 = one CTA per tile (cta_group::1, 128x256), 1 = CTA pair per tile (cta_group::2, 256x256)
+static std::atomic<int> g_variant{-1};
+static int variant() {
+  int v = g_variant.load();
+  if (v < 0) {
+    const char* e = getenv("PSB_GEMM_VARIANT");
+    v = (e && e[0] == '1') ? 0 : 1;  // PSB_GEMM_VARIANT=1cta selects the single-CTA kernel
+    g_variant.store(v);
+  }
+  return v;
+}
+
 static int launch(const void* x, const void* w, Params& p, cudaStream_t s) {
   PSB_REQUIRE(p.M > 0 && p.N > 0 && p.K > 0, PSB_EINVAL, "gemm: empty problem %dx%dx%d", p.M, p.N,
               p.K);
@@ -494,6 +517,10 @@ static int launch(const void* x, const void* w, Params& p, cudaStream_t s) {
               "gemm: bad output dtype %d", p.out_dtype);
   PSB_REQUIRE((p.out_dtype == PSB_BF16 ? p.N % 8 : p.N % 4) == 0, PSB_EINVAL,
               "gemm: N=%d breaks 16-byte row alignment of the output", p.N);
+  if (variant() == 1)
+    return gemm2_launch(x, w, p.y, p.bias, p.M, p.N, p.K, p.out_dtype, p.fused, p.gather_ctas,
+                        p.rank, p.world, p.w_peer, p.w_local, p.tile_flags, p.version_pad, p.epoch,
+                        p.skip_wait, s);
   CUtensorMap map_a, map_b;
   if (int rc = make_map(&map_a, x, p.M, p.K, BM)) return rc;
   if (int rc = make_map(&map_b, w, p.N, p.K, BN)) return rc;
@@ -521,6 +548,12 @@ static int launch(const void* x, const void* w, Params& p, cudaStream_t s) {
 using namespace psb;
 
 extern "C" {
+
+int psb_gemm_select(int variant) {
+  PSB_REQUIRE(variant == 0 || variant == 1, PSB_EINVAL, "psb_gemm_select: variant must be 0 or 1");
+  gemm::g_variant.store(variant);
+  return 0;
+}
 
 int psb_gemm_bf16_tn(const void* x, const void* w, const float* bias, void* y, int M, int N, int K,
                      int out_dtype, psb_stream_t stream) {

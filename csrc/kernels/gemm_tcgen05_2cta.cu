@@ -1,0 +1,520 @@
+// gemm_tcgen05_2cta.cu — K2f GEMM, CTA-pair version: tcgen05.mma.cta_group::2.
+//
+//   Y[M,N] = X[M,K] · W[N,K]^T (+ bias), bf16 in, fp32 accumulate in TMEM.
+//
+// Two CTAs of one cluster (the two SMs of a TPC) work on one 256x256 output tile.  Each CTA
+// TMA-loads its own 128 rows of X and HALF of the W tile (128 of the 256 rows), so a k-block
+// costs 32 KB of L2->smem traffic per SM instead of 48 KB and the ring holds 6 stages instead
+// of 4.  One elected thread of the leader CTA issues 256x256x16 UMMAs that read A from both
+// CTAs' shared memory and the two B halves; each CTA keeps the accumulator rows of its own
+// 128 output rows in its own TMEM (2 x 256 columns, double-buffered) and runs its own
+// epilogue.  Barrier protocol (as in CUTLASS 2-SM kernels): both CTAs' TMA loads complete_tx
+// on the LEADER's full barrier; tcgen05.commit multicasts to both CTAs' empty / tmem_full
+// barriers; the epilogue warps of both CTAs arrive on the leader's tmem_empty barrier.
+// The fused all-gather mode is the same as in gemm_tcgen05.cu (gather clusters + tile flags).
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace psb {
+namespace gemm2 {
+
+constexpr int BM = 256;        // per cluster; 128 per CTA
+constexpr int BN = 256;        // per cluster; each CTA loads 128 rows of W
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int STAGES = 6;
+constexpr int A_BYTES = 128 * BK * 2;  // 16 KB per CTA
+constexpr int B_BYTES = 128 * BK * 2;  // 16 KB per CTA
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int THREADS = 192;
+constexpr int TMEM_COLS = 512;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
+constexpr int G_CHUNK = 32768;
+constexpr int G_STAGES = 6;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 rem;\n\t"
+      "mapa.shared::cluster.u32 rem, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [rem];\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+// 2-SM TMA load: data lands in THIS CTA's shared memory, the transaction bytes are counted on
+// the leader CTA's barrier (address with the peer bit cleared)
+__device__ __forceinline__ void tma_load_2d_2sm(const CUtensorMap* map, uint64_t* bar, void* smem,
+                                                int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem)),
+      "l"(map), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem, const void* gmem, uint32_t bytes,
+                                          uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem)),
+      "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gmem, const void* smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem),
+               "r"(smem_u32(smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols)
+               : "memory");
+}
+__device__ __forceinline__ void umma2_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// commit to the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t r[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t make_smem_desc(const void* tile) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(tile) & 0x3ffff) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+// D = fp32, A = B = bf16, K-major, M = 256 (pair), N = 256
+constexpr uint32_t kInstrDesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                                ((uint32_t)(BM >> 4) << 24);
+
+struct Params {
+  void* y;
+  const float* bias;
+  int M, N, K;
+  int out_dtype;
+  int fused, gather_ctas, rank, world;
+  const char* w_peer[PSB_MAX_PEERS];
+  char* w_local;
+  uint32_t* tile_flags;
+  const uint32_t* version_pad;
+  const uint32_t* epoch;
+  int skip_wait;
+};
+
+__device__ void gather_role(const Params& p, uint8_t* ring, uint64_t* bars, int gidx) {
+  const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
+  const size_t chunks_per_slice = slice_bytes / G_CHUNK;
+  const size_t tile_bytes = (size_t)BN * p.K * 2;
+  const size_t n_remote = chunks_per_slice * (size_t)(p.world - 1);
+  const size_t n_items =
+      n_remote > (size_t)gidx ? (n_remote - gidx + p.gather_ctas - 1) / p.gather_ctas : 0;
+  auto item_offset = [&](size_t it, int& owner) -> size_t {
+    const size_t c = gidx + it * p.gather_ctas;
+    const int ord = (int)(c / chunks_per_slice);
+    owner = (p.rank + 1 + ord) % p.world;
+    return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK;
+  };
+  uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
+  const uint32_t target = p.skip_wait ? 0u : *p.epoch;
+  size_t prev_off = 0;
+  bool have_prev = false;
+  for (size_t i = 0; i < n_items + (G_STAGES - 1); ++i) {
+    if (i < n_items) {
+      const int s = (int)(i % G_STAGES);
+      if (i >= G_STAGES) bulk_wait_read<0>();
+      int owner;
+      const size_t off = item_offset(i, owner);
+      if (!((waited >> owner) & 1u)) {
+        wait_ge_sys(p.version_pad + owner, target);
+        fence_proxy_async();
+        waited |= 1u << owner;
+      }
+      mbar_expect_tx(&bars[s], G_CHUNK);
+      bulk_load(ring + (size_t)s * G_CHUNK, p.w_peer[owner] + off, G_CHUNK, &bars[s]);
+    }
+    if (i >= G_STAGES - 1) {
+      const size_t j = i - (G_STAGES - 1);
+      if (j < n_items) {
+        const int s = (int)(j % G_STAGES);
+        mbar_wait(&bars[s], (uint32_t)((j / G_STAGES) & 1));
+        int owner;
+        const size_t off = item_offset(j, owner);
+        bulk_store(p.w_local + off, ring + (size_t)s * G_CHUNK, G_CHUNK);
+        bulk_commit();
+        if (have_prev) {
+          bulk_wait<1>();
+          red_release_gpu_add(p.tile_flags + prev_off / tile_bytes, 1u);
+        }
+        prev_off = off;
+        have_prev = true;
+      }
+    }
+  }
+  if (have_prev) {
+    bulk_wait<0>();
+    red_release_gpu_add(p.tile_flags + prev_off / tile_bytes, 1u);
+  }
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+    gemm2_bf16_kernel(const __grid_constant__ CUtensorMap map_a,
+                      const __grid_constant__ CUtensorMap map_b, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* gbars = tmem_empty + 2;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(gbars + G_STAGES);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();  // 0 = leader
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int gather_clusters = p.fused ? p.gather_ctas >> 1 : 0;
+
+  if (cluster_id < gather_clusters) {  // both CTAs of a gather cluster copy, independently
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < G_STAGES; ++i) mbar_init(&gbars[i], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      fence_proxy_async();
+      gather_role(p, smem, gbars, blockIdx.x);
+    }
+    return;
+  }
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full[i], 2);   // leader's expect_tx arrive + the peer producer's arrive
+      mbar_init(&empty[i], 1);  // one multicast commit
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);   // one multicast commit
+      mbar_init(&tmem_empty[i], 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's copy
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+  }
+  cluster_sync();  // barriers of both CTAs exist before anybody signals across the pair
+  if (warp == 1) tmem_alloc2(tmem_base_slot, TMEM_COLS);
+  tc_fence_before();
+  cluster_sync();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  const int num_m = (p.M + BM - 1) / BM;
+  const int num_n = (p.N + BN - 1) / BN;
+  const int n_start = p.fused ? p.rank * (num_n / p.world) : 0;
+  const int num_tiles = num_m * num_n;
+  const int num_k = (p.K + BK - 1) / BK;
+  const int first = cluster_id - gather_clusters;
+  const int step = num_clusters - gather_clusters;
+  auto decode = [&](int t, int& m_blk, int& n_blk) {
+    const int n_ord = t / num_m;
+    m_blk = t - n_ord * num_m;
+    n_blk = n_start + n_ord;
+    if (n_blk >= num_n) n_blk -= num_n;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (one per CTA) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int n_per_rank = p.fused ? num_n / p.world : 0;
+      const uint32_t chunks_per_tile = p.fused ? (uint32_t)((size_t)BN * p.K * 2 / G_CHUNK) : 0;
+      for (int t = first; t < num_tiles; t += step) {
+        int m_blk, n_blk;
+        decode(t, m_blk, n_blk);
+        if (p.fused && n_blk / n_per_rank != p.rank) {
+          while (ld_acquire_gpu(p.tile_flags + n_blk) < chunks_per_tile) __nanosleep(64);
+          fence_proxy_async();
+        }
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (cta == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);  // both CTAs' bytes
+          else mbar_arrive_cluster(&full[stage], 0);
+          tma_load_2d_2sm(&map_a, &full[stage], smem_a + stage * A_BYTES, kb * BK,
+                          m_blk * BM + (int)cta * 128);
+          tma_load_2d_2sm(&map_b, &full[stage], smem_b + stage * B_BYTES, kb * BK,
+                          n_blk * BN + (int)cta * 128);
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (cta == 0 && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = first; t < num_tiles; t += step, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint64_t da = make_smem_desc(smem_a + stage * A_BYTES);
+          const uint64_t db = make_smem_desc(smem_b + stage * B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma2_bf16(tmem_d, da + 2 * k, db + 2 * k, kInstrDesc, (kb | k) != 0);
+          umma2_commit_mc(&empty[stage]);  // frees the slot in both CTAs
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+        umma2_commit_mc(&tmem_full[acc]);  // accumulator ready in both CTAs
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5 of each CTA) =====================
+    const int quarter = warp & 3;
+    int it = 0;
+    for (int t = first; t < num_tiles; t += step, ++it) {
+      int m_blk, n_blk;
+      decode(t, m_blk, n_blk);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + (int)cta * 128 + quarter * 32 + lane;
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n_blk * BN + c * 32;
+        if (row < p.M && col0 < p.N) {
+          float f[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(r[k]);
+          if (p.bias) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k)
+              if (col0 + k < p.N) f[k] += __ldg(p.bias + col0 + k);
+          }
+          if (p.out_dtype == PSB_BF16) {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.y) + (size_t)row * p.N + col0;
+            if (col0 + 32 <= p.N) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) st_stream_16(dst + q * 8, pack8(f + q * 8));
+            } else {
+#pragma unroll
+              for (int k = 0; k < 32; ++k)
+                if (col0 + k < p.N) dst[k] = __float2bfloat16_rn(f[k]);
+            }
+          } else {
+            float* dst = reinterpret_cast<float*>(p.y) + (size_t)row * p.N + col0;
+            if (col0 + 32 <= p.N) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                st_stream_f4(dst + q * 4,
+                             make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]));
+            } else {
+#pragma unroll
+              for (int k = 0; k < 32; ++k)
+                if (col0 + k < p.N) dst[k] = f[k];
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);  // leader's barrier
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync();  // nobody touches the peer's smem / TMEM after this
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, TMEM_COLS);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols) {
+  EncodeTiledFn enc = get_encode();
+  PSB_REQUIRE(enc, PSB_EUNSUPPORTED, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, 128};
+  cuuint32_t elem[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PSB_REQUIRE(r == CUDA_SUCCESS, PSB_EINVAL, "cuTensorMapEncodeTiled failed with CUresult %d",
+              (int)r);
+  return 0;
+}
+
+}  // namespace gemm2
+
+// Entry used by gemm_tcgen05.cu when the pair kernel is selected.  `fused` fields of the
+// caller's parameter block are passed through unchanged.
+int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M, int N, int K,
+                 int out_dtype, int fused, int gather_ctas, int rank, int world,
+                 const char* const* w_peer, char* w_local, uint32_t* tile_flags,
+                 const uint32_t* version_pad, const uint32_t* epoch, int skip_wait,
+                 cudaStream_t s) {
+  using namespace gemm2;
+  Params p{};
+  p.y = y, p.bias = bias, p.M = M, p.N = N, p.K = K, p.out_dtype = out_dtype;
+  p.fused = fused, p.gather_ctas = gather_ctas, p.rank = rank, p.world = world;
+  for (int i = 0; i < world && i < PSB_MAX_PEERS; ++i) p.w_peer[i] = w_peer ? w_peer[i] : nullptr;
+  p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
+  p.skip_wait = skip_wait;
+  CUtensorMap map_a, map_b;
+  if (int rc = make_map(&map_a, x, M, K)) return rc;
+  if (int rc = make_map(&map_b, w, N, K)) return rc;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    SMEM_BYTES);
+  });
+  PSB_CUDA_OK(attr_err);
+  const int num_tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
+  if (fused) {
+    clusters = kNumSMs / 2;
+    if (num_tiles + gather_ctas / 2 < clusters) clusters = num_tiles + gather_ctas / 2;
+  }
+  gemm2_bf16_kernel<<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, p);
+  PSB_LAUNCH_OK("gemm_bf16_tcgen05_2cta");
+  return 0;
+}
+
+}  // namespace psb

@@ -312,6 +312,9 @@ int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, ps
 // replica by TMA stores, so the all-gather of the first layer overlaps its GEMM
 // tile by tile.  No counterpart in the reference (north-star item).
 // ---------------------------------------------------------------------------
+// kernel variant: 1 (default) = CTA pair per 256x256 tile (tcgen05.mma.cta_group::2),
+// 0 = one CTA per 128x256 tile (cta_group::1).  Also PSB_GEMM_VARIANT=1cta|2cta.
+int psb_gemm_select(int variant);
 int psb_gemm_bf16_tn(const void* x, const void* w, const float* bias, void* y, int M, int N, int K,
                      int out_dtype, psb_stream_t stream);
 typedef struct PsbGemmAG {

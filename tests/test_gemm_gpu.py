@@ -14,6 +14,14 @@ pytestmark = pytest.mark.gpu
 DEV = torch.device("cuda:0")
 
 
+@pytest.fixture(autouse=True, params=[1, 0], ids=["cta_pair", "single_cta"])
+def gemm_variant(request):
+    """Every test runs on both kernels: cta_group::2 (default) and cta_group::1."""
+    _lib.check(_lib.load().psb_gemm_select(request.param))
+    yield request.param
+    _lib.check(_lib.load().psb_gemm_select(1))
+
+
 def _check(y, x, w, bias=None):
     exp = x.float() @ w.float().t()
     if bias is not None:
