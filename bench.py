@@ -34,7 +34,7 @@ def parse():
     ap.add_argument("--batch-per-gpu", type=int, default=0,
                     help="0 = config default (mlp 4096, gpt2 8 x 1024 tokens, resnet50 128)")
     ap.add_argument("--optimizer", default="sgd")
-    ap.add_argument("--pull", default="broadcast", choices=["broadcast", "gather"])
+    ap.add_argument("--pull", default="broadcast", choices=["broadcast", "gather", "hybrid"])
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--push-grid", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")

@@ -135,10 +135,11 @@ class DeviceBackend:
     def push(self, b: int, *, reduce_only: bool = False, from_reduced: bool = False,
              no_wait: bool = False, masked: bool = False, clip: bool = False,
              seqlock: bool = False, mask_ptr: Optional[int] = None,
-             grad_off_ptr: Optional[int] = None) -> None:
+             grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None) -> None:
         """K1 on the current stream."""
         a = self._push_args[b]
-        flags = _lib.PUSH_BROADCAST if self.broadcast else 0
+        bc = self.broadcast if broadcast is None else broadcast
+        flags = _lib.PUSH_BROADCAST if bc else 0
         if seqlock:
             flags |= _lib.PUSH_SEQLOCK
         if self.push_tma:

@@ -31,7 +31,11 @@ class ShardedParameterServer:
                  group=None, bucket_mb: float = 64.0, broadcast: bool = True,
                  clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
-                 grad_ring: int = 1, push_tma: bool = False):
+                 grad_ring: int = 1, push_tma: bool = False, lazy_dedicated: bool = False):
+        """``broadcast``: owners write new slices into every replica inside K1 (push-mode
+        all-gather).  ``lazy_dedicated``: buckets named in ``dedicated`` are the exception — their
+        owners publish locally only and the consumer gathers them itself (the fused all-gather
+        GEMM of the first layer), which halves the un-overlappable tail of the last push."""
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
         if not named_params:
             raise ValueError("no trainable parameters")
@@ -50,6 +54,7 @@ class ShardedParameterServer:
         self.clip_norm = clip_norm
         self.overlap = overlap and self.is_cuda
         self.broadcast = broadcast
+        self.lazy_dedicated = lazy_dedicated
         optim = OptimConfig(**{**optim.__dict__, "grad_scale": optim.grad_scale / world})
         self.optim = optim
 
@@ -164,21 +169,27 @@ class ShardedParameterServer:
             return g.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
         return g.contiguous()
 
+    def _bcast(self, b: int) -> bool:
+        """Does the owner of bucket ``b`` write its new slice into every replica?"""
+        if self.lazy_dedicated and self.plan.buckets[b].dedicated and self._fused_first_layer:
+            return False
+        return self.broadcast
+
     def _flush(self, b: int) -> None:
         self._stage(b)
         self._flushed[b] = True
         clip = self.clip_norm is not None
         if not self.is_cuda:
-            self.backend.push(b, reduce_only=clip)
+            self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
             return
         if self.overlap:
             ev = self._events[b]
             ev.record(torch.cuda.current_stream(self.device))
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                self.backend.push(b, reduce_only=clip)
+                self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
         else:
-            self.backend.push(b, reduce_only=clip)
+            self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
 
     # ------------------------------------------------------------------ end of iteration
     def step(self) -> None:
@@ -198,18 +209,25 @@ class ShardedParameterServer:
             if self.clip_norm is not None:
                 be.norm_allreduce(self.clip_norm)
                 for b in range(nb):
-                    be.push(b, from_reduced=True, clip=True)
+                    be.push(b, from_reduced=True, clip=True, broadcast=self._bcast(b))
             be.advance_step()
-            if not self.broadcast:
-                for b in range(nb):
-                    if not self.plan.buckets[b].dedicated or not self._fused_first_layer:
-                        be.pull(b)
+            for b in range(nb):
+                fused = self.plan.buckets[b].dedicated and self._fused_first_layer
+                if not self._bcast(b) and not fused:
+                    be.pull(b)  # pull-mode bucket without a fused consumer: K2
         if self.is_cuda:
             cur = torch.cuda.current_stream(self.device)
             if self.overlap:
                 cur.wait_stream(self.comm_stream)
-            if self.broadcast:
-                be.wait_versions()
+            # broadcast buckets: wait until every owner's slice has landed in the replica
+            lo = None
+            for b in range(nb + 1):
+                bc = b < nb and self._bcast(b)
+                if bc and lo is None:
+                    lo = b
+                if not bc and lo is not None:
+                    be.wait_versions(lo, b)
+                    lo = None
         self._flushed = [False] * nb
         self.steps_done += 1
 

@@ -68,7 +68,8 @@ class HostBackend:
         return out
 
     def push(self, b: int, *, reduce_only: bool = False, from_reduced: bool = False,
-             no_wait: bool = False, masked: bool = False, clip: bool = False) -> None:
+             no_wait: bool = False, masked: bool = False, clip: bool = False,
+             broadcast=None, **_unused) -> None:
         bk = self.plan.buckets[b]
         s = bk.slice_elems
         if from_reduced:
@@ -95,7 +96,7 @@ class HostBackend:
         mine = self.shard_slice(self.master, b).to(self.param_flat.dtype)
         pb = self.param_bucket(b)
         pb[self.rank * s:(self.rank + 1) * s].copy_(mine)
-        if self.broadcast:
+        if self.broadcast if broadcast is None else broadcast:
             for r, sl in enumerate(self._gather_slices(mine)):
                 pb[r * s:(r + 1) * s].copy_(sl)
         self.epoch[b] += 1

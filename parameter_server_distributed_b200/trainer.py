@@ -78,14 +78,18 @@ class Trainer:
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
                  staleness: int = 0, push_grid: int = 0, push_tma: bool = False):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
-        ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer)."""
+        ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
+        ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
+        fused into the first GEMM of the next forward (K2f)."""
         if mode not in ("sync", "async", "ssp"):
             raise ValueError(f"unknown mode {mode!r}")
         self.model, self.loss_fn, self.ctx = model, loss_fn, ctx
         self.device = ctx.device
         dedicated = ()
         first = getattr(model, "first_weight_name", None)
-        want_fused = (pull == "gather") if fused_first_layer is None else fused_first_layer
+        if pull not in ("broadcast", "gather", "hybrid"):
+            raise ValueError(f"unknown pull mode {pull!r}")
+        want_fused = (pull in ("gather", "hybrid")) if fused_first_layer is None else fused_first_layer
         if want_fused and first is not None and ctx.device.type == "cuda":
             from .parallel.fused_linear import FusedFirstLinear
             shape = tuple(dict(model.named_parameters())[first()].shape)
@@ -94,15 +98,15 @@ class Trainer:
         if mode == "sync":
             self.ps = ShardedParameterServer(
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
-                bucket_mb=bucket_mb, broadcast=(pull == "broadcast"), clip_norm=clip_norm,
+                bucket_mb=bucket_mb, broadcast=(pull != "gather"), clip_norm=clip_norm,
                 dedicated=dedicated, overlap=overlap, push_grid=push_grid,
-                push_tma=push_tma)
+                push_tma=push_tma, lazy_dedicated=(pull == "hybrid"))
         else:
             from .parallel.async_engine import AsyncParameterServer
             self.ps = AsyncParameterServer(
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
                 bucket_mb=bucket_mb, staleness=(staleness if mode == "ssp" else None))
-        if dedicated and pull == "gather":
+        if dedicated and pull in ("gather", "hybrid"):
             from .parallel.fused_linear import FusedFirstLinear
             model.first_linear_fn = FusedFirstLinear(self.ps, dedicated[0])
         self._dev_inputs = None

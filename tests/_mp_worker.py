@@ -55,7 +55,7 @@ def check_training(ctx, pull, kind, clip, tma=False):
         for n in masters:
             reference.optim_step(rcfg, masters[n].view(-1), grads[n].view(-1), m[n].view(-1),
                                  v[n].view(-1), clip_coef=coef, step=it)
-        if pull == "gather":
+        if pull in ("gather", "hybrid"):
             # the first-layer weight is gathered lazily by the fused GEMM of the next forward
             with torch.no_grad():
                 model(xs[ctx.rank].to(ctx.device))
@@ -181,7 +181,8 @@ def main():
     _log("fused gemm ok")
     for pull, kind, clip, tma in [("broadcast", "sgd", None, False), ("broadcast", "adamw", 0.5, False),
                                   ("gather", "momentum", None, False), ("gather", "adam", None, False),
-                                  ("broadcast", "sgd", None, True), ("gather", "adamw", None, True)]:
+                                  ("broadcast", "sgd", None, True), ("gather", "adamw", None, True),
+                                  ("hybrid", "momentum", None, True), ("hybrid", "adamw", 1.0, False)]:
         check_training(ctx, pull, kind, clip, tma)
         dist.barrier()
         _log(f"training {pull} {kind} tma={tma} ok")
