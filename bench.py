@@ -38,8 +38,9 @@ def parse():
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--push-grid", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")
-    ap.add_argument("--push-tma", action="store_true",
-                    help="bulk-copy K1 variant (few SMs) instead of the register-path kernel")
+    ap.add_argument("--push", default="auto", choices=["auto", "tma", "ldg"],
+                    help="K1 variant: auto = bulk-copy kernel on 32 SMs for overlapped buckets, "
+                         "register-path kernel on all SMs for the last one")
     return ap.parse_args()
 
 
@@ -138,7 +139,7 @@ def run_ours(args):
     optim = psd.OptimConfig(kind=args.optimizer, lr=1e-3 if args.optimizer != "sgd" else 1e-2)
     trainer = psd.Trainer(model, wl.loss, ctx, optim, pull=args.pull, bucket_mb=args.bucket_mb,
                           overlap=not args.no_overlap, push_grid=args.push_grid,
-                          push_tma=args.push_tma)
+                          push_tma={"auto": None, "tma": True, "ldg": False}[args.push])
     B = wl.batch
     gen = torch.Generator().manual_seed(100 + ctx.rank)
     n_host = 4  # rotate a few distinct pinned batches

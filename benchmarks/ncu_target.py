@@ -24,8 +24,12 @@ reps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 x = (torch.randn(4096, 4096, device=DEV) * 0.1).to(torch.bfloat16)
 w = (torch.randn(8192, 4096, device=DEV) * 0.1).to(torch.bfloat16)
 y = torch.empty(4096, 8192, dtype=torch.bfloat16, device=DEV)
-for _ in range(reps):
-    native.gemm_bf16(x, w, out=y)
+from parameter_server_distributed_b200 import _lib
+for variant in (1, 0):  # cta_group::2 (default), then cta_group::1
+    _lib.check(_lib.load().psb_gemm_select(variant))
+    for _ in range(reps):
+        native.gemm_bf16(x, w, out=y)
+_lib.check(_lib.load().psb_gemm_select(1))
 
 # K3: AdamW on a 64M-element shard
 n = 64 << 20
@@ -45,6 +49,8 @@ be = DeviceBackend(fab, plan, OptimConfig(kind="adamw", lr=1e-3))
 be.grad_flat.normal_()
 for _ in range(reps):
     be.push(0)
+for _ in range(reps):
+    be.push(0, tma=True, grid=32)  # bulk-copy variant on 32 SMs
 
 # K4 / K6
 for _ in range(reps):

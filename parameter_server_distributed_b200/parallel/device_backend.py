@@ -135,15 +135,17 @@ class DeviceBackend:
     def push(self, b: int, *, reduce_only: bool = False, from_reduced: bool = False,
              no_wait: bool = False, masked: bool = False, clip: bool = False,
              seqlock: bool = False, mask_ptr: Optional[int] = None,
-             grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None) -> None:
+             grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None,
+             tma: Optional[bool] = None, grid: Optional[int] = None) -> None:
         """K1 on the current stream."""
         a = self._push_args[b]
         bc = self.broadcast if broadcast is None else broadcast
         flags = _lib.PUSH_BROADCAST if bc else 0
         if seqlock:
             flags |= _lib.PUSH_SEQLOCK
-        if self.push_tma:
+        if self.push_tma if tma is None else tma:
             flags |= _lib.PUSH_TMA
+        a.grid = self.push_grid if grid is None else grid
         a.peer_mask = mask_ptr if mask_ptr is not None else self.peer_mask.data_ptr()
         a.grad_off = grad_off_ptr
         if reduce_only:

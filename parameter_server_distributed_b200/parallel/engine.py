@@ -31,7 +31,8 @@ class ShardedParameterServer:
                  group=None, bucket_mb: float = 64.0, broadcast: bool = True,
                  clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
-                 grad_ring: int = 1, push_tma: bool = False, lazy_dedicated: bool = False):
+                 grad_ring: int = 1, push_tma: Optional[bool] = None, lazy_dedicated: bool = False,
+                 overlap_grid: int = 32):
         """``broadcast``: owners write new slices into every replica inside K1 (push-mode
         all-gather).  ``lazy_dedicated``: buckets named in ``dedicated`` are the exception — their
         owners publish locally only and the consumer gathers them itself (the fused all-gather
@@ -55,6 +56,12 @@ class ShardedParameterServer:
         self.overlap = overlap and self.is_cuda
         self.broadcast = broadcast
         self.lazy_dedicated = lazy_dedicated
+        # K1 variant policy.  None = auto: buckets pushed while backward is still running use the
+        # bulk-copy kernel on `overlap_grid` SMs (the rest keep computing); the last bucket has
+        # nothing left to overlap with and takes the whole GPU with the register-path kernel.
+        self.push_tma = push_tma
+        self.overlap_grid = overlap_grid
+        self._user_grid = push_grid
         optim = OptimConfig(**{**optim.__dict__, "grad_scale": optim.grad_scale / world})
         self.optim = optim
 
@@ -72,7 +79,7 @@ class ShardedParameterServer:
             self.backend = DeviceBackend(fabric, self.plan, optim, grad_dtype=torch.bfloat16,
                                          broadcast=broadcast, clip=clip_norm is not None,
                                          push_grid=push_grid, grad_ring=grad_ring,
-                                         push_tma=push_tma)
+                                         push_tma=bool(push_tma))
             self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         else:
             from .host_backend import HostBackend
@@ -175,21 +182,33 @@ class ShardedParameterServer:
             return False
         return self.broadcast
 
+    def _variant(self, b: int) -> dict:
+        """Kernel variant / grid of K1 for bucket ``b`` (see ``push_tma`` above)."""
+        if not self.is_cuda:
+            return {}
+        if self.push_tma is not None:
+            return {"tma": self.push_tma, "grid": self._user_grid}
+        last = b == len(self.plan.buckets) - 1
+        if self.world > 1 and self.overlap and not last and self.clip_norm is None:
+            return {"tma": True, "grid": self._user_grid or self.overlap_grid}
+        return {"tma": False, "grid": self._user_grid}
+
     def _flush(self, b: int) -> None:
         self._stage(b)
         self._flushed[b] = True
         clip = self.clip_norm is not None
+        kw = dict(reduce_only=clip, broadcast=self._bcast(b), **self._variant(b))
         if not self.is_cuda:
-            self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
+            self.backend.push(b, **kw)
             return
         if self.overlap:
             ev = self._events[b]
             ev.record(torch.cuda.current_stream(self.device))
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
+                self.backend.push(b, **kw)
         else:
-            self.backend.push(b, reduce_only=clip, broadcast=self._bcast(b))
+            self.backend.push(b, **kw)
 
     # ------------------------------------------------------------------ end of iteration
     def step(self) -> None:

@@ -76,7 +76,7 @@ class Trainer:
                  optim: OptimConfig, *, mode: str = "sync", bucket_mb: float = 64.0,
                  pull: str = "broadcast", clip_norm: Optional[float] = None,
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
-                 staleness: int = 0, push_grid: int = 0, push_tma: bool = False):
+                 staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
         ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
