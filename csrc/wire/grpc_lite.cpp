@@ -148,16 +148,14 @@ void Server::serve_forever() {
 
 void Server::shutdown() {
   bool was = running_.exchange(false);
-  if (listen_fd_ >= 0) {
-    ::shutdown(listen_fd_, SHUT_RDWR);
-    ::close(listen_fd_);
-    listen_fd_ = -1;
-  }
+  const int lfd = listen_fd_.load();
+  if (lfd >= 0) ::shutdown(lfd, SHUT_RDWR);  // wakes poll(); the fd is closed after the join
   {
     std::lock_guard<std::mutex> lk(conns_mu_);
     for (int fd : conn_fds_) ::shutdown(fd, SHUT_RDWR);
   }
   if (accept_thread_.joinable()) accept_thread_.join();
+  if (lfd >= 0 && listen_fd_.exchange(-1) == lfd) ::close(lfd);
   if (was)
     for (int i = 0; i < 500 && active_.load() > 0; ++i)
       std::this_thread::sleep_for(std::chrono::milliseconds(10));
@@ -165,10 +163,12 @@ void Server::shutdown() {
 
 void Server::accept_loop() {
   while (running_) {
-    pollfd pfd{listen_fd_, POLLIN, 0};
+    const int lfd = listen_fd_.load();
+    if (lfd < 0) break;
+    pollfd pfd{lfd, POLLIN, 0};
     int pr = ::poll(&pfd, 1, 200);
     if (pr <= 0) continue;
-    int fd = ::accept(listen_fd_, nullptr, nullptr);
+    int fd = ::accept(lfd, nullptr, nullptr);
     if (fd < 0) {
       if (!running_) break;
       continue;

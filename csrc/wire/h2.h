@@ -135,7 +135,7 @@ class Server {
   void accept_loop();
   void serve_conn(int fd);
   std::map<std::string, Handler> handlers_;
-  int listen_fd_ = -1;
+  std::atomic<int> listen_fd_{-1};
   int port_ = -1;
   std::atomic<bool> running_{false};
   std::thread accept_thread_;
