@@ -605,7 +605,14 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* a, psb_stream_t stream) {
   if (!flags[dev]) PSB_CUDA_OK(cudaMalloc(&flags[dev], kMaxTiles * sizeof(uint32_t)));
   PSB_CUDA_OK(cudaMemsetAsync(flags[dev], 0, num_n * sizeof(uint32_t), s));
   p.fused = 1;
-  p.gather_ctas = 16;
+  {
+    // SMs for the gather ring vs the tensor cores, from the two sides of the roofline:
+    // time of the math at ~1.5 PFLOP/s vs time of the remote slices at ~700 GB/s
+    const double t_gemm = 2.0 * a->M * a->N * a->K / 1.5e15;
+    const double t_link = (double)(f.world - 1) / f.world * a->N * a->K * 2.0 / 700e9;
+    const double r = t_link / t_gemm;
+    p.gather_ctas = r < 0.6 ? 16 : r < 1.2 ? 24 : r < 2.5 ? 32 : 48;
+  }
   p.rank = f.rank, p.world = f.world;
   for (int i = 0; i < f.world; ++i) p.w_peer[i] = reinterpret_cast<const char*>(a->w[i]);
   p.w_local = reinterpret_cast<char*>(a->w[f.rank]);

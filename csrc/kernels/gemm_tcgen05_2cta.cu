@@ -33,7 +33,7 @@ constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 constexpr int G_CHUNK = 32768;
-constexpr int G_STAGES = 6;
+constexpr int G_STAGES = 6;  // x 32 KB = the 192 KB the GEMM ring would use
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -206,6 +206,14 @@ struct Params {
   int skip_wait;
 };
 
+// One thread drives a ring of G_STAGES buffers.  Item i is loaded at iteration i and stored
+// G_LAG iterations later; its buffer is reused G_STAGES - G_LAG iterations after the store was
+// issued, and its arrival counter is bumped once G_DONE_LAG younger stores have been committed,
+// so neither the smem-read nor the global-write completion of a store is ever waited for
+// directly (the first version waited for both every iteration and reached 160 GB/s).
+constexpr int G_LAG = 4;       // loads in flight
+constexpr int G_DONE_LAG = 3;  // committed stores that may still be completing
+
 __device__ void gather_role(const Params& p, uint8_t* ring, uint64_t* bars, int gidx) {
   const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
   const size_t chunks_per_slice = slice_bytes / G_CHUNK;
@@ -221,12 +229,12 @@ __device__ void gather_role(const Params& p, uint8_t* ring, uint64_t* bars, int 
   };
   uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
   const uint32_t target = p.skip_wait ? 0u : *p.epoch;
-  size_t prev_off = 0;
-  bool have_prev = false;
-  for (size_t i = 0; i < n_items + (G_STAGES - 1); ++i) {
+  for (size_t i = 0; i < n_items + G_LAG + G_DONE_LAG; ++i) {
     if (i < n_items) {
       const int s = (int)(i % G_STAGES);
-      if (i >= G_STAGES) bulk_wait_read<0>();
+      // buffer s last held item i - G_STAGES, stored at iteration i - G_STAGES + G_LAG: at most
+      // G_STAGES - G_LAG - 1 younger stores exist, let those keep reading
+      if (i >= G_STAGES) bulk_wait_read<G_STAGES - G_LAG - 1>();
       int owner;
       const size_t off = item_offset(i, owner);
       if (!((waited >> owner) & 1u)) {
@@ -237,27 +245,28 @@ __device__ void gather_role(const Params& p, uint8_t* ring, uint64_t* bars, int 
       mbar_expect_tx(&bars[s], G_CHUNK);
       bulk_load(ring + (size_t)s * G_CHUNK, p.w_peer[owner] + off, G_CHUNK, &bars[s]);
     }
-    if (i >= G_STAGES - 1) {
-      const size_t j = i - (G_STAGES - 1);
-      if (j < n_items) {
-        const int s = (int)(j % G_STAGES);
-        mbar_wait(&bars[s], (uint32_t)((j / G_STAGES) & 1));
-        int owner;
-        const size_t off = item_offset(j, owner);
-        bulk_store(p.w_local + off, ring + (size_t)s * G_CHUNK, G_CHUNK);
-        bulk_commit();
-        if (have_prev) {
-          bulk_wait<1>();
-          red_release_gpu_add(p.tile_flags + prev_off / tile_bytes, 1u);
-        }
-        prev_off = off;
-        have_prev = true;
-      }
+    if (i >= G_LAG && i - G_LAG < n_items) {
+      const size_t j = i - G_LAG;
+      const int s = (int)(j % G_STAGES);
+      mbar_wait(&bars[s], (uint32_t)((j / G_STAGES) & 1));
+      int owner;
+      const size_t off = item_offset(j, owner);
+      bulk_store(p.w_local + off, ring + (size_t)s * G_CHUNK, G_CHUNK);
+      bulk_commit();
     }
-  }
-  if (have_prev) {
-    bulk_wait<0>();
-    red_release_gpu_add(p.tile_flags + prev_off / tile_bytes, 1u);
+    if (i >= G_LAG + G_DONE_LAG) {
+      const size_t d = i - G_LAG - G_DONE_LAG;  // < n_items by the loop bound
+      // stores are committed in item order: all but the youngest G_DONE_LAG (or fewer, near the
+      // end) groups complete => item d is globally visible
+      const size_t younger = n_items - 1 - d < (size_t)G_DONE_LAG ? n_items - 1 - d : G_DONE_LAG;
+      if (younger >= 3) bulk_wait<3>();
+      else if (younger == 2) bulk_wait<2>();
+      else if (younger == 1) bulk_wait<1>();
+      else bulk_wait<0>();
+      int owner;
+      const size_t off = item_offset(d, owner);
+      red_release_gpu_add(p.tile_flags + off / tile_bytes, 1u);
+    }
   }
 }
 
@@ -320,10 +329,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int num_k = (p.K + BK - 1) / BK;
   const int first = cluster_id - gather_clusters;
   const int step = num_clusters - gather_clusters;
+  // Tile order: regions of N-tiles by owner (the locally owned slice first, so the gather of the
+  // next owner's slice overlaps the math on this one); inside a region tiles are walked in
+  // groups of kGroupM row-blocks so that one wave of 74 clusters touches ~8 A panels and ~9 W
+  // panels (L2-resident) instead of streaming all of X once per N-tile.
+  constexpr int kGroupM = 8;
+  const int region_n = p.fused ? num_n / p.world : num_n;
+  const int tiles_per_region = num_m * region_n;
   auto decode = [&](int t, int& m_blk, int& n_blk) {
-    const int n_ord = t / num_m;
-    m_blk = t - n_ord * num_m;
-    n_blk = n_start + n_ord;
+    const int region = t / tiles_per_region;
+    const int local = t - region * tiles_per_region;
+    const int per_group = kGroupM * region_n;
+    const int g = local / per_group;
+    const int first_m = g * kGroupM;
+    const int gm = num_m - first_m < kGroupM ? num_m - first_m : kGroupM;
+    const int in_group = local - g * per_group;
+    m_blk = first_m + in_group % gm;
+    n_blk = n_start + region * region_n + in_group / gm;
     if (n_blk >= num_n) n_blk -= num_n;
   };
 
