@@ -611,7 +611,7 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* a, psb_stream_t stream) {
     const double t_gemm = 2.0 * a->M * a->N * a->K / 1.5e15;
     const double t_link = (double)(f.world - 1) / f.world * a->N * a->K * 2.0 / 700e9;
     const double r = t_link / t_gemm;
-    p.gather_ctas = r < 0.6 ? 16 : r < 1.2 ? 24 : r < 2.5 ? 32 : 48;
+    p.gather_ctas = r < 0.15 ? 16 : r < 0.4 ? 24 : r < 0.8 ? 40 : 64;
   }
   p.rank = f.rank, p.world = f.world;
   for (int i = 0; i < f.world; ++i) p.w_peer[i] = reinterpret_cast<const char*>(a->w[i]);

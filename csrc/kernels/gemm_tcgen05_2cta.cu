@@ -32,8 +32,13 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int THREADS = 192;
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
-constexpr int G_CHUNK = 32768;
-constexpr int G_STAGES = 6;  // x 32 KB = the 192 KB the GEMM ring would use
+// Gather: every warp of a gather CTA is an independent copier of 8 KB items (peer -> registers
+// -> local replica, 16 x 16-byte loads in flight per lane).  Measured on B200 at N = 2: a ring
+// of cp.async.bulk copies driven by one thread moves only ~8-10 GB/s per CTA from a peer
+// (loads of 32 KB complete at ~1 GB/s each, bulk stores complete one after the other), plain
+// 16-byte peer loads from many threads are what fills NVLink — as in K1 / K2.
+constexpr int G_CHUNK = 8192;
+constexpr int G_WARPS = 6;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -206,67 +211,67 @@ struct Params {
   int skip_wait;
 };
 
-// One thread drives a ring of G_STAGES buffers.  Item i is loaded at iteration i and stored
-// G_LAG iterations later; its buffer is reused G_STAGES - G_LAG iterations after the store was
-// issued, and its arrival counter is bumped once G_DONE_LAG younger stores have been committed,
-// so neither the smem-read nor the global-write completion of a store is ever waited for
-// directly (the first version waited for both every iteration and reached 160 GB/s).
-constexpr int G_LAG = 4;       // loads in flight
-constexpr int G_DONE_LAG = 3;  // committed stores that may still be completing
-
-__device__ void gather_role(const Params& p, uint8_t* ring, uint64_t* bars, int gidx) {
+// Items (8 KB pieces of the remote slices, in owner order) are dealt round-robin to all gather
+// warps of the grid.  After its stores a warp makes them visible (membar + release) and bumps
+// the arrival counter of the piece's N-tile; a tile is complete at tile_bytes / G_CHUNK.
+__device__ void gather_role(const Params& p, int gidx) {
   const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
   const size_t chunks_per_slice = slice_bytes / G_CHUNK;
   const size_t tile_bytes = (size_t)BN * p.K * 2;
   const size_t n_remote = chunks_per_slice * (size_t)(p.world - 1);
-  const size_t n_items =
-      n_remote > (size_t)gidx ? (n_remote - gidx + p.gather_ctas - 1) / p.gather_ctas : 0;
-  auto item_offset = [&](size_t it, int& owner) -> size_t {
-    const size_t c = gidx + it * p.gather_ctas;
-    const int ord = (int)(c / chunks_per_slice);
-    owner = (p.rank + 1 + ord) % p.world;
-    return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK;
-  };
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const size_t worker = (size_t)gidx * G_WARPS + warp;
+  const size_t workers = (size_t)p.gather_ctas * G_WARPS;
   uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
   const uint32_t target = p.skip_wait ? 0u : *p.epoch;
-  for (size_t i = 0; i < n_items + G_LAG + G_DONE_LAG; ++i) {
-    if (i < n_items) {
-      const int s = (int)(i % G_STAGES);
-      // buffer s last held item i - G_STAGES, stored at iteration i - G_STAGES + G_LAG: at most
-      // G_STAGES - G_LAG - 1 younger stores exist, let those keep reading
-      if (i >= G_STAGES) bulk_wait_read<G_STAGES - G_LAG - 1>();
-      int owner;
-      const size_t off = item_offset(i, owner);
-      if (!((waited >> owner) & 1u)) {
-        wait_ge_sys(p.version_pad + owner, target);
-        fence_proxy_async();
-        waited |= 1u << owner;
-      }
-      mbar_expect_tx(&bars[s], G_CHUNK);
-      bulk_load(ring + (size_t)s * G_CHUNK, p.w_peer[owner] + off, G_CHUNK, &bars[s]);
+  constexpr int V = G_CHUNK / 512;
+  auto locate = [&](size_t c) -> size_t {  // byte offset of item c; waits for its owner once
+    const int ord = (int)(c / chunks_per_slice);
+    const int owner = (p.rank + 1 + ord) % p.world;
+    if (!((waited >> owner) & 1u)) {
+      if (lane == 0) wait_ge_sys(p.version_pad + owner, target);  // owner's slice is final
+      __syncwarp();
+      waited |= 1u << owner;
     }
-    if (i >= G_LAG && i - G_LAG < n_items) {
-      const size_t j = i - G_LAG;
-      const int s = (int)(j % G_STAGES);
-      mbar_wait(&bars[s], (uint32_t)((j / G_STAGES) & 1));
-      int owner;
-      const size_t off = item_offset(j, owner);
-      bulk_store(p.w_local + off, ring + (size_t)s * G_CHUNK, G_CHUNK);
-      bulk_commit();
+    return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK;
+  };
+  auto load = [&](size_t off, uint4 (&v)[V]) {
+    const char* src = p.w_peer[off / slice_bytes] + off + lane * 16;
+#pragma unroll
+    for (int k = 0; k < V; ++k) v[k] = ld_stream_16(src + k * 512);
+  };
+  auto store = [&](size_t off, const uint4 (&v)[V]) {
+    char* dst = p.w_local + off + lane * 16;
+#pragma unroll
+    for (int k = 0; k < V; ++k) st_stream_16(dst + k * 512, v[k]);
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) red_release_gpu_add(p.tile_flags + off / tile_bytes, 1u);
+  };
+  // two items in flight per warp: the loads of the next one are issued before the stores and
+  // the fence of the current one
+  uint4 va[V], vb[V];
+  size_t c = worker;
+  if (c >= n_remote) return;
+  size_t off_a = locate(c), off_b = 0;
+  load(off_a, va);
+  while (true) {
+    const bool more_b = c + workers < n_remote;
+    if (more_b) {
+      off_b = locate(c + workers);
+      load(off_b, vb);
     }
-    if (i >= G_LAG + G_DONE_LAG) {
-      const size_t d = i - G_LAG - G_DONE_LAG;  // < n_items by the loop bound
-      // stores are committed in item order: all but the youngest G_DONE_LAG (or fewer, near the
-      // end) groups complete => item d is globally visible
-      const size_t younger = n_items - 1 - d < (size_t)G_DONE_LAG ? n_items - 1 - d : G_DONE_LAG;
-      if (younger >= 3) bulk_wait<3>();
-      else if (younger == 2) bulk_wait<2>();
-      else if (younger == 1) bulk_wait<1>();
-      else bulk_wait<0>();
-      int owner;
-      const size_t off = item_offset(d, owner);
-      red_release_gpu_add(p.tile_flags + off / tile_bytes, 1u);
+    store(off_a, va);
+    if (!more_b) break;
+    c += workers;
+    const bool more_a = c + workers < n_remote;
+    if (more_a) {
+      off_a = locate(c + workers);
+      load(off_a, va);
     }
+    store(off_b, vb);
+    if (!more_a) break;
+    c += workers;
   }
 }
 
@@ -281,8 +286,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint64_t* gbars = tmem_empty + 2;
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(gbars + G_STAGES);
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -292,12 +296,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int gather_clusters = p.fused ? p.gather_ctas >> 1 : 0;
 
   if (cluster_id < gather_clusters) {  // both CTAs of a gather cluster copy, independently
-    if (threadIdx.x == 0) {
-      for (int i = 0; i < G_STAGES; ++i) mbar_init(&gbars[i], 1);
-      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-      fence_proxy_async();
-      gather_role(p, smem, gbars, blockIdx.x);
-    }
+    gather_role(p, blockIdx.x);
     return;
   }
 
