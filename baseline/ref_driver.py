@@ -153,7 +153,7 @@ def run(args, lib_path: str) -> int:
     dt = time.perf_counter() - t0
     nparams = sum(b.size for b in host_p)
     out = {
-        "metric": "samples/sec (sync-SGD through the sharded parameter server)",
+        "metric": "samples/sec (training through parameter-server push/pull)",
         "value": B * args.steps / dt, "unit": "samples/s", "n_gpus": n_gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16 compute, fp32 parameter server",

@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--push-grid", type=int, default=0)
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--mode", default="sync", choices=["sync", "async", "ssp"])
+    ap.add_argument("--staleness", type=int, default=1)
     ap.add_argument("--push", default="auto", choices=["auto", "tma", "ldg"],
                     help="K1 variant: auto = bulk-copy kernel on 32 SMs for overlapped buckets, "
                          "register-path kernel on all SMs for the last one")
@@ -137,7 +139,8 @@ def run_ours(args):
     if wl.memory_format is not None:
         model = model.to(memory_format=wl.memory_format)
     optim = psd.OptimConfig(kind=args.optimizer, lr=1e-3 if args.optimizer != "sgd" else 1e-2)
-    trainer = psd.Trainer(model, wl.loss, ctx, optim, pull=args.pull, bucket_mb=args.bucket_mb,
+    trainer = psd.Trainer(model, wl.loss, ctx, optim, mode=args.mode, staleness=args.staleness,
+                          pull=args.pull, bucket_mb=args.bucket_mb,
                           overlap=not args.no_overlap, push_grid=args.push_grid,
                           push_tma={"auto": None, "tma": True, "ldg": False}[args.push])
     B = wl.batch
@@ -169,16 +172,18 @@ def run_ours(args):
     # ---------------- push+pull alone (gradients already staged): latency per step
     ps = trainer.ps
     host_barrier(ctx)
-    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    p0.record()
-    for _ in range(args.steps):
-        for b in range(len(ps.plan.buckets)):
-            ps._flushed[b] = True
-            ps.backend.push(b)
-        ps.step()
-    p1.record()
-    host_barrier(ctx)
-    pp_ms = max_over_ranks(p0.elapsed_time(p1), ctx) / args.steps
+    pp_ms = None
+    if args.mode == "sync":
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for _ in range(args.steps):
+            for b in range(len(ps.plan.buckets)):
+                ps._flushed[b] = True
+                ps.backend.push(b, broadcast=ps._bcast(b))
+            ps.step()
+        p1.record()
+        host_barrier(ctx)
+        pp_ms = max_over_ranks(p0.elapsed_time(p1), ctx) / args.steps
 
     # ---------------- end to end through Trainer.step: pinned host -> device, loss -> host
     for i in range(args.warmup):
@@ -198,6 +203,8 @@ def run_ours(args):
     host_barrier(ctx)
     e2e_ms = max(s0.elapsed_time(s1), (time.perf_counter() - t0) * 1e3)
     e2e_ms = max_over_ranks(e2e_ms, ctx)
+    if args.mode != "sync":
+        ps.drain()  # apply what is still in flight so every rank ends with the same model
 
     global_batch = B * world
     value = global_batch * args.steps / (dev_ms / 1e3)
@@ -205,7 +212,7 @@ def run_ours(args):
     if ctx.rank == 0:
         flops = wl.flops_per_sample * global_batch * args.steps
         out = {
-            "metric": "samples/sec (sync-SGD through the sharded parameter server)",
+            "metric": "samples/sec (training through parameter-server push/pull)",
             "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -214,6 +221,8 @@ def run_ours(args):
             "config": {"model": f"{wl.label} ({nparams / 1e6:.1f}M params)",
                        "global_batch": global_batch, "seq_len": wl.seq_len,
                        "parallelism": f"dp{world} / {world} PS shards", "optimizer": args.optimizer,
+                       "mode": args.mode if args.mode != "ssp" else f"ssp(staleness={args.staleness})",
+                       "push": args.push,
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
                        "l2": "working set (weights+grads+state+activations > 1 GB) exceeds the "
                              "126 MB L2; inputs rotate over 4 batches"},

@@ -22,6 +22,7 @@ import torch
 
 from ..ops import native
 from ..ops.native import OptimConfig
+from ..utils.tracing import Metrics, nvtx_range
 from .buckets import BucketPlan, ParamSlot, plan_buckets
 
 
@@ -125,6 +126,7 @@ class ShardedParameterServer:
         for name, p in named_params:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(name)))
         self.steps_done = 0
+        self.metrics = Metrics()
 
     # ------------------------------------------------------------------ setup helpers
     def _sync_replicas(self) -> None:
@@ -198,6 +200,12 @@ class ShardedParameterServer:
         self._flushed[b] = True
         clip = self.clip_norm is not None
         kw = dict(reduce_only=clip, broadcast=self._bcast(b), **self._variant(b))
+        bk = self.plan.buckets[b]
+        self.metrics.inc("pushes")
+        # bytes entering this GPU over NVLink for the bucket: peers' gradient slices of my shard
+        # plus (broadcast) the other owners' refreshed slices of my replica
+        link = (self.world - 1) * bk.slice_elems * 2
+        self.metrics.inc("nvlink_in_bytes", link * (2 if self._bcast(b) else 1))
         if not self.is_cuda:
             self.backend.push(b, **kw)
             return
@@ -205,10 +213,11 @@ class ShardedParameterServer:
             ev = self._events[b]
             ev.record(torch.cuda.current_stream(self.device))
             self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
+            with torch.cuda.stream(self.comm_stream), nvtx_range(f"psb.push[{b}]"):
                 self.backend.push(b, **kw)
         else:
-            self.backend.push(b, **kw)
+            with nvtx_range(f"psb.push[{b}]"):
+                self.backend.push(b, **kw)
 
     # ------------------------------------------------------------------ end of iteration
     def step(self) -> None:
@@ -249,6 +258,7 @@ class ShardedParameterServer:
                     lo = None
         self._flushed = [False] * nb
         self.steps_done += 1
+        self.metrics.inc("steps")
 
     _fused_first_layer = False
 

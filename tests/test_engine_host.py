@@ -138,3 +138,18 @@ def test_async_engine_host_emulation_matches_sequential_application():
     for a, b in zip(m.parameters(), ref.parameters()):
         assert torch.allclose(a, b, atol=1e-6)
     ps.drain()  # no-op on the host
+
+
+def test_engine_metrics_and_prometheus_text():
+    torch.manual_seed(4)
+    m = MLP(CFG)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind="sgd", lr=0.1),
+                                bucket_mb=0.005)
+    for _ in range(2):
+        mse_loss(m(torch.randn(4, 32)), torch.randn(4, 8)).backward()
+        ps.step()
+    snap = ps.metrics.snapshot()
+    assert snap["steps"] == 2 and snap["pushes"] == 2 * len(ps.plan.buckets)
+    assert snap["nvlink_in_bytes"] == 0  # one rank: nothing crosses a link
+    text = ps.metrics.prometheus()
+    assert "# TYPE psb_steps counter" in text and "psb_pushes " in text

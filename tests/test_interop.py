@@ -259,3 +259,33 @@ def test_cpp_worker_against_grpcio_servers(tmp_path):
     finally:
         ps_srv.stop(0)
         co_srv.stop(0)
+
+
+def test_barrier_membership_follows_eviction(servers):
+    """T7: a worker that dies (stops heart-beating) is evicted and no longer blocks a barrier of
+    "all registered workers" — the reference's sync barrier would stall forever."""
+    _, co_port, _, _, _ = servers
+    ch = grpc.insecure_channel(f"127.0.0.1:{co_port}")
+    co = protos.Stub(ch, "coordinator.Coordinator")
+    ext = protos.Stub(ch, "psb.CoordinatorExt")
+    for wid in (0, 1):
+        co.RegisterWorker(M("coordinator.WorkerInfo")(worker_id=wid, address="localhost"), timeout=5)
+    stop = threading.Event()
+
+    def beat():  # only worker 0 stays alive (eviction timeout 1 s, scan 200 ms)
+        c = protos.Stub(grpc.insecure_channel(f"127.0.0.1:{co_port}"), "coordinator.Coordinator")
+        while not stop.is_set():
+            c.Heartbeat(M("coordinator.HeartbeatRequest")(worker_id=0, status=1), timeout=5)
+            time.sleep(0.2)
+
+    t = threading.Thread(target=beat)
+    t.start()
+    try:
+        t0 = time.time()
+        r = ext.Barrier(M("psb.BarrierRequest")(name="epoch", worker_id=0, generation=1, expected=0,
+                                                timeout_ms=8000), timeout=15)
+        assert r.released and r.arrived == 1
+        assert 0.5 < time.time() - t0 < 6.0  # opened when worker 1 was evicted, not by timeout
+    finally:
+        stop.set()
+        t.join()
