@@ -50,7 +50,7 @@ def _probe_ungrouped(lib_path: str, n_gpus: int) -> bool:
         "rc = lib.ref_nccl_aggregate(C.c_void_p(m), C.c_void_p(x.ctypes.data), C.c_longlong(1024), 0)\n"
         "sys.exit(0 if rc == 1 and abs(float(x[0]) - 1.0) < 1e-6 else 3)\n")
     try:
-        r = subprocess.run([sys.executable, "-c", code], timeout=90, capture_output=True)
+        r = subprocess.run([sys.executable, "-c", code], timeout=60, capture_output=True)
         return r.returncode == 0
     except subprocess.TimeoutExpired:
         return False
