@@ -130,7 +130,8 @@ def run_ours(args):
         return 1
     wl = Workload(args.config, args.batch_per_gpu)
     nparams = wl.nparams
-    ctx = psd.init(heap_bytes=nparams * 4 + (512 << 20))
+    ring = 1 if args.mode == "sync" else 4 if args.mode == "async" else max(2, args.staleness + 1)
+    ctx = psd.init(heap_bytes=nparams * 2 * (1 + ring) + (512 << 20))  # replica + gradient ring
     world = ctx.world
     if world != args.gpus and ctx.rank == 0:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)
