@@ -8,9 +8,13 @@
 #include <iostream>
 #include <thread>
 
+#include "../wire/hpack.h"
 #include "../control/coordinator_service.h"
 #include "../ps/ps_service.h"
 #include "../worker/worker.h"
+
+#include <string>
+#include <vector>
 
 #define CHECK(cond)                                                              \
   do {                                                                           \
@@ -20,8 +24,45 @@
     }                                                                            \
   } while (0)
 
+static std::string unhex(const char* h) {
+  std::string out;
+  for (; h[0] && h[1]; h += 2) out.push_back(static_cast<char>(std::stoi(std::string(h, 2), nullptr, 16)));
+  return out;
+}
+
+// RFC 7541 Appendix C.4: three consecutive requests with Huffman strings and a dynamic table
+// that carries over from one header block to the next.
+static int hpack_rfc_vectors() {
+  using psb::hpack::Header;
+  psb::hpack::Decoder dec;
+  std::vector<Header> h;
+  CHECK(dec.decode(unhex("828684418cf1e3c2e5f23a6ba0ab90f4ff"), h));
+  CHECK(h.size() == 4 && h[0] == Header(":method", "GET") && h[1] == Header(":scheme", "http") &&
+        h[2] == Header(":path", "/") && h[3] == Header(":authority", "www.example.com"));
+  h.clear();
+  CHECK(dec.decode(unhex("828684be5886a8eb10649cbf"), h));
+  CHECK(h.size() == 5 && h[3] == Header(":authority", "www.example.com") &&
+        h[4] == Header("cache-control", "no-cache"));
+  h.clear();
+  CHECK(dec.decode(unhex("828785bf408825a849e95ba97d7f8925a849e95bb8e8b4bf"), h));
+  CHECK(h.size() == 5 && h[1] == Header(":scheme", "https") && h[2] == Header(":path", "/index.html") &&
+        h[4] == Header("custom-key", "custom-value"));
+  // what our own encoder emits must decode to the same list
+  psb::hpack::Encoder enc;
+  std::string block;
+  std::vector<Header> in = {{":status", "200"}, {"content-type", "application/grpc"},
+                            {"grpc-status", "0"}, {"x-empty", ""}};
+  enc.encode(in, block);
+  std::vector<Header> out;
+  CHECK(psb::hpack::Decoder().decode(block, out) && out == in);
+  std::string s;
+  CHECK(!psb::hpack::huffman_decode(std::string("\xff\xff\xff\xff", 4), s));  // EOS in a string
+  return 0;
+}
+
 int main() {
   using namespace psb;
+  if (hpack_rfc_vectors() != 0) return 1;
   ParameterServerService ps(2, 0, PsOptions());
   int ps_port = ps.listen("127.0.0.1:0");
   CHECK(ps_port > 0);
