@@ -193,7 +193,24 @@ __device__ __forceinline__ uint64_t make_smem_desc(const void* tile) {
   d |= (uint64_t)2 << 61;  // SWIZZLE_128B
   return d;
 }
-// D = fp32, A = B = bf16, K-major, M = 256 (pair), N = 256
+// MN-major operand (the reduction index is the OUTER dimension of the row-major source, e.g.
+// W[N_red, K_out] as the B operand of dX = dY * W).  One TMA box per 64-element MN atom:
+// {64 MN elements = 128 bytes, BK reduction rows}, swizzle 128B, 8 KB; the two atoms of a
+// CTA's 128 rows / columns sit 8 KB apart (leading byte offset), groups of 8 reduction rows
+// 1 KB apart (stride byte offset).  One UMMA of K = 16 consumes 16 rows = 2 KB.
+constexpr int MN_ATOM_BYTES = 64 * BK * 2;
+__device__ __forceinline__ uint64_t make_smem_desc_mn(const void* tile) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(tile) & 0x3ffff) >> 4);
+  d |= (uint64_t)(MN_ATOM_BYTES >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+constexpr uint32_t kDescStepK = (UMMA_K * 2) >> 4;           // K-major: 32 bytes inside the atom
+constexpr uint32_t kDescStepMN = (UMMA_K * 128) >> 4;        // MN-major: 16 rows of 128 bytes
+// D = fp32, A = B = bf16, K-major, M = 256 (pair), N = 256; bit 15 / 16 = A / B is MN-major
 constexpr uint32_t kInstrDesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
 
@@ -209,7 +226,28 @@ struct Params {
   const uint32_t* version_pad;
   const uint32_t* epoch;
   int skip_wait;
+  int a_mn, b_mn;                // operand is MN-major (stored [K, M] / [K, N] row-major)
+  const __nv_bfloat16* aux_in;   // EPI_DGELU: pre-activation Z [M, N]
+  __nv_bfloat16* aux_out;        // EPI_GELU: where Z goes (optional)
 };
+
+enum { EPI_NONE = 0, EPI_GELU = 1, EPI_DGELU = 2 };
+
+// tanh-form GELU, as torch.nn.functional.gelu(approximate="tanh")
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gelu_tanh(float z) {
+  const float u = 0.7978845608028654f * (z + 0.044715f * z * z * z);
+  return 0.5f * z * (1.f + tanh_approx(u));
+}
+__device__ __forceinline__ float dgelu_tanh(float z) {
+  const float z2 = z * z;
+  const float t = tanh_approx(0.7978845608028654f * (z + 0.044715f * z * z2));
+  return 0.5f * (1.f + t) + 0.5f * z * (1.f - t * t) * 0.7978845608028654f * (1.f + 0.134145f * z2);
+}
 
 // Items (8 KB pieces of the remote slices, in owner order) are dealt round-robin to all gather
 // warps of the grid.  After its stores a warp makes them visible (membar + release) and bumps
@@ -275,6 +313,7 @@ __device__ void gather_role(const Params& p, int gidx) {
   }
 }
 
+template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     gemm2_bf16_kernel(const __grid_constant__ CUtensorMap map_a,
                       const __grid_constant__ CUtensorMap map_b, const Params p) {
@@ -366,10 +405,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
           mbar_wait(&empty[stage], phase ^ 1);
           if (cta == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);  // both CTAs' bytes
           else mbar_arrive_cluster(&full[stage], 0);
-          tma_load_2d_2sm(&map_a, &full[stage], smem_a + stage * A_BYTES, kb * BK,
-                          m_blk * BM + (int)cta * 128);
-          tma_load_2d_2sm(&map_b, &full[stage], smem_b + stage * B_BYTES, kb * BK,
-                          n_blk * BN + (int)cta * 128);
+          uint8_t* sa = smem_a + stage * A_BYTES;
+          uint8_t* sb = smem_b + stage * B_BYTES;
+          const int m0 = m_blk * BM + (int)cta * 128, n0 = n_blk * BN + (int)cta * 128;
+          if (!p.a_mn) {
+            tma_load_2d_2sm(&map_a, &full[stage], sa, kb * BK, m0);
+          } else {
+            tma_load_2d_2sm(&map_a, &full[stage], sa, m0, kb * BK);
+            tma_load_2d_2sm(&map_a, &full[stage], sa + MN_ATOM_BYTES, m0 + 64, kb * BK);
+          }
+          if (!p.b_mn) {
+            tma_load_2d_2sm(&map_b, &full[stage], sb, kb * BK, n0);
+          } else {
+            tma_load_2d_2sm(&map_b, &full[stage], sb, n0, kb * BK);
+            tma_load_2d_2sm(&map_b, &full[stage], sb + MN_ATOM_BYTES, n0 + 64, kb * BK);
+          }
           if (++stage == STAGES) stage = 0, phase ^= 1;
         }
       }
@@ -380,6 +430,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      const uint32_t idesc = kInstrDesc | (p.a_mn ? 1u << 15 : 0u) | (p.b_mn ? 1u << 16 : 0u);
+      const uint32_t step_a = p.a_mn ? kDescStepMN : kDescStepK;
+      const uint32_t step_b = p.b_mn ? kDescStepMN : kDescStepK;
       for (int t = first; t < num_tiles; t += step, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
@@ -389,11 +442,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint64_t da = make_smem_desc(smem_a + stage * A_BYTES);
-          const uint64_t db = make_smem_desc(smem_b + stage * B_BYTES);
+          const uint64_t da = p.a_mn ? make_smem_desc_mn(smem_a + stage * A_BYTES)
+                                     : make_smem_desc(smem_a + stage * A_BYTES);
+          const uint64_t db = p.b_mn ? make_smem_desc_mn(smem_b + stage * B_BYTES)
+                                     : make_smem_desc(smem_b + stage * B_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma2_bf16(tmem_d, da + 2 * k, db + 2 * k, kInstrDesc, (kb | k) != 0);
+            umma2_bf16(tmem_d, da + step_a * k, db + step_b * k, idesc, (kb | k) != 0);
           umma2_commit_mc(&empty[stage]);  // frees the slot in both CTAs
           if (++stage == STAGES) stage = 0, phase ^= 1;
         }
@@ -427,6 +482,41 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
 #pragma unroll
             for (int k = 0; k < 32; ++k)
               if (col0 + k < p.N) f[k] += __ldg(p.bias + col0 + k);
+          }
+          const bool full_cols = col0 + 32 <= p.N;
+          if constexpr (EPI == EPI_GELU) {
+            // Z is rounded to bf16 first: that is the value the backward pass will see
+#pragma unroll
+            for (int k = 0; k < 32; ++k) f[k] = __bfloat162float(__float2bfloat16_rn(f[k]));
+            if (p.aux_out) {
+              __nv_bfloat16* z = p.aux_out + (size_t)row * p.N + col0;
+              if (full_cols) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) st_stream_16(z + q * 8, pack8(f + q * 8));
+              } else {
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                  if (col0 + k < p.N) z[k] = __float2bfloat16_rn(f[k]);
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 32; ++k) f[k] = gelu_tanh(f[k]);
+          }
+          if constexpr (EPI == EPI_DGELU) {
+            const __nv_bfloat16* z = p.aux_in + (size_t)row * p.N + col0;
+            if (full_cols) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                float zz[8];
+                unpack8(ld_stream_16(z + q * 8), zz);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[q * 8 + k] *= dgelu_tanh(zz[k]);
+              }
+            } else {
+#pragma unroll
+              for (int k = 0; k < 32; ++k)
+                if (col0 + k < p.N) f[k] *= dgelu_tanh(__bfloat162float(z[k]));
+            }
           }
           if (p.out_dtype == PSB_BF16) {
             __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.y) + (size_t)row * p.N + col0;
@@ -501,6 +591,58 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return 0;
 }
 
+// MN-major source: `red` rows of `mn` contiguous elements; one box = one 64-element atom
+static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_t mn) {
+  EncodeTiledFn enc = get_encode();
+  PSB_REQUIRE(enc, PSB_EUNSUPPORTED, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {mn, red};
+  cuuint64_t strides[1] = {mn * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)BK};
+  cuuint32_t elem[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PSB_REQUIRE(r == CUDA_SUCCESS, PSB_EINVAL, "cuTensorMapEncodeTiled (MN-major) failed with CUresult %d",
+              (int)r);
+  return 0;
+}
+
+template <int EPI>
+static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const Params& p,
+                      int clusters, cudaStream_t s) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  });
+  PSB_CUDA_OK(attr_err);
+  gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, p);
+  PSB_LAUNCH_OK(EPI == EPI_NONE ? "gemm_bf16_tcgen05_2cta"
+                                : EPI == EPI_GELU ? "gemm_bf16_tcgen05_2cta_gelu"
+                                                  : "gemm_bf16_tcgen05_2cta_dgelu");
+  return 0;
+}
+
+static int launch(const void* a, const void* b, const Params& p, int epi, cudaStream_t s) {
+  CUtensorMap map_a, map_b;
+  if (int rc = p.a_mn ? make_map_mn(&map_a, a, p.K, p.M) : make_map(&map_a, a, p.M, p.K)) return rc;
+  if (int rc = p.b_mn ? make_map_mn(&map_b, b, p.K, p.N) : make_map(&map_b, b, p.N, p.K)) return rc;
+  const int num_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+  int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
+  if (p.fused) {
+    clusters = kNumSMs / 2;
+    if (num_tiles + p.gather_ctas / 2 < clusters) clusters = num_tiles + p.gather_ctas / 2;
+  }
+  switch (epi) {
+    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, p, clusters, s);
+    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, p, clusters, s);
+    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, p, clusters, s);
+  }
+  PSB_REQUIRE(false, PSB_EINVAL, "gemm: unknown epilogue %d", epi);
+  return 0;
+}
+
 }  // namespace gemm2
 
 // Entry used by gemm_tcgen05.cu when the pair kernel is selected.  `fused` fields of the
@@ -517,25 +659,39 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
   for (int i = 0; i < world && i < PSB_MAX_PEERS; ++i) p.w_peer[i] = w_peer ? w_peer[i] : nullptr;
   p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
   p.skip_wait = skip_wait;
-  CUtensorMap map_a, map_b;
-  if (int rc = make_map(&map_a, x, M, K)) return rc;
-  if (int rc = make_map(&map_b, w, N, K)) return rc;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    SMEM_BYTES);
-  });
-  PSB_CUDA_OK(attr_err);
-  const int num_tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-  int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
-  if (fused) {
-    clusters = kNumSMs / 2;
-    if (num_tiles + gather_ctas / 2 < clusters) clusters = num_tiles + gather_ctas / 2;
-  }
-  gemm2_bf16_kernel<<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, p);
-  PSB_LAUNCH_OK("gemm_bf16_tcgen05_2cta");
-  return 0;
+  return launch(x, w, p, EPI_NONE, s);
 }
 
 }  // namespace psb
+
+extern "C" int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream) {
+  using namespace psb;
+  using namespace psb::gemm2;
+  PSB_REQUIRE(g && g->a && g->b && g->y, PSB_EINVAL, "psb_gemm_bf16: null operand");
+  PSB_REQUIRE(g->M > 0 && g->N > 0 && g->K > 0, PSB_EINVAL, "psb_gemm_bf16: empty problem %dx%dx%d",
+              g->M, g->N, g->K);
+  PSB_REQUIRE(g->out_dtype == PSB_BF16 || g->out_dtype == PSB_F32, PSB_EINVAL,
+              "psb_gemm_bf16: bad output dtype %d", g->out_dtype);
+  // every row of every operand starts on a 16-byte boundary (TMA strides, vector epilogue)
+  PSB_REQUIRE((g->trans_a ? g->M : g->K) % 8 == 0, PSB_EINVAL,
+              "psb_gemm_bf16: the contiguous dimension of A (%d) must be a multiple of 8",
+              g->trans_a ? g->M : g->K);
+  PSB_REQUIRE((g->trans_b ? g->N : g->K) % 8 == 0, PSB_EINVAL,
+              "psb_gemm_bf16: the contiguous dimension of B (%d) must be a multiple of 8",
+              g->trans_b ? g->N : g->K);
+  PSB_REQUIRE(g->N % 8 == 0, PSB_EINVAL, "psb_gemm_bf16: N=%d must be a multiple of 8", g->N);
+  PSB_REQUIRE(((uintptr_t)g->a & 15) == 0 && ((uintptr_t)g->b & 15) == 0 &&
+                  ((uintptr_t)g->y & 15) == 0 && ((uintptr_t)g->aux_in & 15) == 0 &&
+                  ((uintptr_t)g->aux_out & 15) == 0,
+              PSB_EINVAL, "psb_gemm_bf16: operands must be 16-byte aligned");
+  PSB_REQUIRE(g->epilogue >= PSB_EPI_NONE && g->epilogue <= PSB_EPI_DGELU, PSB_EINVAL,
+              "psb_gemm_bf16: unknown epilogue %d", g->epilogue);
+  PSB_REQUIRE(g->epilogue != PSB_EPI_DGELU || g->aux_in, PSB_EINVAL,
+              "psb_gemm_bf16: the dGELU epilogue needs the pre-activation in aux_in");
+  Params p{};
+  p.y = g->y, p.bias = g->bias, p.M = g->M, p.N = g->N, p.K = g->K, p.out_dtype = g->out_dtype;
+  p.a_mn = g->trans_a != 0, p.b_mn = g->trans_b != 0;
+  p.aux_in = reinterpret_cast<const __nv_bfloat16*>(g->aux_in);
+  p.aux_out = reinterpret_cast<__nv_bfloat16*>(g->aux_out);
+  return launch(g->a, g->b, p, g->epilogue, (cudaStream_t)stream);
+}

@@ -331,6 +331,31 @@ typedef struct PsbGemmAG {
 } PsbGemmAG;
 int psb_gemm_allgather_bf16(const PsbGemmAG* args, psb_stream_t stream);
 
+// General form used by the training layers (forward, dX and dW of a Linear without any
+// transposed copy):  Y[M,N] = op(A) · op(B) (+ bias) with an optional fused epilogue.
+//   trans_a = 0: A stored [M,K] row-major (K-major operand)   1: A stored [K,M] (MN-major)
+//   trans_b = 0: B stored [N,K] row-major (K-major operand)   1: B stored [K,N] (MN-major)
+// forward  Y  = X · W^T      : trans_a 0, trans_b 0
+// dX           = dY · W       : trans_a 0, trans_b 1
+// dW           = dY^T · X     : trans_a 1, trans_b 1   (A = dY [batch,N_out], B = X [batch,K_in])
+// Epilogues (tanh-form GELU): PSB_EPI_GELU stores Z = acc + bias rounded to bf16 into aux_out
+// (optional) and gelu(Z) into Y; PSB_EPI_DGELU stores acc * gelu'(aux_in) — the activation
+// gradient of the PREVIOUS layer is applied by the dX GEMM of this one.  CTA-pair kernel only.
+enum { PSB_EPI_NONE = 0, PSB_EPI_GELU = 1, PSB_EPI_DGELU = 2 };
+typedef struct PsbGemm {
+  const void* a;
+  const void* b;
+  void* y;             // [M,N] row-major, out_dtype
+  const float* bias;   // optional [N] fp32
+  const void* aux_in;  // PSB_EPI_DGELU: Z [M,N] bf16
+  void* aux_out;       // PSB_EPI_GELU: Z [M,N] bf16 (optional)
+  int32_t M, N, K;
+  int32_t trans_a, trans_b;
+  int32_t out_dtype;   // PSB_BF16 / PSB_F32
+  int32_t epilogue;
+} PsbGemm;
+int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

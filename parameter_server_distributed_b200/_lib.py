@@ -81,6 +81,16 @@ class PsbGemmAG(C.Structure):
                 ("epoch", C.c_void_p), ("skip_wait", C.c_int32)]
 
 
+EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2
+
+
+class PsbGemm(C.Structure):
+    _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("y", C.c_void_p), ("bias", C.c_void_p),
+                ("aux_in", C.c_void_p), ("aux_out", C.c_void_p), ("M", C.c_int32),
+                ("N", C.c_int32), ("K", C.c_int32), ("trans_a", C.c_int32),
+                ("trans_b", C.c_int32), ("out_dtype", C.c_int32), ("epilogue", C.c_int32)]
+
+
 class PsbError(RuntimeError):
     pass
 
@@ -138,6 +148,7 @@ def _declare(lib) -> None:
         "psb_gemm_select": (i32, [i32]),
         "psb_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
         "psb_gemm_allgather_bf16": (i32, [C.POINTER(PsbGemmAG), vp]),
+        "psb_gemm_bf16": (i32, [C.POINTER(PsbGemm), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

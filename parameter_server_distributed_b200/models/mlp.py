@@ -3,7 +3,10 @@ workers").  The reference has no model at all: its only tensor is a fabricated
 ``weight[10,10]`` (src/worker.cpp:346-353) with constant gradients (:316-320).
 
 The first Linear can run through the fused all-gather + tcgen05 GEMM (K2f) when the
-parameter server is in pull mode; every other GEMM is a plain library call.
+parameter server is in pull mode.  On a GPU every layer is a ``[GELU ->] Linear [-> GELU]``
+link of :mod:`..ops.linear`: forward, dX and dW run on the repo's CTA-pair tcgen05 kernel with
+the activation and its derivative fused into the GEMM epilogues; on the CPU the same links
+are plain PyTorch.
 """
 from __future__ import annotations
 
@@ -13,6 +16,8 @@ from typing import Optional, Sequence
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+from ..ops import linear
 
 
 @dataclass
@@ -48,14 +53,15 @@ class MLP(nn.Module):
         return "layers.0.weight"
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        n = len(self.layers)
+        z, act = x, None  # pre-activation of the previous layer and gelu() of it
         for i, layer in enumerate(self.layers):
             if i == 0 and self.first_linear_fn is not None:
-                x = self.first_linear_fn(x, layer.weight, layer.bias)
+                z, act = self.first_linear_fn(x, layer.weight, layer.bias), None
             else:
-                x = layer(x)
-            if i + 1 < len(self.layers):
-                x = F.gelu(x, approximate="tanh")
-        return x
+                z, act = linear.link(z, act, layer.weight, layer.bias,
+                                     gelu_in=i > 0, gelu_out=i + 1 < n)
+        return z
 
 
 def mse_loss(out: torch.Tensor, target: torch.Tensor) -> torch.Tensor:

@@ -213,3 +213,51 @@ def gemm_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = N
         check(_lib.load().psb_gemm_bf16_tn(x.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(),
                                            M, N, K, _dt(out), _stream(x)), "psb_gemm_bf16_tn")
     return out
+
+
+_EPILOGUES = {None: _lib.EPI_NONE, "none": _lib.EPI_NONE, "gelu": _lib.EPI_GELU,
+              "dgelu": _lib.EPI_DGELU}
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bool = False,
+         bias: Optional[torch.Tensor] = None, epilogue: Optional[str] = None,
+         aux: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16,
+         out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``Y[M,N] = op(A) · op(B) (+ bias)`` on the CTA-pair tcgen05 kernel, no transposed copies.
+
+    ``trans_a``: A is stored ``[K,M]`` (else ``[M,K]``); ``trans_b``: B is stored ``[K,N]``
+    (else ``[N,K]``, i.e. a Linear weight).  ``epilogue="gelu"`` returns ``gelu(Z)`` and
+    writes ``Z = acc + bias`` (bf16) into ``aux`` when given; ``epilogue="dgelu"`` returns
+    ``acc * gelu'(aux)``.  (include/psb_kernels.h: psb_gemm_bf16)
+    """
+    _need_cuda(a, b, bias, out, aux)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
+        raise TypeError("gemm: operands must be bfloat16")
+    if a.dim() != 2 or b.dim() != 2 or not a.is_contiguous() or not b.is_contiguous():
+        raise ValueError("gemm: operands must be contiguous 2-D tensors")
+    K, M = (a.shape if trans_a else a.shape[::-1])
+    Kb, N = (b.shape if trans_b else b.shape[::-1])
+    if K != Kb:
+        raise ValueError(f"gemm: reduction sizes differ ({K} vs {Kb})")
+    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != N):
+        raise ValueError("gemm: bias must be float32 [N]")
+    epi = _EPILOGUES[epilogue]
+    if aux is not None and (aux.dtype != torch.bfloat16 or tuple(aux.shape) != (M, N)
+                            or not aux.is_contiguous()):
+        raise ValueError("gemm: aux must be a contiguous bfloat16 [M,N] tensor")
+    if epi == _lib.EPI_DGELU and aux is None:
+        raise ValueError("gemm: epilogue='dgelu' needs aux (the pre-activation)")
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    elif tuple(out.shape) != (M, N) or not out.is_contiguous():
+        raise ValueError("gemm: out must be a contiguous [M,N] tensor")
+    g = _lib.PsbGemm()
+    g.a, g.b, g.y, g.bias = a.data_ptr(), b.data_ptr(), out.data_ptr(), _ptr(bias)
+    g.aux_in = aux.data_ptr() if epi == _lib.EPI_DGELU else None
+    g.aux_out = aux.data_ptr() if (epi == _lib.EPI_GELU and aux is not None) else None
+    g.M, g.N, g.K = M, N, K
+    g.trans_a, g.trans_b = int(trans_a), int(trans_b)
+    g.out_dtype, g.epilogue = _dt(out), epi
+    with torch.cuda.device(a.device):
+        check(_lib.load().psb_gemm_bf16(C.byref(g), _stream(a)), "psb_gemm_bf16")
+    return out
