@@ -39,6 +39,8 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 // 16-byte peer loads from many threads are what fills NVLink — as in K1 / K2.
 constexpr int G_CHUNK = 8192;
 constexpr int G_WARPS = 6;
+constexpr int CLC_SLOTS = 4;   // responses in flight: the producer runs up to ~3 tiles ahead
+constexpr int CLC_OFF = 256;   // byte offset of the CLC ring inside the 512-byte barrier area
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -86,6 +88,45 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "}" ::"r"(smem_u32(bar)),
       "r"(parity)
       : "memory");
+}
+// ---- cluster launch control: a running cluster cancels the launch of a not-yet-started one and
+// takes over its tile.  The 16-byte response lands in BOTH CTAs' shared memory (multicast) and
+// completes 16 bytes on the barrier at the same offset in each of them.
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint64_t* bar, uint32_t cta, uint32_t bytes) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 rem;\n\t"
+      "mapa.shared::cluster.u32 rem, %0, %1;\n\t"
+      "mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [rem], %2;\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(cta), "r"(bytes)
+      : "memory");
+}
+__device__ __forceinline__ void clc_try_cancel(void* response, uint64_t* bar) {
+  asm volatile(
+      "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes"
+      ".multicast::cluster::all.b128 [%0], [%1];" ::"r"(smem_u32(response)),
+      "r"(smem_u32(bar))
+      : "memory");
+}
+// returns the x index of the first CTA of the cancelled cluster, or -1 when nothing was left
+__device__ __forceinline__ int clc_read(const void* response) {
+  uint32_t x, valid;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p1;\n\t"
+      ".reg .b128 r;\n\t"
+      "ld.shared.b128 r, [%2];\n\t"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n\t"
+      "selp.u32 %1, 1, 0, p1;\n\t"
+      "mov.u32 %0, 0;\n\t"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, _, _, _}, r;\n\t"
+      "}"
+      : "=r"(x), "=r"(valid)
+      : "r"(smem_u32(response))
+      : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  return valid ? (int)x : -1;
 }
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async;" ::: "memory");
@@ -226,6 +267,7 @@ struct Params {
   const uint32_t* version_pad;
   const uint32_t* epoch;
   int skip_wait;
+  int clc;                       // tiles come from cluster launch control (grid = one pair per tile)
   int a_mn, b_mn;                // operand is MN-major (stored [K, M] / [K, N] row-major)
   const __nv_bfloat16* aux_in;   // EPI_DGELU: pre-activation Z [M, N]
   __nv_bfloat16* aux_out;        // EPI_GELU: where Z goes (optional)
@@ -326,6 +368,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   uint64_t* tmem_full = empty + STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint8_t* clc_resp = smem + STAGES * STAGE_BYTES + CLC_OFF;  // CLC_SLOTS x 16 bytes
+  uint64_t* clc_full = reinterpret_cast<uint64_t*>(clc_resp + CLC_SLOTS * 16);
+  uint64_t* clc_empty = clc_full + CLC_SLOTS;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -350,6 +395,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       mbar_init(&tmem_full[i], 1);   // one multicast commit
       mbar_init(&tmem_empty[i], 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's copy
     }
+    for (int i = 0; i < CLC_SLOTS; ++i) {
+      mbar_init(&clc_full[i], 1);    // the issuer's expect_tx; the response completes the bytes
+      mbar_init(&clc_empty[i], 10);  // readers besides the issuer: MMA, 2 x 4 epilogue warps, peer producer
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
   }
@@ -367,6 +416,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int num_k = (p.K + BK - 1) / BK;
   const int first = cluster_id - gather_clusters;
   const int step = num_clusters - gather_clusters;
+  // Tile walk.  Static: t = first, first + step, ...  CLC (plain GEMM): the grid has one cluster
+  // per tile, a cluster starts on its own tile and then takes over the tiles of clusters whose
+  // launch it cancels, so the kernel neither waits for SMs that another stream's kernel holds
+  // nor leaves a tail when some clusters start late.
+  auto clc_next = [&](int slot, uint32_t phase) -> int {
+    mbar_wait(&clc_full[slot], phase);
+    const int x = clc_read(clc_resp + slot * 16);
+    return x < 0 ? num_tiles : (x >> 1);
+  };
   // Tile order: regions of N-tiles by owner (the locally owned slice first, so the gather of the
   // next owner's slice overlaps the math on this one); inside a region tiles are walked in
   // groups of kGroupM row-blocks so that one wave of 74 clusters touches ~8 A panels and ~9 W
@@ -394,7 +452,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       uint32_t phase = 0;
       const int n_per_rank = p.fused ? num_n / p.world : 0;
       const uint32_t chunks_per_tile = p.fused ? (uint32_t)((size_t)BN * p.K * 2 / G_CHUNK) : 0;
-      for (int t = first; t < num_tiles; t += step) {
+      int cs = 0, issued = 0;
+      uint32_t cph = 0;
+      auto clc_issue = [&](int q) {  // leader only: query number q goes to slot q % CLC_SLOTS
+        const int slot = q % CLC_SLOTS;
+        mbar_wait(&clc_empty[slot], ((uint32_t)(q / CLC_SLOTS) & 1u) ^ 1u);
+        mbar_expect_tx(&clc_full[slot], 16);
+        mbar_expect_tx_cluster(&clc_full[slot], 1, 16);
+        clc_try_cancel(clc_resp + slot * 16, &clc_full[slot]);
+      };
+      if (p.clc && cta == 0) clc_issue(0);
+      for (int t = first; t < num_tiles;) {
+        int t_next = t + step;
+        if (p.clc) {
+          // the answer asked for one tile ago; a new query only after a successful one
+          t_next = clc_next(cs, cph);
+          if (cta != 0) mbar_arrive_cluster(&clc_empty[cs], 0);
+          if (++cs == CLC_SLOTS) cs = 0, cph ^= 1;
+          if (cta == 0 && t_next < num_tiles) clc_issue(++issued);
+        }
         int m_blk, n_blk;
         decode(t, m_blk, n_blk);
         if (p.fused && n_blk / n_per_rank != p.rank) {
@@ -422,6 +498,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
           }
           if (++stage == STAGES) stage = 0, phase ^= 1;
         }
+        t = t_next;
       }
     }
   } else if (warp == 1) {
@@ -433,7 +510,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       const uint32_t idesc = kInstrDesc | (p.a_mn ? 1u << 15 : 0u) | (p.b_mn ? 1u << 16 : 0u);
       const uint32_t step_a = p.a_mn ? kDescStepMN : kDescStepK;
       const uint32_t step_b = p.b_mn ? kDescStepMN : kDescStepK;
-      for (int t = first; t < num_tiles; t += step, ++it) {
+      int cs = 0;
+      uint32_t cph = 0;
+      for (int t = first; t < num_tiles; ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -453,13 +532,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
           if (++stage == STAGES) stage = 0, phase ^= 1;
         }
         umma2_commit_mc(&tmem_full[acc]);  // accumulator ready in both CTAs
+        if (p.clc) {
+          t = clc_next(cs, cph);
+          mbar_arrive_cluster(&clc_empty[cs], 0);
+          if (++cs == CLC_SLOTS) cs = 0, cph ^= 1;
+        } else {
+          t += step;
+        }
       }
     }
   } else {
     // ===================== epilogue (warps 2..5 of each CTA) =====================
     const int quarter = warp & 3;
     int it = 0;
-    for (int t = first; t < num_tiles; t += step, ++it) {
+    int cs = 0;
+    uint32_t cph = 0;
+    for (int t = first; t < num_tiles; ++it) {
       int m_blk, n_blk;
       decode(t, m_blk, n_blk);
       const int acc = it & 1;
@@ -546,6 +634,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tmem_empty[acc], 0);  // leader's barrier
+      if (p.clc) {
+        t = clc_next(cs, cph);
+        __syncwarp();  // every lane has read the response before the slot is handed back
+        if (lane == 0) mbar_arrive_cluster(&clc_empty[cs], 0);
+        if (++cs == CLC_SLOTS) cs = 0, cph ^= 1;
+      } else {
+        t += step;
+      }
     }
   }
 
@@ -624,20 +720,33 @@ static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const 
   return 0;
 }
 
+// PSB_GEMM_SCHED=static keeps the persistent static tile walk for plain GEMMs as well
+static bool clc_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("PSB_GEMM_SCHED");
+    return !(e && e[0] == 's');
+  }();
+  return on;
+}
+
 static int launch(const void* a, const void* b, const Params& p, int epi, cudaStream_t s) {
   CUtensorMap map_a, map_b;
   if (int rc = p.a_mn ? make_map_mn(&map_a, a, p.K, p.M) : make_map(&map_a, a, p.M, p.K)) return rc;
   if (int rc = p.b_mn ? make_map_mn(&map_b, b, p.K, p.N) : make_map(&map_b, b, p.N, p.K)) return rc;
   const int num_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
   int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
+  Params q = p;
   if (p.fused) {
     clusters = kNumSMs / 2;
     if (num_tiles + p.gather_ctas / 2 < clusters) clusters = num_tiles + p.gather_ctas / 2;
+  } else if (clc_enabled()) {
+    q.clc = 1;
+    clusters = num_tiles;  // one pair per tile; running pairs cancel and absorb the rest
   }
   switch (epi) {
-    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, p, clusters, s);
-    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, p, clusters, s);
-    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, p, clusters, s);
+    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, q, clusters, s);
+    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, q, clusters, s);
+    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, q, clusters, s);
   }
   PSB_REQUIRE(false, PSB_EINVAL, "gemm: unknown epilogue %d", epi);
   return 0;

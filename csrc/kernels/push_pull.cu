@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
     if ((threadIdx.x & 31) == 0) warp_part[threadIdx.x >> 5] = sumsq;
     __syncthreads();
     if (threadIdx.x < 32) {
-      float w = threadIdx.x < kPushThreads / 32 ? warp_part[threadIdx.x] : 0.f;
+      float w = threadIdx.x < (blockDim.x >> 5) ? warp_part[threadIdx.x] : 0.f;
       w = warp_sum(w);
       if (threadIdx.x == 0 && a.sumsq_acc) atomicAdd(a.sumsq_acc, w);
     }
@@ -444,6 +444,7 @@ static int check_fabric(const PsbFabric& f, const char* who) {
 
 template <int KIND, int GDT>
 static void launch_push(const PsbPush& a, int grid, cudaStream_t s) {
+  const int kPushThreads = a.block > 0 ? a.block : psb::kPushThreads;
   switch (a.fabric.world) {
     case 1: push_fused_kernel<KIND, GDT, 1><<<grid, kPushThreads, 0, s>>>(a); break;
     case 2: push_fused_kernel<KIND, GDT, 2><<<grid, kPushThreads, 0, s>>>(a); break;
@@ -496,11 +497,15 @@ int psb_push_fused(const PsbPush* args, psb_stream_t stream) {
 
   if ((a.flags & PSB_PUSH_TMA) && !reduce_only && !from_reduced)
     return push_fused_tma_dispatch(a, (cudaStream_t)stream);
+  PSB_REQUIRE(a.block == 0 || (a.block % 32 == 0 && a.block >= 64 && a.block <= kPushThreads),
+              PSB_EINVAL, "psb_push_fused: block=%d must be a multiple of 32 in [64, %d]", a.block,
+              kPushThreads);
   const size_t nvec = a.slice_elems / 8;
   int grid = a.grid;
   if (grid <= 0) {
     // enough CTAs to keep ~2 MB in flight over NVLink, never more than one wave
-    size_t want = (nvec + kPushThreads * 2 - 1) / (kPushThreads * 2);
+    const size_t per_cta = (size_t)(a.block > 0 ? a.block : kPushThreads) * 2;
+    size_t want = (nvec + per_cta - 1) / per_cta;
     grid = (int)(want < 1 ? 1 : (want > (size_t)kNumSMs ? kNumSMs : want));
   }
   cudaStream_t s = (cudaStream_t)stream;

@@ -235,6 +235,9 @@ typedef struct PsbPush {
   int32_t grid;                     // CTAs (0 = auto)
   PsbOptim opt;
   const uint64_t* grad_off;         // optional device array [world]: byte offset added to grad[w]
+  int32_t block;                    // threads per CTA of the register-path kernel (0 = 512).  256
+                                    // lets a K1 CTA share an SM with a CTA of the tcgen05 GEMM
+                                    // (32 K + 24 K registers), so an overlapped push really overlaps
                                     // (which slot of the worker's gradient ring to read)
 } PsbPush;
 int psb_push_fused(const PsbPush* args, psb_stream_t stream);

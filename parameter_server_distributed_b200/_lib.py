@@ -59,7 +59,8 @@ class PsbPush(C.Structure):
                 ("slice_elems", C.c_uint64), ("bucket", C.c_int32), ("grad_dtype", C.c_int32),
                 ("epoch", C.c_void_p), ("step", C.c_void_p), ("clip_coef", C.c_void_p),
                 ("peer_mask", C.c_void_p), ("done_counter", C.c_void_p), ("flags", C.c_int32),
-                ("grid", C.c_int32), ("opt", PsbOptim), ("grad_off", C.c_void_p)]
+                ("grid", C.c_int32), ("opt", PsbOptim), ("grad_off", C.c_void_p),
+                ("block", C.c_int32)]
 
 
 class PsbPull(C.Structure):

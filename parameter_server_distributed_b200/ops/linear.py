@@ -49,6 +49,20 @@ def _dgelu(z: torch.Tensor) -> torch.Tensor:
     return 0.5 * (1 + t) + 0.5 * z * (1 - t * t) * k0 * (1 + 3 * k1 * z * z)
 
 
+def grad_to_sink(sink, produce):
+    """Run ``produce(out)``; with a sink the result goes into the gradient bucket, is committed
+    and ``None`` is returned to autograd, otherwise a fresh tensor is returned.
+
+    The commit may queue the push of the bucket, which updates the parameters IN PLACE on the
+    push stream: call this only after every kernel of the layer that reads the parameter (the
+    dX GEMM) has been queued on the current stream."""
+    if sink is None:
+        return produce(None)
+    produce(sink.view())
+    sink.commit()
+    return None
+
+
 class _LinkFn(torch.autograd.Function):
     """``(z_in, act_in, W, b) -> (z_out, act_out)``.
 
@@ -78,18 +92,26 @@ class _LinkFn(torch.autograd.Function):
         ctx.save_for_backward(a2d, w, z_in2d if gelu_in else None)
         ctx.gelu_in = gelu_in
         ctx.has_bias = bias is not None
+        # parameter-server gradient sinks (parallel/engine.py: GradSink), if the engine set them
+        ctx.sink_w = getattr(weight, "_psb_sink", None)
+        ctx.sink_b = getattr(bias, "_psb_sink", None) if bias is not None else None
         ctx.in_shape = z_in.shape
         ctx.mark_non_differentiable(act_out)
+        ctx.set_materialize_grads(False)  # no zero tensor for the gradient of act_out
         lead = z_in.shape[:-1]
         return z_out.view(*lead, n_out), (act_out.view(*lead, n_out) if gelu_out else act_out)
 
     @staticmethod
     def backward(ctx, gz, _g_act):
+        if gz is None:
+            return None, None, None, None, None, None
         a2d, w, z_in2d = ctx.saved_tensors
         gz2d = gz.reshape(-1, gz.shape[-1])
         if not gz2d.is_contiguous():
             gz2d = gz2d.contiguous()
         g_in = g_w = g_b = None
+        # dX first: committing a parameter gradient may start the push that rewrites W in place,
+        # so every reader of W on this stream has to be queued before the commit
         if ctx.needs_input_grad[0]:
             if ctx.gelu_in:
                 zc = z_in2d if z_in2d.is_contiguous() else z_in2d.contiguous()
@@ -97,10 +119,12 @@ class _LinkFn(torch.autograd.Function):
             else:
                 g_in = native.gemm(gz2d, w, trans_b=True)
             g_in = g_in.view(ctx.in_shape)
-        if ctx.needs_input_grad[2]:
-            g_w = native.gemm(gz2d, a2d, trans_a=True, trans_b=True)
+        # with a sink the parameter gradients land in the gradient bucket: no staging copy
         if ctx.has_bias and ctx.needs_input_grad[3]:
-            g_b = gz2d.sum(0)
+            g_b = grad_to_sink(ctx.sink_b, lambda out: torch.sum(gz2d, 0, out=out))
+        if ctx.needs_input_grad[2]:
+            g_w = grad_to_sink(ctx.sink_w, lambda out: native.gemm(
+                gz2d, a2d, trans_a=True, trans_b=True, out=out))
         return g_in, None, g_w, g_b, None, None
 
 

@@ -136,8 +136,9 @@ class DeviceBackend:
              no_wait: bool = False, masked: bool = False, clip: bool = False,
              seqlock: bool = False, mask_ptr: Optional[int] = None,
              grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None,
-             tma: Optional[bool] = None, grid: Optional[int] = None) -> None:
-        """K1 on the current stream."""
+             tma: Optional[bool] = None, grid: Optional[int] = None, block: int = 0) -> None:
+        """K1 on the current stream.  ``block``: threads per CTA of the register-path kernel
+        (0 = 512; 256 shares an SM with a tcgen05 GEMM CTA)."""
         a = self._push_args[b]
         bc = self.broadcast if broadcast is None else broadcast
         flags = _lib.PUSH_BROADCAST if bc else 0
@@ -148,6 +149,7 @@ class DeviceBackend:
         a.grid = self.push_grid if grid is None else grid
         a.peer_mask = mask_ptr if mask_ptr is not None else self.peer_mask.data_ptr()
         a.grad_off = grad_off_ptr
+        a.block = block
         if reduce_only:
             flags |= _lib.PUSH_REDUCE_ONLY
         if from_reduced:

@@ -16,6 +16,8 @@ src/parameter_server.cpp:18-91) happens here inside one process per GPU:
 """
 from __future__ import annotations
 
+import os
+
 from typing import Dict, Iterable, List, Optional, Sequence, Tuple
 
 import torch
@@ -24,6 +26,25 @@ from ..ops import native
 from ..ops.native import OptimConfig
 from ..utils.tracing import Metrics, nvtx_range
 from .buckets import BucketPlan, ParamSlot, plan_buckets
+
+
+class GradSink:
+    """Where a layer may write one parameter's gradient itself (attribute ``_psb_sink`` of the
+    parameter).  ``view()`` is the parameter-shaped window of the gradient bucket, ``commit()``
+    tells the engine that the kernel producing it is queued on the current stream; the layer
+    then returns ``None`` as that parameter's gradient so autograd does not deliver it twice."""
+
+    __slots__ = ("ps", "slot")
+
+    def __init__(self, ps: "ShardedParameterServer", slot: ParamSlot):
+        self.ps, self.slot = ps, slot
+
+    def view(self) -> torch.Tensor:
+        s = self.slot
+        return self.ps.backend.grad_bucket(s.bucket)[s.offset:s.offset + s.numel].view(s.shape)
+
+    def commit(self) -> None:
+        self.ps._arrive(self.slot, None)
 
 
 class ShardedParameterServer:
@@ -125,6 +146,16 @@ class ShardedParameterServer:
         self._hooks = []
         for name, p in named_params:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(name)))
+        # gradient sinks: layers that know about them (ops/linear.py) write dW / db straight into
+        # the bucket and report it the moment the GEMM is queued, before their dX GEMM, so the
+        # push of that bucket starts one GEMM earlier and no staging copy is made
+        self._sinks: List[GradSink] = []
+        if self._sinks_supported():
+            for name, p in named_params:
+                if name not in self._nhwc:
+                    p._psb_sink = GradSink(self, self.plan.slots[name])
+                    self._sinks.append(p._psb_sink)
+        self._sink_params = [p for _, p in named_params if hasattr(p, "_psb_sink")]
         self.steps_done = 0
         self.metrics = Metrics()
 
@@ -149,12 +180,24 @@ class ShardedParameterServer:
 
         def hook(p: torch.nn.Parameter):
             g = p.grad
+            if g is None:
+                return  # the layer delivered this gradient through the sink (autograd still
+                        # runs the hook when a backward function returns None)
             p.grad = None
-            self._pending[slot.bucket].append((slot, g))
-            if len(self._pending[slot.bucket]) == len(self.plan.buckets[slot.bucket].slots):
-                self._flush(slot.bucket)
+            self._arrive(slot, g)
 
         return hook
+
+    def _arrive(self, slot: ParamSlot, g: Optional[torch.Tensor]) -> None:
+        """One parameter's gradient is ready (``g is None``: already written in the bucket)."""
+        self._pending[slot.bucket].append((slot, g))
+        if len(self._pending[slot.bucket]) == len(self.plan.buckets[slot.bucket].slots):
+            self._flush(slot.bucket)
+
+    def _sinks_supported(self) -> bool:
+        """In-place gradient buckets need the bucket to be free for the whole backward pass:
+        true for the synchronous engine (``step`` joins the push stream before the next forward)."""
+        return type(self) is ShardedParameterServer
 
     # ------------------------------------------------------------------ per-bucket push
     def _stage(self, b: int) -> None:
@@ -162,11 +205,17 @@ class ShardedParameterServer:
         be = self.backend
         pend = self._pending[b]
         bucket = be.grad_bucket(b)
-        if len(pend) < len(self.plan.buckets[b].slots):
-            bucket.zero_()
+        slots = self.plan.buckets[b].slots
+        if len(pend) < len(slots):  # parameters that took no part in this backward pass
+            have = {s.name for s, _ in pend}
+            for s in slots:
+                if s.name not in have:
+                    bucket[s.offset:s.offset + s.numel].zero_()
+        pend = [(s, g) for s, g in pend if g is not None]  # None: written in place by a sink
         if self.is_cuda:
-            native.gather_to_bucket([self._flat_grad(s, g) for s, g in pend], bucket,
-                                    [s.offset for s, _ in pend])
+            if pend:
+                native.gather_to_bucket([self._flat_grad(s, g) for s, g in pend], bucket,
+                                        [s.offset for s, _ in pend])
         else:
             for s, g in pend:
                 bucket[s.offset:s.offset + s.numel].copy_(self._flat_grad(s, g).reshape(-1))
@@ -193,7 +242,11 @@ class ShardedParameterServer:
         last = b == len(self.plan.buckets) - 1
         if self.world > 1 and self.overlap and not last and self.clip_norm is None:
             return {"tma": True, "grid": self._user_grid or self.overlap_grid}
-        return {"tma": False, "grid": self._user_grid}
+        # register-path kernel, 512 threads per CTA.  (Measured on B200, 1 GPU, MLP step: 256-thread
+        # CTAs that share the SMs with the tcgen05 GEMM cost 0.08-0.15 ms per step more than
+        # 512-thread CTAs that take turns with it — profiles/overlap_matrix_1gpu.txt.)
+        block = int(os.environ.get("PSB_PUSH_BLOCK", "0"))  # experiment knob
+        return {"tma": False, "grid": self._user_grid, "block": block}
 
     def _flush(self, b: int) -> None:
         self._stage(b)
@@ -333,3 +386,7 @@ class ShardedParameterServer:
         for h in self._hooks:
             h.remove()
         self._hooks = []
+        for p in self._sink_params:
+            if hasattr(p, "_psb_sink"):
+                del p._psb_sink
+        self._sink_params = []

@@ -15,6 +15,7 @@ import torch
 
 from .. import _lib
 from .._lib import PsbGemmAG, check
+from ..ops import linear, native
 
 
 class FusedFirstLinear:
@@ -83,6 +84,8 @@ class _FusedLinearFn(torch.autograd.Function):
         y = op.launch(x2d, bias_f32)
         ctx.save_for_backward(x2d, weight)
         ctx.has_bias = bias is not None
+        ctx.sink_w = getattr(weight, "_psb_sink", None)
+        ctx.sink_b = getattr(bias, "_psb_sink", None) if bias is not None else None
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], weight.shape[0])
 
@@ -90,11 +93,18 @@ class _FusedLinearFn(torch.autograd.Function):
     def backward(ctx, gy):
         x2d, weight = ctx.saved_tensors
         gy2d = gy.reshape(-1, gy.shape[-1])
+        if not gy2d.is_contiguous():
+            gy2d = gy2d.contiguous()
         gx = gw = gb = None
-        if ctx.needs_input_grad[0]:
-            gx = (gy2d @ weight).view(ctx.x_shape)
-        if ctx.needs_input_grad[1]:
-            gw = gy2d.t() @ x2d
+        own = linear.supported(gy2d, weight)  # dW / dX on the tcgen05 kernel, in place
+        if ctx.needs_input_grad[0]:  # readers of W before any commit (see grad_to_sink)
+            gx = (native.gemm(gy2d, weight, trans_b=True) if own else gy2d @ weight).view(ctx.x_shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = gy2d.sum(0)
+            gb = linear.grad_to_sink(ctx.sink_b, lambda out: torch.sum(gy2d, 0, out=out))
+        if ctx.needs_input_grad[1]:
+            if own:
+                gw = linear.grad_to_sink(ctx.sink_w, lambda out: native.gemm(
+                    gy2d, x2d, trans_a=True, trans_b=True, out=out))
+            else:
+                gw = gy2d.t() @ x2d
         return gx, gw, gb, None

@@ -153,3 +153,64 @@ def test_engine_metrics_and_prometheus_text():
     assert snap["nvlink_in_bytes"] == 0  # one rank: nothing crosses a link
     text = ps.metrics.prometheus()
     assert "# TYPE psb_steps counter" in text and "psb_pushes " in text
+
+
+class _SinkLinear(torch.autograd.Function):
+    """A layer that uses the engine's gradient sinks the way ops/linear.py does on the GPU:
+    parameter gradients are written into the bucket and committed after dX is computed."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        from parameter_server_distributed_b200.ops.linear import grad_to_sink  # noqa: F401
+        ctx.save_for_backward(x, w)
+        ctx.set_materialize_grads(False)
+        ctx.sinks = (getattr(w, "_psb_sink", None), getattr(b, "_psb_sink", None))
+        return x @ w.t() + b
+
+    @staticmethod
+    def backward(ctx, gy):
+        from parameter_server_distributed_b200.ops.linear import grad_to_sink
+        x, w = ctx.saved_tensors
+        sw, sb = ctx.sinks
+        gx = gy @ w  # before the commits: a commit may start the in-place update of w
+        gb = grad_to_sink(sb, lambda out: torch.sum(gy, 0, out=out))
+        gw = grad_to_sink(sw, lambda out: torch.mm(gy.t(), x, out=out))
+        return gx, gw, gb
+
+
+class _SinkMLP(torch.nn.Module):
+    def __init__(self, base: MLP):
+        super().__init__()
+        self.layers = base.layers
+
+    def forward(self, x):
+        for i, layer in enumerate(self.layers):
+            x = _SinkLinear.apply(x, layer.weight, layer.bias)
+            if i + 1 < len(self.layers):
+                x = torch.nn.functional.gelu(x, approximate="tanh")
+        return x
+
+
+def test_gradient_sinks_push_once_per_bucket_and_match_torch():
+    torch.manual_seed(5)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind="sgd", lr=0.05),
+                                bucket_mb=0.005)
+    assert all(hasattr(p, "_psb_sink") for p in m.parameters())
+    sm = _SinkMLP(m)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    nb = len(ps.plan.buckets)
+    for it in range(3):
+        x, y = torch.randn(16, 32), torch.randn(16, 8)
+        mse_loss(sm(x), y).backward()
+        assert all(p.grad is None for p in m.parameters())  # delivered through the sinks
+        ps.step()
+        assert ps.metrics.counters["pushes"] == nb * (it + 1)
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        opt.step()
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+    ps.close()
+    assert not any(hasattr(p, "_psb_sink") for p in m.parameters())
