@@ -94,6 +94,19 @@ __device__ __forceinline__ float4 ld_stream_f4(const float* p) {
   return make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
                      __uint_as_float(r.w));
 }
+// 256-bit accesses (sm_100: LDG.E.256 / STG.E.256), p 32-byte aligned.  One instruction per
+// 8 floats: a warp covers whole 32-byte sectors instead of two half-sector passes.
+__device__ __forceinline__ void ld_stream_f8(const float* p, float f[8]) {
+  asm volatile("ld.global.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(f[0]), "=f"(f[1]), "=f"(f[2]), "=f"(f[3]), "=f"(f[4]), "=f"(f[5]), "=f"(f[6]),
+                 "=f"(f[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void st_stream_f8(float* p, const float f[8]) {
+  asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p),
+               "f"(f[0]), "f"(f[1]), "f"(f[2]), "f"(f[3]), "f"(f[4]), "f"(f[5]), "f"(f[6]), "f"(f[7])
+               : "memory");
+}
 __device__ __forceinline__ void st_stream_f4(float* p, const float4& v) {
   st_stream_16(p, make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z),
                              __float_as_uint(v.w)));

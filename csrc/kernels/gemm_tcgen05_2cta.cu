@@ -267,6 +267,7 @@ struct Params {
   const uint32_t* version_pad;
   const uint32_t* epoch;
   int skip_wait;
+  int bias_bf16;                 // `bias` points at bf16 values
   int clc;                       // tiles come from cluster launch control (grid = one pair per tile)
   int a_mn, b_mn;                // operand is MN-major (stored [K, M] / [K, N] row-major)
   const __nv_bfloat16* aux_in;   // EPI_DGELU: pre-activation Z [M, N]
@@ -567,9 +568,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
 #pragma unroll
           for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(r[k]);
           if (p.bias) {
+            if (p.bias_bf16) {
+              const __nv_bfloat16* bb = reinterpret_cast<const __nv_bfloat16*>(p.bias);
 #pragma unroll
-            for (int k = 0; k < 32; ++k)
-              if (col0 + k < p.N) f[k] += __ldg(p.bias + col0 + k);
+              for (int k = 0; k < 32; ++k)
+                if (col0 + k < p.N) f[k] += __bfloat162float(bb[col0 + k]);
+            } else {
+#pragma unroll
+              for (int k = 0; k < 32; ++k)
+                if (col0 + k < p.N) f[k] += __ldg(p.bias + col0 + k);
+            }
           }
           const bool full_cols = col0 + 32 <= p.N;
           if constexpr (EPI == EPI_GELU) {
@@ -798,7 +806,10 @@ extern "C" int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream) {
   PSB_REQUIRE(g->epilogue != PSB_EPI_DGELU || g->aux_in, PSB_EINVAL,
               "psb_gemm_bf16: the dGELU epilogue needs the pre-activation in aux_in");
   Params p{};
-  p.y = g->y, p.bias = g->bias, p.M = g->M, p.N = g->N, p.K = g->K, p.out_dtype = g->out_dtype;
+  PSB_REQUIRE(g->bias_dtype == PSB_F32 || g->bias_dtype == PSB_BF16, PSB_EINVAL,
+              "psb_gemm_bf16: bad bias dtype %d", g->bias_dtype);
+  p.bias_bf16 = g->bias_dtype == PSB_BF16;
+  p.y = g->y, p.bias = reinterpret_cast<const float*>(g->bias), p.M = g->M, p.N = g->N, p.K = g->K, p.out_dtype = g->out_dtype;
   p.a_mn = g->trans_a != 0, p.b_mn = g->trans_b != 0;
   p.aux_in = reinterpret_cast<const __nv_bfloat16*>(g->aux_in);
   p.aux_out = reinterpret_cast<__nv_bfloat16*>(g->aux_out);

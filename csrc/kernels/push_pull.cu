@@ -50,14 +50,8 @@ struct GradVec<PSB_F32> {
   }
 };
 
-__device__ __forceinline__ void load8(const float* p, float f[8]) {
-  float4 a = ld_stream_f4(p), b = ld_stream_f4(p + 4);
-  f[0] = a.x, f[1] = a.y, f[2] = a.z, f[3] = a.w, f[4] = b.x, f[5] = b.y, f[6] = b.z, f[7] = b.w;
-}
-__device__ __forceinline__ void store8(float* p, const float f[8]) {
-  st_stream_f4(p, make_float4(f[0], f[1], f[2], f[3]));
-  st_stream_f4(p + 4, make_float4(f[4], f[5], f[6], f[7]));
-}
+__device__ __forceinline__ void load8(const float* p, float f[8]) { ld_stream_f8(p, f); }
+__device__ __forceinline__ void store8(float* p, const float f[8]) { st_stream_f8(p, f); }
 
 // ------------------------------------------------------------------------------------
 // K1.  WORLD > 0: compile-time peer count (fully unrolled peer loads); WORLD == 0: dynamic.
@@ -67,7 +61,9 @@ __device__ __forceinline__ void store8(float* p, const float f[8]) {
 template <int KIND, int GDT, int WORLD>
 __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPush a) {
   constexpr int MAXW = WORLD > 0 ? WORLD : PSB_MAX_PEERS;
-  constexpr int U = (GDT == PSB_BF16 && MAXW <= 4) ? 2 : 1;
+  constexpr int U = GDT != PSB_BF16 ? 1
+                    : (KIND == PSB_OPT_SGD && MAXW <= 2) ? 4
+                    : MAXW <= 4 ? 2 : 1;
   const int rank = a.fabric.rank;
   const int world = WORLD > 0 ? WORLD : a.fabric.world;
   const int flags = a.flags;
@@ -145,14 +141,23 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
       continue;
     }
 
+    // state of every in-flight vector is requested before the first update
+    float ps[U][8], ms[U][8] = {}, vs[U][8] = {};
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!valid[u]) continue;
+      const size_t le = (i0 + u * stride) * 8;
+      load8(a.master + le, ps[u]);
+      if constexpr (KIND != PSB_OPT_SGD) load8(a.m + le, ms[u]);
+      if constexpr (KIND == PSB_OPT_ADAM || KIND == PSB_OPT_ADAMW) load8(a.v + le, vs[u]);
+    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (!valid[u]) continue;
       const size_t le = (i0 + u * stride) * 8;  // element inside my slice
-      float p[8], mm[8] = {}, vv[8] = {};
-      load8(a.master + le, p);
-      if constexpr (KIND != PSB_OPT_SGD) load8(a.m + le, mm);
-      if constexpr (KIND == PSB_OPT_ADAM || KIND == PSB_OPT_ADAMW) load8(a.v + le, vv);
+      float(&p)[8] = ps[u];
+      float(&mm)[8] = ms[u];
+      float(&vv)[8] = vs[u];
 #pragma unroll
       for (int k = 0; k < 8; ++k) update1<KIND>(c, p[k], mm[k], vv[k], g[u][k] * clip);
       store8(a.master + le, p);
@@ -497,6 +502,8 @@ int psb_push_fused(const PsbPush* args, psb_stream_t stream) {
 
   if ((a.flags & PSB_PUSH_TMA) && !reduce_only && !from_reduced)
     return push_fused_tma_dispatch(a, (cudaStream_t)stream);
+  PSB_REQUIRE((((uintptr_t)a.master | (uintptr_t)a.m | (uintptr_t)a.v | (uintptr_t)a.reduced) & 31) == 0,
+              PSB_EINVAL, "psb_push_fused: master / m / v / reduced must be 32-byte aligned");
   PSB_REQUIRE(a.block == 0 || (a.block % 32 == 0 && a.block >= 64 && a.block <= kPushThreads),
               PSB_EINVAL, "psb_push_fused: block=%d must be a multiple of 32 in [64, %d]", a.block,
               kPushThreads);

@@ -71,8 +71,7 @@ __device__ __forceinline__ void lds8f(const float* p, float f[8]) {
   f[6] = __uint_as_float(b.z), f[7] = __uint_as_float(b.w);
 }
 __device__ __forceinline__ void stg8f(float* p, const float f[8]) {
-  st_stream_f4(p, make_float4(f[0], f[1], f[2], f[3]));
-  st_stream_f4(p + 4, make_float4(f[4], f[5], f[6], f[7]));
+  st_stream_f8(p, f);
 }
 
 // Stage layout: [grad of peer 0 .. world-1][master][m][v], each kChunk elements.

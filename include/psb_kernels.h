@@ -349,15 +349,34 @@ typedef struct PsbGemm {
   const void* a;
   const void* b;
   void* y;             // [M,N] row-major, out_dtype
-  const float* bias;   // optional [N] fp32
+  const void* bias;    // optional [N], fp32 or bf16 (bias_dtype)
   const void* aux_in;  // PSB_EPI_DGELU: Z [M,N] bf16
   void* aux_out;       // PSB_EPI_GELU: Z [M,N] bf16 (optional)
   int32_t M, N, K;
   int32_t trans_a, trans_b;
   int32_t out_dtype;   // PSB_BF16 / PSB_F32
   int32_t epilogue;
+  int32_t bias_dtype;  // PSB_F32 (0, default) or PSB_BF16: element type behind `bias`
 } PsbGemm;
 int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream);
+
+// ---------------------------------------------------------------------------
+// Memory-bound pieces of the training step between the GEMMs (train_ops.cu).
+// psb_colsum_bf16: out[n] = sum_m x[m,n] (bias gradient), x bf16 [M,N], fp32 accumulation in a
+//   fixed order; scratch of psb_colsum_scratch_bytes(M,N) bytes, zero-filled before first use
+//   (it holds arrival counters that the kernel leaves at zero), one launch in flight per scratch.
+// psb_mse_fwd_bf16 / psb_mse_bwd_bf16: loss = mean((a-b)^2) and da = 2(a-b)/n * (*gout);
+//   scratch of PSB_MSE_SCRATCH_FLOATS floats, zero-filled before first use.
+// ---------------------------------------------------------------------------
+#define PSB_MSE_SCRATCH_FLOATS 304
+int psb_colsum_slabs(int M, int N);
+size_t psb_colsum_scratch_bytes(int M, int N);
+int psb_colsum_bf16(const void* x, void* out, int out_dtype, int M, int N, void* scratch,
+                    psb_stream_t stream);
+int psb_mse_fwd_bf16(const void* a, const void* b, size_t n, float* scratch, float* loss,
+                     psb_stream_t stream);
+int psb_mse_bwd_bf16(const void* a, const void* b, const float* gout, size_t n, void* da,
+                     psb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -89,7 +89,8 @@ class PsbGemm(C.Structure):
     _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("y", C.c_void_p), ("bias", C.c_void_p),
                 ("aux_in", C.c_void_p), ("aux_out", C.c_void_p), ("M", C.c_int32),
                 ("N", C.c_int32), ("K", C.c_int32), ("trans_a", C.c_int32),
-                ("trans_b", C.c_int32), ("out_dtype", C.c_int32), ("epilogue", C.c_int32)]
+                ("trans_b", C.c_int32), ("out_dtype", C.c_int32), ("epilogue", C.c_int32),
+                ("bias_dtype", C.c_int32)]
 
 
 class PsbError(RuntimeError):
@@ -150,6 +151,10 @@ def _declare(lib) -> None:
         "psb_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),
         "psb_gemm_allgather_bf16": (i32, [C.POINTER(PsbGemmAG), vp]),
         "psb_gemm_bf16": (i32, [C.POINTER(PsbGemm), vp]),
+        "psb_colsum_scratch_bytes": (sz, [i32, i32]),
+        "psb_colsum_bf16": (i32, [vp, vp, i32, i32, i32, vp, vp]),
+        "psb_mse_fwd_bf16": (i32, [vp, vp, sz, vp, vp, vp]),
+        "psb_mse_bwd_bf16": (i32, [vp, vp, vp, sz, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -17,7 +17,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from ..ops import linear
+from ..ops import linear, native
 
 
 @dataclass
@@ -64,5 +64,23 @@ class MLP(nn.Module):
         return z
 
 
+class _MseFn(torch.autograd.Function):
+    """mean((out - target)^2) in fp32 from bf16 inputs: one kernel forward, one backward."""
+
+    @staticmethod
+    def forward(ctx, out, target):
+        ctx.save_for_backward(out, target)
+        return native.mse_fwd(out, target)
+
+    @staticmethod
+    def backward(ctx, g):
+        out, target = ctx.saved_tensors
+        return native.mse_bwd(out, target, g.float().contiguous()), None
+
+
 def mse_loss(out: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    if (linear.ENABLED and out.is_cuda and out.dtype == torch.bfloat16
+            and target.dtype == torch.bfloat16 and out.shape == target.shape
+            and out.is_contiguous() and target.is_contiguous()):
+        return _MseFn.apply(out, target)
     return F.mse_loss(out.float(), target.float())

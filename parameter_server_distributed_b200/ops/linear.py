@@ -81,12 +81,14 @@ class _LinkFn(torch.autograd.Function):
             a2d = a2d.contiguous()
         w = weight if weight.is_contiguous() else weight.contiguous()
         n_out = w.shape[0]
-        bias_f32 = bias.detach().float() if bias is not None else None
+        b = bias.detach() if bias is not None else None  # bf16 or fp32, read by the epilogue
+        if b is not None and (b.dtype not in (torch.bfloat16, torch.float32) or not b.is_contiguous()):
+            b = b.float().contiguous()
         z_out = torch.empty((a2d.shape[0], n_out), dtype=torch.bfloat16, device=a2d.device)
         if gelu_out:
-            act_out = native.gemm(a2d, w, bias=bias_f32, epilogue="gelu", aux=z_out)
+            act_out = native.gemm(a2d, w, bias=b, epilogue="gelu", aux=z_out)
         else:
-            native.gemm(a2d, w, bias=bias_f32, out=z_out)
+            native.gemm(a2d, w, bias=b, out=z_out)
             act_out = z_out.new_empty(0)
         z_in2d = z_in.reshape(-1, z_in.shape[-1]) if gelu_in else None
         ctx.save_for_backward(a2d, w, z_in2d if gelu_in else None)
@@ -121,7 +123,7 @@ class _LinkFn(torch.autograd.Function):
             g_in = g_in.view(ctx.in_shape)
         # with a sink the parameter gradients land in the gradient bucket: no staging copy
         if ctx.has_bias and ctx.needs_input_grad[3]:
-            g_b = grad_to_sink(ctx.sink_b, lambda out: torch.sum(gz2d, 0, out=out))
+            g_b = grad_to_sink(ctx.sink_b, lambda out: native.colsum(gz2d, out=out))
         if ctx.needs_input_grad[2]:
             g_w = grad_to_sink(ctx.sink_w, lambda out: native.gemm(
                 gz2d, a2d, trans_a=True, trans_b=True, out=out))

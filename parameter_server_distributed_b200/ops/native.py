@@ -239,8 +239,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     Kb, N = (b.shape if trans_b else b.shape[::-1])
     if K != Kb:
         raise ValueError(f"gemm: reduction sizes differ ({K} vs {Kb})")
-    if bias is not None and (bias.dtype != torch.float32 or bias.numel() != N):
-        raise ValueError("gemm: bias must be float32 [N]")
+    if bias is not None and (bias.dtype not in (torch.float32, torch.bfloat16) or bias.numel() != N):
+        raise ValueError("gemm: bias must be float32 or bfloat16 [N]")
     epi = _EPILOGUES[epilogue]
     if aux is not None and (aux.dtype != torch.bfloat16 or tuple(aux.shape) != (M, N)
                             or not aux.is_contiguous()):
@@ -258,6 +258,68 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     g.M, g.N, g.K = M, N, K
     g.trans_a, g.trans_b = int(trans_a), int(trans_b)
     g.out_dtype, g.epilogue = _dt(out), epi
+    g.bias_dtype = _dt(bias) if bias is not None else F32
     with torch.cuda.device(a.device):
         check(_lib.load().psb_gemm_bf16(C.byref(g), _stream(a)), "psb_gemm_bf16")
     return out
+
+
+# ---------------------------------------------------------------- training-step helpers
+_SCRATCH: dict = {}
+
+
+def _scratch(key, nbytes: int, device) -> torch.Tensor:
+    """Zero-initialised per-device scratch that the kernels leave clean (arrival counters)."""
+    t = _SCRATCH.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _SCRATCH[key] = t
+    return t
+
+
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None,
+           out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    """``x.sum(0)`` of a contiguous bf16 ``[M,N]`` matrix (the bias gradient), fp32 accumulation
+    in a fixed order.  (include/psb_kernels.h: psb_colsum_bf16)"""
+    _need_cuda(x, out)
+    if x.dtype != torch.bfloat16 or x.dim() != 2 or not x.is_contiguous():
+        raise ValueError("colsum: x must be a contiguous bfloat16 [M,N] tensor")
+    M, N = x.shape
+    if out is None:
+        out = torch.empty(N, dtype=out_dtype, device=x.device)
+    elif out.numel() != N or not out.is_contiguous():
+        raise ValueError("colsum: out must be a contiguous tensor of N elements")
+    lib = _lib.load()
+    stream = _stream(x)
+    scratch = _scratch(("colsum", x.device.index, stream), lib.psb_colsum_scratch_bytes(M, N), x.device)
+    with torch.cuda.device(x.device):
+        check(lib.psb_colsum_bf16(x.data_ptr(), out.data_ptr(), _dt(out), M, N, scratch.data_ptr(),
+                                  stream), "psb_colsum_bf16")
+    return out
+
+
+def mse_fwd(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``mean((a-b)**2)`` of two contiguous bf16 tensors as an fp32 scalar, one kernel."""
+    _need_cuda(a, b)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.shape != b.shape \
+            or not a.is_contiguous() or not b.is_contiguous():
+        raise ValueError("mse_fwd: need two contiguous bfloat16 tensors of one shape")
+    loss = torch.empty((), dtype=torch.float32, device=a.device)
+    stream = _stream(a)
+    scratch = _scratch(("mse", a.device.index, stream), 4 * 304, a.device)
+    with torch.cuda.device(a.device):
+        check(_lib.load().psb_mse_fwd_bf16(a.data_ptr(), b.data_ptr(), a.numel(), scratch.data_ptr(),
+                                           loss.data_ptr(), stream), "psb_mse_fwd_bf16")
+    return loss
+
+
+def mse_bwd(a: torch.Tensor, b: torch.Tensor, gout: Optional[torch.Tensor]) -> torch.Tensor:
+    """Gradient of :func:`mse_fwd` w.r.t. ``a``: ``2 (a-b) / n * gout`` in bf16."""
+    _need_cuda(a, b, gout)
+    if gout is not None and (gout.dtype != torch.float32 or gout.numel() != 1):
+        raise ValueError("mse_bwd: gout must be a float32 scalar")
+    da = torch.empty_like(a)
+    with torch.cuda.device(a.device):
+        check(_lib.load().psb_mse_bwd_bf16(a.data_ptr(), b.data_ptr(), _ptr(gout), a.numel(),
+                                           da.data_ptr(), _stream(a)), "psb_mse_bwd_bf16")
+    return da

@@ -100,7 +100,8 @@ class _FusedLinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:  # readers of W before any commit (see grad_to_sink)
             gx = (native.gemm(gy2d, weight, trans_b=True) if own else gy2d @ weight).view(ctx.x_shape)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = linear.grad_to_sink(ctx.sink_b, lambda out: torch.sum(gy2d, 0, out=out))
+            gb = linear.grad_to_sink(ctx.sink_b, lambda out: (
+                native.colsum(gy2d, out=out) if own else torch.sum(gy2d, 0, out=out)))
         if ctx.needs_input_grad[1]:
             if own:
                 gw = linear.grad_to_sink(ctx.sink_w, lambda out: native.gemm(

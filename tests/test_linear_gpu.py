@@ -126,6 +126,51 @@ def test_link_chain_backward(batch, dims):
         _close(b.grad, r.grad, tol=5e-2)
 
 
+def test_colsum_scratch_reuse_across_shapes():
+    """One scratch serves every shape on a stream: counters must not alias partial sums."""
+    for M, N in [(777, 2056), (200, 264), (4096, 1024), (200, 72), (200, 520), (777, 2056)]:
+        x = _rand(M, N, scale=1.0)
+        got = native.colsum(x, out_dtype=torch.float32)
+        exp = x.float().sum(0)
+        assert (got - exp).abs().max().item() <= 1e-4 * exp.abs().max().item() + 1e-6, (M, N)
+
+
+@pytest.mark.parametrize("M,N", [(4096, 8192), (4096, 1024), (100, 264), (1, 8), (777, 2056)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_colsum(M, N, dtype):
+    x = _rand(M, N, scale=1.0)
+    for _ in range(2):  # the arrival counters must be left clean
+        got = native.colsum(x, out_dtype=dtype)
+        exp = x.float().sum(0)
+        assert got.dtype == dtype
+        tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+        assert (got.float() - exp).abs().max().item() <= tol * exp.abs().max().item() + 1e-6
+    assert torch.equal(native.colsum(x, out_dtype=dtype), got)  # fixed summation order
+
+
+@pytest.mark.parametrize("shape", [(4096, 1024), (33, 24), (7,), (300, 1000)])
+def test_fused_mse_loss(shape):
+    from parameter_server_distributed_b200.models import mse_loss
+    a = _rand(*shape, scale=1.0).requires_grad_()
+    b = _rand(*shape, scale=1.0)
+    loss = mse_loss(a, b)
+    (loss * 3.0).backward()
+    ar = a.detach().float().requires_grad_()
+    ref = F.mse_loss(ar, b.float())
+    (ref * 3.0).backward()
+    assert loss.dtype == torch.float32
+    assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    _close(a.grad, ar.grad, tol=1e-2)
+    assert mse_loss(a, b).item() == loss.item()  # scratch left clean, fixed order
+
+
+def test_gemm_bf16_bias():
+    x, w = _rand(256, 128), _rand(264, 128)
+    bias = _rand(264, scale=2.0)
+    y = native.gemm(x, w, bias=bias, out_dtype=torch.float32)
+    _close(y, x.float() @ w.float().t() + bias.float(), tol=1e-5)
+
+
 def test_mlp_uses_own_gemm_and_matches_library_path():
     from parameter_server_distributed_b200 import _lib
     torch.manual_seed(3)
@@ -135,7 +180,8 @@ def test_mlp_uses_own_gemm_and_matches_library_path():
     n0 = _lib.launch_count()
     out = model(x)
     F.mse_loss(out.float(), y.float()).backward()
-    assert _lib.launch_count() - n0 == 3 + 3 + 2  # 3 forward, 3 dW, 2 dX (the input needs no grad)
+    # 3 forward, 3 dW, 2 dX (the input needs no grad), 3 bias-gradient column sums
+    assert _lib.launch_count() - n0 == 3 + 3 + 2 + 3
     grads = [p.grad.clone() for p in model.parameters()]
     model.zero_grad(set_to_none=True)
     linear.ENABLED = False
