@@ -29,7 +29,10 @@ constexpr int STAGES = 6;
 constexpr int A_BYTES = 128 * BK * 2;  // 16 KB per CTA
 constexpr int B_BYTES = 128 * BK * 2;  // 16 KB per CTA
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int THREADS = 192;
+constexpr int EPI_WARPS = 8;   // two warps per TMEM lane quarter, each takes half of the columns:
+                               // halves the drain time of an accumulator, which matters for the
+                               // GELU / dGELU epilogues and for short-K tiles
+constexpr int THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 // Gather: every warp of a gather CTA is an independent copier of 8 KB items (peer -> registers
@@ -38,7 +41,7 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 // (loads of 32 KB complete at ~1 GB/s each, bulk stores complete one after the other), plain
 // 16-byte peer loads from many threads are what fills NVLink — as in K1 / K2.
 constexpr int G_CHUNK = 8192;
-constexpr int G_WARPS = 6;
+constexpr int G_WARPS = THREADS / 32;
 constexpr int CLC_SLOTS = 4;   // responses in flight: the producer runs up to ~3 tiles ahead
 constexpr int CLC_OFF = 256;   // byte offset of the CLC ring inside the 512-byte barrier area
 
@@ -394,11 +397,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);   // one multicast commit
-      mbar_init(&tmem_empty[i], 8);  // 4 epilogue warps x 2 CTAs arrive on the leader's copy
+      mbar_init(&tmem_empty[i], 2 * EPI_WARPS);  // epilogue warps of both CTAs arrive on the leader's copy
     }
     for (int i = 0; i < CLC_SLOTS; ++i) {
       mbar_init(&clc_full[i], 1);    // the issuer's expect_tx; the response completes the bytes
-      mbar_init(&clc_empty[i], 10);  // readers besides the issuer: MMA, 2 x 4 epilogue warps, peer producer
+      mbar_init(&clc_empty[i], 2 + 2 * EPI_WARPS);  // readers besides the issuer: MMA, peer producer, epilogue warps
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
@@ -543,8 +546,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5 of each CTA) =====================
-    const int quarter = warp & 3;
+    // ===================== epilogue (warps 2.. of each CTA) =====================
+    const int quarter = warp & 3;            // TMEM lanes this warp may read
+    const int half = (warp - 2) / 4;         // which half of the tile's columns it drains
+    constexpr int kChunks = BN / 32 / (EPI_WARPS / 4);
     int it = 0;
     int cs = 0;
     uint32_t cph = 0;
@@ -558,7 +563,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       const int row = m_blk * BM + (int)cta * 128 + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = half * kChunks; c < (half + 1) * kChunks; ++c) {
         uint32_t r[32];
         tmem_ld32(taddr + c * 32, r);
         tmem_ld_wait();
