@@ -131,7 +131,7 @@ def run_ours(args):
     wl = Workload(args.config, args.batch_per_gpu)
     nparams = wl.nparams
     ring = 1 if args.mode == "sync" else 4 if args.mode == "async" else max(2, args.staleness + 1)
-    ctx = psd.init(heap_bytes=nparams * 2 * (1 + ring) + (512 << 20))  # replica + gradient ring
+    ctx = psd.init(heap_bytes=nparams * 2 * (2 + ring) + (512 << 20))  # 2 replicas + gradient ring
     world = ctx.world
     if world != args.gpus and ctx.rank == 0:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}", file=sys.stderr)

@@ -59,5 +59,22 @@ bucket = torch.empty(n, dtype=torch.bfloat16, device=DEV)
 srcs = [g[i * (n // 8):(i + 1) * (n // 8)] for i in range(8)]
 for _ in range(reps):
     native.gather_to_bucket(srcs, bucket, [i * (n // 8) for i in range(8)])
+# training GEMMs of the MLP (cluster-launch-control tile walk): forward + GELU, dX * dGELU with an
+# MN-major B operand, dW with both operands MN-major; bias gradient; fused MSE loss
+if len(sys.argv) > 2 and sys.argv[2] == "train":
+    B, K_in, N_out = 4096, 8192, 8192
+    a_in = (torch.randn(B, K_in, device=DEV) * 0.1).to(torch.bfloat16)
+    wt = (torch.randn(N_out, K_in, device=DEV) * 0.02).to(torch.bfloat16)
+    bias = (torch.randn(N_out, device=DEV) * 0.1).to(torch.bfloat16)
+    z = torch.empty(B, N_out, dtype=torch.bfloat16, device=DEV)
+    gz = (torch.randn(B, N_out, device=DEV) * 0.1).to(torch.bfloat16)
+    zin = (torch.randn(B, K_in, device=DEV)).to(torch.bfloat16)
+    for _ in range(reps):
+        native.gemm(a_in, wt, bias=bias, epilogue="gelu", aux=z)
+        native.gemm(gz, wt, trans_b=True, epilogue="dgelu", aux=zin)
+        native.gemm(gz, a_in, trans_a=True, trans_b=True)
+        native.colsum(gz)
+        loss = native.mse_fwd(a_in, zin)
+        native.mse_bwd(a_in, zin, None)
 torch.cuda.synchronize()
 print("ncu_target ok")

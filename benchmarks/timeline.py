@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     args = ap.parse_args()
     wl = Workload(args.config, 0)
-    ctx = psd.init(heap_bytes=wl.nparams * 4 + (512 << 20))
+    ctx = psd.init(heap_bytes=wl.nparams * 6 + (512 << 20))
     torch.manual_seed(1234)
     model = wl.build().to(ctx.device, torch.bfloat16)
     trainer = psd.Trainer(model, wl.loss, ctx, psd.OptimConfig(kind="sgd", lr=1e-2))

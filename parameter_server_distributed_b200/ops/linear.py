@@ -112,21 +112,36 @@ class _LinkFn(torch.autograd.Function):
         if not gz2d.is_contiguous():
             gz2d = gz2d.contiguous()
         g_in = g_w = g_b = None
-        # dX first: committing a parameter gradient may start the push that rewrites W in place,
-        # so every reader of W on this stream has to be queued before the commit
-        if ctx.needs_input_grad[0]:
+        def input_grad():
+            if not ctx.needs_input_grad[0]:
+                return None
             if ctx.gelu_in:
                 zc = z_in2d if z_in2d.is_contiguous() else z_in2d.contiguous()
-                g_in = native.gemm(gz2d, w, trans_b=True, epilogue="dgelu", aux=zc)
+                g = native.gemm(gz2d, w, trans_b=True, epilogue="dgelu", aux=zc)
             else:
-                g_in = native.gemm(gz2d, w, trans_b=True)
-            g_in = g_in.view(ctx.in_shape)
-        # with a sink the parameter gradients land in the gradient bucket: no staging copy
-        if ctx.has_bias and ctx.needs_input_grad[3]:
-            g_b = grad_to_sink(ctx.sink_b, lambda out: native.colsum(gz2d, out=out))
-        if ctx.needs_input_grad[2]:
-            g_w = grad_to_sink(ctx.sink_w, lambda out: native.gemm(
-                gz2d, a2d, trans_a=True, trans_b=True, out=out))
+                g = native.gemm(gz2d, w, trans_b=True)
+            return g.view(ctx.in_shape)
+
+        def param_grads():
+            # with a sink the parameter gradients land in the gradient bucket: no staging copy
+            gb = gw = None
+            if ctx.has_bias and ctx.needs_input_grad[3]:
+                gb = grad_to_sink(ctx.sink_b, lambda out: native.colsum(gz2d, out=out))
+            if ctx.needs_input_grad[2]:
+                gw = grad_to_sink(ctx.sink_w, lambda out: native.gemm(
+                    gz2d, a2d, trans_a=True, trans_b=True, out=out))
+            return gw, gb
+
+        # A commit may start the push that rewrites W in place, so normally every reader of W
+        # (the dX GEMM) is queued first.  With sinks marked `early` (the push writes the other
+        # parameter replica) dW goes first and its push overlaps the dX GEMM.
+        sinks = [s for s in (ctx.sink_w, ctx.sink_b) if s is not None]
+        if sinks and all(s.early for s in sinks):
+            g_w, g_b = param_grads()
+            g_in = input_grad()
+        else:
+            g_in = input_grad()
+            g_w, g_b = param_grads()
         return g_in, None, g_w, g_b, None, None
 
 

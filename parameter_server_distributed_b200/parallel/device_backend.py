@@ -23,7 +23,7 @@ class DeviceBackend:
     def __init__(self, fabric: Fabric, plan: BucketPlan, optim: OptimConfig,
                  grad_dtype: torch.dtype = torch.bfloat16, broadcast: bool = True,
                  clip: bool = False, push_grid: int = 0, grad_ring: int = 1,
-                 push_tma: bool = False):
+                 push_tma: bool = False, alt_params: bool = False):
         if len(plan.buckets) > _lib.MAX_BUCKETS:
             raise ValueError(f"{len(plan.buckets)} buckets exceed MAX_BUCKETS={_lib.MAX_BUCKETS}")
         self.fabric, self.plan, self.optim = fabric, plan, optim
@@ -43,6 +43,10 @@ class DeviceBackend:
         self.P = fabric.alloc(total * 2, align=4096)
         self.grad_flat = self.G.view(grad_dtype)[:total]
         self.param_flat = self.P.view(torch.bfloat16)
+        # second replica: a push may write the new parameters of a bucket while kernels of the
+        # same iteration still read the old ones (the engine swaps the two after every step)
+        self.P2 = fabric.alloc(total * 2, align=4096) if alt_params else None
+        self.param_flat2 = self.P2.view(torch.bfloat16) if alt_params else None
         shard = plan.shard_elems
         dev = self.device
         self.master = torch.zeros(shard, dtype=torch.float32, device=dev)
@@ -59,17 +63,20 @@ class DeviceBackend:
         self.norm_seq = torch.zeros(1, dtype=torch.int32, device=dev)
         self.peer_mask = torch.zeros(1, dtype=torch.int32, device=dev)
         self._push_args: List[PsbPush] = [self._make_push(b) for b in range(nb)]
+        self._push_args_alt: List[PsbPush] = (
+            [self._make_push(b, self.P2) for b in range(nb)] if alt_params else [])
         self._pull_args: List[PsbPull] = [self._make_pull(b) for b in range(nb)]
 
     # ------------------------------------------------------------------ argument blocks
-    def _make_push(self, b: int) -> PsbPush:
+    def _make_push(self, b: int, P=None) -> PsbPush:
+        P = self.P if P is None else P
         bk = self.plan.buckets[b]
         gsz = 2 if self.grad_dtype == torch.bfloat16 else 4
         a = PsbPush()
         a.fabric = self.fabric.c_fabric()
         for r in range(self.world):
             a.grad[r] = self.G.peer_ptr(r) + bk.base * gsz
-            a.param[r] = self.P.peer_ptr(r) + bk.base * 2
+            a.param[r] = P.peer_ptr(r) + bk.base * 2
         sb = bk.shard_base(self.world)
         a.master = self.master[sb:].data_ptr()
         a.m = self.m[sb:].data_ptr() if self.m is not None else None
@@ -111,7 +118,7 @@ class DeviceBackend:
     def set_optim(self, optim: OptimConfig) -> None:
         """Change hyper-parameters (e.g. lr schedule); buffers stay."""
         self.optim = optim
-        for a in self._push_args:
+        for a in self._push_args + self._push_args_alt:
             a.opt = optim.to_c()
 
     # ------------------------------------------------------------------ views
@@ -136,10 +143,12 @@ class DeviceBackend:
              no_wait: bool = False, masked: bool = False, clip: bool = False,
              seqlock: bool = False, mask_ptr: Optional[int] = None,
              grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None,
-             tma: Optional[bool] = None, grid: Optional[int] = None, block: int = 0) -> None:
+             tma: Optional[bool] = None, grid: Optional[int] = None, block: int = 0,
+             alt: bool = False) -> None:
         """K1 on the current stream.  ``block``: threads per CTA of the register-path kernel
-        (0 = 512; 256 shares an SM with a tcgen05 GEMM CTA)."""
-        a = self._push_args[b]
+        (0 = 512; 256 shares an SM with a tcgen05 GEMM CTA).  ``alt``: the new parameters go to
+        the second replica."""
+        a = self._push_args_alt[b] if alt else self._push_args[b]
         bc = self.broadcast if broadcast is None else broadcast
         flags = _lib.PUSH_BROADCAST if bc else 0
         if seqlock:

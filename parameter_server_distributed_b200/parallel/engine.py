@@ -46,6 +46,13 @@ class GradSink:
     def commit(self) -> None:
         self.ps._arrive(self.slot, None)
 
+    @property
+    def early(self) -> bool:
+        """May the layer commit BEFORE it has queued the kernels that still read the parameter
+        (its dX GEMM)?  True when the push of this bucket cannot touch the replica those kernels
+        read: it writes the other replica, or (clipping) it only reduces."""
+        return self.ps._early_ok(self.slot.bucket)
+
 
 class ShardedParameterServer:
     def __init__(self, named_params: Sequence[Tuple[str, torch.nn.Parameter]], optim: OptimConfig,
@@ -54,11 +61,15 @@ class ShardedParameterServer:
                  clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
                  grad_ring: int = 1, push_tma: Optional[bool] = None, lazy_dedicated: bool = False,
-                 overlap_grid: int = 32):
+                 overlap_grid: int = 32, alt_params: Optional[bool] = None):
         """``broadcast``: owners write new slices into every replica inside K1 (push-mode
         all-gather).  ``lazy_dedicated``: buckets named in ``dedicated`` are the exception — their
         owners publish locally only and the consumer gathers them itself (the fused all-gather
-        GEMM of the first layer), which halves the un-overlappable tail of the last push."""
+        GEMM of the first layer), which halves the un-overlappable tail of the last push.
+        ``alt_params`` (None = on for the synchronous CUDA engine with more than one rank): keep
+        two parameter replicas and alternate between them, so that a bucket can be pushed as
+        soon as its gradients exist — before the layer's dX GEMM, which still reads the old
+        weights — instead of after it."""
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
         if not named_params:
             raise ValueError("no trainable parameters")
@@ -98,10 +109,21 @@ class ShardedParameterServer:
                 raise TypeError(f"unsupported parameter dtype {gdt}")
             if any(p.dtype != torch.bfloat16 for _, p in named_params):
                 raise TypeError("the CUDA backend keeps bf16 replicas: cast the model to bfloat16")
-            self.backend = DeviceBackend(fabric, self.plan, optim, grad_dtype=torch.bfloat16,
-                                         broadcast=broadcast, clip=clip_norm is not None,
-                                         push_grid=push_grid, grad_ring=grad_ring,
-                                         push_tma=bool(push_tma))
+            if alt_params is None:
+                alt_params = (world > 1 and broadcast and clip_norm is None
+                              and type(self) is ShardedParameterServer)
+            mk = lambda alt: DeviceBackend(fabric, self.plan, optim, grad_dtype=torch.bfloat16,  # noqa: E731
+                                           broadcast=broadcast, clip=clip_norm is not None,
+                                           push_grid=push_grid, grad_ring=grad_ring,
+                                           push_tma=bool(push_tma), alt_params=alt)
+            if "PSB_ALT_PARAMS" in os.environ:  # A/B knob
+                alt_params = alt_params and os.environ["PSB_ALT_PARAMS"] != "0"
+            if alt_params:
+                # gradient ring + two replicas must fit in what is left of the symmetric heap
+                need = (grad_ring + 2) * (self.plan.total_elems * 2 + 8192)
+                if fabric.free_bytes() < need:
+                    alt_params = False
+            self.backend = mk(alt_params)
             self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         else:
             from .host_backend import HostBackend
@@ -149,6 +171,9 @@ class ShardedParameterServer:
         # gradient sinks: layers that know about them (ops/linear.py) write dW / db straight into
         # the bucket and report it the moment the GEMM is queued, before their dX GEMM, so the
         # push of that bucket starts one GEMM earlier and no staging copy is made
+        self._alt = bool(self.is_cuda and getattr(self.backend, "P2", None) is not None)
+        self._area = [0] * len(self.plan.buckets)   # replica the model reads, per bucket
+        self._wrote = [None] * len(self.plan.buckets)  # replica the push of this step writes
         self._sinks: List[GradSink] = []
         if self._sinks_supported():
             for name, p in named_params:
@@ -193,6 +218,41 @@ class ShardedParameterServer:
         self._pending[slot.bucket].append((slot, g))
         if len(self._pending[slot.bucket]) == len(self.plan.buckets[slot.bucket].slots):
             self._flush(slot.bucket)
+
+    def _alt_ok(self, b: int) -> bool:
+        """Is bucket ``b`` double-buffered?  Broadcast buckets only; the bucket of the fused
+        first layer stays single (its GEMM reads the peers' first replicas directly)."""
+        return (self._alt and self._bcast(b)
+                and not (self.plan.buckets[b].dedicated and self._fused_first_layer))
+
+    def _early_ok(self, b: int) -> bool:
+        return self.is_cuda and (self.clip_norm is not None or self._alt_ok(b))
+
+    def _param_view(self, flat: torch.Tensor, name: str, shape) -> torch.Tensor:
+        slot = self.plan.slots[name]
+        bk = self.plan.buckets[slot.bucket]
+        view = flat[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
+        if name in self._nhwc:
+            n, c, h, w = shape
+            return view.view(n, h, w, c).permute(0, 3, 1, 2)
+        return view.view(shape)
+
+    def _swap_replicas(self) -> None:
+        """After the pushes of a step: the model reads, from now on, the replica they wrote."""
+        be = self.backend
+        changed = set()
+        for b, area in enumerate(self._wrote):
+            if area is not None and area != self._area[b]:
+                self._area[b] = area
+                changed.add(b)
+            self._wrote[b] = None
+        if not changed:
+            return
+        for name, p in self.named_params:
+            b = self.plan.slots[name].bucket
+            if b in changed:
+                flat = be.param_flat2 if self._area[b] == 1 else be.param_flat
+                p.data = self._param_view(flat, name, p.shape)
 
     def _sinks_supported(self) -> bool:
         """In-place gradient buckets need the bucket to be free for the whole backward pass:
@@ -253,6 +313,9 @@ class ShardedParameterServer:
         self._flushed[b] = True
         clip = self.clip_norm is not None
         kw = dict(reduce_only=clip, broadcast=self._bcast(b), **self._variant(b))
+        if self._alt_ok(b):
+            self._wrote[b] = 1 - self._area[b]
+            kw["alt"] = self._wrote[b] == 1
         bk = self.plan.buckets[b]
         self.metrics.inc("pushes")
         # bytes entering this GPU over NVLink for the bucket: peers' gradient slices of my shard
@@ -309,6 +372,8 @@ class ShardedParameterServer:
                 if not bc and lo is not None:
                     be.wait_versions(lo, b)
                     lo = None
+        if self._alt:
+            self._swap_replicas()
         self._flushed = [False] * nb
         self.steps_done += 1
         self.metrics.inc("steps")
@@ -369,8 +434,10 @@ class ShardedParameterServer:
                         lo = sb + (slot.offset + a) - r * bk.slice_elems
                         shard[lo:lo + (b - a)].copy_(flat[a:b])
                 if which == "master":
-                    view = be.param_flat[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
-                    view.copy_(flat.to(view.dtype))
+                    for pf in (be.param_flat, getattr(be, "param_flat2", None)):
+                        if pf is not None:
+                            view = pf[bk.base + slot.offset: bk.base + slot.offset + slot.numel]
+                            view.copy_(flat.to(view.dtype))
         if self.is_cuda:
             torch.cuda.synchronize(self.device)
 

@@ -150,6 +150,10 @@ class Fabric:
         self._cursor = off + nbytes
         return SymBuffer(self, off, int(nbytes))
 
+    def free_bytes(self) -> int:
+        """Bytes of the symmetric heap not handed out yet (same value on every rank)."""
+        return self.heap_bytes - self._cursor
+
     def c_fabric(self) -> PsbFabric:
         return self._cfab
 
