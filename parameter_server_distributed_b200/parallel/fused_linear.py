@@ -4,7 +4,8 @@ fused with the tcgen05 GEMM that consumes it.
 In pull mode the owner of each row-slice of ``W`` publishes only its own slice (K1 without
 broadcast).  The forward of the first layer then launches ONE kernel that pulls the remote
 slices over NVLink with bulk copies into the local replica while the tensor cores already
-work on the locally owned tiles.  Backward uses plain library GEMMs.
+work on the locally owned tiles.  Backward: dX and dW on the same tcgen05 kernel (MN-major
+operands, ``ops.native.gemm``), written through the engine's gradient sinks.
 """
 from __future__ import annotations
 
