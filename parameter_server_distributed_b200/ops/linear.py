@@ -49,6 +49,12 @@ def _dgelu(z: torch.Tensor) -> torch.Tensor:
     return 0.5 * (1 + t) + 0.5 * z * (1 - t * t) * k0 * (1 + 3 * k1 * z * z)
 
 
+def take_sink(param, needs_grad: bool):
+    """In a layer's forward: the parameter's gradient sink, if the engine installed one."""
+    sink = getattr(param, "_psb_sink", None) if (param is not None and needs_grad) else None
+    return sink.acquire() if sink is not None else None
+
+
 def grad_to_sink(sink, produce):
     """Run ``produce(out)``; with a sink the result goes into the gradient bucket, is committed
     and ``None`` is returned to autograd, otherwise a fresh tensor is returned.
@@ -56,7 +62,7 @@ def grad_to_sink(sink, produce):
     The commit may queue the push of the bucket, which updates the parameters IN PLACE on the
     push stream: call this only after every kernel of the layer that reads the parameter (the
     dX GEMM) has been queued on the current stream."""
-    if sink is None:
+    if sink is None or not sink.exclusive:
         return produce(None)
     produce(sink.view())
     sink.commit()
@@ -95,8 +101,8 @@ class _LinkFn(torch.autograd.Function):
         ctx.gelu_in = gelu_in
         ctx.has_bias = bias is not None
         # parameter-server gradient sinks (parallel/engine.py: GradSink), if the engine set them
-        ctx.sink_w = getattr(weight, "_psb_sink", None)
-        ctx.sink_b = getattr(bias, "_psb_sink", None) if bias is not None else None
+        ctx.sink_w = take_sink(weight, ctx.needs_input_grad[2])
+        ctx.sink_b = take_sink(bias, bias is not None and ctx.needs_input_grad[3])
         ctx.in_shape = z_in.shape
         ctx.mark_non_differentiable(act_out)
         ctx.set_materialize_grads(False)  # no zero tensor for the gradient of act_out
@@ -135,7 +141,7 @@ class _LinkFn(torch.autograd.Function):
         # A commit may start the push that rewrites W in place, so normally every reader of W
         # (the dX GEMM) is queued first.  With sinks marked `early` (the push writes the other
         # parameter replica) dW goes first and its push overlaps the dX GEMM.
-        sinks = [s for s in (ctx.sink_w, ctx.sink_b) if s is not None]
+        sinks = [s for s in (ctx.sink_w, ctx.sink_b) if s is not None and s.exclusive]
         if sinks and all(s.early for s in sinks):
             g_w, g_b = param_grads()
             g_in = input_grad()

@@ -34,10 +34,22 @@ class GradSink:
     tells the engine that the kernel producing it is queued on the current stream; the layer
     then returns ``None`` as that parameter's gradient so autograd does not deliver it twice."""
 
-    __slots__ = ("ps", "slot")
+    __slots__ = ("ps", "slot", "uses")
 
     def __init__(self, ps: "ShardedParameterServer", slot: ParamSlot):
         self.ps, self.slot = ps, slot
+        self.uses = 0  # forward passes that took this sink since the last step()
+
+    def acquire(self) -> "GradSink":
+        """Called by a layer's forward.  A parameter used by more than one layer call in a step
+        (tied weights) needs its gradients ADDED, which autograd does: `exclusive` is then
+        false and the layers return their gradients the ordinary way."""
+        self.uses += 1
+        return self
+
+    @property
+    def exclusive(self) -> bool:
+        return self.uses == 1
 
     def view(self) -> torch.Tensor:
         s = self.slot
@@ -374,6 +386,8 @@ class ShardedParameterServer:
                     lo = None
         if self._alt:
             self._swap_replicas()
+        for s in self._sinks:
+            s.uses = 0
         self._flushed = [False] * nb
         self.steps_done += 1
         self.metrics.inc("steps")

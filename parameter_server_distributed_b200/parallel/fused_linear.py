@@ -85,8 +85,8 @@ class _FusedLinearFn(torch.autograd.Function):
         y = op.launch(x2d, bias_f32)
         ctx.save_for_backward(x2d, weight)
         ctx.has_bias = bias is not None
-        ctx.sink_w = getattr(weight, "_psb_sink", None)
-        ctx.sink_b = getattr(bias, "_psb_sink", None) if bias is not None else None
+        ctx.sink_w = linear.take_sink(weight, ctx.needs_input_grad[1])
+        ctx.sink_b = linear.take_sink(bias, bias is not None and ctx.needs_input_grad[2])
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], weight.shape[0])
 

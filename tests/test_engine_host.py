@@ -164,7 +164,8 @@ class _SinkLinear(torch.autograd.Function):
         from parameter_server_distributed_b200.ops.linear import grad_to_sink  # noqa: F401
         ctx.save_for_backward(x, w)
         ctx.set_materialize_grads(False)
-        ctx.sinks = (getattr(w, "_psb_sink", None), getattr(b, "_psb_sink", None))
+        from parameter_server_distributed_b200.ops.linear import take_sink
+        ctx.sinks = (take_sink(w, ctx.needs_input_grad[1]), take_sink(b, ctx.needs_input_grad[2]))
         return x @ w.t() + b
 
     @staticmethod
@@ -214,3 +215,26 @@ def test_gradient_sinks_push_once_per_bucket_and_match_torch():
         assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
     ps.close()
     assert not any(hasattr(p, "_psb_sink") for p in m.parameters())
+
+
+def test_gradient_sinks_with_tied_weights_fall_back_to_autograd():
+    """A parameter used by two layer calls in one step needs its gradients added: the sink is
+    not exclusive then and the ordinary hook path (autograd accumulation) delivers it once."""
+    torch.manual_seed(6)
+    lin = torch.nn.Linear(16, 16)
+    ref = copy.deepcopy(lin)
+    ps = ShardedParameterServer(list(lin.named_parameters()), OptimConfig(kind="sgd", lr=0.1),
+                                bucket_mb=0.005)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.1)
+    for it in range(2):
+        x = torch.randn(8, 16)
+        y = _SinkLinear.apply(torch.tanh(_SinkLinear.apply(x, lin.weight, lin.bias)),
+                              lin.weight, lin.bias)
+        y.square().mean().backward()
+        ps.step()
+        assert ps.metrics.counters["pushes"] == len(ps.plan.buckets) * (it + 1)
+        opt.zero_grad()
+        ref(torch.tanh(ref(x))).square().mean().backward()
+        opt.step()
+    for a, b in zip(lin.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
