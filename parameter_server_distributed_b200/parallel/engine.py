@@ -142,7 +142,10 @@ class ShardedParameterServer:
             pdt = named_params[0][1].dtype
             self.backend = HostBackend(self.plan, optim, rank, world, group, param_dtype=pdt,
                                        grad_dtype=pdt, broadcast=broadcast,
-                                       clip=clip_norm is not None)
+                                       clip=clip_norm is not None,
+                                       alt_params=bool(alt_params) and broadcast
+                                       and clip_norm is None
+                                       and type(self) is ShardedParameterServer)
             self.comm_stream = None
         self.fabric = fabric
 
@@ -183,7 +186,7 @@ class ShardedParameterServer:
         # gradient sinks: layers that know about them (ops/linear.py) write dW / db straight into
         # the bucket and report it the moment the GEMM is queued, before their dX GEMM, so the
         # push of that bucket starts one GEMM earlier and no staging copy is made
-        self._alt = bool(self.is_cuda and getattr(self.backend, "P2", None) is not None)
+        self._alt = getattr(self.backend, "param_flat2", None) is not None
         self._area = [0] * len(self.plan.buckets)   # replica the model reads, per bucket
         self._wrote = [None] * len(self.plan.buckets)  # replica the push of this step writes
         self._sinks: List[GradSink] = []
@@ -238,7 +241,7 @@ class ShardedParameterServer:
                 and not (self.plan.buckets[b].dedicated and self._fused_first_layer))
 
     def _early_ok(self, b: int) -> bool:
-        return self.is_cuda and (self.clip_norm is not None or self._alt_ok(b))
+        return self.clip_norm is not None or self._alt_ok(b)
 
     def _param_view(self, flat: torch.Tensor, name: str, shape) -> torch.Tensor:
         slot = self.plan.slots[name]

@@ -22,7 +22,7 @@ class HostBackend:
     def __init__(self, plan: BucketPlan, optim: OptimConfig, rank: int = 0, world: int = 1,
                  group=None, param_dtype: torch.dtype = torch.float32,
                  grad_dtype: torch.dtype = torch.float32, broadcast: bool = True,
-                 clip: bool = False):
+                 clip: bool = False, alt_params: bool = False):
         self.plan, self.optim = plan, optim
         self.rank, self.world, self.group = rank, world, group
         self.device = torch.device("cpu")
@@ -31,6 +31,8 @@ class HostBackend:
         total, shard = plan.total_elems, plan.shard_elems
         self.grad_flat = torch.zeros(total, dtype=grad_dtype)
         self.param_flat = torch.zeros(total, dtype=param_dtype)
+        # second replica (see DeviceBackend): pushes with alt=True write here
+        self.param_flat2 = torch.zeros(total, dtype=param_dtype) if alt_params else None
         self.master = torch.zeros(shard, dtype=torch.float32)
         self.m = torch.zeros(shard, dtype=torch.float32) if optim.needs_m() else None
         self.v = torch.zeros(shard, dtype=torch.float32) if optim.needs_v() else None
@@ -69,7 +71,7 @@ class HostBackend:
 
     def push(self, b: int, *, reduce_only: bool = False, from_reduced: bool = False,
              no_wait: bool = False, masked: bool = False, clip: bool = False,
-             broadcast=None, **_unused) -> None:
+             broadcast=None, alt: bool = False, **_unused) -> None:
         bk = self.plan.buckets[b]
         s = bk.slice_elems
         if from_reduced:
@@ -94,7 +96,7 @@ class HostBackend:
                        clip_coef=float(self.clip_coef.item()) if clip else 1.0,
                        step=int(self.step_word.item()))
         mine = self.shard_slice(self.master, b).to(self.param_flat.dtype)
-        pb = self.param_bucket(b)
+        pb = (self.param_flat2[bk.base:bk.base + bk.numel] if alt else self.param_bucket(b))
         pb[self.rank * s:(self.rank + 1) * s].copy_(mine)
         if self.broadcast if broadcast is None else broadcast:
             for r, sl in enumerate(self._gather_slices(mine)):

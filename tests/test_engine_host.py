@@ -72,7 +72,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, kind, broadcast, q):
+def _worker(rank, world, port, kind, broadcast, q, alt=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -80,7 +80,9 @@ def _worker(rank, world, port, kind, broadcast, q):
     m = MLP(CFG)
     ref = copy.deepcopy(m)
     ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind=kind, lr=0.01),
-                                world=world, rank=rank, bucket_mb=0.005, broadcast=broadcast)
+                                world=world, rank=rank, bucket_mb=0.005, broadcast=broadcast,
+                                alt_params=alt)
+    fwd = _SinkMLP(m) if alt else m  # with two replicas: sink layers that commit before dX
     opt = _torch_opt(kind, list(ref.parameters()))
     for g in opt.param_groups:
         g["weight_decay"] = 0.0
@@ -88,7 +90,7 @@ def _worker(rank, world, port, kind, broadcast, q):
     for _ in range(3):
         xs = torch.randn(world, 8, 32, generator=gen)
         ys = torch.randn(world, 8, 8, generator=gen)
-        mse_loss(m(xs[rank]), ys[rank]).backward()
+        mse_loss(fwd(xs[rank]), ys[rank]).backward()
         ps.step()
         # oracle: mean over workers of the per-worker gradients
         opt.zero_grad()
@@ -100,12 +102,15 @@ def _worker(rank, world, port, kind, broadcast, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind,broadcast", [("sgd", True), ("adam", True), ("momentum", False)])
-def test_gloo_two_workers_match_mean_gradient(kind, broadcast):
+@pytest.mark.parametrize("kind,broadcast,alt", [("sgd", True, False), ("adam", True, False),
+                                                ("momentum", False, False), ("sgd", True, True),
+                                                ("adam", True, True)])
+def test_gloo_two_workers_match_mean_gradient(kind, broadcast, alt):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, kind, broadcast, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, kind, broadcast, q, alt))
+             for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in procs]
@@ -173,9 +178,14 @@ class _SinkLinear(torch.autograd.Function):
         from parameter_server_distributed_b200.ops.linear import grad_to_sink
         x, w = ctx.saved_tensors
         sw, sb = ctx.sinks
-        gx = gy @ w  # before the commits: a commit may start the in-place update of w
+        live = [s for s in (sw, sb) if s is not None and s.exclusive]
+        early = bool(live) and all(s.early for s in live)
+        if not early:
+            gx = gy @ w  # before the commits: a commit may start the in-place update of w
         gb = grad_to_sink(sb, lambda out: torch.sum(gy, 0, out=out))
         gw = grad_to_sink(sw, lambda out: torch.mm(gy.t(), x, out=out))
+        if early:
+            gx = gy @ w  # the push went to the other replica (or only reduced): w is intact
         return gx, gw, gb
 
 
@@ -238,3 +248,38 @@ def test_gradient_sinks_with_tied_weights_fall_back_to_autograd():
         opt.step()
     for a, b in zip(lin.parameters(), ref.parameters()):
         assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+
+
+@pytest.mark.parametrize("clip", [None, 0.05])
+def test_alternating_replicas_allow_commit_before_dx(clip):
+    """With two parameter replicas (or in clip mode, where a flush only reduces) the sinks are
+    `early`: the layer commits dW before it computes dX from the same weights.  The host
+    backend applies a push synchronously, so any aliasing of the two replicas would corrupt dX
+    and show up against torch."""
+    torch.manual_seed(8)
+    m = MLP(CFG)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind="sgd", lr=0.05),
+                                bucket_mb=0.005, alt_params=clip is None, clip_norm=clip)
+    assert all(p._psb_sink.early for p in m.parameters())
+    sm = _SinkMLP(m)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    ptrs = []
+    for it in range(4):
+        x, y = torch.randn(16, 32), torch.randn(16, 8)
+        mse_loss(sm(x), y).backward()
+        ps.step()
+        ptrs.append(m.layers[1].weight.data_ptr())
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        if clip is not None:
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), clip)
+        opt.step()
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+    if clip is None:  # the model reads the two replicas in turn
+        assert ptrs[0] == ptrs[2] and ptrs[1] == ptrs[3] and ptrs[0] != ptrs[1]
+        # state written back (checkpoint restore) lands in the replica the model reads
+        state = ps.gather_state("master")
+        ps.scatter_state({k: v * 0 + 1.5 for k, v in state.items()}, "master")
+        assert all(torch.all(p == 1.5) for p in m.parameters())
