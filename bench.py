@@ -123,6 +123,7 @@ def run_ours(args):
 
     import parameter_server_distributed_b200 as psd
     from parameter_server_distributed_b200 import _lib
+    from parameter_server_distributed_b200.ops import linear as _linear
     from parameter_server_distributed_b200.utils import ClockSampler
 
     if not torch.cuda.is_available():
@@ -225,6 +226,8 @@ def run_ours(args):
                        "mode": args.mode if args.mode != "ssp" else f"ssp(staleness={args.staleness})",
                        "push": args.push,
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
+                       "layer_gemms": "own tcgen05 kernel" if _linear.ENABLED else "library",
+                       "alt_param_replicas": bool(getattr(ps, "_alt", False)),
                        "l2": "working set (weights+grads+state+activations > 1 GB) exceeds the "
                              "126 MB L2; inputs rotate over 4 batches"},
             "push_pull_ms_per_step": pp_ms,
