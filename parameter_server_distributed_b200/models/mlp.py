@@ -41,6 +41,8 @@ class MLPConfig:
 
 
 class MLP(nn.Module):
+    grad_sink_layers = True  # its links write dW / db through the engine's gradient sinks
+
     def __init__(self, cfg: MLPConfig = MLPConfig()):
         super().__init__()
         self.cfg = cfg

@@ -100,7 +100,10 @@ class Trainer:
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
                 bucket_mb=bucket_mb, broadcast=(pull != "gather"), clip_norm=clip_norm,
                 dedicated=dedicated, overlap=overlap, push_grid=push_grid,
-                push_tma=push_tma, lazy_dedicated=(pull == "hybrid"))
+                push_tma=push_tma, lazy_dedicated=(pull == "hybrid"),
+                # two parameter replicas pay off only for layers that commit their gradients
+                # before their dX GEMM (ops/linear.py); other models keep one replica
+                alt_params=None if getattr(model, "grad_sink_layers", False) else False)
         else:
             from .parallel.async_engine import AsyncParameterServer
             self.ps = AsyncParameterServer(
