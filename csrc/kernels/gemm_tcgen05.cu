@@ -524,13 +524,9 @@ static int launch(const void* x, const void* w, Params& p, cudaStream_t s) {
   CUtensorMap map_a, map_b;
   if (int rc = make_map(&map_a, x, p.M, p.K, BM)) return rc;
   if (int rc = make_map(&map_b, w, p.N, p.K, BN)) return rc;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    SMEM_BYTES);
-  });
-  PSB_CUDA_OK(attr_err);
+  // per launch, not once per process: the attribute belongs to the current device's context
+  PSB_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   SMEM_BYTES));
   const int num_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
   int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
   if (p.fused) {

@@ -719,13 +719,9 @@ static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_
 template <int EPI>
 static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const Params& p,
                       int clusters, cudaStream_t s) {
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-  });
-  PSB_CUDA_OK(attr_err);
+  // per launch, not once per process: the attribute belongs to the current device's context
+  PSB_CUDA_OK(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
   gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, p);
   PSB_LAUNCH_OK(EPI == EPI_NONE ? "gemm_bf16_tcgen05_2cta"
                                 : EPI == EPI_GELU ? "gemm_bf16_tcgen05_2cta_gelu"
