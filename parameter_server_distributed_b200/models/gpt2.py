@@ -2,17 +2,23 @@
 reduce-scatter").  Architecture of the public GPT-2: learned positions, pre-LayerNorm blocks,
 tanh-GELU MLP, tied input/output embeddings; random init (no checkpoints offline).  Attention
 uses ``F.scaled_dot_product_attention`` (library kernel); the parameter-server kernels of this
-repo handle every gradient push / optimizer update / parameter pull.
+repo handle every gradient push / optimizer update / parameter pull.  With ``own_gemms`` the
+four Linear layers of every block run as links of :mod:`..ops.linear` (tcgen05 GEMMs for
+forward, dX and dW, GELU / dGELU fused into the c_fc / c_proj2 epilogues); the tied LM head
+(50 257 rows, not a multiple of 8) stays a library GEMM.
 The reference has no model (src/worker.cpp:316-320 fills gradients with 0.01).
 """
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+
+from ..ops import linear
 
 
 @dataclass
@@ -22,6 +28,8 @@ class GPT2Config:
     n_embd: int = 1024
     n_layer: int = 24
     n_head: int = 16
+    # block Linears on the repo's tcgen05 kernel (CUDA bf16 only; PSB_GPT2_OWN_GEMMS=0/1 overrides)
+    own_gemms: bool = False
 
     @staticmethod
     def medium() -> "GPT2Config":
@@ -52,6 +60,8 @@ class Block(nn.Module):
         super().__init__()
         d = cfg.n_embd
         self.n_head = cfg.n_head
+        env = os.environ.get("PSB_GPT2_OWN_GEMMS")
+        self.own_gemms = cfg.own_gemms if env is None else env != "0"
         self.ln_1 = nn.LayerNorm(d)
         self.c_attn = nn.Linear(d, 3 * d)
         self.c_proj = nn.Linear(d, d)
@@ -59,15 +69,25 @@ class Block(nn.Module):
         self.c_fc = nn.Linear(d, 4 * d)
         self.c_proj2 = nn.Linear(4 * d, d)
 
+    def _lin(self, layer: nn.Linear, x: torch.Tensor) -> torch.Tensor:
+        if self.own_gemms:
+            return linear.link(x, None, layer.weight, layer.bias, gelu_in=False, gelu_out=False)[0]
+        return layer(x)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, T, D = x.shape
-        q, k, v = self.c_attn(self.ln_1(x)).split(D, dim=2)
+        q, k, v = self._lin(self.c_attn, self.ln_1(x)).split(D, dim=2)
         h = self.n_head
         q = q.view(B, T, h, D // h).transpose(1, 2)
         k = k.view(B, T, h, D // h).transpose(1, 2)
         v = v.view(B, T, h, D // h).transpose(1, 2)
         a = F.scaled_dot_product_attention(q, k, v, is_causal=True)
-        x = x + self.c_proj(a.transpose(1, 2).reshape(B, T, D))
+        x = x + self._lin(self.c_proj, a.transpose(1, 2).reshape(B, T, D))
+        if self.own_gemms:
+            z, act = linear.link(self.ln_2(x), None, self.c_fc.weight, self.c_fc.bias,
+                                 gelu_in=False, gelu_out=True)
+            return x + linear.link(z, act, self.c_proj2.weight, self.c_proj2.bias,
+                                   gelu_in=True, gelu_out=False)[0]
         x = x + self.c_proj2(F.gelu(self.c_fc(self.ln_2(x)), approximate="tanh"))
         return x
 

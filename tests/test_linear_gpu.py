@@ -193,3 +193,24 @@ def test_mlp_uses_own_gemm_and_matches_library_path():
     _close(out, ref, tol=3e-2)
     for g, p in zip(grads, model.parameters()):
         _close(g, p.grad, tol=5e-2)
+
+
+def test_gpt2_blocks_on_own_gemms_match_library_path():
+    import dataclasses
+    from parameter_server_distributed_b200.models import GPT2, GPT2Config, lm_loss
+    cfg = dataclasses.replace(GPT2Config.tiny(), n_embd=128, n_head=4)
+    torch.manual_seed(0)
+    lib = GPT2(cfg).to(DEV, torch.bfloat16)
+    torch.manual_seed(0)
+    own = GPT2(dataclasses.replace(cfg, own_gemms=True)).to(DEV, torch.bfloat16)
+    idx = torch.randint(0, cfg.vocab_size, (4, 65), device=DEV)
+    x, y = idx[:, :-1].contiguous(), idx[:, 1:].contiguous()
+    lo, ll = own(x), lib(x)
+    _close(lo, ll, tol=3e-2)
+    lm_loss(lo, y).backward()
+    lm_loss(ll, y).backward()
+    for (n, a), b in zip(own.named_parameters(), lib.parameters()):
+        assert a.grad is not None, n
+        err = (a.grad.float() - b.grad.float()).abs().max().item()
+        scale = b.grad.float().abs().max().item() + 1e-6
+        assert err / scale < 8e-2, (n, err, scale)
