@@ -67,10 +67,47 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
 }
 __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 
+// ---- watchdog of the peer spin-waits ---------------------------------------------------
+// A peer that died (or whose kernel never launched) would leave a waiting kernel spinning for
+// ever and the GPU unusable.  Every spin loop on a word written by a peer ticks a SpinWatch;
+// when the loop has run longer than the limit the kernel traps: the launch ends with a CUDA
+// error that the host reports (the process has to restart from a checkpoint, as after any
+// sticky CUDA error) and the GPU is free again.  The limit is a per-device word in every
+// translation unit that waits (static __device__), set by psb_set_spin_timeout_ms().
+static __device__ unsigned long long g_spin_limit_ns = 300ull * 1000000000ull;
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+struct SpinWatch {
+  unsigned long long t0 = 0;
+  uint32_t n = 0;
+  __device__ __forceinline__ void tick() {
+    if ((++n & 1023u) != 0) return;  // look at the clock once per 1024 polls
+    const unsigned long long now = globaltimer_ns();
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > g_spin_limit_ns) __trap();
+  }
+};
+
+// host side of the limit for the translation unit that includes this header
+static inline cudaError_t set_spin_limit_in_this_unit(unsigned long long ns) {
+  return cudaMemcpyToSymbol(g_spin_limit_ns, &ns, sizeof(ns));
+}
+#define PSB_EXPORT_SPIN_LIMIT(tag)                                         \
+  extern "C" int psb_spin_limit_##tag(unsigned long long ns) {             \
+    return (int)psb::set_spin_limit_in_this_unit(ns);                      \
+  }
+
 // spin until *p >= target (wrap-safe signed distance)
 __device__ __forceinline__ void wait_ge_sys(const uint32_t* p, uint32_t target) {
+  SpinWatch watch;
   while ((int32_t)(ld_acquire_sys(p) - target) < 0) {
     __nanosleep(32);
+    watch.tick();
   }
 }
 

@@ -620,3 +620,5 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* a, psb_stream_t stream) {
 }
 
 }  // extern "C"
+
+PSB_EXPORT_SPIN_LIMIT(gemm1)

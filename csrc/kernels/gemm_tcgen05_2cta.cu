@@ -816,3 +816,5 @@ extern "C" int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream) {
   p.aux_out = reinterpret_cast<__nv_bfloat16*>(g->aux_out);
   return launch(g->a, g->b, p, g->epilogue, (cudaStream_t)stream);
 }
+
+PSB_EXPORT_SPIN_LIMIT(gemm2)

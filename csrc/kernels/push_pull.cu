@@ -239,7 +239,11 @@ __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a)
       while (true) {
         if (threadIdx.x == 0) {
           uint32_t v;
-          while ((v = ld_acquire_sys(vpad + owner)) & 1u) __nanosleep(64);
+          SpinWatch watch;
+          while ((v = ld_acquire_sys(vpad + owner)) & 1u) {
+            __nanosleep(64);
+            watch.tick();
+          }
           v0s = v;
         }
         __syncthreads();
@@ -418,10 +422,12 @@ __global__ void __launch_bounds__(32)
     const uint64_t* src = reinterpret_cast<const uint64_t*>(f.pad[f.rank] + PSB_PAD_NORM_OFF) +
                           par * PSB_MAX_PEERS + threadIdx.x;
     uint64_t w;
+    SpinWatch watch;
     do {
       w = ld_acquire_sys_u64(src);
       if ((int32_t)((uint32_t)(w >> 32) - s) >= 0) break;
       __nanosleep(32);
+      watch.tick();
     } while (true);
     got = __uint_as_float((uint32_t)w);
   }
@@ -642,3 +648,20 @@ int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, ps
 }
 
 }  // extern "C"
+
+PSB_EXPORT_SPIN_LIMIT(push_pull)
+extern "C" int psb_spin_limit_push_tma(unsigned long long ns);
+extern "C" int psb_spin_limit_gemm1(unsigned long long ns);
+extern "C" int psb_spin_limit_gemm2(unsigned long long ns);
+
+extern "C" int psb_set_spin_timeout_ms(uint64_t ms) {
+  PSB_REQUIRE(ms >= 1, PSB_EINVAL, "psb_set_spin_timeout_ms: the limit must be at least 1 ms");
+  const unsigned long long ns = (unsigned long long)ms * 1000000ull;
+  // one copy of the limit per translation unit that spins on peer words (current device)
+  int (*setters[])(unsigned long long) = {psb_spin_limit_push_pull, psb_spin_limit_push_tma,
+                                          psb_spin_limit_gemm1, psb_spin_limit_gemm2};
+  for (auto set : setters) {
+    PSB_CUDA_OK((cudaError_t)set(ns));
+  }
+  return 0;
+}

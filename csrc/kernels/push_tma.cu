@@ -263,3 +263,5 @@ int push_fused_tma_dispatch(const PsbPush& a, cudaStream_t s) {
 }
 
 }  // namespace psb
+
+PSB_EXPORT_SPIN_LIMIT(push_tma)

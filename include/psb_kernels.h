@@ -304,6 +304,13 @@ int psb_async_ack(const PsbAsync* a, psb_stream_t stream);
 int psb_async_gate(const PsbAsync* a, uint32_t clock, int32_t staleness, psb_stream_t stream);
 // store `value` into word [word_base + rank] of every rank's pad (release.sys)
 int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, psb_stream_t stream);
+// Watchdog of every spin-wait on a word written by a peer (K1 ready flags, K2 / K9 version
+// flags, barriers, norm all-reduce, async clocks, the gather of K2f): a kernel that has been
+// waiting longer than this traps instead of spinning for ever on a dead peer; the launch then
+// fails with a CUDA error and the GPU is released.  Default 300 s; per device (call it with
+// the device current).  No counterpart in the reference, whose host-side waits poll for ever
+// (src/worker.cpp:293-306).
+int psb_set_spin_timeout_ms(uint64_t ms);
 
 // ---------------------------------------------------------------------------
 // K2f — bf16 GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed

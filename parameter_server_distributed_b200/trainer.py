@@ -35,10 +35,15 @@ class Context:
             dist.destroy_process_group()
 
 
-def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None) -> Context:
+def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
+         spin_timeout_s: Optional[float] = None) -> Context:
     """Join the job described by RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* (torchrun) and
     build the symmetric heap.  ``torch.distributed`` is used only as control plane (handle
-    exchange, host barriers); the data plane is peer memory."""
+    exchange, host barriers); the data plane is peer memory.
+
+    ``spin_timeout_s`` (or ``PSB_SPIN_TIMEOUT_S``; kernel default 300 s): how long a kernel may
+    wait on a flag of a peer before it traps — a dead peer then surfaces as a CUDA error on this
+    rank instead of a GPU that spins for ever."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
@@ -46,6 +51,12 @@ def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None) -> Context:
     if cuda:
         torch.cuda.set_device(local_rank)
         device = torch.device("cuda", local_rank)
+        if spin_timeout_s is None and "PSB_SPIN_TIMEOUT_S" in os.environ:
+            spin_timeout_s = float(os.environ["PSB_SPIN_TIMEOUT_S"])
+        if spin_timeout_s is not None:
+            from . import _lib
+            _lib.check(_lib.load().psb_set_spin_timeout_ms(max(1, int(spin_timeout_s * 1000))),
+                       "psb_set_spin_timeout_ms")
     else:
         device = torch.device("cpu")
     if world > 1 and not dist.is_initialized():
