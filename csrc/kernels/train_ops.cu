@@ -1,8 +1,10 @@
 // train_ops.cu — small memory-bound kernels of the training step that sit between the GEMMs of
 // the flagship MLP: bias gradient (column sum of dZ) and the MSE loss with its gradient.
 // The reference has no model code at all (src/worker.cpp:316-320 fabricates gradients); these
-// replace chains of generic PyTorch elementwise / reduce launches (profiles/timeline_mlp_1gpu.tsv:
-// ~100 us of reduce_kernel and ~60 us of loss kernels per 2.1 ms step).
+// replace chains of generic PyTorch elementwise / reduce launches, which took ~100 us
+// (reduce_kernel) and ~60 us (loss: two casts, mse, mean, fills, backward) of a 2.1 ms step
+// before; now 16-19 us per 64 MB column sum and 9 + 7 us for the loss
+// (profiles/timeline_mlp_1gpu.tsv).
 #include "common.cuh"
 
 namespace psb {
