@@ -154,6 +154,7 @@ class Trainer:
                                  for t in host_inputs] for _ in range(2)]
             self._consumed = [None, None]
             self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._loss_stream = torch.cuda.Stream(device=self.device)
             self._loss_ring = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(4)]
             self.h2d_bytes = sum(t.numel() * t.element_size() for t in host_inputs)
         slot = self._ring_i & 1
@@ -166,13 +167,25 @@ class Trainer:
             copied = torch.cuda.Event()
             copied.record(self._copy_stream)
         cur.wait_event(copied)
-        loss = self.step_device(*self._dev_inputs[slot])
+        *xs, target = self._dev_inputs[slot]
+        loss = self.loss_fn(self.model(*xs), target)
+        # the loss goes home as soon as the forward pass has produced it (its own stream), not
+        # after backward and the pushes: a caller that reads it every step then waits for a
+        # third of a step instead of a whole one and keeps the launch queue fuller
+        host = self._loss_ring[self._ring_i % len(self._loss_ring)]
+        self._ring_i += 1
+        loss_val = loss.detach().float()
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        with torch.cuda.stream(self._loss_stream):
+            self._loss_stream.wait_event(ready)
+            host.copy_(loss_val, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._loss_stream)
+        loss_val.record_stream(self._loss_stream)
+        loss.backward()
+        self.ps.step()
         done = torch.cuda.Event()
         done.record(cur)
         self._consumed[slot] = done
-        host = self._loss_ring[self._ring_i % len(self._loss_ring)]
-        self._ring_i += 1
-        host.copy_(loss.float(), non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(cur)
         return LossHandle(host, ev)
