@@ -128,6 +128,9 @@ class ShardedParameterServer:
                                            broadcast=broadcast, clip=clip_norm is not None,
                                            push_grid=push_grid, grad_ring=grad_ring,
                                            push_tma=bool(push_tma), alt_params=alt)
+            # a second replica only makes sense where pushes write parameters during backward
+            alt_params = (bool(alt_params) and broadcast and clip_norm is None
+                          and type(self) is ShardedParameterServer)
             if "PSB_ALT_PARAMS" in os.environ:  # A/B knob
                 alt_params = alt_params and os.environ["PSB_ALT_PARAMS"] != "0"
             if alt_params:
