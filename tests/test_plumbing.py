@@ -158,3 +158,17 @@ def test_missing_worker_times_out_with_done_false(tmp_path):
     finally:
         ps.stop()
         co.stop()
+
+
+def test_example_script_trains_and_checkpoints(tmp_path):
+    """examples/train_mlp.py: the public API end to end on the host backend."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ckpt = tmp_path / "mlp.ckpt"
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "train_mlp.py"), "--steps", "12",
+                        "--checkpoint", str(ckpt)], capture_output=True, text=True, timeout=300,
+                       env=env)
+    assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
+    assert "checkpoint" in r.stdout and ckpt.exists() and ckpt.stat().st_size > 1000
