@@ -172,3 +172,25 @@ def test_example_script_trains_and_checkpoints(tmp_path):
                        env=env)
     assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
     assert "checkpoint" in r.stdout and ckpt.exists() and ckpt.stat().st_size > 1000
+
+
+def test_python_worker_example_against_cpp_servers(tmp_path):
+    """examples/python_worker.py: a grpcio worker drives the C++ coordinator and parameter
+    server through the reference's wire schema."""
+    import sys
+    bin_dir, root = BIN, ROOT
+    cport, pport = free_port(), free_port()
+    ps = Proc([os.path.join(bin_dir, "parameter_server"), f"0.0.0.0:{pport}", "1", "0",
+               "--optimizer=sgd", "--lr=0.1"], str(tmp_path), str(tmp_path / "ps.log"))
+    co = Proc([os.path.join(bin_dir, "coordinator"), f"0.0.0.0:{cport}", f"127.0.0.1:{pport}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    try:
+        assert wait_port(pport) and wait_port(cport)
+        r = subprocess.run([sys.executable, os.path.join(root, "examples", "python_worker.py"),
+                            "--coordinator", f"127.0.0.1:{cport}", "--iterations", "6"],
+                           capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
+        assert r.stdout.count("done=true") == 6
+    finally:
+        ps.stop()
+        co.stop()
