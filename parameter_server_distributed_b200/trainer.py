@@ -129,6 +129,23 @@ class Trainer:
         self.h2d_bytes = 0
         self.d2h_bytes = 4
 
+    # ------------------------------------------------------------------ checkpoints
+    def save_checkpoint(self, path: str, epoch: int = 0) -> None:
+        """Collective.  Writes the fp32 master weights in the reference's checkpoint format
+        (loadable by the reference's ``LoadCheckpoint``, /root/reference/src/parameter_server.cpp:
+        146-188) plus a ``.psb`` sidecar with the optimizer state.  In async / ssp mode the
+        gradients still in flight are applied first."""
+        from .utils.checkpoint import save_checkpoint
+        if hasattr(self.ps, "drain"):
+            self.ps.drain()
+        save_checkpoint(self.ps, path, epoch=epoch)
+
+    def load_checkpoint(self, path: str):
+        """Collective.  Restores master weights (and optimizer state when the sidecar exists);
+        returns ``(epoch, iteration)``."""
+        from .utils.checkpoint import load_checkpoint
+        return load_checkpoint(self.ps, path)
+
     # ------------------------------------------------------------------ device-resident step
     def step_device(self, *inputs: torch.Tensor) -> torch.Tensor:
         """Forward + backward + push/pull on tensors already on the device; returns the loss

@@ -88,3 +88,24 @@ def test_file_loads_in_cpp_server(tmp_path):
             assert torch.equal(p, q)
     finally:
         srv.stop()
+
+
+def test_trainer_checkpoint_methods_round_trip(tmp_path):
+    """Trainer.save_checkpoint / load_checkpoint: the public spelling of the same functions."""
+    import parameter_server_distributed_b200 as psd
+    from parameter_server_distributed_b200.models import mse_loss
+    ctx = psd.init()
+    torch.manual_seed(4)
+    model = MLP(CFG)
+    tr = psd.Trainer(model, mse_loss, ctx, OptimConfig(kind="adam", lr=0.01), bucket_mb=0.001)
+    x, y = torch.randn(8, CFG.d_in), torch.randn(8, CFG.d_out)
+    for _ in range(2):
+        tr.step(x, y).item()
+    path = str(tmp_path / "t.ckpt")
+    tr.save_checkpoint(path, epoch=3)
+    saved = [p.detach().clone() for p in model.parameters()]
+    tr.step(x, y).item()
+    assert any(not torch.equal(p, s) for p, s in zip(model.parameters(), saved))
+    assert tr.load_checkpoint(path) == (3, 1)
+    for p, s in zip(model.parameters(), saved):
+        assert torch.equal(p, s)
