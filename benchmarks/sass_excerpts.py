@@ -1,0 +1,72 @@
+#!/usr/bin/env python
+"""Regenerates profiles/sass_excerpts.txt and profiles/sass_mnemonics.txt from the built
+library (no GPU needed): the SASS around the instructions that prove each mechanism."""
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "parameter_server_distributed_b200", "_native", "libpsb_kernels.so")
+
+SECTIONS = [
+    ("gemm2_bf16_kernelILi0E",
+     ["UTCHMMA", "UTMALDG", "UGETNEXTWORKID", "UTCBAR", "LDTM", "UTCATOMSWS", "SYNCS.ARRIVE.TRANS64.RED"],
+     "CTA-pair tcgen05 GEMM (plain epilogue): TMA loads, UMMA issue, commit, TMEM loads, cluster launch control"),
+    ("gemm2_bf16_kernelILi2E", ["MUFU.TANH", "LDG.E.128", "UTCHMMA"],
+     "same kernel, dX*dGELU epilogue: tanh.approx and the 16-byte loads of Z"),
+    ("push_fused_kernelILi3ELi1ELi8E",
+     ["LDG.E.128", "LDG.E.NA", "STG.E", "256", "ATOM", "MEMBAR", "LD.E.STRONG.SYS", "ST.E.STRONG.SYS"],
+     "K1 register path, AdamW, bf16 gradients, 8 peers"),
+    ("push_fused_tma_kernelILi0ELi1E", ["UBLKCP", "SYNCS", "STG.E"], "K1 bulk-copy path (SGD)"),
+    ("colsum_bf16_kernel", ["LDG", "STG", "ATOM", "BAR"], "bias-gradient column sum"),
+]
+MNEMONICS = (r"\b(LDTM|SYNCS|UBLKCP|UCGABAR|UTCATOMSWS|UTCBAR|UTCHMMA|UTMALDG|UTMASTG|UTMACCTL|"
+             r"UGETNEXTWORKID|UTMACMDFLUSH|LDG\.E[A-Z0-9.]*256|STG\.E[A-Z0-9.]*256)[A-Za-z0-9_.]*")
+
+
+def main() -> int:
+    sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    funcs, cur = {}, None
+    for line in sass.split("\n"):
+        m = re.match(r"\s*Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            funcs[cur] = []
+        elif cur and re.match(r"\s+/\*[0-9a-f]{4}\*/", line):
+            funcs[cur].append(re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", line).rstrip())
+    out = ["# Excerpts of `cuobjdump -sass parameter_server_distributed_b200/_native/libpsb_kernels.so` (sm_100a):",
+           "# the instructions that prove each mechanism, with two lines of context; '...' marks a gap.",
+           "# Regenerate with `python benchmarks/sass_excerpts.py`.  Full counts: sass_mnemonics.txt."]
+    for sub, pats, title in SECTIONS:
+        name = next((k for k in funcs if sub in k), None)
+        if name is None:
+            print("missing kernel", sub, file=sys.stderr)
+            return 1
+        ins = funcs[name]
+        keep = set()
+        for i, l in enumerate(ins):
+            if any(p in l for p in pats):
+                keep.update(range(max(0, i - 2), min(len(ins), i + 3)))
+        out += ["", f"## {title}", f"# {name}  ({len(ins)} instructions)"]
+        last = -2
+        for n, i in enumerate(sorted(keep)):
+            if n >= 140:
+                break
+            if i != last + 1:
+                out.append("        ...")
+            out.append(ins[i])
+            last = i
+    with open(os.path.join(ROOT, "profiles", "sass_excerpts.txt"), "w") as f:
+        f.write("\n".join(out) + "\n")
+    counts = {}
+    for m in re.finditer(MNEMONICS, sass):
+        counts[m.group(0)] = counts.get(m.group(0), 0) + 1
+    with open(os.path.join(ROOT, "profiles", "sass_mnemonics.txt"), "w") as f:
+        for k in sorted(counts):
+            f.write(f"{counts[k]:7d} {k}\n")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
