@@ -20,7 +20,13 @@ HDRS := $(wildcard csrc/*/*.h) include/psb_kernels.h
 obj = $(patsubst csrc/%.cpp,$(OBJ)/%.o,$(1))
 
 all: binaries kernels
-binaries: $(BIN)/coordinator $(BIN)/parameter_server $(BIN)/worker_main $(BIN)/psb_selftest $(BIN)/psb_pbtool
+CONTROL_LIB := parameter_server_distributed_b200/_native/libpsb_control$(if $(SAN),-$(SAN),).so
+binaries: $(BIN)/coordinator $(BIN)/parameter_server $(BIN)/worker_main $(BIN)/psb_selftest $(BIN)/psb_pbtool $(CONTROL_LIB)
+
+# native coordinator client of the Python package (C ABI: include/psb_control.h); no CUDA
+$(CONTROL_LIB): $(WIRE_SRC) csrc/control/client.cpp $(HDRS) include/psb_control.h
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -fPIC -shared $(WIRE_SRC) csrc/control/client.cpp -o $@
 
 $(OBJ)/%.o: csrc/%.cpp $(HDRS)
 	@mkdir -p $(dir $@)

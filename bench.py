@@ -101,20 +101,14 @@ class Workload:
 
 
 def max_over_ranks(x: float, ctx) -> float:
-    import torch
-    import torch.distributed as dist
-    if ctx.world == 1:
-        return x
-    t = torch.tensor([x], dtype=torch.float64, device=ctx.device)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    """Max over the ranks, through the job's control plane (coordinator, else torch.distributed)."""
+    return ctx.reduce_max(x, "bench/max")
 
 
 def host_barrier(ctx):
     import torch
-    import torch.distributed as dist
-    if ctx.world > 1:
-        dist.barrier()
+    torch.cuda.synchronize(ctx.device)
+    ctx.barrier("bench")
     torch.cuda.synchronize(ctx.device)
 
 

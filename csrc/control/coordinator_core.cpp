@@ -128,6 +128,14 @@ int32_t CoordinatorCore::update_clock(int32_t worker_id, int32_t clock) {
 
 void CoordinatorCore::put_handle(const std::string& key, int32_t rank, const std::string& blob) {
   std::lock_guard<std::mutex> lk(mu_);
+  if (blob.empty()) {  // an empty blob withdraws the entry (keeps repeated exchanges bounded)
+    auto it = handles_.find(key);
+    if (it != handles_.end()) {
+      it->second.erase(rank);
+      if (it->second.empty()) handles_.erase(it);
+    }
+    return;
+  }
   handles_[key][rank] = blob;
 }
 

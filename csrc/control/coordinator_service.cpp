@@ -150,11 +150,19 @@ void run_coordinator_server(const std::string& server_address, const std::string
   if (const char* e = std::getenv("PSB_STALE_SCAN_MS")) scan_ms = std::atoi(e);
   if (const char* e = std::getenv("PSB_STALE_TIMEOUT_S")) timeout_s = std::atoi(e);
   CoordinatorService svc(ps_address, ps_port, scan_ms, timeout_s);
-  if (svc.listen(server_address) < 0) {
+  const int bound = svc.listen(server_address);
+  if (bound < 0) {
     std::cerr << "coordinator failed to listen on " << server_address << std::endl;
     std::exit(1);
   }
-  std::cout << "coordinator listening on " << server_address << std::endl;
+  std::string shown = server_address;  // port 0 = "pick one": show the port that was picked
+  {
+    std::string h;
+    int p = -1;
+    if (grpc_lite::split_host_port(server_address, h, p) && p == 0)
+      shown = h + ":" + std::to_string(bound);
+  }
+  std::cout << "coordinator listening on " << shown << std::endl;
   std::cout << "parameter server: " << ps_address << ":" << ps_port << std::endl;
   svc.serve_forever();
 }

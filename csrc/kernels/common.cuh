@@ -75,6 +75,17 @@ __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" 
 // sticky CUDA error) and the GPU is free again.  The limit is a per-device word in every
 // translation unit that waits (static __device__), set by psb_set_spin_timeout_ms().
 static __device__ unsigned long long g_spin_limit_ns = 300ull * 1000000000ull;
+// Abort word: a 32-bit word in host-mapped memory (psb_abort_word_create).  The control plane
+// sets it when a peer was evicted (control/client.cpp: psbc_watch); spin-waits then give up and
+// return instead of running into the watchdog's trap, so the CUDA context of the surviving
+// ranks stays usable (they can still write a checkpoint or leave cleanly).  Data produced by a
+// kernel that gave up is undefined — the caller must not use it.
+static __device__ const uint32_t* g_abort_word = nullptr;
+
+__device__ __forceinline__ bool abort_requested() {
+  const uint32_t* w = g_abort_word;
+  return w != nullptr && *reinterpret_cast<const volatile uint32_t*>(w) != 0u;
+}
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -85,11 +96,14 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 struct SpinWatch {
   unsigned long long t0 = 0;
   uint32_t n = 0;
-  __device__ __forceinline__ void tick() {
-    if ((++n & 1023u) != 0) return;  // look at the clock once per 1024 polls
+  // true: stop waiting (the job is being torn down, see g_abort_word)
+  __device__ __forceinline__ bool tick() {
+    if ((++n & 1023u) != 0) return false;  // look at the clock / abort word once per 1024 polls
+    if (abort_requested()) return true;
     const unsigned long long now = globaltimer_ns();
     if (t0 == 0) t0 = now;
     else if (now - t0 > g_spin_limit_ns) __trap();
+    return false;
   }
 };
 
@@ -97,9 +111,15 @@ struct SpinWatch {
 static inline cudaError_t set_spin_limit_in_this_unit(unsigned long long ns) {
   return cudaMemcpyToSymbol(g_spin_limit_ns, &ns, sizeof(ns));
 }
+static inline cudaError_t set_abort_word_in_this_unit(const uint32_t* dev_ptr) {
+  return cudaMemcpyToSymbol(g_abort_word, &dev_ptr, sizeof(dev_ptr));
+}
 #define PSB_EXPORT_SPIN_LIMIT(tag)                                         \
   extern "C" int psb_spin_limit_##tag(unsigned long long ns) {             \
     return (int)psb::set_spin_limit_in_this_unit(ns);                      \
+  }                                                                        \
+  extern "C" int psb_abort_word_##tag(const uint32_t* dev_ptr) {           \
+    return (int)psb::set_abort_word_in_this_unit(dev_ptr);                 \
   }
 
 // spin until *p >= target (wrap-safe signed distance)
@@ -107,7 +127,7 @@ __device__ __forceinline__ void wait_ge_sys(const uint32_t* p, uint32_t target) 
   SpinWatch watch;
   while ((int32_t)(ld_acquire_sys(p) - target) < 0) {
     __nanosleep(32);
-    watch.tick();
+    if (watch.tick()) return;
   }
 }
 

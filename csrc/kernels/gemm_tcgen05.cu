@@ -341,7 +341,11 @@ __global__ void __launch_bounds__(THREADS, 1)
         order.decode(t, m_blk, n_blk);
         if (p.fused && n_blk / n_per_rank != p.rank) {
           // gathered tile: wait until every chunk of it has landed in the local replica
-          while (ld_acquire_gpu(p.tile_flags + n_blk) < chunks_per_tile) __nanosleep(64);
+          SpinWatch watch;
+          while (ld_acquire_gpu(p.tile_flags + n_blk) < chunks_per_tile) {
+            __nanosleep(64);
+            if (watch.tick()) break;
+          }
           fence_proxy_async();
         }
         for (int kb = 0; kb < num_k; ++kb) {

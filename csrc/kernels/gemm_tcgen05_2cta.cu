@@ -454,7 +454,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
         int m_blk, n_blk;
         decode(t, m_blk, n_blk);
         if (p.fused && n_blk / n_per_rank != p.rank) {
-          while (ld_acquire_gpu(p.tile_flags + n_blk) < chunks_per_tile) __nanosleep(64);
+          SpinWatch watch;  // the gather behind this flag waits on peers: same watchdog
+          while (ld_acquire_gpu(p.tile_flags + n_blk) < chunks_per_tile) {
+            __nanosleep(64);
+            if (watch.tick()) break;
+          }
           fence_proxy_async();
         }
         for (int kb = 0; kb < num_k; ++kb) {

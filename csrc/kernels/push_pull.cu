@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a)
           SpinWatch watch;
           while ((v = ld_acquire_sys(vpad + owner)) & 1u) {
             __nanosleep(64);
-            watch.tick();
+            if (watch.tick()) break;
           }
           v0s = v;
         }
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a)
           v1s = ld_acquire_sys(vpad + owner);
         }
         __syncthreads();
-        const bool stable = v1s == v0s;
+        const bool stable = v1s == v0s || abort_requested();
         __syncthreads();  // nobody may still be comparing when thread 0 rewrites v0s
         if (stable) break;
       }
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(32)
       w = ld_acquire_sys_u64(src);
       if ((int32_t)((uint32_t)(w >> 32) - s) >= 0) break;
       __nanosleep(32);
-      watch.tick();
+      if (watch.tick()) break;
     } while (true);
     got = __uint_as_float((uint32_t)w);
   }
@@ -653,6 +653,38 @@ PSB_EXPORT_SPIN_LIMIT(push_pull)
 extern "C" int psb_spin_limit_push_tma(unsigned long long ns);
 extern "C" int psb_spin_limit_gemm1(unsigned long long ns);
 extern "C" int psb_spin_limit_gemm2(unsigned long long ns);
+
+extern "C" int psb_abort_word_push_tma(const uint32_t* p);
+extern "C" int psb_abort_word_gemm1(const uint32_t* p);
+extern "C" int psb_abort_word_gemm2(const uint32_t* p);
+
+// Host-mapped abort word (see common.cuh).  create: allocates the word (zero), points the
+// kernels of the CURRENT device at it and returns its host address; the caller (or the control
+// plane's heartbeat thread) stores 1 there to make every peer spin-wait on this device give up.
+extern "C" int psb_abort_word_create(uint32_t** host_word) {
+  PSB_REQUIRE(host_word, PSB_EINVAL, "psb_abort_word_create: null argument");
+  uint32_t* h = nullptr;
+  PSB_CUDA_OK(cudaHostAlloc(reinterpret_cast<void**>(&h), sizeof(uint32_t),
+                            cudaHostAllocMapped | cudaHostAllocPortable));
+  *h = 0u;
+  uint32_t* d = nullptr;
+  PSB_CUDA_OK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), h, 0));
+  int (*setters[])(const uint32_t*) = {psb_abort_word_push_pull, psb_abort_word_push_tma,
+                                       psb_abort_word_gemm1, psb_abort_word_gemm2};
+  for (auto set : setters) PSB_CUDA_OK((cudaError_t)set(d));
+  *host_word = h;
+  return 0;
+}
+
+// Detaches the kernels of the current device from the word and frees it.
+extern "C" int psb_abort_word_destroy(uint32_t* host_word) {
+  int (*setters[])(const uint32_t*) = {psb_abort_word_push_pull, psb_abort_word_push_tma,
+                                       psb_abort_word_gemm1, psb_abort_word_gemm2};
+  for (auto set : setters) PSB_CUDA_OK((cudaError_t)set(nullptr));
+  PSB_CUDA_OK(cudaDeviceSynchronize());
+  if (host_word) PSB_CUDA_OK(cudaFreeHost(host_word));
+  return 0;
+}
 
 extern "C" int psb_set_spin_timeout_ms(uint64_t ms) {
   PSB_REQUIRE(ms >= 1, PSB_EINVAL, "psb_set_spin_timeout_ms: the limit must be at least 1 ms");

@@ -33,16 +33,25 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
   if (iteration > current_iteration_.load()) current_iteration_.store(iteration);
 
   if (opt_.mode != PsMode::kSync) {
-    // async / SSP: apply this worker's contribution at once, scaled like one share of the mean
-    const float share = 1.0f / static_cast<float>(std::max(1, total_workers_.load()));
-    std::vector<HostTensor> scaled = grads;
-    for (auto& t : scaled)
-      for (auto& x : t.data) x *= share;
-    apply_locked(scaled);
-    clocks_[worker_id] = std::max(clocks_.count(worker_id) ? clocks_[worker_id] : -1, iteration);
+    // async / SSP: apply this worker's contribution at once, scaled like one share of the mean.
+    // A clock is applied once: the transport re-sends an RPC whose connection died after the
+    // request may already have been delivered, and such a duplicate must not count twice.
+    auto ck = clocks_.find(worker_id);
+    if (ck != clocks_.end() && iteration <= ck->second) return true;
+    if (params_.empty()) {
+      apply_locked(grads);  // bootstrap from the unscaled tensor, as in sync mode
+    } else {
+      const float share = 1.0f / static_cast<float>(std::max(1, total_workers_.load()));
+      std::vector<HostTensor> scaled = grads;
+      for (auto& t : scaled)
+        for (auto& x : t.data) x *= share;
+      apply_locked(scaled);
+    }
+    clocks_[worker_id] = iteration;
     IterState& st = iters_[iteration];
     st.seen[worker_id] = true;
     st.aggregated = true;
+    prune_locked();
     return true;
   }
 
@@ -50,19 +59,27 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
   if (st.aggregated) return true;  // idempotent retry after completion
   st.staged[worker_id] = grads;    // a re-push from the same worker overwrites its slot
   st.seen[worker_id] = true;
-  const size_t count = st.staged.size();
-  if (count < static_cast<size_t>(std::max(1, total_workers_.load()))) return false;
+  if (st.staged.size() < static_cast<size_t>(std::max(1, total_workers_.load()))) return false;
+  // names / shapes / dtypes come from the completing push
+  aggregate_locked(st, grads);
+  prune_locked();
+  return true;
+}
 
-  // names / shapes / dtypes come from the completing push; shorter contributions are truncated
-  std::vector<HostTensor> mean(grads.size());
-  for (size_t i = 0; i < grads.size(); ++i) {
+// Mean over the staged contributions in ascending worker id (deterministic summation order),
+// shaped like `tmpl`; shorter contributions are truncated element-wise (reference semantics,
+// src/parameter_server.cpp:40-63).
+void ParameterServerCore::aggregate_locked(IterState& st, const std::vector<HostTensor>& tmpl) {
+  const size_t count = st.staged.size();
+  std::vector<HostTensor> mean(tmpl.size());
+  for (size_t i = 0; i < tmpl.size(); ++i) {
     HostTensor& a = mean[i];
-    a.name = grads[i].name;
-    a.shape = grads[i].shape;
-    a.dtype = grads[i].dtype;
-    const size_t n = grads[i].data.size();
+    a.name = tmpl[i].name;
+    a.shape = tmpl[i].shape;
+    a.dtype = tmpl[i].dtype;
+    const size_t n = tmpl[i].data.size();
     a.data.assign(n, 0.0f);
-    for (const auto& kv : st.staged) {  // ascending worker id: deterministic summation order
+    for (const auto& kv : st.staged) {
       if (i >= kv.second.size()) continue;
       const std::vector<float>& g = kv.second[i].data;
       const size_t lim = std::min(n, g.size());
@@ -74,8 +91,31 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
   apply_locked(mean);
   st.aggregated = true;
   st.staged.clear();  // the reference keeps every copy forever
+}
+
+void ParameterServerCore::prune_locked() {
   while (static_cast<int>(iters_.size()) > opt_.keep_iterations) iters_.erase(iters_.begin());
-  return true;
+}
+
+// Membership change (a worker was evicted by the coordinator, or came back).  Iterations that
+// were waiting for the missing worker are re-evaluated at once and complete with the mean of
+// the live workers' gradients — the reference keeps total_workers fixed for the life of the
+// process and stalls for ever (src/coordinator.cpp:52-67 evicts,
+// src/parameter_main.cpp:13-15 never hears of it).
+int ParameterServerCore::set_total_workers(int n) {
+  std::lock_guard<std::mutex> lk(mu_);
+  total_workers_.store(n);
+  int completed = 0;
+  if (opt_.mode != PsMode::kSync) return 0;
+  const size_t need = static_cast<size_t>(std::max(1, n));
+  for (auto& kv : iters_) {  // ascending iteration
+    IterState& st = kv.second;
+    if (st.aggregated || st.staged.empty() || st.staged.size() < need) continue;
+    const std::vector<HostTensor> tmpl = st.staged.rbegin()->second;  // copy: staged is cleared
+    aggregate_locked(st, tmpl);
+    ++completed;
+  }
+  return completed;
 }
 
 void ParameterServerCore::apply_locked(const std::vector<HostTensor>& g) {
@@ -98,7 +138,13 @@ void ParameterServerCore::apply_locked(const std::vector<HostTensor>& g) {
 void ParameterServerCore::update_tensor(size_t idx, const std::vector<float>& g) {
   std::vector<float>& p = params_[idx].data;
   const size_t n = std::min(p.size(), g.size());
-  if (dev_ && dev_->update(idx, g.data(), n, opt_step_)) return;
+  if (dev_ && dev_->active()) {
+    if (dev_->update(idx, g.data(), n, opt_step_)) return;
+    // the launch failed: fetch the newest moments and weights (the download retires the GPU
+    // copy), then this and every later update run on the host
+    dev_->download_state(m_, v_);
+    dev_->download(params_);
+  }
   const std::string& kind = opt_.optimizer;
   const float lr = opt_.lr, wd = opt_.weight_decay;
   if (kind == "sgd") {
@@ -196,7 +242,13 @@ bool ParameterServerCore::write_file(int32_t epoch, const std::string& path) {
 
 bool ParameterServerCore::save_checkpoint(int32_t epoch, const std::string& path) {
   std::lock_guard<std::mutex> lk(mu_);
-  if (dev_) dev_->download(params_);
+  if (dev_) {
+    // moments of an HBM-resident shard live only on the device: without this the sidecar would
+    // carry opt_step_ with empty m / v and a resumed Adam would run late-step bias correction
+    // on zero moments
+    if (!dev_->download(params_)) return false;
+    if (!dev_->download_state(m_, v_)) return false;
+  }
   if (!write_file(epoch, path)) return false;
   // sidecar: optimizer state and mode, so the base file stays loadable by the reference
   bool has_state = false;
@@ -293,7 +345,7 @@ bool ParameterServerCore::load_checkpoint(const std::string& path, int32_t& epoc
       }
     }
   }
-  if (dev_) dev_->upload(params_);
+  if (dev_ && dev_->upload(params_)) dev_->upload_state(m_, v_);
   version_++;
   return true;
 }

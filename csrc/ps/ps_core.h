@@ -59,13 +59,18 @@ class ParameterServerCore {
   bool load_checkpoint(const std::string& path, int32_t& epoch);
 
   int get_total_workers() const { return total_workers_.load(); }
-  void set_total_workers(int n) { total_workers_.store(n); }  // eviction shrinks the barrier
+  // Follow the coordinator's registry: pending sync iterations that are complete for the new
+  // count aggregate at once.  Returns how many iterations that completed.
+  int set_total_workers(int n);
   int32_t get_current_iteration() const { return current_iteration_.load(); }
   int64_t version() const { return version_.load(); }
   const PsOptions& options() const { return opt_; }
 
  private:
+  struct IterState;
   void apply_locked(const std::vector<HostTensor>& mean_grads);
+  void aggregate_locked(IterState& st, const std::vector<HostTensor>& tmpl);
+  void prune_locked();
   void update_tensor(size_t idx, const std::vector<float>& g);
   bool write_file(int32_t epoch, const std::string& path);
 

@@ -35,6 +35,8 @@ struct DeviceShard::Impl {
   };
   std::vector<Slot> slots;
   bool dirty = false;  // device copy is newer than the host copy
+  bool disabled = false;       // allocation / copy failure: the host path owns the shard
+  bool failed_update = false;  // a launch failed: retire the GPU copy at the next download
 
   void free_slots() {
     for (auto& s : slots) {
@@ -98,32 +100,53 @@ DeviceShard::~DeviceShard() {
   delete impl_;
 }
 
-void DeviceShard::upload(const std::vector<HostTensor>& params) {
+bool DeviceShard::active() const { return impl_ && !impl_->disabled; }
+
+bool DeviceShard::upload(const std::vector<HostTensor>& params) {
   Impl& im = *impl_;
   im.set_device(im.opt.device);
   im.free_slots();
+  im.disabled = false;
   im.slots.resize(params.size());
   const bool need_m = im.opt.optimizer != "sgd";
   const bool need_v = im.opt.optimizer == "adam" || im.opt.optimizer == "adamw";
-  for (size_t i = 0; i < params.size(); ++i) {
+  bool ok = true;
+  // every allocation is checked: psb_heap_alloc leaves *ptr untouched on failure, so a reused
+  // pointer would silently alias two buffers
+  auto alloc = [&](size_t bytes) -> void* {
+    void* p = nullptr;
+    if (!ok || im.heap_alloc(bytes, &p) != 0 || !p) {
+      ok = false;
+      return nullptr;
+    }
+    return p;
+  };
+  for (size_t i = 0; i < params.size() && ok; ++i) {
     Impl::Slot& s = im.slots[i];
     s.n = params[i].data.size();
     if (s.n == 0) continue;
     const size_t bytes = s.n * sizeof(float);
-    void* p = nullptr;
-    im.heap_alloc(bytes, &p), s.master = static_cast<float*>(p);
-    im.heap_alloc(bytes, &p), s.grad = static_cast<float*>(p);
-    if (need_m) im.heap_alloc(bytes, &p), s.m = static_cast<float*>(p);
-    if (need_v) im.heap_alloc(bytes, &p), s.v = static_cast<float*>(p);
-    im.heap_alloc(256, &p), s.step = static_cast<uint32_t*>(p);
-    im.h2d(s.master, params[i].data.data(), bytes, nullptr);
+    s.master = static_cast<float*>(alloc(bytes));
+    s.grad = static_cast<float*>(alloc(bytes));
+    if (need_m) s.m = static_cast<float*>(alloc(bytes));
+    if (need_v) s.v = static_cast<float*>(alloc(bytes));
+    s.step = static_cast<uint32_t*>(alloc(256));
+    if (ok && im.h2d(s.master, params[i].data.data(), bytes, nullptr) != 0) ok = false;
   }
-  im.stream_sync(nullptr);
+  if (ok && im.stream_sync(nullptr) != 0) ok = false;
+  if (!ok) {
+    std::cerr << "device shard disabled (falling back to the host path): " << im.last_error()
+              << std::endl;
+    im.free_slots();
+    im.disabled = true;
+  }
   im.dirty = false;
+  return ok;
 }
 
 bool DeviceShard::update(size_t idx, const float* grad, size_t n, int64_t opt_step) {
   Impl& im = *impl_;
+  if (im.disabled) return false;
   if (idx >= im.slots.size() || im.slots[idx].n == 0 || n != im.slots[idx].n) return false;
   Impl::Slot& s = im.slots[idx];
   im.set_device(im.opt.device);
@@ -134,29 +157,84 @@ bool DeviceShard::update(size_t idx, const float* grad, size_t n, int64_t opt_st
   o.lr = im.opt.lr, o.momentum = im.opt.momentum, o.beta1 = im.opt.beta1, o.beta2 = im.opt.beta2;
   o.eps = im.opt.eps, o.weight_decay = im.opt.weight_decay, o.grad_scale = 1.0f;
   const uint32_t completed = static_cast<uint32_t>(opt_step > 0 ? opt_step - 1 : 0);
-  im.h2d(s.step, &completed, sizeof(completed), nullptr);
-  im.h2d(s.grad, grad, n * sizeof(float), nullptr);
-  int rc = im.optim_step(&o, s.master, s.m, s.v, s.grad, PSB_F32, nullptr, n, nullptr, s.step,
-                         nullptr);
+  int rc = im.h2d(s.step, &completed, sizeof(completed), nullptr);
+  if (rc == 0) rc = im.h2d(s.grad, grad, n * sizeof(float), nullptr);
+  if (rc == 0)
+    rc = im.optim_step(&o, s.master, s.m, s.v, s.grad, PSB_F32, nullptr, n, nullptr, s.step,
+                       nullptr);
+  // the staged host gradient may be reused by the caller, so the copy must have finished
+  if (rc == 0) rc = im.stream_sync(nullptr);
   if (rc != 0) {
-    std::cerr << "device update failed: " << im.last_error() << std::endl;
+    // The device copy of this tensor can no longer be trusted as the newest one.  Bring back
+    // what is still readable, then stop using the GPU: the host path continues from there.
+    std::cerr << "device update failed (" << im.last_error() << "): shard falls back to the host"
+              << std::endl;
+    im.failed_update = true;
     return false;
   }
-  im.stream_sync(nullptr);  // the staged host gradient may be reused by the caller
   im.dirty = true;
   return true;
 }
 
-void DeviceShard::download(std::vector<HostTensor>& params) {
+bool DeviceShard::download(std::vector<HostTensor>& params) {
   Impl& im = *impl_;
-  if (!im.dirty) return;
+  if (im.disabled || !im.dirty) return true;
   im.set_device(im.opt.device);
+  bool ok = true;
   for (size_t i = 0; i < params.size() && i < im.slots.size(); ++i) {
     if (im.slots[i].n == 0 || im.slots[i].n != params[i].data.size()) continue;
-    im.d2h(params[i].data.data(), im.slots[i].master, im.slots[i].n * sizeof(float), nullptr);
+    ok = ok && im.d2h(params[i].data.data(), im.slots[i].master, im.slots[i].n * sizeof(float),
+                      nullptr) == 0;
   }
-  im.stream_sync(nullptr);
+  ok = ok && im.stream_sync(nullptr) == 0;
+  if (!ok) {
+    std::cerr << "device download failed: " << im.last_error() << std::endl;
+    return false;
+  }
   im.dirty = false;
+  if (im.failed_update) {  // host copy is current again: retire the GPU copy for good
+    im.free_slots();
+    im.disabled = true;
+  }
+  return true;
+}
+
+bool DeviceShard::download_state(std::vector<std::vector<float>>& m,
+                                 std::vector<std::vector<float>>& v) {
+  Impl& im = *impl_;
+  if (im.disabled) return true;
+  im.set_device(im.opt.device);
+  bool ok = true;
+  for (size_t i = 0; i < im.slots.size(); ++i) {
+    const Impl::Slot& s = im.slots[i];
+    if (s.n == 0) continue;
+    if (s.m && i < m.size()) {
+      m[i].resize(s.n);
+      ok = ok && im.d2h(m[i].data(), s.m, s.n * sizeof(float), nullptr) == 0;
+    }
+    if (s.v && i < v.size()) {
+      v[i].resize(s.n);
+      ok = ok && im.d2h(v[i].data(), s.v, s.n * sizeof(float), nullptr) == 0;
+    }
+  }
+  return ok && im.stream_sync(nullptr) == 0;
+}
+
+bool DeviceShard::upload_state(const std::vector<std::vector<float>>& m,
+                               const std::vector<std::vector<float>>& v) {
+  Impl& im = *impl_;
+  if (im.disabled) return true;
+  im.set_device(im.opt.device);
+  bool ok = true;
+  for (size_t i = 0; i < im.slots.size(); ++i) {
+    const Impl::Slot& s = im.slots[i];
+    if (s.n == 0) continue;
+    if (s.m && i < m.size() && m[i].size() == s.n)
+      ok = ok && im.h2d(s.m, m[i].data(), s.n * sizeof(float), nullptr) == 0;
+    if (s.v && i < v.size() && v[i].size() == s.n)
+      ok = ok && im.h2d(s.v, v[i].data(), s.n * sizeof(float), nullptr) == 0;
+  }
+  return ok && im.stream_sync(nullptr) == 0;
 }
 
 }  // namespace psb

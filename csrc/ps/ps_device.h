@@ -16,9 +16,19 @@ class DeviceShard {
  public:
   static DeviceShard* create(const PsOptions& opt);  // nullptr when CUDA / the library is missing
   ~DeviceShard();
-  void upload(const std::vector<HostTensor>& params);
+  // Allocates the slots and copies the parameters in.  On any allocation or copy failure the
+  // slots are released and the shard disables itself: update() then answers false and the
+  // caller's host path takes over.  Returns whether the shard is usable.
+  bool upload(const std::vector<HostTensor>& params);
   bool update(size_t idx, const float* grad, size_t n, int64_t opt_step);
-  void download(std::vector<HostTensor>& params);
+  // false: a copy failed and `params` may be stale (the caller keeps its host copy)
+  bool download(std::vector<HostTensor>& params);
+  // Optimizer moments for the checkpoint sidecar: device -> host before a save, host -> device
+  // after a load (sizes that do not match a slot are left alone).
+  bool download_state(std::vector<std::vector<float>>& m, std::vector<std::vector<float>>& v);
+  bool upload_state(const std::vector<std::vector<float>>& m,
+                    const std::vector<std::vector<float>>& v);
+  bool active() const;
 
  private:
   DeviceShard() = default;

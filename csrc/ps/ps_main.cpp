@@ -4,6 +4,8 @@
 // Extensions are trailing --key=value flags or PSB_* environment variables:
 //   --mode=sync|async|ssp  --staleness=N  --optimizer=sgd|momentum|adam|adamw  --lr=F
 //   --momentum=F --beta1=F --beta2=F --eps=F --weight-decay=F  --device=N (HBM-resident shard)
+//   --coordinator=host:port  --membership-poll-ms=N   follow the coordinator's worker registry:
+//       an evicted worker no longer blocks the sync barrier (PSB_COORDINATOR, PSB_MEMBERSHIP_POLL_MS)
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -33,6 +35,10 @@ int main(int argc, char** argv) {
   if (const char* e = env("PSB_OPTIMIZER")) opt.optimizer = e;
   if (const char* e = env("PSB_LR")) opt.lr = std::strtof(e, nullptr);
   if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
+  std::string coordinator;
+  int membership_poll_ms = 1000;
+  if (const char* e = env("PSB_COORDINATOR")) coordinator = e;
+  if (const char* e = env("PSB_MEMBERSHIP_POLL_MS")) membership_poll_ms = std::atoi(e);
   std::vector<std::string> pos;
   for (int i = 1; i < argc; ++i) {
     std::string a = argv[i], v;
@@ -48,6 +54,8 @@ int main(int argc, char** argv) {
     else if (flag(a, "eps", v)) opt.eps = std::strtof(v.c_str(), nullptr);
     else if (flag(a, "weight-decay", v)) opt.weight_decay = std::strtof(v.c_str(), nullptr);
     else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
+    else if (flag(a, "coordinator", v)) coordinator = v;
+    else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
     else if (a.rfind("--", 0) == 0) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;
@@ -56,6 +64,6 @@ int main(int argc, char** argv) {
   if (pos.size() > 0) listen = pos[0];
   if (pos.size() > 1) total_workers = std::stoi(pos[1]);
   if (pos.size() > 2) checkpoint_interval = std::stoi(pos[2]);
-  psb::run_server(listen, total_workers, checkpoint_interval, opt);
+  psb::run_server(listen, total_workers, checkpoint_interval, opt, coordinator, membership_poll_ms);
   return 0;
 }

@@ -34,7 +34,7 @@ pb::Tensor to_pb(HostTensor&& h) {
 ParameterServerService::ParameterServerService(int total_workers, int checkpoint_interval,
                                                const PsOptions& opt, int checkpoint_scan_ms)
     : core_(total_workers, opt), checkpoint_interval_(checkpoint_interval),
-      scan_ms_(checkpoint_scan_ms) {
+      scan_ms_(checkpoint_scan_ms), configured_workers_(total_workers) {
   const std::string base = "/parameter_server.ParameterServer/";
   server_.add(base + "ReceiveGradients", [this](const std::string& req, std::string& resp) {
     pb::GradientUpdate in;
@@ -137,6 +137,41 @@ void ParameterServerService::periodic_checkpoint() {
   }
 }
 
+void ParameterServerService::follow_membership(const std::string& coordinator_address,
+                                               int poll_ms) {
+  if (coordinator_address.empty() || membership_thread_.joinable()) return;
+  membership_thread_ = std::thread(&ParameterServerService::membership_loop, this,
+                                   coordinator_address, poll_ms > 0 ? poll_ms : 1000);
+}
+
+void ParameterServerService::membership_loop(std::string coordinator_address, int poll_ms) {
+  grpc_lite::Channel coord(coordinator_address);
+  bool seen_full = false;  // never shrink before every configured worker has registered once
+  int waited = poll_ms;
+  while (running_) {
+    if (waited < poll_ms) {
+      std::this_thread::sleep_for(std::chrono::milliseconds(20));
+      waited += 20;
+      continue;
+    }
+    waited = 0;
+    std::string resp;
+    Status s = coord.call("/coordinator.Coordinator/ListWorkers", std::string(), resp, 2000);
+    pb::ListWorkersResponse lw;
+    if (!s.ok() || !lw.decode(resp)) continue;  // coordinator away: keep the current count
+    const int live = static_cast<int>(lw.workers.size());
+    if (live >= configured_workers_) seen_full = true;
+    int target = configured_workers_;
+    if (seen_full && live >= 1 && live < configured_workers_) target = live;
+    const int cur = core_.get_total_workers();
+    if (target != cur) {
+      const int completed = core_.set_total_workers(target);
+      std::cout << "membership: total_workers " << cur << " -> " << target << " (" << live
+                << " live), " << completed << " pending iteration(s) completed" << std::endl;
+    }
+  }
+}
+
 int ParameterServerService::listen(const std::string& address) { return server_.listen(address); }
 void ParameterServerService::serve_forever() { server_.serve_forever(); }
 void ParameterServerService::start() { server_.start(); }
@@ -145,11 +180,13 @@ void ParameterServerService::shutdown() {
   if (running_.exchange(false)) {
     server_.shutdown();
     if (checkpoint_thread_.joinable()) checkpoint_thread_.join();
+    if (membership_thread_.joinable()) membership_thread_.join();
   }
 }
 
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
-                const PsOptions& opt) {
+                const PsOptions& opt, const std::string& coordinator_address,
+                int membership_poll_ms) {
   int scan_ms = 5000;
   if (const char* e = std::getenv("PSB_CHECKPOINT_SCAN_MS")) scan_ms = std::atoi(e);
   ParameterServerService svc(total_workers, checkpoint_interval, opt, scan_ms);
@@ -161,6 +198,10 @@ void run_server(const std::string& server_address, int total_workers, int checkp
   if (checkpoint_interval > 0)
     std::cout << "periodic checkpointing every " << checkpoint_interval << " iterations"
               << std::endl;
+  if (!coordinator_address.empty()) {
+    svc.follow_membership(coordinator_address, membership_poll_ms);
+    std::cout << "following worker membership of coordinator " << coordinator_address << std::endl;
+  }
   svc.serve_forever();
 }
 

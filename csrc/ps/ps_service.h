@@ -15,6 +15,13 @@ class ParameterServerService {
  public:
   ParameterServerService(int total_workers, int checkpoint_interval, const PsOptions& opt,
                          int checkpoint_scan_ms = 5000);
+  // Follow the coordinator's worker registry (ListWorkers every `poll_ms`): once the job has
+  // been complete, an eviction shrinks the sync barrier to the live workers and pending
+  // iterations complete with their mean; a worker that re-registers grows it back (never above
+  // the configured count).  The reference's coordinator and parameter server never talk
+  // (SURVEY D9); this uses the reference's own ListWorkers RPC, so it also works against a
+  // reference coordinator.
+  void follow_membership(const std::string& coordinator_address, int poll_ms = 1000);
   ~ParameterServerService();
   int listen(const std::string& address);
   void serve_forever();
@@ -24,17 +31,21 @@ class ParameterServerService {
 
  private:
   void periodic_checkpoint();
+  void membership_loop(std::string coordinator_address, int poll_ms);
   ParameterServerCore core_;
   grpc_lite::Server server_;
   int checkpoint_interval_;
   int scan_ms_;
   std::thread checkpoint_thread_;
+  std::thread membership_thread_;
+  int configured_workers_;
   std::atomic<bool> running_{true};
 };
 
 // Blocking entry point with the reference's signature and log lines
 // (include/parameter_server_service.h:5, src/parameter_server_service.cpp:177-191).
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
-                const PsOptions& opt = PsOptions());
+                const PsOptions& opt = PsOptions(), const std::string& coordinator_address = "",
+                int membership_poll_ms = 1000);
 
 }  // namespace psb

@@ -311,6 +311,17 @@ int psb_pad_post(const PsbFabric* fabric, uint32_t word_base, uint32_t value, ps
 // the device current).  No counterpart in the reference, whose host-side waits poll for ever
 // (src/worker.cpp:293-306).
 int psb_set_spin_timeout_ms(uint64_t ms);
+// Abort word: the soft counterpart of the watchdog.  psb_abort_word_create allocates one 32-bit
+// word of host-mapped memory, points the spin-waits of the CURRENT device at it and returns its
+// host address.  Whoever stores 1 there — the coordinator client's heartbeat thread when a peer
+// was evicted (psbc_watch, include/psb_control.h), or the application — makes every kernel that
+// is waiting on a peer's flag return within ~0.1 ms instead of trapping after the watchdog
+// limit: the CUDA context survives, so the rank can leave cleanly (the results of kernels that
+// gave up are undefined; training resumes from the last checkpoint with the smaller world).
+// The reference has no counterpart: its workers wait for a dead peer's iteration for ever
+// (src/worker.cpp:372-397).
+int psb_abort_word_create(uint32_t** host_word);
+int psb_abort_word_destroy(uint32_t* host_word);
 
 // ---------------------------------------------------------------------------
 // K2f — bf16 GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed

@@ -147,6 +147,8 @@ def _declare(lib) -> None:
         "psb_async_gate": (i32, [C.POINTER(PsbAsync), u32, i32, vp]),
         "psb_set_spin_timeout_ms": (i32, [C.c_uint64]),
         "psb_pad_post": (i32, [C.POINTER(PsbFabric), u32, u32, vp]),
+        "psb_abort_word_create": (i32, [C.POINTER(vp)]),
+        "psb_abort_word_destroy": (i32, [vp]),
         "psb_sumsq_noalloc": (i32, [vp, i32, sz, vp, vp]),
         "psb_gemm_select": (i32, [i32]),
         "psb_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, vp]),

@@ -403,15 +403,18 @@ class ShardedParameterServer:
     # ------------------------------------------------------------------ shard state <-> names
     def gather_state(self, which: str = "master", group=None) -> Dict[str, torch.Tensor]:
         """Reassemble a sharded fp32 state (``master`` / ``m`` / ``v``) into named tensors on
-        every rank.  Control-plane path (checkpoints, tests): uses torch.distributed."""
-        import torch.distributed as dist
+        every rank.  Control-plane path (checkpoints, tests).  On CUDA the shards are read from
+        the peers through the symmetric heap; the host backend uses its gloo group."""
         be = self.backend
         shard = getattr(be, which)
         if shard is None:
             return {}
         if self.is_cuda:
             torch.cuda.synchronize(self.device)
-        if self.world > 1:
+        if self.world > 1 and self.is_cuda:
+            parts = self.fabric.all_gather(shard)
+        elif self.world > 1:
+            import torch.distributed as dist
             parts = [torch.empty_like(shard) for _ in range(self.world)]
             dist.all_gather(parts, shard.contiguous(), group=group)
         else:

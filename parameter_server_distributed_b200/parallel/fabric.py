@@ -56,6 +56,17 @@ class SymBuffer:
     def peer_ptrs(self) -> List[int]:
         return [self.peer_ptr(r) for r in range(self.fabric.world)]
 
+    def peer(self, r: int) -> torch.Tensor:
+        """uint8 view of rank ``r``'s copy (reads / writes go over NVLink)."""
+        if r == self.fabric.rank:
+            return self.local
+        return _wrap(self.peer_ptr(r), self.nbytes, self.fabric.device)
+
+    def free(self) -> None:
+        """Give the range back to the heap.  Collective in the same sense as ``alloc``: every
+        rank frees the same buffers in the same order, and nothing may still be using it."""
+        self.fabric._free(self)
+
 
 class Fabric:
     """Peer-mapped heap and signal pad of one rank."""
@@ -96,6 +107,7 @@ class Fabric:
                         self._opened.append(q.value)
         self.heap_u8 = _wrap(self.heap_base[rank], self.heap_bytes, self.device)
         self._cursor = 0
+        self._holes: List[List[int]] = []  # free ranges [offset, nbytes] below the cursor, sorted
         self.pad = self.alloc(self.pad_bytes(), align=4096)
         self._barrier_seq = torch.zeros(64, dtype=torch.int32, device=self.device)
         self._cfab = PsbFabric()
@@ -107,6 +119,17 @@ class Fabric:
     @staticmethod
     def pad_bytes() -> int:
         return _lib.PAD_WORDS * 4
+
+    @classmethod
+    def from_coordinator(cls, coord, device: torch.device, heap_bytes: int) -> "Fabric":
+        """One rank per process; the handles of the heap segments travel through the
+        coordinator's blob exchange (PutHandle / GetHandles + Barrier, proto/psb_ext.proto) —
+        the role the reference gives its coordinator for addresses
+        (/root/reference/src/worker.cpp:141-186)."""
+        fab = cls(coord.rank, coord.world, device, heap_bytes,
+                  exchange=lambda h: coord.allgather("fabric/heap", h))
+        coord.barrier("fabric/mapped")  # every peer has mapped every segment before first use
+        return fab
 
     @classmethod
     def from_process_group(cls, device: torch.device, heap_bytes: int, group=None) -> "Fabric":
@@ -144,15 +167,70 @@ class Fabric:
 
     # ------------------------------------------------------------------ allocation
     def alloc(self, nbytes: int, align: int = 256) -> SymBuffer:
+        """Sub-allocate ``nbytes`` at the same offset on every rank.  First fit in the ranges
+        that were freed, else at the end; deterministic, so ranks that issue the same sequence
+        of ``alloc`` / ``free`` calls stay symmetric."""
+        nbytes = int(nbytes)
+        for i, (lo, size) in enumerate(self._holes):
+            off = (lo + align - 1) // align * align
+            if off + nbytes <= lo + size:
+                rest = []
+                if off > lo:
+                    rest.append([lo, off - lo])
+                if off + nbytes < lo + size:
+                    rest.append([off + nbytes, lo + size - off - nbytes])
+                self._holes[i:i + 1] = rest
+                return SymBuffer(self, off, nbytes)
         off = (self._cursor + align - 1) // align * align
         if off + nbytes > self.heap_bytes:
             raise MemoryError(f"symmetric heap exhausted: need {off + nbytes} of {self.heap_bytes} B")
+        if off > self._cursor:
+            self._holes.append([self._cursor, off - self._cursor])
         self._cursor = off + nbytes
-        return SymBuffer(self, off, int(nbytes))
+        return SymBuffer(self, off, nbytes)
+
+    def _free(self, buf: SymBuffer) -> None:
+        if buf.nbytes <= 0:
+            return
+        self._holes.append([buf.offset, buf.nbytes])
+        self._holes.sort()
+        merged: List[List[int]] = []
+        for lo, size in self._holes:
+            if merged and merged[-1][0] + merged[-1][1] >= lo:
+                merged[-1][1] = max(merged[-1][1], lo + size - merged[-1][0])
+            else:
+                merged.append([lo, size])
+        if merged and merged[-1][0] + merged[-1][1] >= self._cursor:  # trailing hole: shrink
+            self._cursor = merged.pop()[0]
+        self._holes = merged
+        buf.nbytes = 0
 
     def free_bytes(self) -> int:
-        """Bytes of the symmetric heap not handed out yet (same value on every rank)."""
-        return self.heap_bytes - self._cursor
+        """Largest allocation that is certain to succeed (same value on every rank)."""
+        tail = self.heap_bytes - self._cursor
+        return max([tail] + [size for _, size in self._holes])
+
+    def all_gather(self, t: torch.Tensor) -> List[torch.Tensor]:
+        """Copies of every rank's ``t`` (same shape / dtype everywhere), through the symmetric
+        heap: stage locally, device barrier, read the peers' staging ranges over NVLink.
+        Control-path helper (checkpoints, tests) — replaces ``torch.distributed.all_gather``."""
+        if self.world == 1:
+            return [t.clone()]
+        flat = t.contiguous().view(-1).view(torch.uint8)
+        emulated = not self._owns
+        if emulated:
+            raise RuntimeError("Fabric.all_gather needs one process per rank")
+        with torch.cuda.device(self.device):
+            stage = self.alloc(flat.numel(), align=256)
+            stage.local.copy_(flat)
+            if not emulated:
+                self.barrier(2)
+            out = [stage.peer(r).clone().view(t.dtype).view(t.shape) for r in range(self.world)]
+            if not emulated:
+                self.barrier(2)
+            torch.cuda.synchronize()
+            stage.free()
+        return out
 
     def c_fabric(self) -> PsbFabric:
         return self._cfab

@@ -22,32 +22,90 @@ from .parallel.fabric import Fabric
 
 @dataclass
 class Context:
+    """One rank of a job: identity, device, symmetric heap, and the host-side control plane
+    (``coord``: the C++ coordinator; else a ``torch.distributed`` group; else single rank)."""
     rank: int
     world: int
     local_rank: int
     device: torch.device
     fabric: Optional[Fabric]
+    coord: Optional[object] = None   # control.client.CoordinatorClient
+    abort: Optional[object] = None   # utils.elastic.AbortWord
+
+    # ---- host-side collectives of the control plane (small, off the training path)
+    def barrier(self, name: str = "host") -> None:
+        if self.world == 1:
+            return
+        if self.coord is not None:
+            self.coord.barrier(name)
+        elif dist.is_initialized():
+            dist.barrier()
+
+    def all_gather_object(self, obj, key: str = "obj") -> list:
+        if self.world == 1:
+            return [obj]
+        if self.coord is not None:
+            return self.coord.allgather_object(key, obj)
+        out = [None] * self.world
+        dist.all_gather_object(out, obj)
+        return out
+
+    def reduce_max(self, x: float, key: str = "max") -> float:
+        return max(self.all_gather_object(float(x), key))
+
+    @property
+    def peer_lost(self) -> bool:
+        """A peer was evicted by the coordinator (missed heartbeats) since ``init``."""
+        return self.coord is not None and self.coord.peer_lost
 
     def close(self) -> None:
+        if self.coord is not None:
+            self.coord.watch(0)
         if self.fabric is not None:
             self.fabric.close()
+            self.fabric = None
+        if self.abort is not None:
+            self.abort.close()
+            self.abort = None
+        if self.coord is not None:
+            self.coord.close()
+            self.coord = None
         if dist.is_initialized():
             dist.destroy_process_group()
 
 
 def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
-         spin_timeout_s: Optional[float] = None) -> Context:
-    """Join the job described by RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* (torchrun) and
-    build the symmetric heap.  ``torch.distributed`` is used only as control plane (handle
-    exchange, host barriers); the data plane is peer memory.
+         spin_timeout_s: Optional[float] = None, control: Optional[str] = None) -> Context:
+    """Join the job described by RANK / LOCAL_RANK / WORLD_SIZE (torchrun, or
+    scripts/deploy_box.sh) and build the symmetric heap.
+
+    Control plane (``control`` / ``PSB_CONTROL``):
+
+    * ``"coordinator"`` — default for CUDA jobs with more than one rank: every rank registers
+      with the C++ coordinator (``PSB_COORDINATOR=host:port``; under plain torchrun rank 0
+      launches ``build/bin/coordinator`` itself), heartbeats from a native thread, registers its
+      PS shard, exchanges the heap handles and synchronises on the host through it — the
+      bootstrap of the reference's workers (/root/reference/src/worker.cpp:108-122, 141-186,
+      216-238).  No ``torch.distributed`` process group exists in this mode.
+    * ``"dist"`` — ``torch.distributed`` (gloo on CPU: the host backend moves its data through
+      it; nccl on CUDA) as control plane.
 
     ``spin_timeout_s`` (or ``PSB_SPIN_TIMEOUT_S``; kernel default 300 s): how long a kernel may
     wait on a flag of a peer before it traps — a dead peer then surfaces as a CUDA error on this
-    rank instead of a GPU that spins for ever."""
+    rank instead of a GPU that spins for ever.  With the coordinator the heartbeat thread
+    normally gets there first: an evicted peer raises the abort word and waiting kernels
+    return (``Context.peer_lost``)."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
     cuda = torch.cuda.is_available()
+    control = control or os.environ.get("PSB_CONTROL")
+    if control is None:
+        from .control import client as _client
+        want = cuda and (world > 1 or "PSB_COORDINATOR" in os.environ)
+        control = "coordinator" if want and _client.available() else "dist"
+    if control not in ("coordinator", "dist"):
+        raise ValueError(f"unknown control plane {control!r}")
     if cuda:
         torch.cuda.set_device(local_rank)
         device = torch.device("cuda", local_rank)
@@ -59,6 +117,20 @@ def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
                        "psb_set_spin_timeout_ms")
     else:
         device = torch.device("cpu")
+    coord = abort = None
+    if control == "coordinator":
+        from .control.client import ensure_coordinator
+        coord = ensure_coordinator(rank, world)
+        if cuda:
+            coord.register_shard(rank, f"hbm://{os.uname().nodename}/gpu{local_rank}", local_rank)
+            fabric = Fabric.from_coordinator(coord, device, heap_bytes)
+            from .utils.elastic import AbortWord
+            abort = AbortWord()           # host-mapped word polled by every peer spin-wait
+            coord.barrier("init/registered")
+            coord.watch(world, abort.host_ptr)
+        else:
+            fabric = None
+        return Context(rank, world, local_rank, device, fabric, coord, abort)
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
@@ -87,11 +159,16 @@ class Trainer:
                  optim: OptimConfig, *, mode: str = "sync", bucket_mb: float = 64.0,
                  pull: str = "broadcast", clip_norm: Optional[float] = None,
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
-                 staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None):
+                 staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None,
+                 checkpoint_every: int = 0, checkpoint_path: Optional[str] = None):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
         ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
-        fused into the first GEMM of the next forward (K2f)."""
+        fused into the first GEMM of the next forward (K2f).
+
+        ``checkpoint_every`` / ``checkpoint_path``: write a checkpoint (reference format +
+        sidecar, atomically) every so many steps; it is what the surviving ranks restart from
+        after a :class:`~parameter_server_distributed_b200.utils.elastic.PeerLost`."""
         if mode not in ("sync", "async", "ssp"):
             raise ValueError(f"unknown mode {mode!r}")
         self.model, self.loss_fn, self.ctx = model, loss_fn, ctx
@@ -123,6 +200,11 @@ class Trainer:
         if dedicated and pull in ("gather", "hybrid"):
             from .parallel.fused_linear import FusedFirstLinear
             model.first_linear_fn = FusedFirstLinear(self.ps, dedicated[0])
+        self.checkpoint_every = int(checkpoint_every)
+        self.checkpoint_path = checkpoint_path
+        if self.checkpoint_every and not checkpoint_path:
+            raise ValueError("checkpoint_every needs a checkpoint_path")
+        self.steps = 0
         self._dev_inputs = None
         self._loss_ring = None
         self._ring_i = 0
@@ -146,15 +228,35 @@ class Trainer:
         from .utils.checkpoint import load_checkpoint
         return load_checkpoint(self.ps, path)
 
+    # ------------------------------------------------------------------ failure handling
+    def _guard(self) -> None:
+        """Before any launch of a step: has the coordinator evicted a peer?  Its heartbeat
+        thread has then already raised the abort word, so kernels that were waiting for the dead
+        rank have returned; nothing computed since is trustworthy."""
+        if self.ctx.peer_lost:
+            from .utils.elastic import PeerLost
+            raise PeerLost(f"rank {self.ctx.rank}: a peer left the job (coordinator reports "
+                           f"{self.ctx.coord.live_workers()} of {self.ctx.world} workers alive); "
+                           f"restart from the last checkpoint"
+                           + (f" ({self.checkpoint_path})" if self.checkpoint_path else ""))
+
+    def _after_step(self) -> None:
+        self.steps += 1
+        if self.checkpoint_every and self.steps % self.checkpoint_every == 0:
+            self._guard()  # never publish a checkpoint of a step that a lost peer left half done
+            self.save_checkpoint(self.checkpoint_path, epoch=self.steps // self.checkpoint_every)
+
     # ------------------------------------------------------------------ device-resident step
     def step_device(self, *inputs: torch.Tensor) -> torch.Tensor:
         """Forward + backward + push/pull on tensors already on the device; returns the loss
         tensor (on device)."""
+        self._guard()
         *xs, target = inputs
         out = self.model(*xs)
         loss = self.loss_fn(out, target)
         loss.backward()
         self.ps.step()
+        self._after_step()
         return loss.detach()
 
     # ------------------------------------------------------------------ end-to-end step
@@ -166,6 +268,7 @@ class Trainer:
         if self.device.type != "cuda":
             loss = self.step_device(*host_inputs)
             return LossHandle(loss.reshape(()).float(), None)
+        self._guard()
         if self._dev_inputs is None:
             self._dev_inputs = [[torch.empty(t.shape, dtype=t.dtype, device=self.device)
                                  for t in host_inputs] for _ in range(2)]
@@ -205,4 +308,5 @@ class Trainer:
         done = torch.cuda.Event()
         done.record(cur)
         self._consumed[slot] = done
+        self._after_step()
         return LossHandle(host, ev)

@@ -28,9 +28,20 @@ if [ "$MODE" = "gpu" ]; then
   python -c "import sys; sys.path.insert(0, '$ROOT'); from parameter_server_distributed_b200 import _build; _build.build_kernels()"
   SCRIPT="${1:-$ROOT/bench.py}"
   [ $# -gt 0 ] && shift
-  echo "[2/4] launching ${GPUS} ranks (one worker + one PS shard per GPU): $SCRIPT $*"
-  exec python -m torch.distributed.run --nnodes=1 --nproc-per-node "$GPUS" \
-    --master-addr 127.0.0.1 --master-port "${MASTER_PORT:-29500}" "$SCRIPT" --gpus "$GPUS" "$@"
+  echo "[2/4] starting coordinator on :$COORDINATOR_PORT"
+  COORDINATOR_PORT="$COORDINATOR_PORT" PS_ADDRESS="127.0.0.1:$PS_PORT" BINARY_PATH="$BIN/coordinator" \
+    LOG_FILE="$RUN_DIR/coordinator.log" PID_FILE="$RUN_DIR/coordinator.pid" \
+    bash "$ROOT/scripts/start_coordinator.sh"
+  trap 'kill "$(cat "$RUN_DIR/coordinator.pid")" 2>/dev/null || true' EXIT
+  echo "[3/4] launching ${GPUS} ranks (one worker + one PS shard per GPU): $SCRIPT $*"
+  echo "      the ranks register, exchange heap handles and synchronise through the coordinator"
+  # the launcher only sets RANK / LOCAL_RANK / WORLD_SIZE; membership, shard map, handle
+  # exchange and host barriers go through the coordinator (PSB_COORDINATOR)
+  PSB_COORDINATOR="127.0.0.1:$COORDINATOR_PORT" python -m torch.distributed.run --nnodes=1 \
+    --nproc-per-node "$GPUS" --master-addr 127.0.0.1 --master-port "${MASTER_PORT:-29500}" \
+    "$SCRIPT" --gpus "$GPUS" "$@"
+  echo "[4/4] done; coordinator log: $RUN_DIR/coordinator.log"
+  exit 0
 fi
 
 echo "[2/4] starting coordinator on :$COORDINATOR_PORT"
@@ -39,6 +50,7 @@ COORDINATOR_PORT="$COORDINATOR_PORT" PS_ADDRESS="127.0.0.1:$PS_PORT" BINARY_PATH
   bash "$ROOT/scripts/start_coordinator.sh"
 echo "[3/4] starting parameter server on :$PS_PORT for $WORKER_COUNT workers"
 PS_PORT="$PS_PORT" TOTAL_WORKERS="$WORKER_COUNT" CHECKPOINT_INTERVAL="$CHECKPOINT_INTERVAL" \
+  COORDINATOR_ADDR="127.0.0.1:$COORDINATOR_PORT" \
   BINARY_PATH="$BIN/parameter_server" LOG_FILE="$RUN_DIR/parameter_server.log" \
   PID_FILE="$RUN_DIR/parameter_server.pid" PS_WORKDIR="$RUN_DIR" PS_FLAGS="${PS_FLAGS:-}" \
   bash "$ROOT/scripts/start_parameter_server.sh"

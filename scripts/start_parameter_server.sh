@@ -1,8 +1,10 @@
 #!/bin/bash
 # Start a parameter-server shard in the background.  Environment contract of the reference
 # script: PS_PORT, TOTAL_WORKERS, CHECKPOINT_INTERVAL, BINARY_PATH, LOG_FILE.  Additions:
-# PID_FILE, PS_WORKDIR (checkpoints are written to the server's cwd) and PS_FLAGS for the
-# trailing --mode= / --optimizer= / --lr= / --device= extensions.
+# PID_FILE, PS_WORKDIR (checkpoints are written to the server's cwd), PS_FLAGS for the
+# trailing --mode= / --optimizer= / --lr= / --device= extensions, and COORDINATOR_ADDR: when
+# set the server follows the coordinator's worker registry, so an evicted worker stops
+# blocking the sync barrier (the reference's two services never talk).
 set -euo pipefail
 
 PS_PORT="${PS_PORT:-50051}"
@@ -12,6 +14,7 @@ BINARY_PATH="${BINARY_PATH:-/opt/parameter-server/parameter_server}"
 LOG_FILE="${LOG_FILE:-/var/log/parameter_server.log}"
 PID_FILE="${PID_FILE:-/var/run/parameter_server.pid}"
 PS_FLAGS="${PS_FLAGS:-}"
+if [ -n "${COORDINATOR_ADDR:-}" ]; then PS_FLAGS="$PS_FLAGS --coordinator=${COORDINATOR_ADDR}"; fi
 
 if [ -n "${PS_WORKDIR:-}" ]; then cd "$PS_WORKDIR"; fi
 # shellcheck disable=SC2086

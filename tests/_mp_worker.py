@@ -1,6 +1,7 @@
 """Multi-GPU worker script (one rank per GPU, launched by torch.distributed.run from
 test_multigpu.py).  Checks the real cross-rank protocol of K1/K2/K2f over NVLink peer memory
-against NCCL collectives + PyTorch fp32 math.  Prints 'MP_OK <rank>' on success."""
+against PyTorch fp32 math, with the C++ coordinator as the only control plane (no
+torch.distributed process group is created).  Prints 'MP_OK <rank>' on success."""
 import os
 import sys
 
@@ -8,7 +9,6 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 import torch
-import torch.distributed as dist
 
 import parameter_server_distributed_b200 as psd
 from parameter_server_distributed_b200 import OptimConfig
@@ -76,8 +76,7 @@ def check_training(ctx, pull, kind, clip, tma=False):
             assert abs(got - tot ** 0.5) < 2e-2 * tot ** 0.5, (it, got, tot ** 0.5)
     # all ranks hold identical replicas
     flat = tr.ps.backend.param_flat.clone()
-    ref0 = flat.clone()
-    dist.broadcast(ref0, 0)
+    ref0 = ctx.fabric.all_gather(flat)[0]
     assert torch.equal(flat, ref0), "replicas diverged"
     tr.ps.close()
 
@@ -96,7 +95,7 @@ def check_fused_gemm(ctx):
     t.zero_()
     t[rank * rows:(rank + 1) * rows].copy_(w_full[rank * rows:(rank + 1) * rows])
     torch.cuda.synchronize()
-    dist.barrier()
+    ctx.barrier()
     x = (torch.randn(M, K, device=ctx.device) * 0.5).to(torch.bfloat16)
     y = torch.empty(M, N, dtype=torch.bfloat16, device=ctx.device)
     a = _lib.PsbGemmAG()
@@ -113,7 +112,8 @@ def check_fused_gemm(ctx):
     err = (y.float() - exp).abs().max().item() / exp.abs().max().item()
     assert err < 1.5e-2, err
     assert torch.equal(t, w_full), "gathered weight differs"
-    dist.barrier()
+    ctx.barrier()
+    buf.free()
 
 
 class _Vec(torch.nn.Module):
@@ -167,16 +167,73 @@ def check_async(ctx, staleness):
         assert torch.allclose(got, exp, rtol=1e-5, atol=1e-5), (k, got.flatten()[:3], exp.flatten()[:3])
         assert torch.equal(p.detach(), got.to(torch.bfloat16)), f"replica of {k} is not the master"
     flat = ps.backend.param_flat.clone()
-    ref0 = flat.clone()
-    dist.broadcast(ref0, 0)
+    ref0 = ctx.fabric.all_gather(flat)[0]
     assert torch.equal(flat, ref0), "async replicas diverged after drain"
     ps.close()
     return worst
 
 
+def check_tracks_oracle(ctx):
+    """A run whose loss MOVES: 200 steps of a teacher-student regression at lr 0.1 through the
+    sharded parameter server must follow a single-process fp32 run on the global batch.  At the
+    noise floor of random targets a wrong reduction hides; here a missing or doubled worker
+    changes the trajectory by far more than the tolerance."""
+    torch.manual_seed(21)
+    cfg = MLPConfig(d_in=256, hidden=(512,), d_out=256)
+    teacher = MLP(cfg).to(ctx.device, torch.float32)
+    model = MLP(cfg).to(ctx.device, torch.bfloat16)
+    oracle = MLP(cfg).to(ctx.device, torch.float32)
+    oracle.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
+    opt = torch.optim.SGD(oracle.parameters(), lr=0.1)
+    tr = psd.Trainer(model, mse_loss, ctx, OptimConfig(kind="sgd", lr=0.1), bucket_mb=0.25)
+    gen = torch.Generator(device="cpu").manual_seed(77)
+    B = 128
+    first = last = olast = None
+    for it in range(200):
+        x = torch.randn(ctx.world, B, cfg.d_in, generator=gen)
+        with torch.no_grad():
+            y = teacher(x.to(ctx.device).view(-1, cfg.d_in)).view(ctx.world, B, cfg.d_out)
+        loss = tr.step_device(x[ctx.rank].to(ctx.device, torch.bfloat16),
+                              y[ctx.rank].to(torch.bfloat16))
+        opt.zero_grad()
+        ol = torch.nn.functional.mse_loss(oracle(x.to(ctx.device).view(-1, cfg.d_in)),
+                                          y.view(-1, cfg.d_out))
+        ol.backward()
+        opt.step()
+        if it == 0:
+            first = float(ol.item())
+        last, olast = float(loss.item()), float(ol.item())
+    mean_last = sum(ctx.all_gather_object(last, "oracle/loss")) / ctx.world
+    assert olast < 0.5 * first, ("the oracle itself did not learn", first, olast)
+    assert abs(mean_last - olast) < 0.15 * olast + 1e-4, \
+        ("loss left the fp32 oracle's trajectory", mean_last, olast, first)
+    worst = 0.0
+    for (n, p), (_, q) in zip(model.named_parameters(), oracle.named_parameters()):
+        rel = (p.float() - q).norm().item() / (q.norm().item() + 1e-12)
+        worst = max(worst, rel)
+    assert worst < 0.05, ("weights left the fp32 oracle's trajectory", worst)
+    tr.ps.close()
+    return first, olast, mean_last, worst
+
+
+def check_control_plane(ctx):
+    """The coordinator is the membership / shard-assignment authority of the GPU plane."""
+    assert ctx.coord is not None, "the GPU plane did not come up through the coordinator"
+    assert not torch.distributed.is_initialized(), "a torch.distributed group exists"
+    assert ctx.coord.list_workers() == list(range(ctx.world)), ctx.coord.list_workers()
+    shards, total = ctx.coord.shard_map()
+    assert [s[0] for s in shards] == list(range(ctx.world)) and total == ctx.world, (shards, total)
+    assert sorted(s[2] for s in shards) == list(range(ctx.world)), shards  # one GPU each
+    got = ctx.all_gather_object({"rank": ctx.rank}, "cp/obj")
+    assert [g["rank"] for g in got] == list(range(ctx.world))
+    assert ctx.reduce_max(float(ctx.rank), "cp/max") == ctx.world - 1
+
+
 def main():
     ctx = psd.init(heap_bytes=256 << 20)
     assert ctx.world >= 2
+    check_control_plane(ctx)
+    _log("control plane ok")
     check_fused_gemm(ctx)
     _log("fused gemm ok")
     for pull, kind, clip, tma in [("broadcast", "sgd", None, False), ("broadcast", "adamw", 0.5, False),
@@ -184,13 +241,18 @@ def main():
                                   ("broadcast", "sgd", None, True), ("gather", "adamw", None, True),
                                   ("hybrid", "momentum", None, True), ("hybrid", "adamw", 1.0, False)]:
         check_training(ctx, pull, kind, clip, tma)
-        dist.barrier()
+        ctx.barrier()
         _log(f"training {pull} {kind} tma={tma} ok")
     for st in (None, 1, 0):
         worst = check_async(ctx, st)
-        dist.barrier()
+        ctx.barrier()
         if ctx.rank == 0:
             print(f"async staleness={st}: worst observed lag {worst}", flush=True)
+    first, olast, mine, wrel = check_tracks_oracle(ctx)
+    ctx.barrier()
+    if ctx.rank == 0:
+        print(f"oracle tracking: loss {first:.4f} -> oracle {olast:.5f} / ours {mine:.5f}, "
+              f"worst relative weight distance {wrel:.4f}", flush=True)
     print(f"MP_OK {ctx.rank}", flush=True)
     ctx.close()
 

@@ -1,0 +1,176 @@
+"""T7: a worker dies -> the coordinator evicts it -> the parameter server's sync
+barrier shrinks and the live workers carry on; plus the native coordinator client that gives the
+GPU ranks the same membership view (barriers, blob exchange, peer-loss watch).
+
+The reference stalls for ever in this situation (D9: /root/reference/src/coordinator.cpp:52-67
+evicts, src/parameter_main.cpp:13-15 keeps total_workers fixed, nobody tells anybody)."""
+import ctypes as C
+import multiprocessing as mp
+import os
+import re
+import signal
+import subprocess
+import time
+
+import pytest
+
+from parameter_server_distributed_b200.control import client as cc
+from tests._native import BIN, Proc, ensure_binaries, free_port, wait_port
+
+ensure_binaries()
+
+FAST = {"PSB_STALE_SCAN_MS": "100", "PSB_STALE_TIMEOUT_S": "1"}
+
+
+def _done_lines(text):
+    return [(int(m.group(1)), m.group(2) == "true")
+            for m in re.finditer(r"iter (\d+) done=(true|false)", text)]
+
+
+def test_dead_worker_no_longer_stalls_the_parameter_server(tmp_path):
+    """Kill 1 of 3 C++ workers mid-run: the other two reach done=true on every iteration."""
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"), env=FAST)
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "3", "0",
+               f"--coordinator=127.0.0.1:{co_port}", "--membership-poll-ms=100"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    workers = []
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        iters = 1500
+        for wid in range(3):
+            n = iters if wid < 2 else 10_000_000  # worker 2 never finishes on its own
+            workers.append(Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(wid), str(n),
+                                 "--heartbeat-ms=100", "--sync-timeout-ms=8000"], str(tmp_path),
+                                str(tmp_path / f"w{wid}.log")))
+        # let the job get going, then kill worker 2 without ceremony
+        end = time.time() + 20
+        while time.time() < end and len(_done_lines(workers[0].output())) < 20:
+            time.sleep(0.02)
+        assert len(_done_lines(workers[0].output())) >= 20, workers[0].output()[-300:]
+        workers[2].p.send_signal(signal.SIGKILL)
+        killed_at = len(_done_lines(workers[0].output()))
+        for w in workers[:2]:
+            w.p.wait(timeout=120)
+        for wid in (0, 1):
+            lines = _done_lines(workers[wid].output())
+            assert len(lines) == iters, (wid, len(lines))
+            assert all(ok for _, ok in lines), [i for i, ok in lines if not ok][:5]
+        assert killed_at < iters, "worker 2 was killed after the others had finished"
+        out = ps.output()
+        assert "following worker membership of coordinator" in out
+        assert re.search(r"membership: total_workers 3 -> 2 \(2 live\)", out), out[-400:]
+        assert "evicted stale worker 2" in co.output()
+    finally:
+        for w in workers:
+            w.stop()
+        ps.stop()
+        co.stop()
+
+
+def test_worker_that_returns_grows_the_barrier_back(tmp_path):
+    """ParameterServerCore::set_total_workers through the service: 2 configured, one evicted,
+    then it registers again — the count follows (never above the configured one)."""
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"), env=FAST)
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0",
+               f"--coordinator=127.0.0.1:{co_port}", "--membership-poll-ms=50"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        a = cc.CoordinatorClient(f"127.0.0.1:{co_port}", 0, 2, heartbeat_ms=100)
+        b = cc.CoordinatorClient(f"127.0.0.1:{co_port}", 1, 2, heartbeat_ms=100)
+        assert a.ps_address == f"127.0.0.1:{ps_port}"
+        time.sleep(0.4)
+        b.close()  # heartbeats of worker 1 stop -> eviction after ~1 s
+        end = time.time() + 10
+        while time.time() < end and "total_workers 2 -> 1" not in ps.output():
+            time.sleep(0.05)
+        assert "membership: total_workers 2 -> 1 (1 live)" in ps.output()
+        b = cc.CoordinatorClient(f"127.0.0.1:{co_port}", 1, 2, heartbeat_ms=100)
+        end = time.time() + 10
+        while time.time() < end and "total_workers 1 -> 2" not in ps.output():
+            time.sleep(0.05)
+        assert "membership: total_workers 1 -> 2 (2 live)" in ps.output()
+        a.close()
+        b.close()
+    finally:
+        ps.stop()
+        co.stop()
+
+
+# ------------------------------------------------------------------ native coordinator client
+def _rank(rank, world, addr, q, die):
+    try:
+        c = cc.CoordinatorClient(addr, rank, world, heartbeat_ms=100)
+        c.register_shard(rank, f"hbm://test/gpu{rank}", rank)
+        c.barrier("up")
+        got = c.allgather("handles", bytes([rank]) * 64)
+        objs = c.allgather_object("objs", {"rank": rank, "pad": "x" * (rank * 100)})
+        mx = c.reduce_max("mx", float(rank))
+        for _ in range(3):  # the same key again: rounds must not mix
+            again = c.allgather("handles", bytes([rank + 10]) * 64)
+        shards, total = c.shard_map()
+        word = C.c_uint32(0)
+        c.barrier("registered")
+        c.watch(world, C.addressof(word))
+        if rank == die:
+            os._exit(0)  # no close(): heartbeats simply stop
+        t0 = time.time()
+        while not c.peer_lost and time.time() - t0 < 15:
+            time.sleep(0.02)
+        q.put((rank, [g[0] for g in got], [o["rank"] for o in objs], mx, [a[0] for a in again],
+               shards, total, c.peer_lost, word.value, c.list_workers()))
+        c.close()
+    except BaseException as e:  # noqa: BLE001
+        q.put((rank, "error", repr(e)))
+
+
+def test_ranks_bootstrap_and_watch_each_other_through_the_coordinator(tmp_path):
+    """What psd.init() does on a GPU box, minus the GPUs: register, shard map, handle exchange,
+    barrier, small all-gathers — then one rank dies and the others are told (abort word set)."""
+    proc, addr = cc.spawn_coordinator(env=FAST, log_path=str(tmp_path / "co.log"))
+    try:
+        world, die = 3, 2
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        ps = [ctx.Process(target=_rank, args=(r, world, addr, q, die)) for r in range(world)]
+        for p in ps:
+            p.start()
+        res = {}
+        for _ in range(world - 1):
+            r = q.get(timeout=60)
+            assert r[1] != "error", r
+            res[r[0]] = r
+        for p in ps:
+            p.join(timeout=10)
+        for rank in (0, 1):
+            _, got, objs, mx, again, shards, total, lost, word, alive = res[rank]
+            assert got == [0, 1, 2] and objs == [0, 1, 2] and mx == 2.0
+            assert again == [10, 11, 12]
+            assert [(s[0], s[2]) for s in shards] == [(0, 0), (1, 1), (2, 2)] and total == 3
+            assert shards[1][1] == "hbm://test/gpu1"
+            assert lost and word == 1, "the survivor was not told about the lost peer"
+            assert alive == [0, 1]
+    finally:
+        cc._stop(proc)
+
+
+def test_ensure_coordinator_rendezvous(tmp_path, monkeypatch):
+    """The torchrun case: nobody started a coordinator; rank 0 launches the binary and the
+    address reaches the other ranks through the rendezvous file."""
+    monkeypatch.setenv("PSB_RENDEZVOUS_DIR", str(tmp_path))
+    monkeypatch.setenv("MASTER_PORT", "31999")
+    monkeypatch.delenv("PSB_COORDINATOR", raising=False)
+    c0 = cc.ensure_coordinator(0, 2, heartbeat_ms=200)
+    c1 = cc.ensure_coordinator(1, 2, heartbeat_ms=200)
+    assert c0.address == c1.address
+    assert c0._proc is not None and c1._proc is None
+    assert c0.list_workers() == [0, 1]
+    c1.close()
+    proc = c0._proc
+    c0.close()
+    assert not os.listdir(tmp_path), os.listdir(tmp_path)
+    assert proc.poll() is not None, "the coordinator launched by rank 0 outlived it"

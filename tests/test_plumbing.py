@@ -90,11 +90,13 @@ def test_async_mode_applies_each_push_and_ssp_bounds_staleness(tmp_path):
             worker_id=wid, iteration=it, gradients=[T("w", [v] * 8)]), timeout=5)
         pull = lambda wid, it: stub.ServeParameters(M("parameter_server.PullRequest")(
             worker_id=wid, iteration=it), timeout=5)
-        assert push(0, 0, 1.0).aggregation_complete       # bootstrap: params = share of the push
+        assert push(0, 0, 1.0).aggregation_complete       # bootstrap: the push becomes the model
         w = np.array(pull(0, 1).parameters[0].data)
-        assert np.allclose(w, 0.5)                         # 1.0 / total_workers
+        assert np.allclose(w, 1.0)                         # unscaled, as in sync mode (D8)
         assert push(0, 1, 0.2).aggregation_complete        # applied at once: no barrier
-        assert np.allclose(np.array(pull(0, 1).parameters[0].data), 0.5 - 0.1)
+        assert np.allclose(np.array(pull(0, 1).parameters[0].data), 1.0 - 0.1)  # share = 1/2
+        push(0, 1, 0.2)                                    # a re-sent clock is not applied twice
+        assert np.allclose(np.array(pull(0, 1).parameters[0].data), 1.0 - 0.1)
         # worker 1 never pushed: it has completed 0 clocks, so clock 2 of worker 0 is 2 ahead
         assert pull(0, 1).ready            # 1 - 0 <= 1
         assert not pull(0, 2).ready        # 2 - 0 >  1
