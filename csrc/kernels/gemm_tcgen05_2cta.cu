@@ -665,11 +665,13 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
-static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols) {
+// `ld`: elements between two rows of the source (0 = packed)
+static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
+                    uint64_t ld = 0) {
   EncodeTiledFn enc = get_encode();
   PSB_REQUIRE(enc, PSB_EUNSUPPORTED, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {cols * 2};
+  cuuint64_t strides[1] = {(ld ? ld : cols) * 2};
   cuuint32_t box[2] = {(cuuint32_t)BK, 128};
   cuuint32_t elem[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
@@ -681,11 +683,12 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
 }
 
 // MN-major source: `red` rows of `mn` contiguous elements; one box = one 64-element atom
-static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_t mn) {
+static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_t mn,
+                       uint64_t ld = 0) {
   EncodeTiledFn enc = get_encode();
   PSB_REQUIRE(enc, PSB_EUNSUPPORTED, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t dims[2] = {mn, red};
-  cuuint64_t strides[1] = {mn * 2};
+  cuuint64_t strides[1] = {(ld ? ld : mn) * 2};
   cuuint32_t box[2] = {64, (cuuint32_t)BK};
   cuuint32_t elem[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
@@ -718,10 +721,13 @@ static bool clc_enabled() {
   return on;
 }
 
-static int launch(const void* a, const void* b, const Params& p, int epi, cudaStream_t s) {
+static int launch(const void* a, const void* b, const Params& p, int epi, cudaStream_t s,
+                  int lda = 0, int ldb = 0) {
   CUtensorMap map_a, map_b;
-  if (int rc = p.a_mn ? make_map_mn(&map_a, a, p.K, p.M) : make_map(&map_a, a, p.M, p.K)) return rc;
-  if (int rc = p.b_mn ? make_map_mn(&map_b, b, p.K, p.N) : make_map(&map_b, b, p.N, p.K)) return rc;
+  if (int rc = p.a_mn ? make_map_mn(&map_a, a, p.K, p.M, lda) : make_map(&map_a, a, p.M, p.K, lda))
+    return rc;
+  if (int rc = p.b_mn ? make_map_mn(&map_b, b, p.K, p.N, ldb) : make_map(&map_b, b, p.N, p.K, ldb))
+    return rc;
   const int num_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
   int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
   Params q = p;
@@ -794,7 +800,13 @@ extern "C" int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream) {
   p.a_mn = g->trans_a != 0, p.b_mn = g->trans_b != 0;
   p.aux_in = reinterpret_cast<const __nv_bfloat16*>(g->aux_in);
   p.aux_out = reinterpret_cast<__nv_bfloat16*>(g->aux_out);
-  return launch(g->a, g->b, p, g->epilogue, (cudaStream_t)stream);
+  PSB_REQUIRE(g->lda >= 0 && g->ldb >= 0 && g->lda % 8 == 0 && g->ldb % 8 == 0, PSB_EINVAL,
+              "psb_gemm_bf16: lda=%d / ldb=%d must be non-negative multiples of 8", g->lda, g->ldb);
+  PSB_REQUIRE(g->lda == 0 || g->lda >= (g->trans_a ? g->M : g->K), PSB_EINVAL,
+              "psb_gemm_bf16: lda=%d is shorter than a row of A", g->lda);
+  PSB_REQUIRE(g->ldb == 0 || g->ldb >= (g->trans_b ? g->N : g->K), PSB_EINVAL,
+              "psb_gemm_bf16: ldb=%d is shorter than a row of B", g->ldb);
+  return launch(g->a, g->b, p, g->epilogue, (cudaStream_t)stream, g->lda, g->ldb);
 }
 
 PSB_EXPORT_SPIN_LIMIT(gemm2)

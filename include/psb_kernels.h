@@ -375,6 +375,9 @@ typedef struct PsbGemm {
   int32_t out_dtype;   // PSB_BF16 / PSB_F32
   int32_t epilogue;
   int32_t bias_dtype;  // PSB_F32 (0, default) or PSB_BF16: element type behind `bias`
+  int32_t lda, ldb;    // elements between two stored rows of A / B (0 = packed).  A column block
+                       // of a wider matrix is an operand in place: dW of rows [r0, r1) of a
+                       // weight = dY[:, r0:r1]^T · X takes a = dY + r0, lda = N_out
 } PsbGemm;
 int psb_gemm_bf16(const PsbGemm* g, psb_stream_t stream);
 

@@ -90,7 +90,7 @@ class PsbGemm(C.Structure):
                 ("aux_in", C.c_void_p), ("aux_out", C.c_void_p), ("M", C.c_int32),
                 ("N", C.c_int32), ("K", C.c_int32), ("trans_a", C.c_int32),
                 ("trans_b", C.c_int32), ("out_dtype", C.c_int32), ("epilogue", C.c_int32),
-                ("bias_dtype", C.c_int32)]
+                ("bias_dtype", C.c_int32), ("lda", C.c_int32), ("ldb", C.c_int32)]
 
 
 class PsbError(RuntimeError):

@@ -62,8 +62,8 @@ def grad_to_sink(sink, produce):
     The commit may queue the push of the bucket, which updates the parameters IN PLACE on the
     push stream: call this only after every kernel of the layer that reads the parameter (the
     dX GEMM) has been queued on the current stream."""
-    if sink is None or not sink.exclusive:
-        return produce(None)
+    if sink is None or not sink.exclusive or len(sink.parts()) > 1:
+        return produce(None)  # (a row-split tensor delivered whole is cut up by the engine's hook)
     produce(sink.view())
     sink.commit()
     return None
@@ -134,8 +134,17 @@ class _LinkFn(torch.autograd.Function):
             if ctx.has_bias and ctx.needs_input_grad[3]:
                 gb = grad_to_sink(ctx.sink_b, lambda out: native.colsum(gz2d, out=out))
             if ctx.needs_input_grad[2]:
-                gw = grad_to_sink(ctx.sink_w, lambda out: native.gemm(
-                    gz2d, a2d, trans_a=True, trans_b=True, out=out))
+                sink = ctx.sink_w
+                if sink is not None and sink.exclusive and len(sink.parts()) > 1:
+                    # the plan cut this weight into row blocks with a bucket each: dW block by
+                    # block (dY[:, lo:hi]^T · X, operands in place), each committed at once so
+                    # that its push runs under the next block's GEMM
+                    for lo, hi, out, commit in sink.parts():
+                        native.gemm(gz2d[:, lo:hi], a2d, trans_a=True, trans_b=True, out=out)
+                        commit()
+                else:
+                    gw = grad_to_sink(sink, lambda out: native.gemm(
+                        gz2d, a2d, trans_a=True, trans_b=True, out=out))
             return gw, gb
 
         # A commit may start the push that rewrites W in place, so normally every reader of W

@@ -226,15 +226,16 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     """``Y[M,N] = op(A) · op(B) (+ bias)`` on the CTA-pair tcgen05 kernel, no transposed copies.
 
     ``trans_a``: A is stored ``[K,M]`` (else ``[M,K]``); ``trans_b``: B is stored ``[K,N]``
-    (else ``[N,K]``, i.e. a Linear weight).  ``epilogue="gelu"`` returns ``gelu(Z)`` and
+    (else ``[N,K]``, i.e. a Linear weight).  Operands may be column blocks of wider matrices
+    (``t[:, lo:hi]``, lo a multiple of 8).  ``epilogue="gelu"`` returns ``gelu(Z)`` and
     writes ``Z = acc + bias`` (bf16) into ``aux`` when given; ``epilogue="dgelu"`` returns
     ``acc * gelu'(aux)``.  (include/psb_kernels.h: psb_gemm_bf16)
     """
     _need_cuda(a, b, bias, out, aux)
     if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
         raise TypeError("gemm: operands must be bfloat16")
-    if a.dim() != 2 or b.dim() != 2 or not a.is_contiguous() or not b.is_contiguous():
-        raise ValueError("gemm: operands must be contiguous 2-D tensors")
+    if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:
+        raise ValueError("gemm: operands must be 2-D with unit stride along their rows")
     K, M = (a.shape if trans_a else a.shape[::-1])
     Kb, N = (b.shape if trans_b else b.shape[::-1])
     if K != Kb:
@@ -259,6 +260,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     g.trans_a, g.trans_b = int(trans_a), int(trans_b)
     g.out_dtype, g.epilogue = _dt(out), epi
     g.bias_dtype = _dt(bias) if bias is not None else F32
+    # a column block of a wider matrix (row stride > row length) is used in place
+    g.lda = 0 if a.is_contiguous() else a.stride(0)
+    g.ldb = 0 if b.is_contiguous() else b.stride(0)
     with torch.cuda.device(a.device):
         check(_lib.load().psb_gemm_bf16(C.byref(g), _stream(a)), "psb_gemm_bf16")
     return out

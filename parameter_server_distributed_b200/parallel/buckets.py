@@ -24,6 +24,14 @@ class ParamSlot:
     bucket: int
     offset: int          # elements from the start of the bucket
     index: int           # position in the model's own parameter order
+    # Row-split tensors: the tensor's own slot (``plan.slots[name]``) lists its ``pieces``; each
+    # piece is a slot of its own bucket (``bucket.slots``) covering rows [row_lo, row_hi) and
+    # naming the tensor in ``parent``.  The pieces' buckets are consecutive and unpadded, so the
+    # tensor stays one contiguous range of the flat space.
+    parent: Optional[str] = None
+    row_lo: int = 0
+    row_hi: int = 0
+    pieces: List["ParamSlot"] = field(default_factory=list)
 
 
 @dataclass
@@ -54,32 +62,55 @@ class BucketPlan:
     def shard_elems(self) -> int:
         return self.total_elems // self.world
 
+    def shard_ranges(self, slot: ParamSlot) -> List[Tuple[int, int, int, int]]:
+        """Where a tensor lives: ``(rank, start, stop, shard_offset)`` — tensor elements
+        ``[start, stop)`` are elements ``shard_offset ...`` of rank's flat shard state."""
+        out = []
+        row_elems = slot.numel // slot.shape[0] if slot.shape else slot.numel
+        for p in (slot.pieces or [slot]):
+            b = self.buckets[p.bucket]
+            sb = b.shard_base(self.world)
+            t0 = p.row_lo * row_elems if p.parent else 0
+            pos, end = p.offset, p.offset + p.numel
+            while pos < end:
+                r = pos // b.slice_elems
+                stop = min(end, (r + 1) * b.slice_elems)
+                out.append((r, t0 + pos - p.offset, t0 + stop - p.offset,
+                            sb + pos - r * b.slice_elems))
+                pos = stop
+        return out
+
     def owner_ranges(self, slot: ParamSlot) -> List[Tuple[int, int, int]]:
         """Pieces of a tensor by owning shard: ``(rank, start, stop)`` in tensor elements."""
-        b = self.buckets[slot.bucket]
-        out = []
-        pos = slot.offset
-        end = slot.offset + slot.numel
-        while pos < end:
-            r = pos // b.slice_elems
-            stop = min(end, (r + 1) * b.slice_elems)
-            out.append((r, pos - slot.offset, stop - slot.offset))
-            pos = stop
-        return out
+        return [(r, a, b) for r, a, b, _ in self.shard_ranges(slot)]
 
 
 def _round_up(x: int, q: int) -> int:
     return (x + q - 1) // q * q
 
 
+def split_rows(shape: Sequence[int], pieces: int, world: int) -> Optional[int]:
+    """Rows per piece if a tensor of ``shape`` can be cut into ``pieces`` row blocks that each
+    fill a bucket exactly (no padding between them), else None."""
+    if pieces < 2 or len(shape) != 2 or shape[0] % pieces:
+        return None
+    rows = shape[0] // pieces
+    if rows % 8 or (rows * shape[1]) % (world * SLICE_QUANTUM):
+        return None
+    return rows
+
+
 def plan_buckets(named_shapes: Sequence[Tuple[str, Sequence[int]]], world: int,
                  bucket_elems: int = 32 << 20, dedicated: Iterable[str] = (),
-                 reverse: bool = True) -> BucketPlan:
+                 reverse: bool = True, split: Optional[Dict[str, int]] = None) -> BucketPlan:
     """Assign tensors to buckets.
 
     ``reverse=True`` walks the model back to front so bucket 0 holds the tensors whose
     gradients are produced first by backward.  Names in ``dedicated`` get a bucket of their
-    own (the first-layer weight, whose row-slices the fused all-gather GEMM reads)."""
+    own (the first-layer weight, whose row-slices the fused all-gather GEMM reads).
+    ``split``: ``name -> k`` cuts a 2-D tensor into ``k`` row blocks, one bucket each, so that
+    the layer can produce and push its gradient block by block (the push of block *i* overlaps
+    the dW GEMM of block *i+1*); requests that do not divide evenly are ignored."""
     if world < 1:
         raise ValueError("world must be >= 1")
     dedicated = set(dedicated)
@@ -117,6 +148,22 @@ def plan_buckets(named_shapes: Sequence[Tuple[str, Sequence[int]]], world: int,
             slots[name] = slot
             cur_fill = numel
             close()
+            continue
+        rows = split_rows(shape, (split or {}).get(name, 0), world)
+        if rows is not None:
+            close()
+            shape_t = tuple(int(d) for d in shape)
+            whole = ParamSlot(name, shape_t, numel, len(buckets), 0, index)
+            for k in range(shape_t[0] // rows):
+                cur = Bucket(len(buckets), base, 0, 0)
+                piece = ParamSlot(f"{name}[{k * rows}:{(k + 1) * rows}]", (rows, shape_t[1]),
+                                  rows * shape_t[1], cur.index, 0, index, parent=name,
+                                  row_lo=k * rows, row_hi=(k + 1) * rows)
+                cur.slots.append(piece)
+                whole.pieces.append(piece)
+                cur_fill = piece.numel
+                close()
+            slots[name] = whole
             continue
         if cur is not None and cur_fill > 0 and cur_fill + numel > bucket_elems:
             close()

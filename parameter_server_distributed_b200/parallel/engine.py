@@ -53,10 +53,27 @@ class GradSink:
 
     def view(self) -> torch.Tensor:
         s = self.slot
+        if s.pieces:
+            raise RuntimeError(f"{s.name} is split over {len(s.pieces)} buckets: use parts()")
         return self.ps.backend.grad_bucket(s.bucket)[s.offset:s.offset + s.numel].view(s.shape)
 
     def commit(self) -> None:
+        if self.slot.pieces:
+            raise RuntimeError(f"{self.slot.name} is split: commit its parts")
         self.ps._arrive(self.slot, None)
+
+    def parts(self):
+        """``[(row_lo, row_hi, view, commit)]``: the row blocks in which the gradient may be
+        produced, each with its window of a gradient bucket and its own commit.  A tensor that
+        the plan did not split has one part covering all rows.  Committing part *i* before
+        computing part *i+1* lets the push of *i* overlap that computation."""
+        s = self.slot
+        if not s.pieces:
+            return [(0, s.shape[0] if s.shape else 1, self.view(), self.commit)]
+        be = self.ps.backend
+        return [(p.row_lo, p.row_hi,
+                 be.grad_bucket(p.bucket)[p.offset:p.offset + p.numel].view(p.shape),
+                 (lambda p=p: self.ps._arrive(p, None))) for p in s.pieces]
 
     @property
     def early(self) -> bool:
@@ -73,7 +90,8 @@ class ShardedParameterServer:
                  clip_norm: Optional[float] = None, dedicated: Iterable[str] = (),
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
                  grad_ring: int = 1, push_tma: Optional[bool] = None, lazy_dedicated: bool = False,
-                 overlap_grid: int = 32, alt_params: Optional[bool] = None):
+                 overlap_grid: int = 32, alt_params: Optional[bool] = None,
+                 split_mb: Optional[float] = None):
         """``broadcast``: owners write new slices into every replica inside K1 (push-mode
         all-gather).  ``lazy_dedicated``: buckets named in ``dedicated`` are the exception — their
         owners publish locally only and the consumer gathers them itself (the fused all-gather
@@ -81,7 +99,12 @@ class ShardedParameterServer:
         ``alt_params`` (None = on for the synchronous CUDA engine with more than one rank): keep
         two parameter replicas and alternate between them, so that a bucket can be pushed as
         soon as its gradients exist — before the layer's dX GEMM, which still reads the old
-        weights — instead of after it."""
+        weights — instead of after it.
+        ``split_mb`` (None = 16 for the synchronous engine with more than one rank, 0 = off;
+        ``PSB_SPLIT_MB``): the weight matrices whose gradients come LAST in backward — nothing is
+        left to hide their push behind — are cut into row blocks of about this size, one bucket
+        each; a layer that uses ``GradSink.parts()`` then computes dW block by block and the push
+        of a block overlaps the GEMM of the next, so only the last block's push is exposed."""
         named_params = [(n, p) for n, p in named_params if p.requires_grad]
         if not named_params:
             raise ValueError("no trainable parameters")
@@ -105,15 +128,21 @@ class ShardedParameterServer:
         # bulk-copy kernel on `overlap_grid` SMs (the rest keep computing); the last bucket has
         # nothing left to overlap with and takes the whole GPU with the register-path kernel.
         self.push_tma = push_tma
-        self.overlap_grid = overlap_grid
+        self.overlap_grid = int(os.environ.get("PSB_OVERLAP_GRID", overlap_grid))
         self._user_grid = push_grid
         optim = OptimConfig(**{**optim.__dict__, "grad_scale": optim.grad_scale / world})
         self.optim = optim
 
         elem_bytes = 2
+        if "PSB_SPLIT_MB" in os.environ:
+            split_mb = float(os.environ["PSB_SPLIT_MB"])
+        if split_mb is None:
+            split_mb = 16.0 if (world > 1 and self.is_cuda
+                                and type(self) is ShardedParameterServer) else 0.0
         self.plan: BucketPlan = plan_buckets(
             [(n, tuple(p.shape)) for n, p in named_params], world,
-            bucket_elems=max(1, int(bucket_mb * (1 << 20) / elem_bytes)), dedicated=dedicated)
+            bucket_elems=max(1, int(bucket_mb * (1 << 20) / elem_bytes)), dedicated=dedicated,
+            split=self._tail_split(named_params, world, split_mb, bucket_mb, set(dedicated)))
         if self.is_cuda:
             from .device_backend import DeviceBackend
             gdt = named_params[0][1].dtype
@@ -203,6 +232,29 @@ class ShardedParameterServer:
         self.metrics = Metrics()
 
     # ------------------------------------------------------------------ setup helpers
+    @staticmethod
+    def _tail_split(named_params, world: int, split_mb: float, bucket_mb: float, skip) -> dict:
+        """``name -> pieces`` for the 2-D tensors among the last ``bucket_mb`` megabytes that
+        backward produces (= the first ones in model order)."""
+        from .buckets import split_rows
+        out = {}
+        if split_mb <= 0:
+            return out
+        seen = 0.0
+        for name, p in named_params:
+            mb = p.numel() * 2 / (1 << 20)
+            if seen >= bucket_mb:
+                break
+            seen += mb
+            if p.dim() != 2 or name in skip or mb <= split_mb:
+                continue
+            want = int(-(-mb // split_mb))
+            for k in range(want, 2 * want + 1):
+                if split_rows(tuple(p.shape), k, world) is not None:
+                    out[name] = k
+                    break
+        return out
+
     def _sync_replicas(self) -> None:
         """Make every replica the concatenation of the owners' slices (owners are
         authoritative), so ranks agree even if their initialisation seeds differed."""
@@ -227,7 +279,11 @@ class ShardedParameterServer:
                 return  # the layer delivered this gradient through the sink (autograd still
                         # runs the hook when a backward function returns None)
             p.grad = None
-            self._arrive(slot, g)
+            if slot.pieces:  # delivered whole by autograd: hand each row block to its bucket
+                for piece in slot.pieces:
+                    self._arrive(piece, g[piece.row_lo:piece.row_hi])
+            else:
+                self._arrive(slot, g)
 
         return hook
 
@@ -318,7 +374,11 @@ class ShardedParameterServer:
         if self.push_tma is not None:
             return {"tma": self.push_tma, "grid": self._user_grid}
         last = b == len(self.plan.buckets) - 1
-        if self.world > 1 and self.overlap and not last and self.clip_norm is None:
+        # the last bucket has nothing left to overlap with: a big one takes the whole GPU with
+        # the register-path kernel; a small one (a row block of a split tensor) is latency-bound
+        # and the bulk-copy kernel is the faster of the two there (bw_sweep: 16 MiB 73 vs 82 us)
+        big_last = last and self.plan.buckets[b].numel * 2 > (32 << 20)
+        if self.world > 1 and self.overlap and not big_last and self.clip_norm is None:
             return {"tma": True, "grid": self._user_grid or self.overlap_grid}
         # register-path kernel, 512 threads per CTA.  (Measured on B200, 1 GPU, MLP step: 256-thread
         # CTAs that share the SMs with the tcgen05 GEMM cost 0.08-0.15 ms per step more than
@@ -421,11 +481,8 @@ class ShardedParameterServer:
             parts = [shard]
         out = {}
         for name, slot in self.plan.slots.items():
-            bk = self.plan.buckets[slot.bucket]
-            sb = bk.shard_base(self.world)
             flat = torch.empty(slot.numel, dtype=torch.float32, device=shard.device)
-            for r, a, b in self.plan.owner_ranges(slot):
-                lo = sb + (slot.offset + a) - r * bk.slice_elems
+            for r, a, b, lo in self.plan.shard_ranges(slot):
                 flat[a:b].copy_(parts[r][lo:lo + (b - a)])
             if name in self._nhwc:
                 n, c, h, w = slot.shape
@@ -447,14 +504,12 @@ class ShardedParameterServer:
                 if slot is None:
                     continue
                 bk = self.plan.buckets[slot.bucket]
-                sb = bk.shard_base(self.world)
                 t = t.detach()
                 if name in self._nhwc:
                     t = t.permute(0, 2, 3, 1)
                 flat = t.reshape(-1).to(device=shard.device, dtype=torch.float32)
-                for r, a, b in self.plan.owner_ranges(slot):
+                for r, a, b, lo in self.plan.shard_ranges(slot):
                     if r == self.rank:
-                        lo = sb + (slot.offset + a) - r * bk.slice_elems
                         shard[lo:lo + (b - a)].copy_(flat[a:b])
                 if which == "master":
                     for pf in (be.param_flat, getattr(be, "param_flat2", None)):

@@ -160,7 +160,8 @@ class Trainer:
                  pull: str = "broadcast", clip_norm: Optional[float] = None,
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
                  staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None,
-                 checkpoint_every: int = 0, checkpoint_path: Optional[str] = None):
+                 checkpoint_every: int = 0, checkpoint_path: Optional[str] = None,
+                 split_mb: Optional[float] = None):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
         ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
@@ -188,7 +189,7 @@ class Trainer:
                 list(model.named_parameters()), optim, ctx.fabric, world=ctx.world, rank=ctx.rank,
                 bucket_mb=bucket_mb, broadcast=(pull != "gather"), clip_norm=clip_norm,
                 dedicated=dedicated, overlap=overlap, push_grid=push_grid,
-                push_tma=push_tma, lazy_dedicated=(pull == "hybrid"),
+                push_tma=push_tma, lazy_dedicated=(pull == "hybrid"), split_mb=split_mb,
                 # two parameter replicas pay off only for layers that commit their gradients
                 # before their dX GEMM (ops/linear.py); other models keep one replica
                 alt_params=None if getattr(model, "grad_sink_layers", False) else False)

@@ -51,3 +51,25 @@ def test_owner_ranges_cover_tensor():
 def test_duplicate_name_rejected():
     with pytest.raises(ValueError):
         plan_buckets([("w", (4,)), ("w", (4,))], 1)
+
+
+def test_row_split_gives_contiguous_unpadded_buckets():
+    world = 2
+    shp = [("first.weight", (4096, 1024)), ("first.bias", (4096,)), ("last.weight", (64, 4096))]
+    plan = plan_buckets(shp, world, bucket_elems=10**9, split={"first.weight": 4, "last.weight": 3})
+    whole = plan.slots["first.weight"]
+    assert len(whole.pieces) == 4 and not plan.slots["last.weight"].pieces  # 64 % 3 != 0: ignored
+    pos = plan.buckets[whole.bucket].base
+    for k, piece in enumerate(whole.pieces):
+        b = plan.buckets[piece.bucket]
+        assert b.slots == [piece] and piece.offset == 0 and b.numel == piece.numel  # no padding
+        assert b.base == pos and (piece.row_lo, piece.row_hi) == (k * 1024, (k + 1) * 1024)
+        assert piece.parent == "first.weight"
+        pos += b.numel
+    # ownership covers the tensor exactly once, in order, over the pieces
+    rngs = plan.shard_ranges(whole)
+    assert rngs[0][1] == 0 and rngs[-1][2] == whole.numel
+    assert all(b0 == a1 for (_, _, b0, _), (_, a1, _, _) in zip(rngs, rngs[1:]))
+    assert [r for r, *_ in rngs] == [0, 1] * 4
+    seen = {s.name for b in plan.buckets for s in b.slots}
+    assert "first.bias" in seen and "last.weight" in seen and "first.weight" not in seen

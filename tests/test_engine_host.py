@@ -44,6 +44,35 @@ def test_single_process_matches_torch(kind):
         assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
 
 
+def test_row_split_tail_tensor_matches_torch():
+    """The tensors whose gradients come last are cut into row blocks with a bucket each
+    (engine: split_mb); gradients delivered whole by autograd are handed out block by block."""
+    torch.manual_seed(3)
+    cfg = MLPConfig(d_in=128, hidden=(256, 64), d_out=8)
+    m = MLP(cfg)
+    ref = copy.deepcopy(m)
+    ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind="adamw", lr=0.01),
+                                bucket_mb=0.0625, split_mb=0.02)
+    whole = ps.plan.slots["layers.0.weight"]
+    assert len(whole.pieces) == 4, [len(s.pieces) for s in ps.plan.slots.values()]
+    assert not ps.plan.slots["layers.1.weight"].pieces  # only the tail of backward is split
+    opt = torch.optim.AdamW(ref.parameters(), lr=0.01, weight_decay=0.0)
+    for _ in range(4):
+        x, y = torch.randn(16, 128), torch.randn(16, 8)
+        mse_loss(m(x), y).backward()
+        ps.step()
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        opt.step()
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=2e-6, rtol=1e-5)
+    got = ps.gather_state("master")
+    for (n, p) in ref.named_parameters():
+        assert torch.allclose(got[n], p, atol=2e-6, rtol=1e-5), n
+    ps.scatter_state({n: torch.zeros_like(p) for n, p in got.items()})
+    assert all(float(p.abs().max()) == 0.0 for p in m.parameters())
+
+
 def test_clip_matches_torch():
     torch.manual_seed(1)
     m = MLP(CFG)

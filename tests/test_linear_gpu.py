@@ -214,3 +214,47 @@ def test_gpt2_blocks_on_own_gemms_match_library_path():
         err = (a.grad.float() - b.grad.float()).abs().max().item()
         scale = b.grad.float().abs().max().item() + 1e-6
         assert err / scale < 8e-2, (n, err, scale)
+
+
+@pytest.mark.parametrize("lo,hi", [(0, 256), (256, 768), (512, 520)])
+def test_gemm_column_block_operands(lo, hi):
+    """dW of a row block of a weight: dY[:, lo:hi]^T · X with both operands used in place
+    (row stride > row length), and the K-major forms of the same."""
+    torch.manual_seed(lo + hi)
+    batch, n_out, k_in = 384, 768, 264
+    dy, x = _rand(batch, n_out), _rand(batch, k_in)
+    got = native.gemm(dy[:, lo:hi], x, trans_a=True, trans_b=True)
+    _close(got, dy[:, lo:hi].float().t() @ x.float())
+    wide = _rand(320, 1024)                       # K-major operands cut out of a wider matrix
+    a, b = wide[:, 128:392], _rand(136, 1024)[:, 256:520]
+    _close(native.gemm(a, b), a.float() @ b.float().t())
+
+
+def test_row_split_weight_trains_like_the_whole_one():
+    """Engine split_mb: the first layer's dW is produced in row blocks, each into its own
+    gradient bucket and pushed at once — same numbers as the unsplit run."""
+    import parameter_server_distributed_b200 as psd
+    from parameter_server_distributed_b200.models import mse_loss
+    ctx = psd.init(heap_bytes=64 << 20)
+    cfg = MLPConfig(d_in=512, hidden=(1024, 256), d_out=128)
+    finals = []
+    try:
+        for split in (0.0, 0.25):
+            torch.manual_seed(5)
+            model = MLP(cfg).to(DEV, torch.bfloat16)
+            tr = psd.Trainer(model, mse_loss, ctx, psd.OptimConfig(kind="momentum", lr=1e-2),
+                             bucket_mb=1.0, split_mb=split)
+            n_pieces = len(tr.ps.plan.slots["layers.0.weight"].pieces)
+            assert n_pieces == (4 if split else 0), n_pieces
+            gen = torch.Generator().manual_seed(9)
+            for _ in range(3):
+                x = torch.randn(256, 512, generator=gen).to(DEV, torch.bfloat16)
+                y = torch.randn(256, 128, generator=gen).to(DEV, torch.bfloat16)
+                tr.step_device(x, y)
+            torch.cuda.synchronize()
+            finals.append([p.detach().float().clone() for p in model.parameters()])
+            tr.ps.close()
+        for a, b in zip(*finals):
+            assert torch.equal(a, b)
+    finally:
+        ctx.close()
