@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--mode", default="sync", choices=["sync", "async", "ssp"])
     ap.add_argument("--staleness", type=int, default=1)
-    ap.add_argument("--push", default="auto", choices=["auto", "tma", "ldg"],
+    ap.add_argument("--push", default="auto", choices=["auto", "tma", "ldg", "nvls"],
                     help="K1 variant: auto = bulk-copy kernel on 32 SMs for overlapped buckets, "
                          "register-path kernel on all SMs for the last one")
     return ap.parse_args()
@@ -138,7 +138,8 @@ def run_ours(args):
     trainer = psd.Trainer(model, wl.loss, ctx, optim, mode=args.mode, staleness=args.staleness,
                           pull=args.pull, bucket_mb=args.bucket_mb,
                           overlap=not args.no_overlap, push_grid=args.push_grid,
-                          push_tma={"auto": None, "tma": True, "ldg": False}[args.push])
+                          push_tma={"auto": None, "tma": True, "ldg": False, "nvls": None}[args.push],
+                          push_nvls=True if args.push == "nvls" else None)
     B = wl.batch
     gen = torch.Generator().manual_seed(100 + ctx.rank)
     n_host = 4  # rotate a few distinct pinned batches

@@ -61,6 +61,9 @@ def main():
     max_elems = int(args.max_mb * (1 << 20) / 2)
     ctx = psd.init(heap_bytes=max_elems * 4 + (64 << 20))
     world, rank = ctx.world, ctx.rank
+    if world > 1 and not dist.is_initialized():
+        # the product path runs on the coordinator; NCCL exists here only as the baseline B1
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=ctx.device)
     cfg = OptimConfig(kind=args.optimizer, lr=1e-3, grad_scale=1.0 / world)
     mb = args.min_mb
     sizes = []
@@ -74,10 +77,10 @@ def main():
         elems = int(mb * (1 << 20) / 2)
         plan = plan_buckets([("vec", (elems,))], world, bucket_elems=1 << 62)
         # re-use the heap: reset the bump allocator past the signal pad
-        ctx.fabric._cursor = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes
+        ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
         for grid in [int(g) for g in args.grids.split(",")]:
             be = DeviceBackend(ctx.fabric, plan, cfg, broadcast=True, push_grid=grid)
-            ctx.fabric._cursor = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes
+            ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
             be.grad_flat.normal_()
             S = plan.total_elems * 2
             link_bytes = (world - 1) / world * S
@@ -115,6 +118,15 @@ def main():
                     emit(f"K1-TMA push+update+broadcast grid={tg}", ts, 2 * link_bytes)
                 be.push_tma = False
                 be._push_args[0].grid = grid
+            if grid == 0 and world > 1 and be.nvls_available:
+                # the switch reduces and replicates: S/N + (N-1)/N*S = S bytes in per GPU
+                for ng in (0, 16, 32):
+                    be._push_args[0].grid = ng
+                    ts = timed(ctx, lambda: be.push(0, nvls=True), args.iters)
+                    emit(f"K1-NVLS push+update+broadcast grid={ng or 'auto'}", ts, S)
+                be._push_args[0].grid = grid
+                ts = timed(ctx, lambda: be.bcast_slice_nvls(0), args.iters)
+                emit("K2-NVLS all-gather (multimem.st)", ts, link_bytes)
             be.broadcast = False
             ts = timed(ctx, lambda: be.push(0), args.iters)
             emit("K1 push+update (no broadcast)", ts, link_bytes)

@@ -57,11 +57,14 @@ def main():
     max_w = max(n * k for _, n, k in shapes) * 2
     ctx = psd.init(heap_bytes=max_w + (64 << 20))
     world, rank = ctx.world, ctx.rank
+    if world > 1 and not dist.is_initialized():
+        # the product path runs on the coordinator; NCCL exists here only as the baseline
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=ctx.device)
     lib = _lib.load()
     for M, N, K in shapes:
         if N % (256 * world):
             continue
-        ctx.fabric._cursor = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes
+        ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
         buf = ctx.fabric.alloc(N * K * 2, align=4096)
         wt = buf.view(torch.bfloat16).view(N, K)
         torch.manual_seed(7)

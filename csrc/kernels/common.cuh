@@ -50,6 +50,8 @@ constexpr int kNumSMs = 148;  // B200
 
 // push_tma.cu
 int push_fused_tma_dispatch(const PsbPush& a, cudaStream_t s);
+// push_nvls.cu
+int push_nvls_dispatch(const PsbPush& a, cudaStream_t s);
 
 // ---- memory-model primitives (system scope: visible across NVLink peers) ------
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {

@@ -506,6 +506,7 @@ int psb_push_fused(const PsbPush* args, psb_stream_t stream) {
     for (int i = 0; i < a.fabric.world; ++i)
       PSB_REQUIRE(a.grad[i], PSB_EINVAL, "psb_push_fused: gradient buffer of peer %d is null", i);
 
+  if (a.flags & PSB_PUSH_NVLS) return push_nvls_dispatch(a, (cudaStream_t)stream);
   if ((a.flags & PSB_PUSH_TMA) && !reduce_only && !from_reduced)
     return push_fused_tma_dispatch(a, (cudaStream_t)stream);
   PSB_REQUIRE((((uintptr_t)a.master | (uintptr_t)a.m | (uintptr_t)a.v | (uintptr_t)a.reduced) & 31) == 0,
@@ -653,10 +654,12 @@ PSB_EXPORT_SPIN_LIMIT(push_pull)
 extern "C" int psb_spin_limit_push_tma(unsigned long long ns);
 extern "C" int psb_spin_limit_gemm1(unsigned long long ns);
 extern "C" int psb_spin_limit_gemm2(unsigned long long ns);
+extern "C" int psb_spin_limit_push_nvls(unsigned long long ns);
 
 extern "C" int psb_abort_word_push_tma(const uint32_t* p);
 extern "C" int psb_abort_word_gemm1(const uint32_t* p);
 extern "C" int psb_abort_word_gemm2(const uint32_t* p);
+extern "C" int psb_abort_word_push_nvls(const uint32_t* p);
 
 // Host-mapped abort word (see common.cuh).  create: allocates the word (zero), points the
 // kernels of the CURRENT device at it and returns its host address; the caller (or the control
@@ -670,7 +673,8 @@ extern "C" int psb_abort_word_create(uint32_t** host_word) {
   uint32_t* d = nullptr;
   PSB_CUDA_OK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), h, 0));
   int (*setters[])(const uint32_t*) = {psb_abort_word_push_pull, psb_abort_word_push_tma,
-                                       psb_abort_word_gemm1, psb_abort_word_gemm2};
+                                       psb_abort_word_gemm1, psb_abort_word_gemm2,
+                                       psb_abort_word_push_nvls};
   for (auto set : setters) PSB_CUDA_OK((cudaError_t)set(d));
   *host_word = h;
   return 0;
@@ -679,7 +683,8 @@ extern "C" int psb_abort_word_create(uint32_t** host_word) {
 // Detaches the kernels of the current device from the word and frees it.
 extern "C" int psb_abort_word_destroy(uint32_t* host_word) {
   int (*setters[])(const uint32_t*) = {psb_abort_word_push_pull, psb_abort_word_push_tma,
-                                       psb_abort_word_gemm1, psb_abort_word_gemm2};
+                                       psb_abort_word_gemm1, psb_abort_word_gemm2,
+                                       psb_abort_word_push_nvls};
   for (auto set : setters) PSB_CUDA_OK((cudaError_t)set(nullptr));
   PSB_CUDA_OK(cudaDeviceSynchronize());
   if (host_word) PSB_CUDA_OK(cudaFreeHost(host_word));
@@ -691,7 +696,8 @@ extern "C" int psb_set_spin_timeout_ms(uint64_t ms) {
   const unsigned long long ns = (unsigned long long)ms * 1000000ull;
   // one copy of the limit per translation unit that spins on peer words (current device)
   int (*setters[])(unsigned long long) = {psb_spin_limit_push_pull, psb_spin_limit_push_tma,
-                                          psb_spin_limit_gemm1, psb_spin_limit_gemm2};
+                                          psb_spin_limit_gemm1, psb_spin_limit_gemm2,
+                                          psb_spin_limit_push_nvls};
   for (auto set : setters) {
     PSB_CUDA_OK((cudaError_t)set(ns));
   }

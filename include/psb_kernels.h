@@ -211,6 +211,9 @@ typedef struct PsbFabric {
                                 // an empty mask makes the launch a no-op (nothing published)
 #define PSB_PUSH_TMA 64         // bulk-copy (cp.async.bulk) smem-ring variant: fills NVLink from ~24 SMs
                                 // instead of ~148, so backward kernels keep the other SMs
+#define PSB_PUSH_NVLS 128       // NVLS variant (push_nvls.cu): multimem.ld_reduce over grad_mc, multimem.st
+                                // into param_mc — the switch reduces and replicates; bf16 gradients, VMM
+                                // heap bound to a multicast object (psb_mc_*); bf16-rounded sum
 #define PSB_PUSH_SEQLOCK 32     // publish 2*epoch (even) instead of epoch: readers pair it with the
                                 // odd mark written by psb_async_plan before the update started
 
@@ -239,6 +242,8 @@ typedef struct PsbPush {
                                     // lets a K1 CTA share an SM with a CTA of the tcgen05 GEMM
                                     // (32 K + 24 K registers), so an overlapped push really overlaps
                                     // (which slot of the worker's gradient ring to read)
+  const void* grad_mc;              // PSB_PUSH_NVLS: multicast address of this bucket's gradient buffer
+  void* param_mc;                   // PSB_PUSH_NVLS: multicast address of this bucket's bf16 replica
 } PsbPush;
 int psb_push_fused(const PsbPush* args, psb_stream_t stream);
 
@@ -260,6 +265,28 @@ typedef struct PsbPull {
   int32_t seqlock;             // async mode: copy each owner slice under a seqlock (retry on change)
 } PsbPull;
 int psb_pull_allgather(const PsbPull* args, psb_stream_t stream);
+
+// K2 over NVLS: the owner stores its slice of the bucket (param_local + rank * slice_bytes)
+// into every replica with multimem.st through `param_mc`; with `epoch` it then publishes
+// version[bucket][rank] = *epoch (consumers: psb_wait_versions).  Push-mode all-gather in which
+// each GPU sends its slice once and the switch replicates it.
+int psb_bcast_slice_nvls(const PsbFabric* fabric, const void* param_local, void* param_mc,
+                         uint64_t slice_bytes, int bucket, const uint32_t* epoch,
+                         uint32_t* done_counter, int grid, psb_stream_t stream);
+
+// VMM heap and multicast (NVLS) plumbing — csrc/fabric/fabric.cu.  A VMM segment is what the
+// IPC heap above is, but allocated with cuMemCreate so that (a) it travels between processes as
+// a POSIX file descriptor and (b) it can be bound to a multicast object.
+int psb_vmm_support(int* vmm, int* multicast);
+int psb_vmm_granularity(int world, int multicast, int recommended, size_t* gran);
+int psb_vmm_alloc(size_t bytes, void** ptr, uint64_t* handle, int* fd);
+int psb_vmm_import(int fd, size_t bytes, void** ptr, uint64_t* handle);
+int psb_vmm_release(void* ptr, size_t bytes, uint64_t handle);
+int psb_mc_create(size_t bytes, int world, uint64_t* mc_handle, int* fd);
+int psb_mc_import(int fd, uint64_t* mc_handle);
+int psb_mc_add_device(uint64_t mc_handle);                 // every rank, then a barrier
+int psb_mc_bind_map(uint64_t mc_handle, uint64_t local_handle, size_t bytes, void** mc_ptr);
+int psb_mc_unbind(uint64_t mc_handle, size_t bytes);
 
 // K9 — device-side waits / barriers (replace the 50 ms CheckSyncStatus poll and
 // the 500 ms sleeps, src/worker.cpp:359-375).

@@ -25,6 +25,7 @@ PUSH_FROM_REDUCED = 8
 PUSH_MASKED = 16
 PUSH_SEQLOCK = 32
 PUSH_TMA = 64
+PUSH_NVLS = 128
 
 PAD_READY_OFF = 0
 PAD_VERSION_OFF = MAX_BUCKETS * MAX_PEERS
@@ -60,7 +61,7 @@ class PsbPush(C.Structure):
                 ("epoch", C.c_void_p), ("step", C.c_void_p), ("clip_coef", C.c_void_p),
                 ("peer_mask", C.c_void_p), ("done_counter", C.c_void_p), ("flags", C.c_int32),
                 ("grid", C.c_int32), ("opt", PsbOptim), ("grad_off", C.c_void_p),
-                ("block", C.c_int32)]
+                ("block", C.c_int32), ("grad_mc", C.c_void_p), ("param_mc", C.c_void_p)]
 
 
 class PsbPull(C.Structure):
@@ -147,6 +148,17 @@ def _declare(lib) -> None:
         "psb_async_gate": (i32, [C.POINTER(PsbAsync), u32, i32, vp]),
         "psb_set_spin_timeout_ms": (i32, [C.c_uint64]),
         "psb_pad_post": (i32, [C.POINTER(PsbFabric), u32, u32, vp]),
+        "psb_bcast_slice_nvls": (i32, [C.POINTER(PsbFabric), vp, vp, C.c_uint64, i32, vp, vp, i32, vp]),
+        "psb_vmm_support": (i32, [C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+        "psb_vmm_granularity": (i32, [i32, i32, i32, C.POINTER(sz)]),
+        "psb_vmm_alloc": (i32, [sz, C.POINTER(vp), C.POINTER(C.c_uint64), C.POINTER(C.c_int)]),
+        "psb_vmm_import": (i32, [i32, sz, C.POINTER(vp), C.POINTER(C.c_uint64)]),
+        "psb_vmm_release": (i32, [vp, sz, C.c_uint64]),
+        "psb_mc_create": (i32, [sz, i32, C.POINTER(C.c_uint64), C.POINTER(C.c_int)]),
+        "psb_mc_import": (i32, [i32, C.POINTER(C.c_uint64)]),
+        "psb_mc_add_device": (i32, [C.c_uint64]),
+        "psb_mc_bind_map": (i32, [C.c_uint64, C.c_uint64, sz, C.POINTER(vp)]),
+        "psb_mc_unbind": (i32, [C.c_uint64, sz]),
         "psb_abort_word_create": (i32, [C.POINTER(vp)]),
         "psb_abort_word_destroy": (i32, [vp]),
         "psb_sumsq_noalloc": (i32, [vp, i32, sz, vp, vp]),

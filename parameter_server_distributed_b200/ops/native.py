@@ -231,7 +231,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans_a: bool = False, trans_b: bo
     writes ``Z = acc + bias`` (bf16) into ``aux`` when given; ``epilogue="dgelu"`` returns
     ``acc * gelu'(aux)``.  (include/psb_kernels.h: psb_gemm_bf16)
     """
-    _need_cuda(a, b, bias, out, aux)
+    _need_cuda(bias, out, aux)
+    if not (a.is_cuda and b.is_cuda):
+        raise TypeError("native ops need CUDA tensors; use ops.reference on the host")
     if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16:
         raise TypeError("gemm: operands must be bfloat16")
     if a.dim() != 2 or b.dim() != 2 or a.stride(1) != 1 or b.stride(1) != 1:

@@ -67,6 +67,15 @@ class DeviceBackend:
             [self._make_push(b, self.P2) for b in range(nb)] if alt_params else [])
         self._pull_args: List[PsbPull] = [self._make_pull(b) for b in range(nb)]
 
+    def close(self) -> None:
+        """Return G / P / P2 to the symmetric heap (in reverse order of allocation)."""
+        for name in ("P2", "P", "G"):
+            buf = getattr(self, name, None)
+            if buf is not None:
+                buf.free()
+                setattr(self, name, None)
+        self.param_flat = self.param_flat2 = self.grad_flat = None
+
     # ------------------------------------------------------------------ argument blocks
     def _make_push(self, b: int, P=None) -> PsbPush:
         P = self.P if P is None else P
@@ -77,6 +86,9 @@ class DeviceBackend:
         for r in range(self.world):
             a.grad[r] = self.G.peer_ptr(r) + bk.base * gsz
             a.param[r] = P.peer_ptr(r) + bk.base * 2
+        # NVLS: one multicast address per buffer names every rank's copy (0 without multicast)
+        a.grad_mc = (self.G.mc_ptr + bk.base * gsz) if self.G.mc_ptr else None
+        a.param_mc = (P.mc_ptr + bk.base * 2) if P.mc_ptr else None
         sb = bk.shard_base(self.world)
         a.master = self.master[sb:].data_ptr()
         a.m = self.m[sb:].data_ptr() if self.m is not None else None
@@ -144,16 +156,20 @@ class DeviceBackend:
              seqlock: bool = False, mask_ptr: Optional[int] = None,
              grad_off_ptr: Optional[int] = None, broadcast: Optional[bool] = None,
              tma: Optional[bool] = None, grid: Optional[int] = None, block: int = 0,
-             alt: bool = False) -> None:
+             alt: bool = False, nvls: bool = False) -> None:
         """K1 on the current stream.  ``block``: threads per CTA of the register-path kernel
         (0 = 512; 256 shares an SM with a tcgen05 GEMM CTA).  ``alt``: the new parameters go to
-        the second replica."""
+        the second replica.  ``nvls``: the switch reduces and replicates (push_nvls.cu)."""
         a = self._push_args_alt[b] if alt else self._push_args[b]
         bc = self.broadcast if broadcast is None else broadcast
         flags = _lib.PUSH_BROADCAST if bc else 0
         if seqlock:
             flags |= _lib.PUSH_SEQLOCK
-        if self.push_tma if tma is None else tma:
+        if nvls:
+            if not a.grad_mc:
+                raise RuntimeError("NVLS push needs a VMM heap bound to a multicast object")
+            flags |= _lib.PUSH_NVLS
+        elif self.push_tma if tma is None else tma:
             flags |= _lib.PUSH_TMA
         a.grid = self.push_grid if grid is None else grid
         a.peer_mask = mask_ptr if mask_ptr is not None else self.peer_mask.data_ptr()
@@ -179,6 +195,22 @@ class DeviceBackend:
         a.seqlock = int(seqlock)
         with torch.cuda.device(self.device):
             check(self.lib.psb_pull_allgather(C.byref(a), self._stream()), "psb_pull_allgather")
+
+    @property
+    def nvls_available(self) -> bool:
+        return bool(self.G.mc_ptr) and self.grad_dtype == torch.bfloat16 and self.grad_ring == 1
+
+    def bcast_slice_nvls(self, b: int, publish: bool = False, grid: int = 0) -> None:
+        """K2 over NVLS: this rank's slice of bucket ``b`` goes into every replica with
+        multimem.st (push-mode all-gather)."""
+        bk = self.plan.buckets[b]
+        fab = self.fabric.c_fabric()
+        with torch.cuda.device(self.device):
+            check(self.lib.psb_bcast_slice_nvls(
+                C.byref(fab), self.P.peer_ptr(self.rank) + bk.base * 2,
+                self.P.mc_ptr + bk.base * 2, bk.slice_elems * 2, b,
+                self.epoch[b:].data_ptr() if publish else None, self.done[b:].data_ptr(), grid,
+                self._stream()), "psb_bcast_slice_nvls")
 
     def wait_versions(self, lo: int = 0, hi: Optional[int] = None) -> None:
         """K9: block the current stream until every owner published buckets [lo, hi)."""

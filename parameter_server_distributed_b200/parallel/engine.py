@@ -91,7 +91,7 @@ class ShardedParameterServer:
                  overlap: bool = True, push_grid: int = 0, sync_init: bool = True,
                  grad_ring: int = 1, push_tma: Optional[bool] = None, lazy_dedicated: bool = False,
                  overlap_grid: int = 32, alt_params: Optional[bool] = None,
-                 split_mb: Optional[float] = None):
+                 split_mb: Optional[float] = None, push_nvls: Optional[bool] = None):
         """``broadcast``: owners write new slices into every replica inside K1 (push-mode
         all-gather).  ``lazy_dedicated``: buckets named in ``dedicated`` are the exception — their
         owners publish locally only and the consumer gathers them itself (the fused all-gather
@@ -100,6 +100,10 @@ class ShardedParameterServer:
         two parameter replicas and alternate between them, so that a bucket can be pushed as
         soon as its gradients exist — before the layer's dX GEMM, which still reads the old
         weights — instead of after it.
+        ``push_nvls`` (``PSB_PUSH_NVLS``): reduce and replicate inside the NVSwitch
+        (multimem.ld_reduce / multimem.st) where the heap is bound to a multicast object; the sum
+        is rounded to bf16 once, so results match the peer-load kernels to bf16 tolerance rather
+        than bit for bit — off unless asked for.
         ``split_mb`` (None = 16 for the synchronous engine with more than one rank, 0 = off;
         ``PSB_SPLIT_MB``): the weight matrices whose gradients come LAST in backward — nothing is
         left to hide their push behind — are cut into row blocks of about this size, one bucket
@@ -128,6 +132,9 @@ class ShardedParameterServer:
         # bulk-copy kernel on `overlap_grid` SMs (the rest keep computing); the last bucket has
         # nothing left to overlap with and takes the whole GPU with the register-path kernel.
         self.push_tma = push_tma
+        if "PSB_PUSH_NVLS" in os.environ:
+            push_nvls = os.environ["PSB_PUSH_NVLS"] != "0"
+        self._want_nvls = bool(push_nvls)
         self.overlap_grid = int(os.environ.get("PSB_OVERLAP_GRID", overlap_grid))
         self._user_grid = push_grid
         optim = OptimConfig(**{**optim.__dict__, "grad_scale": optim.grad_scale / world})
@@ -371,9 +378,14 @@ class ShardedParameterServer:
         """Kernel variant / grid of K1 for bucket ``b`` (see ``push_tma`` above)."""
         if not self.is_cuda:
             return {}
+        last = b == len(self.plan.buckets) - 1
+        if (self._want_nvls and self.world > 1 and self.clip_norm is None
+                and getattr(self.backend, "nvls_available", False)
+                and type(self) is ShardedParameterServer):
+            # one load + one store per 16 bytes: few CTAs fill the link even next to a GEMM
+            return {"nvls": True, "grid": self._user_grid or (0 if last else self.overlap_grid)}
         if self.push_tma is not None:
             return {"tma": self.push_tma, "grid": self._user_grid}
-        last = b == len(self.plan.buckets) - 1
         # the last bucket has nothing left to overlap with: a big one takes the whole GPU with
         # the register-path kernel; a small one (a row block of a split tensor) is latency-bound
         # and the bulk-copy kernel is the faster of the two there (bw_sweep: 16 MiB 73 vs 82 us)
@@ -528,9 +540,18 @@ class ShardedParameterServer:
         self.backend.set_optim(self.optim)
 
     def close(self) -> None:
+        """Detach from the model and give the symmetric buffers back to the heap: the
+        parameters become ordinary tensors holding their current values.  Collective (every
+        rank closes its engines in the same order)."""
         for h in self._hooks:
             h.remove()
         self._hooks = []
+        if self.is_cuda and getattr(self.backend, "P", None) is not None:
+            torch.cuda.synchronize(self.device)
+            with torch.no_grad():
+                for _, p in self.named_params:
+                    p.data = p.data.clone()
+            self.backend.close()
         for p in self._sink_params:
             if hasattr(p, "_psb_sink"):
                 del p._psb_sink

@@ -56,6 +56,11 @@ class SymBuffer:
     def peer_ptrs(self) -> List[int]:
         return [self.peer_ptr(r) for r in range(self.fabric.world)]
 
+    @property
+    def mc_ptr(self) -> int:
+        """Multicast address of the buffer (every rank's copy at once), 0 without NVLS."""
+        return self.fabric.mc_base + self.offset if self.fabric.mc_base else 0
+
     def peer(self, r: int) -> torch.Tensor:
         """uint8 view of rank ``r``'s copy (reads / writes go over NVLink)."""
         if r == self.fabric.rank:
@@ -68,12 +73,73 @@ class SymBuffer:
         self.fabric._free(self)
 
 
+class _Control:
+    """What the fabric needs from the job's control plane while it comes up."""
+
+    def __init__(self, gather_obj: Callable[[str, object], list], barrier: Callable[[str], None]):
+        self.gather_obj, self.barrier = gather_obj, barrier
+
+
+def _exchange_fds(ctl: _Control, rank: int, world: int, mine: List[int]) -> List[List[int]]:
+    """POSIX file descriptors cannot ride in an RPC: every rank serves its own descriptors on a
+    Unix-domain socket (SCM_RIGHTS), the socket paths travel through the control plane, and
+    every rank fetches every peer's.  Returns ``fds[r]`` = rank r's descriptors as valid in
+    THIS process (``fds[rank]`` is ``mine``)."""
+    import os
+    import socket
+    import tempfile
+    import threading
+    path = os.path.join(tempfile.gettempdir(), f"psb_fd_{os.getpid()}_{rank}.sock")
+    try:
+        os.unlink(path)
+    except OSError:
+        pass
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(path)
+    srv.listen(world)
+
+    def serve():
+        for _ in range(world - 1):
+            conn, _ = srv.accept()
+            with conn:
+                socket.send_fds(conn, [len(mine).to_bytes(4, "little")], mine)
+
+    th = threading.Thread(target=serve, daemon=True)
+    th.start()
+    paths = ctl.gather_obj("fabric/fd_sockets", path)
+    out: List[List[int]] = [[] for _ in range(world)]
+    out[rank] = list(mine)
+    for r in range(world):
+        if r == rank:
+            continue
+        with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+            c.connect(paths[r])
+            _, fds, _, _ = socket.recv_fds(c, 4, 8)
+            out[r] = list(fds)
+    th.join(timeout=60)
+    srv.close()
+    ctl.barrier("fabric/fds_done")
+    try:
+        os.unlink(path)
+    except OSError:
+        pass
+    return out
+
+
 class Fabric:
-    """Peer-mapped heap and signal pad of one rank."""
+    """Peer-mapped heap and signal pad of one rank.
+
+    Two kinds of heap segment: ``vmm`` — ``cuMemCreate`` memory shared as POSIX file
+    descriptors, which can also be bound to an NVLS multicast object (``mc_base``: one address
+    for the same offset of every rank's segment; ``multimem.*`` kernels) — and the older
+    ``cudaMalloc`` + CUDA IPC handles.  ``PSB_HEAP=ipc|vmm`` and ``PSB_NVLS=0`` override the
+    automatic choice (VMM and multicast wherever every rank's device supports them)."""
 
     def __init__(self, rank: int, world: int, device: torch.device, heap_bytes: int,
                  exchange: Optional[Callable[[bytes], Sequence[bytes]]] = None,
-                 _local_bases: Optional[List[int]] = None):
+                 _local_bases: Optional[List[int]] = None, control: Optional[_Control] = None,
+                 vmm: Optional[bool] = None):
+        import os
         if not 1 <= world <= _lib.MAX_PEERS:
             raise ValueError(f"world size {world} outside [1, {_lib.MAX_PEERS}]")
         self.rank, self.world, self.device = rank, world, torch.device(device)
@@ -81,30 +147,21 @@ class Fabric:
         self.heap_bytes = (int(heap_bytes) + self.pad_bytes() + (2 << 20) - 1) & ~((2 << 20) - 1)
         self._opened: List[int] = []
         self._owns = _local_bases is None
+        self.mc_base = 0           # multicast mapping of the whole heap (0 = no NVLS)
+        self._vmm: List[tuple] = []  # (ptr, handle) of every VMM mapping of this process
+        self._mc_handle = 0
+        self.kind = "ipc"
         with torch.cuda.device(self.device):
             if _local_bases is not None:
                 # in-process emulation: all "ranks" live on this device (tests on one GPU)
                 self.heap_base = list(_local_bases)
             else:
-                p = C.c_void_p()
-                check(self.lib.psb_heap_alloc(self.heap_bytes, C.byref(p)), "psb_heap_alloc")
-                local = p.value
-                self.heap_base = [0] * world
-                self.heap_base[rank] = local
-                if world > 1:
-                    if exchange is None:
-                        raise ValueError("a multi-rank fabric needs an exchange function")
-                    handle = C.create_string_buffer(_lib.IPC_HANDLE_BYTES)
-                    check(self.lib.psb_ipc_export(local, handle), "psb_ipc_export")
-                    handles = exchange(bytes(handle.raw))
-                    for r in range(world):
-                        if r == rank:
-                            continue
-                        q = C.c_void_p()
-                        check(self.lib.psb_ipc_open(bytes(handles[r]), C.byref(q)),
-                              f"psb_ipc_open(peer {r})")
-                        self.heap_base[r] = q.value
-                        self._opened.append(q.value)
+                use_vmm, use_mc = self._negotiate(control, vmm, os.environ)
+                if use_vmm:
+                    self._build_vmm(control, use_mc)
+                else:
+                    self._build_ipc(exchange if exchange is not None else (
+                        (lambda h: control.gather_obj("fabric/heap", h)) if control else None))
         self.heap_u8 = _wrap(self.heap_base[rank], self.heap_bytes, self.device)
         self._cursor = 0
         self._holes: List[List[int]] = []  # free ranges [offset, nbytes] below the cursor, sorted
@@ -114,6 +171,97 @@ class Fabric:
         self._cfab.rank, self._cfab.world = rank, world
         for r in range(world):
             self._cfab.pad[r] = self.pad.peer_ptr(r)
+
+    # ------------------------------------------------------------------ heap flavours
+    def _negotiate(self, control, vmm, env) -> tuple:
+        """(use_vmm, use_multicast): the same answer on every rank."""
+        v, m = C.c_int(0), C.c_int(0)
+        check(self.lib.psb_vmm_support(C.byref(v), C.byref(m)), "psb_vmm_support")
+        want = env.get("PSB_HEAP", "").lower()
+        ok_v = bool(v.value) and want != "ipc" and vmm is not False
+        ok_m = ok_v and bool(m.value) and self.world > 1 and env.get("PSB_NVLS", "1") != "0"
+        if self.world > 1:
+            if control is None:
+                return False, False  # a bare `exchange` callable can only carry IPC handles
+            flags = control.gather_obj("fabric/caps", (ok_v, ok_m))
+            ok_v = all(f[0] for f in flags)
+            ok_m = ok_v and all(f[1] for f in flags)
+        if (vmm is True or want == "vmm") and not ok_v:
+            raise RuntimeError("a VMM heap was requested but is not available on every rank")
+        return ok_v, ok_m
+
+    def _build_ipc(self, exchange) -> None:
+        rank, world = self.rank, self.world
+        p = C.c_void_p()
+        check(self.lib.psb_heap_alloc(self.heap_bytes, C.byref(p)), "psb_heap_alloc")
+        local = p.value
+        self.heap_base = [0] * world
+        self.heap_base[rank] = local
+        if world > 1:
+            if exchange is None:
+                raise ValueError("a multi-rank fabric needs an exchange function")
+            handle = C.create_string_buffer(_lib.IPC_HANDLE_BYTES)
+            check(self.lib.psb_ipc_export(local, handle), "psb_ipc_export")
+            handles = exchange(bytes(handle.raw))
+            for r in range(world):
+                if r == rank:
+                    continue
+                q = C.c_void_p()
+                check(self.lib.psb_ipc_open(bytes(handles[r]), C.byref(q)),
+                      f"psb_ipc_open(peer {r})")
+                self.heap_base[r] = q.value
+                self._opened.append(q.value)
+
+    def _build_vmm(self, control, use_mc: bool) -> None:
+        import os
+        rank, world, lib = self.rank, self.world, self.lib
+        gran = C.c_size_t()
+        check(lib.psb_vmm_granularity(world, int(use_mc), 0, C.byref(gran)), "psb_vmm_granularity")
+        g = gran.value
+        self.heap_bytes = (self.heap_bytes + g - 1) // g * g
+        ptr, handle, fd = C.c_void_p(), C.c_uint64(), C.c_int(-1)
+        check(lib.psb_vmm_alloc(self.heap_bytes, C.byref(ptr), C.byref(handle), C.byref(fd)),
+              "psb_vmm_alloc")
+        self.kind = "vmm"
+        self._vmm.append((ptr.value, handle.value))
+        self.heap_base = [0] * world
+        self.heap_base[rank] = ptr.value
+        mine = [fd.value]
+        if world == 1:
+            os.close(fd.value)
+            return
+        mc_handle = C.c_uint64(0)
+        if use_mc and rank == 0:
+            mfd = C.c_int(-1)
+            check(lib.psb_mc_create(self.heap_bytes, world, C.byref(mc_handle), C.byref(mfd)),
+                  "psb_mc_create")
+            mine.append(mfd.value)
+        fds = _exchange_fds(control, rank, world, mine)
+        for r in range(world):
+            if r == rank:
+                continue
+            q, h = C.c_void_p(), C.c_uint64()
+            check(lib.psb_vmm_import(fds[r][0], self.heap_bytes, C.byref(q), C.byref(h)),
+                  f"psb_vmm_import(peer {r})")
+            self.heap_base[r] = q.value
+            self._vmm.append((q.value, h.value))
+        if use_mc:
+            if rank != 0:
+                check(lib.psb_mc_import(fds[0][1], C.byref(mc_handle)), "psb_mc_import")
+            self._mc_handle = mc_handle.value
+            check(lib.psb_mc_add_device(self._mc_handle), "psb_mc_add_device")
+            control.barrier("fabric/mc_added")  # every device is in the team before any bind
+            mc = C.c_void_p()
+            check(lib.psb_mc_bind_map(self._mc_handle, handle.value, self.heap_bytes, C.byref(mc)),
+                  "psb_mc_bind_map")
+            self.mc_base = mc.value
+            control.barrier("fabric/mc_bound")
+        for lst in fds:
+            for f in lst:
+                try:
+                    os.close(f)
+                except OSError:
+                    pass
 
     # ------------------------------------------------------------------ construction
     @staticmethod
@@ -126,8 +274,9 @@ class Fabric:
         coordinator's blob exchange (PutHandle / GetHandles + Barrier, proto/psb_ext.proto) —
         the role the reference gives its coordinator for addresses
         (/root/reference/src/worker.cpp:141-186)."""
-        fab = cls(coord.rank, coord.world, device, heap_bytes,
-                  exchange=lambda h: coord.allgather("fabric/heap", h))
+        ctl = _Control(lambda key, obj: coord.allgather_object(key, obj),
+                       lambda name: coord.barrier(name))
+        fab = cls(coord.rank, coord.world, device, heap_bytes, control=ctl)
         coord.barrier("fabric/mapped")  # every peer has mapped every segment before first use
         return fab
 
@@ -139,12 +288,13 @@ class Fabric:
             return cls(0, 1, device, heap_bytes)
         rank, world = dist.get_rank(group), dist.get_world_size(group)
 
-        def exchange(h: bytes):
+        def gather(key, obj):
             out = [None] * world
-            dist.all_gather_object(out, h, group=group)
+            dist.all_gather_object(out, obj, group=group)
             return out
 
-        fab = cls(rank, world, device, heap_bytes, exchange)
+        fab = cls(rank, world, device, heap_bytes,
+                  control=_Control(gather, lambda name: dist.barrier(group=group)))
         dist.barrier(group=group)  # every peer has mapped every segment before first use
         return fab
 
@@ -270,7 +420,16 @@ class Fabric:
             for p in self._opened:
                 self.lib.psb_ipc_close(p)
             self._opened = []
-            if self._owns and self.heap_base[self.rank]:
+            if self.kind == "vmm":
+                if self.mc_base:
+                    self.lib.psb_mc_unbind(self._mc_handle, self.heap_bytes)
+                    self.lib.psb_vmm_release(self.mc_base, self.heap_bytes, self._mc_handle)
+                    self.mc_base = 0
+                for ptr, handle in reversed(self._vmm):
+                    self.lib.psb_vmm_release(ptr, self.heap_bytes, handle)
+                self._vmm = []
+                self.heap_base[self.rank] = 0
+            elif self._owns and self.heap_base[self.rank]:
                 self.lib.psb_heap_free(self.heap_base[self.rank])
                 self.heap_base[self.rank] = 0
             for p in getattr(self, "_group_bases", []):

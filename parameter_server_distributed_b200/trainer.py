@@ -161,7 +161,7 @@ class Trainer:
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
                  staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None,
                  checkpoint_every: int = 0, checkpoint_path: Optional[str] = None,
-                 split_mb: Optional[float] = None):
+                 split_mb: Optional[float] = None, push_nvls: Optional[bool] = None):
         """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
         ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
@@ -190,6 +190,7 @@ class Trainer:
                 bucket_mb=bucket_mb, broadcast=(pull != "gather"), clip_norm=clip_norm,
                 dedicated=dedicated, overlap=overlap, push_grid=push_grid,
                 push_tma=push_tma, lazy_dedicated=(pull == "hybrid"), split_mb=split_mb,
+                push_nvls=push_nvls,
                 # two parameter replicas pay off only for layers that commit their gradients
                 # before their dX GEMM (ops/linear.py); other models keep one replica
                 alt_params=None if getattr(model, "grad_sink_layers", False) else False)
@@ -221,7 +222,9 @@ class Trainer:
         from .utils.checkpoint import save_checkpoint
         if hasattr(self.ps, "drain"):
             self.ps.drain()
-        save_checkpoint(self.ps, path, epoch=epoch)
+        # kernels give up their waits only once the abort word is set, so state gathered while
+        # it is still clear is sound; anything else must not replace the last good file
+        save_checkpoint(self.ps, path, epoch=epoch, validate=self._guard)
 
     def load_checkpoint(self, path: str):
         """Collective.  Restores master weights (and optimizer state when the sidecar exists);
@@ -234,10 +237,11 @@ class Trainer:
         """Before any launch of a step: has the coordinator evicted a peer?  Its heartbeat
         thread has then already raised the abort word, so kernels that were waiting for the dead
         rank have returned; nothing computed since is trustworthy."""
-        if self.ctx.peer_lost:
+        if self.ctx.peer_lost or (self.ctx.abort is not None and self.ctx.abort.is_set):
             from .utils.elastic import PeerLost
+            live = self.ctx.coord.live_workers() if self.ctx.coord is not None else "?"
             raise PeerLost(f"rank {self.ctx.rank}: a peer left the job (coordinator reports "
-                           f"{self.ctx.coord.live_workers()} of {self.ctx.world} workers alive); "
+                           f"{live} of {self.ctx.world} workers alive); "
                            f"restart from the last checkpoint"
                            + (f" ({self.checkpoint_path})" if self.checkpoint_path else ""))
 

@@ -109,12 +109,17 @@ def _read_sidecar(path: str):
     return kind, step, states
 
 
-def save_checkpoint(ps, path: str, epoch: int = 0, iteration: Optional[int] = None) -> None:
+def save_checkpoint(ps, path: str, epoch: int = 0, iteration: Optional[int] = None,
+                    validate=None) -> None:
     """Collective: every rank calls it; rank 0 writes ``path`` (+ ``path.psb`` when the optimizer
-    has state).  Tensors are written in the model's own parameter order."""
+    has state).  Tensors are written in the model's own parameter order.  ``validate`` is
+    called after the state has been gathered and before anything is written; it raises if the
+    gathered data cannot be trusted (a peer was lost while the kernels ran)."""
     masters = ps.gather_state("master")
     m = ps.gather_state("m")
     v = ps.gather_state("v")
+    if validate is not None:
+        validate()
     if ps.rank != 0:
         return
     names = [n for n, _ in ps.named_params]

@@ -24,7 +24,7 @@ def _log(msg):
             f.write(msg + "\n")
 
 
-def check_training(ctx, pull, kind, clip, tma=False):
+def check_training(ctx, pull, kind, clip, tma=False, split_mb=None, nvls=None):
     """Every iteration is checked as ONE step from the engine's actual state: N workers through
     the fused push/pull == fp32 PyTorch update with the mean of the workers' gradients."""
     torch.manual_seed(0)
@@ -32,7 +32,11 @@ def check_training(ctx, pull, kind, clip, tma=False):
     model = MLP(cfg).to(ctx.device, torch.bfloat16)
     optim = OptimConfig(kind=kind, lr=1e-2 if kind == "sgd" else 1e-3)
     tr = psd.Trainer(model, mse_loss, ctx, optim, pull=pull, bucket_mb=1.0, clip_norm=clip,
-                     push_tma=tma)
+                     push_tma=tma, split_mb=split_mb, push_nvls=nvls)
+    if nvls:
+        assert tr.ps._variant(0).get("nvls"), "the NVLS push was not selected"
+    if split_mb:
+        assert len(tr.ps.plan.slots["layers.0.weight"].pieces) > 1, "first layer was not split"
     omodel = MLP(cfg).to(ctx.device, torch.bfloat16)
     gen = torch.Generator(device="cpu").manual_seed(5)
     for it in range(4):
@@ -174,7 +178,7 @@ def check_async(ctx, staleness):
 
 
 def check_tracks_oracle(ctx):
-    """A run whose loss MOVES: 200 steps of a teacher-student regression at lr 0.1 through the
+    """A run whose loss MOVES (about 5x down): 200 steps of a teacher-student regression through the
     sharded parameter server must follow a single-process fp32 run on the global batch.  At the
     noise floor of random targets a wrong reduction hides; here a missing or doubled worker
     changes the trajectory by far more than the tolerance."""
@@ -184,8 +188,8 @@ def check_tracks_oracle(ctx):
     model = MLP(cfg).to(ctx.device, torch.bfloat16)
     oracle = MLP(cfg).to(ctx.device, torch.float32)
     oracle.load_state_dict({k: v.float() for k, v in model.state_dict().items()})
-    opt = torch.optim.SGD(oracle.parameters(), lr=0.1)
-    tr = psd.Trainer(model, mse_loss, ctx, OptimConfig(kind="sgd", lr=0.1), bucket_mb=0.25)
+    opt = torch.optim.SGD(oracle.parameters(), lr=4.0)
+    tr = psd.Trainer(model, mse_loss, ctx, OptimConfig(kind="sgd", lr=4.0), bucket_mb=0.25)
     gen = torch.Generator(device="cpu").manual_seed(77)
     B = 128
     first = last = olast = None
@@ -243,6 +247,20 @@ def main():
         check_training(ctx, pull, kind, clip, tma)
         ctx.barrier()
         _log(f"training {pull} {kind} tma={tma} ok")
+    # NVLS: the switch reduces (multimem.ld_reduce) and replicates (multimem.st); tolerance test
+    if ctx.fabric.mc_base:
+        for kind, split in (("sgd", None), ("adamw", 0.5), ("momentum", None)):
+            check_training(ctx, "broadcast", kind, None, None, split_mb=split, nvls=True)
+            ctx.barrier()
+            _log(f"training nvls {kind} ok")
+    if ctx.rank == 0:
+        print(f"fabric: {ctx.fabric.kind} heap, multicast "
+              f"{'bound (NVLS push tested)' if ctx.fabric.mc_base else 'not available'}", flush=True)
+    # the first layer's weight in row blocks, one bucket each (dW block by block, early pushes)
+    for kind, tma in (("sgd", None), ("adamw", None), ("momentum", False)):
+        check_training(ctx, "broadcast", kind, None, tma, split_mb=0.5)
+        ctx.barrier()
+        _log(f"training split {kind} ok")
     for st in (None, 1, 0):
         worst = check_async(ctx, st)
         ctx.barrier()
