@@ -9,7 +9,8 @@ and one worker per GPU), bf16, synthetic data, random-init weights.
 Prints ONE JSON line on rank 0.  `value` is device-timed (CUDA events, max over ranks) with
 device-resident inputs; `e2e.value` goes through the public `Trainer.step` API with the
 batch coming from pinned host memory and the loss read back every step.
-`--impl reference` runs the reference arm (see baseline/reference_arm.py).
+`--impl reference` runs the reference arm (see baseline/reference_arm.py), `--impl nccl` the
+same workload built from library calls only (NCCL + cuBLAS + torch.optim, baseline/nccl_arm.py).
 """
 from __future__ import annotations
 
@@ -28,7 +29,10 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"],
+                    help="ours = this framework; reference = the unmodified reference classes "
+                         "(baseline/reference_arm.py); nccl = the same workload on library calls only: "
+                         "torch.nn + NCCL reduce-scatter / all-gather + torch.optim (baseline/nccl_arm.py)")
     ap.add_argument("--config", default="mlp",
                     choices=["mlp", "mlp-small", "gpt2m", "gpt2s", "resnet50"])
     ap.add_argument("--batch-per-gpu", type=int, default=0,
@@ -223,6 +227,11 @@ def run_ours(args):
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
                        "layer_gemms": "own tcgen05 kernel" if _linear.ENABLED else "library",
                        "alt_param_replicas": bool(getattr(ps, "_alt", False)),
+                       "control_plane": ("C++ coordinator (register / heartbeat / shard map / handle "
+                                         "exchange / barriers)" if ctx.coord is not None
+                                         else "single rank" if world == 1 else "torch.distributed"),
+                       "heap": (f"{ctx.fabric.kind}" + ("+multicast" if ctx.fabric.mc_base else "")),
+                       "buckets": len(ps.plan.buckets),
                        "l2": "working set (weights+grads+state+activations > 1 GB) exceeds the "
                              "126 MB L2; inputs rotate over 4 batches"},
             "push_pull_ms_per_step": pp_ms,
@@ -244,6 +253,9 @@ def main():
     if args.impl == "reference":
         from baseline.reference_arm import run_reference
         return run_reference(args)
+    if args.impl == "nccl":
+        from baseline.nccl_arm import run_nccl
+        return run_nccl(args)
     return run_ours(args)
 
 

@@ -202,6 +202,10 @@ struct Params {
   const uint32_t* version_pad;  // local pad + PSB_PAD_VERSION_OFF + bucket * PSB_MAX_PEERS
   const uint32_t* epoch;
   int skip_wait;
+  // CTA-pair kernel only: fused epilogue of the all-gather entry (PSB_EPI_*), Z output, bias type
+  int epilogue;
+  void* aux_out;
+  int bias_bf16;
 };
 
 struct TileOrder {
@@ -495,7 +499,8 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
 int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M, int N, int K,
                  int out_dtype, int fused, int gather_ctas, int rank, int world,
                  const char* const* w_peer, char* w_local, uint32_t* tile_flags,
-                 const uint32_t* version_pad, const uint32_t* epoch, int skip_wait, cudaStream_t s);
+                 const uint32_t* version_pad, const uint32_t* epoch, int skip_wait, cudaStream_t s,
+                 int epilogue, void* aux_out, int bias_bf16);
 
 namespace gemm {
 
@@ -524,7 +529,9 @@ static int launch(const void* x, const void* w, Params& p, cudaStream_t s) {
   if (variant() == 1)
     return gemm2_launch(x, w, p.y, p.bias, p.M, p.N, p.K, p.out_dtype, p.fused, p.gather_ctas,
                         p.rank, p.world, p.w_peer, p.w_local, p.tile_flags, p.version_pad, p.epoch,
-                        p.skip_wait, s);
+                        p.skip_wait, s, p.epilogue, p.aux_out, p.bias_bf16);
+  PSB_REQUIRE(p.epilogue == 0 && !p.bias_bf16, PSB_EUNSUPPORTED,
+              "gemm: fused epilogues / bf16 bias need the CTA-pair kernel (psb_gemm_select(1))");
   CUtensorMap map_a, map_b;
   if (int rc = make_map(&map_a, x, p.M, p.K, BM)) return rc;
   if (int rc = make_map(&map_b, w, p.N, p.K, BN)) return rc;
@@ -579,6 +586,13 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* a, psb_stream_t stream) {
   p.bias = a->bias;
   p.M = a->M, p.N = a->N, p.K = a->K;
   p.out_dtype = a->out_dtype;
+  PSB_REQUIRE(a->epilogue == PSB_EPI_NONE || a->epilogue == PSB_EPI_GELU, PSB_EINVAL,
+              "psb_gemm_allgather_bf16: epilogue must be PSB_EPI_NONE or PSB_EPI_GELU");
+  PSB_REQUIRE(a->bias_dtype == PSB_F32 || a->bias_dtype == PSB_BF16, PSB_EINVAL,
+              "psb_gemm_allgather_bf16: bad bias dtype %d", a->bias_dtype);
+  p.epilogue = a->epilogue;
+  p.aux_out = a->aux_out;
+  p.bias_bf16 = a->bias_dtype == PSB_BF16;
   cudaStream_t s = (cudaStream_t)stream;
   if (f.world == 1) {
     p.fused = 0;
@@ -588,7 +602,7 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* a, psb_stream_t stream) {
               "psb_gemm_allgather_bf16: N=%d must be a multiple of %d x world so that every "
               "N-tile has one owner",
               a->N, gemm::BN);
-  PSB_REQUIRE(((size_t)gemm::BN * a->K * 2) % gemm::G_CHUNK == 0, PSB_EINVAL,
+  PSB_REQUIRE(a->K % 64 == 0, PSB_EINVAL,
               "psb_gemm_allgather_bf16: K=%d must be a multiple of 64", a->K);
   PSB_REQUIRE(a->skip_wait || a->epoch, PSB_EINVAL, "psb_gemm_allgather_bf16: epoch missing");
   PSB_REQUIRE(a->bucket >= 0 && a->bucket < PSB_MAX_BUCKETS, PSB_ERANGE,

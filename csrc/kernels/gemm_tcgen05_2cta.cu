@@ -35,13 +35,10 @@ constexpr int EPI_WARPS = 8;   // two warps per TMEM lane quarter, each takes ha
 constexpr int THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
-// Gather: every warp of a gather CTA is an independent copier of 8 KB items (peer -> registers
-// -> local replica, 16 x 16-byte loads in flight per lane).  Measured on B200 at N = 2: a ring
-// of cp.async.bulk copies driven by one thread moves only ~8-10 GB/s per CTA from a peer
-// (loads of 32 KB complete at ~1 GB/s each, bulk stores complete one after the other), plain
-// 16-byte peer loads from many threads are what fills NVLink — as in K1 / K2.
-constexpr int G_CHUNK = 8192;
-constexpr int G_WARPS = THREADS / 32;
+// Gather (fused all-gather mode): pieces of G_CHUNK bytes travel peer -> shared memory -> local
+// replica on the bulk-copy engine, G_STAGES in flight per gather CTA (see gather_role).
+constexpr int G_CHUNK = 16384;
+constexpr int G_STAGES = 11;   // 176 KB of the CTA's dynamic shared memory
 constexpr int CLC_SLOTS = 4;   // responses in flight: the producer runs up to ~3 tiles ahead
 constexpr int CLC_OFF = 256;   // byte offset of the CLC ring inside the 512-byte barrier area
 
@@ -271,67 +268,99 @@ __device__ __forceinline__ float dgelu_tanh(float z) {
   return 0.5f * (1.f + t) + 0.5f * z * (1.f - t * t) * 0.7978845608028654f * (1.f + 0.134145f * z2);
 }
 
-// Items (8 KB pieces of the remote slices, in owner order) are dealt round-robin to all gather
-// warps of the grid.  After its stores a warp makes them visible (membar + release) and bumps
-// the arrival counter of the piece's N-tile; a tile is complete at tile_bytes / G_CHUNK.
-__device__ void gather_role(const Params& p, int gidx) {
+// Gather role: a CTA that does no math streams remote pieces of W into the local replica through
+// a shared-memory ring fed by the bulk-copy engine — peer HBM -> (NVLink) -> smem -> local HBM,
+// no registers involved.  One thread issues cp.async.bulk loads from the owner's replica
+// (G_STAGES x 16 KB in flight per CTA cover the ~4 us peer latency; measured on B200: 16 CTAs
+// reach 710 GB/s from a single peer, 32 CTAs 755 GB/s, benchmarks/probe_fabric.cu), a second
+// thread writes each piece home with a bulk store and, once the store has completed, bumps the
+// arrival counter of the piece's N-tile (a tile is complete at tile_bytes / G_CHUNK).  Pieces
+// are dealt round-robin over the gather CTAs in owner order, so tiles complete in the order in
+// which the GEMM clusters consume them.
+__device__ __forceinline__ void bulk_load(void* smem, const void* gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(smem)),
+      "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gmem, const void* smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem),
+               "r"(smem_u32(smem)), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+__device__ void gather_role(const Params& p, int gidx, uint8_t* smem) {
+  uint8_t* ring = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + G_STAGES * G_CHUNK);
+  uint64_t* empty = full + G_STAGES;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < G_STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+  }
+  __syncthreads();
   const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
   const size_t chunks_per_slice = slice_bytes / G_CHUNK;
   const size_t tile_bytes = (size_t)BN * p.K * 2;
   const size_t n_remote = chunks_per_slice * (size_t)(p.world - 1);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const size_t worker = (size_t)gidx * G_WARPS + warp;
-  const size_t workers = (size_t)p.gather_ctas * G_WARPS;
-  uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
-  const uint32_t target = p.skip_wait ? 0u : *p.epoch;
-  constexpr int V = G_CHUNK / 512;
-  auto locate = [&](size_t c) -> size_t {  // byte offset of item c; waits for its owner once
+  auto offset_of = [&](size_t c, int& owner) -> size_t {
     const int ord = (int)(c / chunks_per_slice);
-    const int owner = (p.rank + 1 + ord) % p.world;
-    if (!((waited >> owner) & 1u)) {
-      if (lane == 0) wait_ge_sys(p.version_pad + owner, target);  // owner's slice is final
-      __syncwarp();
-      waited |= 1u << owner;
-    }
+    owner = (p.rank + 1 + ord) % p.world;
     return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK;
   };
-  auto load = [&](size_t off, uint4 (&v)[V]) {
-    const char* src = p.w_peer[off / slice_bytes] + off + lane * 16;
-#pragma unroll
-    for (int k = 0; k < V; ++k) v[k] = ld_stream_16(src + k * 512);
-  };
-  auto store = [&](size_t off, const uint4 (&v)[V]) {
-    char* dst = p.w_local + off + lane * 16;
-#pragma unroll
-    for (int k = 0; k < V; ++k) st_stream_16(dst + k * 512, v[k]);
-    __threadfence();
-    __syncwarp();
-    if (lane == 0) red_release_gpu_add(p.tile_flags + off / tile_bytes, 1u);
-  };
-  // two items in flight per warp: the loads of the next one are issued before the stores and
-  // the fence of the current one
-  uint4 va[V], vb[V];
-  size_t c = worker;
-  if (c >= n_remote) return;
-  size_t off_a = locate(c), off_b = 0;
-  load(off_a, va);
-  while (true) {
-    const bool more_b = c + workers < n_remote;
-    if (more_b) {
-      off_b = locate(c + workers);
-      load(off_b, vb);
+  if (threadIdx.x == 0) {
+    // ---- producer: peer -> ring
+    uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
+    const uint32_t target = p.skip_wait ? 0u : *p.epoch;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (size_t c = gidx; c < n_remote; c += p.gather_ctas) {
+      int owner;
+      const size_t off = offset_of(c, owner);
+      if (!((waited >> owner) & 1u)) {
+        wait_ge_sys(p.version_pad + owner, target);  // the owner's slice is final
+        fence_proxy_async();                          // ... also for the bulk-copy engine
+        waited |= 1u << owner;
+      }
+      mbar_wait(&empty[stage], phase ^ 1);
+      mbar_expect_tx(&full[stage], G_CHUNK);
+      bulk_load(ring + (size_t)stage * G_CHUNK, p.w_peer[owner] + off, G_CHUNK, &full[stage]);
+      if (++stage == G_STAGES) stage = 0, phase ^= 1;
     }
-    store(off_a, va);
-    if (!more_b) break;
-    c += workers;
-    const bool more_a = c + workers < n_remote;
-    if (more_a) {
-      off_a = locate(c + workers);
-      load(off_a, va);
+  } else if (threadIdx.x == 32) {
+    // ---- consumer: ring -> local replica, then publish
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t tile_of[3];  // tiles of the three most recent stores, oldest first
+    int pending = 0;
+    auto publish = [&](uint32_t tile) {
+      fence_proxy_async();  // the bulk store was made by the async proxy
+      __threadfence();
+      red_release_gpu_add(p.tile_flags + tile, 1u);
+    };
+    for (size_t c = gidx; c < n_remote; c += p.gather_ctas) {
+      int owner;
+      const size_t off = offset_of(c, owner);
+      mbar_wait(&full[stage], phase);
+      bulk_store(p.w_local + off, ring + (size_t)stage * G_CHUNK, G_CHUNK);
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem of the slot is free
+      mbar_arrive(&empty[stage]);
+      if (++stage == G_STAGES) stage = 0, phase ^= 1;
+      if (pending == 3) {  // all but the two newest stores have landed
+        asm volatile("cp.async.bulk.wait_group 2;" ::: "memory");
+        publish(tile_of[0]);
+        tile_of[0] = tile_of[1], tile_of[1] = tile_of[2];
+        pending = 2;
+      }
+      tile_of[pending++] = (uint32_t)(off / tile_bytes);
     }
-    store(off_b, vb);
-    if (!more_a) break;
-    c += workers;
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    for (int i = 0; i < pending; ++i) publish(tile_of[i]);
   }
 }
 
@@ -360,7 +389,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int gather_clusters = p.fused ? p.gather_ctas >> 1 : 0;
 
   if (cluster_id < gather_clusters) {  // both CTAs of a gather cluster copy, independently
-    gather_role(p, blockIdx.x);
+    gather_role(p, blockIdx.x, smem);
     return;
   }
 
@@ -755,15 +784,29 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
                  int out_dtype, int fused, int gather_ctas, int rank, int world,
                  const char* const* w_peer, char* w_local, uint32_t* tile_flags,
                  const uint32_t* version_pad, const uint32_t* epoch, int skip_wait,
-                 cudaStream_t s) {
+                 cudaStream_t s, int epilogue, void* aux_out, int bias_bf16) {
   using namespace gemm2;
   Params p{};
+  p.aux_out = reinterpret_cast<__nv_bfloat16*>(aux_out);
+  p.bias_bf16 = bias_bf16;
   p.y = y, p.bias = bias, p.M = M, p.N = N, p.K = K, p.out_dtype = out_dtype;
   p.fused = fused, p.gather_ctas = gather_ctas, p.rank = rank, p.world = world;
   for (int i = 0; i < world && i < PSB_MAX_PEERS; ++i) p.w_peer[i] = w_peer ? w_peer[i] : nullptr;
   p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
   p.skip_wait = skip_wait;
-  return launch(x, w, p, EPI_NONE, s);
+  if (fused) {
+    // SMs for the gather ring vs the tensor cores.  The bulk-copy ring moves ~45 GB/s per CTA,
+    // so a few CTAs cover the link time of the remote slices within the time of the math.
+    const double t_gemm = 2.0 * M * N * (double)K / 1.5e15;
+    const double t_link = (double)(world - 1) / world * N * (double)K * 2.0 / 700e9;
+    const double r = t_link / t_gemm;
+    p.gather_ctas = r < 0.3 ? 8 : r < 0.7 ? 16 : r < 1.2 ? 24 : 32;
+    if (const char* e = getenv("PSB_GATHER_CTAS")) {
+      const int v = atoi(e);
+      if (v >= 2 && v <= 64) p.gather_ctas = v & ~1;
+    }
+  }
+  return launch(x, w, p, epilogue, s);
 }
 
 }  // namespace psb

@@ -355,16 +355,23 @@ int psb_abort_word_destroy(uint32_t* host_word);
 // shared-memory tiles:  Y[M,N] = X[M,K] · W[N,K]^T (+ bias), fp32 accumulate.
 // psb_gemm_bf16_tn: all operands local.
 // psb_gemm_allgather_bf16: W is row-sharded over the peers (rank r owns rows
-// [r*N/world, (r+1)*N/world)); B tiles are TMA-loaded straight from the owning
-// peer's replica over NVLink for the first M-tile and persisted into the local
-// replica by TMA stores, so the all-gather of the first layer overlaps its GEMM
-// tile by tile.  No counterpart in the reference (north-star item).
+// [r*N/world, (r+1)*N/world)).  The all-gather of W runs INSIDE the GEMM kernel: a few CTAs
+// do no math and stream the remote row-slices from the owners' replicas over NVLink into the
+// local replica through a shared-memory ring on the bulk-copy engine (cp.async.bulk peer ->
+// smem -> local HBM, 176 KB in flight per CTA), bumping an arrival counter per 256-row
+// N-tile; the math clusters start on the locally owned tiles and acquire a tile's counter
+// before their TMA loads touch it.  The gathered W stays in the local replica for the
+// backward pass.  (B tiles are not fed to the MMA straight from the peer: a peer TMA load
+// takes ~4 us, the ring of the MMA pipeline covers ~1.6 us, and every W tile is needed by
+// M/256 row blocks — fetched once, shared through L2.)  Optional GELU epilogue as in
+// psb_gemm_bf16.  No counterpart in the reference (north-star item).
 // ---------------------------------------------------------------------------
 // kernel variant: 1 (default) = CTA pair per 256x256 tile (tcgen05.mma.cta_group::2),
 // 0 = one CTA per 128x256 tile (cta_group::1).  Also PSB_GEMM_VARIANT=1cta|2cta.
 int psb_gemm_select(int variant);
 int psb_gemm_bf16_tn(const void* x, const void* w, const float* bias, void* y, int M, int N, int K,
                      int out_dtype, psb_stream_t stream);
+enum { PSB_EPI_NONE = 0, PSB_EPI_GELU = 1, PSB_EPI_DGELU = 2 };  // fused epilogues, see psb_gemm_bf16
 typedef struct PsbGemmAG {
   PsbFabric fabric;
   void* w[PSB_MAX_PEERS];  // peer-mapped replicas of W [N,K] bf16 (full-size on every rank)
@@ -376,6 +383,9 @@ typedef struct PsbGemmAG {
   int32_t bucket;          // version flags of this bucket gate the remote loads
   const uint32_t* epoch;
   int32_t skip_wait;
+  int32_t epilogue;        // PSB_EPI_NONE / PSB_EPI_GELU (Y = gelu(Z), Z = X·W^T + bias)
+  void* aux_out;           // PSB_EPI_GELU: where Z goes (bf16 [M,N], optional)
+  int32_t bias_dtype;      // PSB_F32 / PSB_BF16
 } PsbGemmAG;
 int psb_gemm_allgather_bf16(const PsbGemmAG* args, psb_stream_t stream);
 
@@ -389,7 +399,6 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* args, psb_stream_t stream);
 // Epilogues (tanh-form GELU): PSB_EPI_GELU stores Z = acc + bias rounded to bf16 into aux_out
 // (optional) and gelu(Z) into Y; PSB_EPI_DGELU stores acc * gelu'(aux_in) — the activation
 // gradient of the PREVIOUS layer is applied by the dX GEMM of this one.  CTA-pair kernel only.
-enum { PSB_EPI_NONE = 0, PSB_EPI_GELU = 1, PSB_EPI_DGELU = 2 };
 typedef struct PsbGemm {
   const void* a;
   const void* b;

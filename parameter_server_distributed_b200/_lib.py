@@ -80,7 +80,8 @@ class PsbGemmAG(C.Structure):
     _fields_ = [("fabric", PsbFabric), ("w", C.c_void_p * MAX_PEERS), ("x", C.c_void_p),
                 ("bias", C.c_void_p), ("y", C.c_void_p), ("M", C.c_int32), ("N", C.c_int32),
                 ("K", C.c_int32), ("out_dtype", C.c_int32), ("bucket", C.c_int32),
-                ("epoch", C.c_void_p), ("skip_wait", C.c_int32)]
+                ("epoch", C.c_void_p), ("skip_wait", C.c_int32), ("epilogue", C.c_int32),
+                ("aux_out", C.c_void_p), ("bias_dtype", C.c_int32)]
 
 
 EPI_NONE, EPI_GELU, EPI_DGELU = 0, 1, 2

@@ -36,8 +36,10 @@ class MLPConfig:
         return sum(d[i] * d[i + 1] + (d[i + 1] if self.bias else 0) for i in range(len(d) - 1))
 
     def flops_per_sample(self) -> int:
+        """Forward + dW of every layer, dX of every layer but the first (the input needs no
+        gradient, so that GEMM is never run): 6 P - 2 d0 d1 per sample."""
         d = self.dims
-        return 6 * sum(d[i] * d[i + 1] for i in range(len(d) - 1))
+        return 6 * sum(d[i] * d[i + 1] for i in range(len(d) - 1)) - 2 * d[0] * d[1]
 
 
 class MLP(nn.Module):
@@ -59,7 +61,7 @@ class MLP(nn.Module):
         z, act = x, None  # pre-activation of the previous layer and gelu() of it
         for i, layer in enumerate(self.layers):
             if i == 0 and self.first_linear_fn is not None:
-                z, act = self.first_linear_fn(x, layer.weight, layer.bias), None
+                z, act = self.first_linear_fn(x, layer.weight, layer.bias, gelu_out=n > 1)
             else:
                 z, act = linear.link(z, act, layer.weight, layer.bias,
                                      gelu_in=i > 0, gelu_out=i + 1 < n)

@@ -57,41 +57,60 @@ class FusedFirstLinear:
         self.lib = _lib.load()
         ps._fused_first_layer = True
 
-    def launch(self, x2d: torch.Tensor, bias_f32: Optional[torch.Tensor],
-               out_dtype: torch.dtype = torch.bfloat16) -> torch.Tensor:
+    def launch(self, x2d: torch.Tensor, bias: Optional[torch.Tensor], gelu: bool = False,
+               out_dtype: torch.dtype = torch.bfloat16):
+        """Returns ``(z, act)``: ``z = x·Wᵀ + b`` and, with ``gelu``, ``act = gelu(z)`` from the
+        same epilogue (``act`` is None otherwise)."""
         a = self.args
         M = x2d.shape[0]
-        y = torch.empty((M, a.N), dtype=out_dtype, device=x2d.device)
+        z = torch.empty((M, a.N), dtype=out_dtype, device=x2d.device)
+        act = torch.empty_like(z) if gelu else None
         a.x = x2d.data_ptr()
-        a.bias = bias_f32.data_ptr() if bias_f32 is not None else None
-        a.y = y.data_ptr()
+        a.bias = bias.data_ptr() if bias is not None else None
+        a.bias_dtype = _lib.BF16 if (bias is not None and bias.dtype == torch.bfloat16) else _lib.F32
+        a.y = act.data_ptr() if gelu else z.data_ptr()
+        a.aux_out = z.data_ptr() if gelu else None
+        a.epilogue = _lib.EPI_GELU if gelu else _lib.EPI_NONE
         a.M = M
         a.out_dtype = _lib.BF16 if out_dtype == torch.bfloat16 else _lib.F32
         with torch.cuda.device(self.device):
             check(self.lib.psb_gemm_allgather_bf16(
                 C.byref(a), torch.cuda.current_stream(self.device).cuda_stream),
                 "psb_gemm_allgather_bf16")
-        return y
+        return z, act
 
-    def __call__(self, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor]):
-        return _FusedLinearFn.apply(x, weight, bias, self)
+    def __call__(self, x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
+                 gelu_out: bool = False):
+        """``(z, gelu(z) or None)`` like :func:`..ops.linear.link`."""
+        z, act = _FusedLinearFn.apply(x, weight, bias, self, gelu_out)
+        return z, (act if gelu_out else None)
 
 
 class _FusedLinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, op: FusedFirstLinear):
+    def forward(ctx, x, weight, bias, op: FusedFirstLinear, gelu_out: bool):
         x2d = x.reshape(-1, x.shape[-1]).contiguous()
-        bias_f32 = bias.detach().float() if bias is not None else None
-        y = op.launch(x2d, bias_f32)
+        b = bias.detach() if bias is not None else None
+        if b is not None and (b.dtype not in (torch.bfloat16, torch.float32) or not b.is_contiguous()):
+            b = b.float().contiguous()
+        y, act = op.launch(x2d, b, gelu=gelu_out)
+        if act is None:
+            act = y.new_empty(0)
+        ctx.mark_non_differentiable(act)  # the next link owns gelu'
+        ctx.set_materialize_grads(False)
         ctx.save_for_backward(x2d, weight)
         ctx.has_bias = bias is not None
         ctx.sink_w = linear.take_sink(weight, ctx.needs_input_grad[1])
         ctx.sink_b = linear.take_sink(bias, bias is not None and ctx.needs_input_grad[2])
         ctx.x_shape = x.shape
-        return y.view(*x.shape[:-1], weight.shape[0])
+        lead = x.shape[:-1]
+        return (y.view(*lead, weight.shape[0]),
+                act.view(*lead, weight.shape[0]) if gelu_out else act)
 
     @staticmethod
-    def backward(ctx, gy):
+    def backward(ctx, gy, _g_act):
+        if gy is None:
+            return None, None, None, None, None
         x2d, weight = ctx.saved_tensors
         gy2d = gy.reshape(-1, gy.shape[-1])
         if not gy2d.is_contiguous():
@@ -109,4 +128,4 @@ class _FusedLinearFn(torch.autograd.Function):
                     gy2d, x2d, trans_a=True, trans_b=True, out=out))
             else:
                 gw = gy2d.t() @ x2d
-        return gx, gw, gb, None
+        return gx, gw, gb, None, None
