@@ -26,4 +26,6 @@ ab grid16 PSB_OVERLAP_GRID=16 --
 ab nvls X=1 -- --push nvls
 ab nvls_nosplit PSB_SPLIT_MB=0 -- --push nvls
 ab nvls_grid16 PSB_OVERLAP_GRID=16 -- --push nvls
+ab hybrid X=1 -- --pull hybrid
+ab nccl X=1 -- --impl nccl
 if [ -z "$NO_SWEEP" ]; then bash benchmarks/r2_sweep.sh $N 256; fi

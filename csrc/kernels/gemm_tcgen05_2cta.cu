@@ -39,6 +39,7 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 // replica on the bulk-copy engine, G_STAGES in flight per gather CTA (see gather_role).
 constexpr int G_CHUNK = 16384;
 constexpr int G_STAGES = 11;   // 176 KB of the CTA's dynamic shared memory
+constexpr int G_PEND = 96;     // stores whose completion has not been published yet (batch = half)
 constexpr int CLC_SLOTS = 4;   // responses in flight: the producer runs up to ~3 tiles ahead
 constexpr int CLC_OFF = 256;   // byte offset of the CLC ring inside the 512-byte barrier area
 
@@ -268,30 +269,38 @@ __device__ __forceinline__ float dgelu_tanh(float z) {
   return 0.5f * (1.f + t) + 0.5f * z * (1.f - t * t) * 0.7978845608028654f * (1.f + 0.134145f * z2);
 }
 
-// Gather role: a CTA that does no math streams remote pieces of W into the local replica through
-// a shared-memory ring fed by the bulk-copy engine — peer HBM -> (NVLink) -> smem -> local HBM,
-// no registers involved.  One thread issues cp.async.bulk loads from the owner's replica
-// (G_STAGES x 16 KB in flight per CTA cover the ~4 us peer latency; measured on B200: 16 CTAs
-// reach 710 GB/s from a single peer, 32 CTAs 755 GB/s, benchmarks/probe_fabric.cu), a second
-// thread writes each piece home with a bulk store and, once the store has completed, bumps the
-// arrival counter of the piece's N-tile (a tile is complete at tile_bytes / G_CHUNK).  Pieces
-// are dealt round-robin over the gather CTAs in owner order, so tiles complete in the order in
-// which the GEMM clusters consume them.
-__device__ __forceinline__ void bulk_load(void* smem, const void* gmem, uint32_t bytes, uint64_t* bar) {
+// Gather role: a CTA that does no math streams remote tiles of W into the local replica through
+// a shared-memory ring fed by TMA — peer HBM -> (NVLink) -> smem -> local HBM, no registers
+// involved.  A piece is one TMA box of the weight's tensor map, 128 rows x 64 columns = 16 KB
+// (the same box the math clusters load): one thread issues cp.async.bulk.tensor loads on the
+// OWNER's tensor map (G_STAGES boxes in flight per CTA cover the ~4 us peer latency; measured on
+// B200, benchmarks/probe_fabric.cu: 16 CTAs reach 710 GB/s from a single peer, 32 CTAs 755 GB/s —
+// 1-D cp.async.bulk copies of the same size stay at ~1 GB/s per copy in flight), a second thread
+// writes each box home with a TMA store on the local map and publishes completed boxes by bumping
+// the arrival counter of their 256-row N-tile (a tile is complete at 2 * K/64 boxes).  Boxes are
+// dealt round-robin over the gather CTAs in owner order, so tiles complete in the order in which
+// the math clusters consume them.
+struct PeerMaps {
+  CUtensorMap m[PSB_MAX_PEERS];
+};
+
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* smem, int c0,
+                                            int c1) {
   asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
           "r"(smem_u32(smem)),
-      "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
-__device__ __forceinline__ void bulk_store(void* gmem, const void* smem, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem),
-               "r"(smem_u32(smem)), "r"(bytes)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+               "r"(smem_u32(smem)), "r"(c0), "r"(c1)
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
-__device__ void gather_role(const Params& p, int gidx, uint8_t* smem) {
+__device__ void gather_role(const Params& p, int gidx, uint8_t* smem, const PeerMaps& peers,
+                            const CUtensorMap* local_map) {
   uint8_t* ring = smem;
   uint64_t* full = reinterpret_cast<uint64_t*>(ring + G_STAGES * G_CHUNK);
   uint64_t* empty = full + G_STAGES;
@@ -304,14 +313,20 @@ __device__ void gather_role(const Params& p, int gidx, uint8_t* smem) {
     fence_proxy_async();
   }
   __syncthreads();
-  const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
-  const size_t chunks_per_slice = slice_bytes / G_CHUNK;
-  const size_t tile_bytes = (size_t)BN * p.K * 2;
-  const size_t n_remote = chunks_per_slice * (size_t)(p.world - 1);
-  auto offset_of = [&](size_t c, int& owner) -> size_t {
-    const int ord = (int)(c / chunks_per_slice);
+  const int rows_per_slice = p.N / p.world;
+  const uint32_t boxes_per_tile = 2u * (uint32_t)(p.K / BK);  // two 128-row halves per k-block
+  const size_t boxes_per_slice = (size_t)(rows_per_slice / BN) * boxes_per_tile;
+  const size_t n_remote = boxes_per_slice * (size_t)(p.world - 1);
+  // box c -> owner, tile, coordinates
+  auto locate = [&](size_t c, int& owner, int& row0, int& col0) -> uint32_t {
+    const int ord = (int)(c / boxes_per_slice);
     owner = (p.rank + 1 + ord) % p.world;
-    return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK;
+    const size_t rem = c - (size_t)ord * boxes_per_slice;
+    const int tile_in_slice = (int)(rem / boxes_per_tile);
+    const uint32_t r2 = (uint32_t)(rem - (size_t)tile_in_slice * boxes_per_tile);
+    row0 = owner * rows_per_slice + tile_in_slice * BN + (int)(r2 & 1u) * 128;
+    col0 = (int)(r2 >> 1) * BK;
+    return (uint32_t)(row0 / BN);
   };
   if (threadIdx.x == 0) {
     // ---- producer: peer -> ring
@@ -320,54 +335,66 @@ __device__ void gather_role(const Params& p, int gidx, uint8_t* smem) {
     int stage = 0;
     uint32_t phase = 0;
     for (size_t c = gidx; c < n_remote; c += p.gather_ctas) {
-      int owner;
-      const size_t off = offset_of(c, owner);
+      int owner, row0, col0;
+      locate(c, owner, row0, col0);
       if (!((waited >> owner) & 1u)) {
         wait_ge_sys(p.version_pad + owner, target);  // the owner's slice is final
-        fence_proxy_async();                          // ... also for the bulk-copy engine
+        fence_proxy_async();                          // ... also for the TMA unit
         waited |= 1u << owner;
       }
       mbar_wait(&empty[stage], phase ^ 1);
       mbar_expect_tx(&full[stage], G_CHUNK);
-      bulk_load(ring + (size_t)stage * G_CHUNK, p.w_peer[owner] + off, G_CHUNK, &full[stage]);
+      tma_load_2d(&peers.m[owner], &full[stage], ring + (size_t)stage * G_CHUNK, col0, row0);
       if (++stage == G_STAGES) stage = 0, phase ^= 1;
     }
   } else if (threadIdx.x == 32) {
     // ---- consumer: ring -> local replica, then publish
     int stage = 0;
     uint32_t phase = 0;
-    uint32_t tile_of[3];  // tiles of the three most recent stores, oldest first
+    // Publishing costs a proxy fence + a membar: far more than the 0.36 us a 16 KB box may
+    // take at the target rate, so completions are published in batches — when G_PEND stores are
+    // unpublished, wait until all but the newest G_PEND/2 have completed
+    // (cp.async.bulk.wait_group), fence once, and bump the counters of that older half (boxes of
+    // one tile merged into one red).
+    uint32_t tile_of[G_PEND];
     int pending = 0;
-    auto publish = [&](uint32_t tile) {
-      fence_proxy_async();  // the bulk store was made by the async proxy
+    auto publish = [&](int n) {  // the n oldest
+      fence_proxy_async();       // the stores were made by the async proxy
       __threadfence();
-      red_release_gpu_add(p.tile_flags + tile, 1u);
+      int i = 0;
+      while (i < n) {
+        int j = i + 1;
+        while (j < n && tile_of[j] == tile_of[i]) ++j;
+        red_release_gpu_add(p.tile_flags + tile_of[i], (uint32_t)(j - i));
+        i = j;
+      }
+      for (int k = n; k < pending; ++k) tile_of[k - n] = tile_of[k];
+      pending -= n;
     };
     for (size_t c = gidx; c < n_remote; c += p.gather_ctas) {
-      int owner;
-      const size_t off = offset_of(c, owner);
+      int owner, row0, col0;
+      const uint32_t tile = locate(c, owner, row0, col0);
       mbar_wait(&full[stage], phase);
-      bulk_store(p.w_local + off, ring + (size_t)stage * G_CHUNK, G_CHUNK);
+      tma_store_2d(local_map, ring + (size_t)stage * G_CHUNK, col0, row0);
       asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // smem of the slot is free
       mbar_arrive(&empty[stage]);
       if (++stage == G_STAGES) stage = 0, phase ^= 1;
-      if (pending == 3) {  // all but the two newest stores have landed
-        asm volatile("cp.async.bulk.wait_group 2;" ::: "memory");
-        publish(tile_of[0]);
-        tile_of[0] = tile_of[1], tile_of[1] = tile_of[2];
-        pending = 2;
+      tile_of[pending++] = tile;
+      if (pending == G_PEND) {
+        asm volatile("cp.async.bulk.wait_group %0;" ::"n"(G_PEND / 2) : "memory");
+        publish(G_PEND / 2);
       }
-      tile_of[pending++] = (uint32_t)(off / tile_bytes);
     }
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    for (int i = 0; i < pending; ++i) publish(tile_of[i]);
+    if (pending) publish(pending);
   }
 }
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     gemm2_bf16_kernel(const __grid_constant__ CUtensorMap map_a,
-                      const __grid_constant__ CUtensorMap map_b, const Params p) {
+                      const __grid_constant__ CUtensorMap map_b,
+                      const __grid_constant__ PeerMaps peers, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
@@ -389,7 +416,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int gather_clusters = p.fused ? p.gather_ctas >> 1 : 0;
 
   if (cluster_id < gather_clusters) {  // both CTAs of a gather cluster copy, independently
-    gather_role(p, blockIdx.x, smem);
+    gather_role(p, blockIdx.x, smem, peers, &map_b);
     return;
   }
 
@@ -460,7 +487,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       const int n_per_rank = p.fused ? num_n / p.world : 0;
-      const uint32_t chunks_per_tile = p.fused ? (uint32_t)((size_t)BN * p.K * 2 / G_CHUNK) : 0;
+      const uint32_t chunks_per_tile = p.fused ? 2u * (uint32_t)(p.K / BK) : 0;  // boxes, see gather_role
       int cs = 0, issued = 0;
       uint32_t cph = 0;
       auto clc_issue = [&](int q) {  // leader only: query number q goes to slot q % CLC_SLOTS
@@ -729,12 +756,12 @@ static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_
 }
 
 template <int EPI>
-static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const Params& p,
-                      int clusters, cudaStream_t s) {
+static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const PeerMaps& peers,
+                      const Params& p, int clusters, cudaStream_t s) {
   // per launch, not once per process: the attribute belongs to the current device's context
   PSB_CUDA_OK(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, p);
+  gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, peers, p);
   PSB_LAUNCH_OK(EPI == EPI_NONE ? "gemm_bf16_tcgen05_2cta"
                                 : EPI == EPI_GELU ? "gemm_bf16_tcgen05_2cta_gelu"
                                                   : "gemm_bf16_tcgen05_2cta_dgelu");
@@ -760,6 +787,14 @@ static int launch(const void* a, const void* b, const Params& p, int epi, cudaSt
   const int num_tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
   int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
   Params q = p;
+  static const PeerMaps kNoPeers = {};
+  PeerMaps fused_peers;
+  if (p.fused) {  // the owners' replicas of W under the same box as the local one
+    for (int r = 0; r < p.world; ++r)
+      if (int rc = make_map(&fused_peers.m[r], p.w_peer[r], p.N, p.K)) return rc;
+    for (int r = p.world; r < PSB_MAX_PEERS; ++r) fused_peers.m[r] = fused_peers.m[0];
+  }
+  const PeerMaps& peers = p.fused ? fused_peers : kNoPeers;
   if (p.fused) {
     clusters = kNumSMs / 2;
     if (num_tiles + p.gather_ctas / 2 < clusters) clusters = num_tiles + p.gather_ctas / 2;
@@ -768,9 +803,9 @@ static int launch(const void* a, const void* b, const Params& p, int epi, cudaSt
     clusters = num_tiles;  // one pair per tile; running pairs cancel and absorb the rest
   }
   switch (epi) {
-    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, q, clusters, s);
-    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, q, clusters, s);
-    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, q, clusters, s);
+    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, peers, q, clusters, s);
+    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, peers, q, clusters, s);
+    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, peers, q, clusters, s);
   }
   PSB_REQUIRE(false, PSB_EINVAL, "gemm: unknown epilogue %d", epi);
   return 0;
@@ -795,12 +830,12 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
   p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
   p.skip_wait = skip_wait;
   if (fused) {
-    // SMs for the gather ring vs the tensor cores.  The bulk-copy ring moves ~45 GB/s per CTA,
-    // so a few CTAs cover the link time of the remote slices within the time of the math.
+    // SMs for the gather ring vs the tensor cores (measured at N = 2, fused_gemm_2gpu_g*.jsonl:
+    // a gather CTA sustains ~10-17 GB/s next to the running GEMM).
     const double t_gemm = 2.0 * M * N * (double)K / 1.5e15;
     const double t_link = (double)(world - 1) / world * N * (double)K * 2.0 / 700e9;
     const double r = t_link / t_gemm;
-    p.gather_ctas = r < 0.3 ? 8 : r < 0.7 ? 16 : r < 1.2 ? 24 : 32;
+    p.gather_ctas = r < 0.15 ? 8 : r < 0.4 ? 16 : r < 0.8 ? 24 : 32;
     if (const char* e = getenv("PSB_GATHER_CTAS")) {
       const int v = atoi(e);
       if (v >= 2 && v <= 64) p.gather_ctas = v & ~1;
