@@ -143,7 +143,7 @@ def run_ours(args):
                           pull=args.pull, bucket_mb=args.bucket_mb,
                           overlap=not args.no_overlap, push_grid=args.push_grid,
                           push_tma={"auto": None, "tma": True, "ldg": False, "nvls": None}[args.push],
-                          push_nvls=True if args.push == "nvls" else None)
+                          push_nvls={"auto": None, "nvls": True}.get(args.push, False))
     B = wl.batch
     gen = torch.Generator().manual_seed(100 + ctx.rank)
     n_host = 4  # rotate a few distinct pinned batches
@@ -223,7 +223,9 @@ def run_ours(args):
                        "global_batch": global_batch, "seq_len": wl.seq_len,
                        "parallelism": f"dp{world} / {world} PS shards", "optimizer": args.optimizer,
                        "mode": args.mode if args.mode != "ssp" else f"ssp(staleness={args.staleness})",
-                       "push": args.push,
+                       "push": args.push + (" -> nvls (multimem.ld_reduce / multimem.st)"
+                                            if getattr(ps, "_want_nvls", False)
+                                            and getattr(ps.backend, "nvls_available", False) else ""),
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
                        "layer_gemms": "own tcgen05 kernel" if _linear.ENABLED else "library",
                        "alt_param_replicas": bool(getattr(ps, "_alt", False)),

@@ -212,6 +212,22 @@ __global__ void __launch_bounds__(kPushThreads, 1) push_fused_kernel(const PsbPu
 }
 
 // ------------------------------------------------------------------------------------
+// Steps 1-2 of K1 as a kernel of their own: one warp announces "my gradients of this bucket
+// are complete" on every owner's pad and waits for everybody's announcement.  Launched in front
+// of a K1 with PSB_PUSH_NO_WAIT, the data kernel starts only when its inputs exist — its CTAs no
+// longer sit on SMs (next to a GEMM that wants them) while the slowest rank finishes its dW.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) push_ready_kernel(PsbFabric f, int bucket,
+                                                        const uint32_t* epoch) {
+  const uint32_t e = *reinterpret_cast<volatile const uint32_t*>(epoch) + 1u;
+  if (threadIdx.x < f.world) {
+    fence_sys();
+    st_release_sys(f.pad[threadIdx.x] + PSB_PAD_READY_OFF + bucket * PSB_MAX_PEERS + f.rank, e);
+    wait_ge_sys(f.pad[f.rank] + PSB_PAD_READY_OFF + bucket * PSB_MAX_PEERS + threadIdx.x, e);
+  }
+}
+
+// ------------------------------------------------------------------------------------
 // K2.  Pull-mode all-gather: each warp copies 512-byte runs from one owner at a time.
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512, 1) pull_allgather_kernel(const PsbPull a) {
@@ -540,6 +556,16 @@ int psb_push_fused(const PsbPush* args, psb_stream_t stream) {
   }
 #undef PSB_DISPATCH
   PSB_LAUNCH_OK("push_fused");
+  return 0;
+}
+
+int psb_push_ready(const PsbPush* args, psb_stream_t stream) {
+  PSB_REQUIRE(args && args->epoch, PSB_EINVAL, "psb_push_ready: null argument");
+  if (int rc = check_fabric(args->fabric, "psb_push_ready")) return rc;
+  PSB_REQUIRE(args->bucket >= 0 && args->bucket < PSB_MAX_BUCKETS, PSB_ERANGE,
+              "psb_push_ready: bucket %d outside [0, %d)", args->bucket, PSB_MAX_BUCKETS);
+  push_ready_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(args->fabric, args->bucket, args->epoch);
+  PSB_LAUNCH_OK("push_ready");
   return 0;
 }
 

@@ -246,6 +246,11 @@ typedef struct PsbPush {
   void* param_mc;                   // PSB_PUSH_NVLS: multicast address of this bucket's bf16 replica
 } PsbPush;
 int psb_push_fused(const PsbPush* args, psb_stream_t stream);
+// Steps 1-2 of the protocol alone (one warp): announce READY for args->bucket at epoch
+// *epoch + 1 and wait for every rank's.  Followed on the same stream by psb_push_fused with
+// PSB_PUSH_NO_WAIT it gives the same result as one waiting launch, but the data kernel's CTAs
+// occupy SMs only once their inputs exist.
+int psb_push_ready(const PsbPush* args, psb_stream_t stream);
 
 // ---------------------------------------------------------------------------
 // K2 — parameter pull: wait for version[b][*] >= *epoch, then gather the N

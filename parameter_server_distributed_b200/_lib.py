@@ -139,6 +139,7 @@ def _declare(lib) -> None:
         "psb_device_sync": (i32, []),
         "psb_pad_bytes": (sz, []),
         "psb_push_fused": (i32, [C.POINTER(PsbPush), vp]),
+        "psb_push_ready": (i32, [C.POINTER(PsbPush), vp]),
         "psb_pull_allgather": (i32, [C.POINTER(PsbPull), vp]),
         "psb_wait_versions": (i32, [C.POINTER(PsbFabric), vp, i32, i32, vp]),
         "psb_device_barrier": (i32, [C.POINTER(PsbFabric), i32, vp, vp]),

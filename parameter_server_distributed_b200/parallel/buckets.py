@@ -150,11 +150,18 @@ def plan_buckets(named_shapes: Sequence[Tuple[str, Sequence[int]]], world: int,
             close()
             continue
         rows = split_rows(shape, (split or {}).get(name, 0), world)
+        tiny = bucket_elems // 64  # a bucket this small is not worth a push of its own
         if rows is not None:
+            # a few small tensors waiting in the open bucket (the layer's bias) ride with the
+            # LAST row block instead of costing a push of their own
+            carried = []
+            if cur is not None and 0 < cur_fill <= tiny:
+                carried, cur, cur_fill = cur.slots, None, 0
             close()
             shape_t = tuple(int(d) for d in shape)
             whole = ParamSlot(name, shape_t, numel, len(buckets), 0, index)
-            for k in range(shape_t[0] // rows):
+            n_pieces = shape_t[0] // rows
+            for k in range(n_pieces):
                 cur = Bucket(len(buckets), base, 0, 0)
                 piece = ParamSlot(f"{name}[{k * rows}:{(k + 1) * rows}]", (rows, shape_t[1]),
                                   rows * shape_t[1], cur.index, 0, index, parent=name,
@@ -162,10 +169,15 @@ def plan_buckets(named_shapes: Sequence[Tuple[str, Sequence[int]]], world: int,
                 cur.slots.append(piece)
                 whole.pieces.append(piece)
                 cur_fill = piece.numel
+                if k == n_pieces - 1:
+                    for c in carried:  # after the block: padding behind it harms nobody
+                        c.bucket, c.offset = cur.index, _round_up(cur_fill, ALIGN_ELEMS)
+                        cur.slots.append(c)
+                        cur_fill = c.offset + c.numel
                 close()
             slots[name] = whole
             continue
-        if cur is not None and cur_fill > 0 and cur_fill + numel > bucket_elems:
+        if cur is not None and cur_fill > tiny and cur_fill + numel > bucket_elems:
             close()
         if cur is None:
             cur = Bucket(len(buckets), base, 0, 0)

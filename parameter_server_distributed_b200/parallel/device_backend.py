@@ -34,6 +34,9 @@ class DeviceBackend:
         self.broadcast = broadcast
         self.push_grid = push_grid
         self.push_tma = push_tma
+        import os
+        self.split_wait = os.environ.get("PSB_SPLIT_WAIT", "1") != "0"
+        self._emulated = not fabric._owns  # ranks emulated in one process: launches are serial
         fabric.reset_flags()  # epoch words below start at 0: drop a previous engine's flags
         gsz = 2 if grad_dtype == torch.bfloat16 else 4
         total = plan.total_elems
@@ -183,9 +186,17 @@ class DeviceBackend:
             flags |= _lib.PUSH_NO_WAIT
         if masked:
             flags |= _lib.PUSH_MASKED
+        # READY handshake as a one-warp kernel of its own in front of the data kernel, so that the
+        # data kernel's CTAs never hold SMs while the slowest rank is still producing gradients
+        ahead = (self.split_wait and self.world > 1 and not self._emulated
+                 and not (no_wait or masked or from_reduced))
+        if ahead:
+            flags |= _lib.PUSH_NO_WAIT
         a.flags = flags
         a.clip_coef = self.clip_coef.data_ptr() if clip else None
         with torch.cuda.device(self.device):
+            if ahead:
+                check(self.lib.psb_push_ready(C.byref(a), self._stream()), "psb_push_ready")
             check(self.lib.psb_push_fused(C.byref(a), self._stream()), "psb_push_fused")
 
     def pull(self, b: int, skip_wait: bool = False, seqlock: bool = False) -> None:
