@@ -19,10 +19,16 @@ SECTIONS = [
      ["LDG.E.128", "LDG.E.NA", "STG.E", "256", "ATOM", "MEMBAR", "LD.E.STRONG.SYS", "ST.E.STRONG.SYS"],
      "K1 register path, AdamW, bf16 gradients, 8 peers"),
     ("push_fused_tma_kernelILi0ELi1E", ["UBLKCP", "SYNCS", "STG.E"], "K1 bulk-copy path (SGD)"),
+    ("push_nvls_kernelILi0E", ["LDGMC", "STG.E.128.STRONG.SYS", "MEMBAR", "LD.E.STRONG.SYS"],
+     "K1 over NVLS (SGD): multimem.ld_reduce = LDGMC...HPADD.BF16x8 (the switch adds the 8 replicas), "
+     "multimem.st = STG.E.128.STRONG.SYS on the multicast address"),
+    ("gemm2_bf16_kernelILi1E", ["UTMASTG", "UTMALDG.2D ", "UTMACMDFLUSH", "RED.E", "REDG"],
+     "fused all-gather GEMM, gather role: TMA loads on the OWNER's tensor map (UTMALDG.2D without "
+     ".2CTA), TMA stores into the local replica (UTMASTG.2D), batched arrival counters"),
     ("colsum_bf16_kernel", ["LDG", "STG", "ATOM", "BAR"], "bias-gradient column sum"),
 ]
 MNEMONICS = (r"\b(LDTM|SYNCS|UBLKCP|UCGABAR|UTCATOMSWS|UTCBAR|UTCHMMA|UTMALDG|UTMASTG|UTMACCTL|"
-             r"UGETNEXTWORKID|UTMACMDFLUSH|LDG\.E[A-Z0-9.]*256|STG\.E[A-Z0-9.]*256)[A-Za-z0-9_.]*")
+             r"UGETNEXTWORKID|UTMACMDFLUSH|LDGMC|LDG\.E[A-Z0-9.]*256|STG\.E[A-Z0-9.]*256)[A-Za-z0-9_.]*")
 
 
 def main() -> int:
