@@ -107,7 +107,7 @@ class ShardedParameterServer:
         4 ranks up, where it moves S bytes per GPU and direction instead of 1.75 S (measured at
         8 GPUs: 64 MB bucket 0.19 vs 0.23 ms, 256 MB 0.60 vs 0.84 ms); ``False`` keeps the
         deterministic peer-load kernels.
-        ``split_mb`` (None = 16 for the synchronous engine with more than one rank, 0 = off;
+        ``split_mb`` (None = 16 for the synchronous engine from 4 ranks up, 0 = off;
         ``PSB_SPLIT_MB``): the weight matrices whose gradients come LAST in backward — nothing is
         left to hide their push behind — are cut into row blocks of about this size, one bucket
         each; a layer that uses ``GradSink.parts()`` then computes dW block by block and the push
@@ -148,7 +148,7 @@ class ShardedParameterServer:
         if "PSB_SPLIT_MB" in os.environ:
             split_mb = float(os.environ["PSB_SPLIT_MB"])
         if split_mb is None:
-            split_mb = 16.0 if (world > 1 and self.is_cuda
+            split_mb = 16.0 if (world >= 4 and self.is_cuda
                                 and type(self) is ShardedParameterServer) else 0.0
         self.plan: BucketPlan = plan_buckets(
             [(n, tuple(p.shape)) for n, p in named_params], world,
