@@ -50,6 +50,13 @@ class DeviceBackend:
         # same iteration still read the old ones (the engine swaps the two after every step)
         self.P2 = fabric.alloc(total * 2, align=4096) if alt_params else None
         self.param_flat2 = self.P2.view(torch.bfloat16) if alt_params else None
+        # The heap hands out ranges that an earlier engine may have used (free list): the padding
+        # between tensors and behind the last one is reduced, normed and updated like everything
+        # else, so it must start at zero — stale parameter values there once showed up as a
+        # gradient norm of 35 instead of 0.02.
+        for buf in (self.G, self.P, self.P2):
+            if buf is not None:
+                buf.local.zero_()
         shard = plan.shard_elems
         dev = self.device
         self.master = torch.zeros(shard, dtype=torch.float32, device=dev)
