@@ -75,3 +75,28 @@ def test_async_single_worker_equals_sync(ctx):
         tr.ps.close()
     for n in outs[0]:
         assert torch.equal(outs[0][n], outs[1][n]), n
+
+
+@pytest.mark.gpu
+def test_second_engine_on_reused_heap_ranges_sees_clean_padding(ctx):
+    """Closing an engine returns its symmetric buffers to the heap's free list and the next
+    engine gets the same ranges back: the padding between tensors (reduced and normed like real
+    elements) must not carry the first engine's values."""
+    import copy
+    dev = ctx.device
+    if True:
+        for rnd in range(3):
+            torch.manual_seed(rnd)
+            cfg = MLPConfig(d_in=264, hidden=(520,), d_out=72)  # odd sizes: padded slots
+            model = MLP(cfg).to(dev, torch.bfloat16)
+            oracle = copy.deepcopy(model).float()
+            tr = psd.Trainer(model, mse_loss, ctx, psd.OptimConfig(kind="sgd", lr=1e-3),
+                             bucket_mb=0.25, clip_norm=1e6)
+            x = torch.randn(64, 264, device=dev).to(torch.bfloat16)
+            y = torch.randn(64, 72, device=dev).to(torch.bfloat16)
+            tr.step_device(x, y)
+            torch.nn.functional.mse_loss(oracle(x.float()), y.float()).backward()
+            exp = torch.sqrt(sum((p.grad ** 2).sum() for p in oracle.parameters())).item()
+            got = tr.ps.grad_norm().item()
+            assert abs(got - exp) < 3e-2 * exp, (rnd, got, exp)
+            tr.ps.close()
