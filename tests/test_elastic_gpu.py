@@ -22,7 +22,12 @@ def _launch(world, addr, phase, ckpt, extra_env=None):
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(world),
-                   PSB_COORDINATOR=addr, PSB_HEARTBEAT_MS="100", PSB_SPIN_TIMEOUT_S="60")
+                   PSB_COORDINATOR=addr, PSB_HEARTBEAT_MS="100", PSB_SPIN_TIMEOUT_S="60",
+                   # peer-load kernels: the survivors keep a mapping of the dead rank's segment, so
+                   # their loads stay legal.  A multicast team does not survive the death of a
+                   # member (its binding goes away under running multimem kernels and the survivors
+                   # get a CUDA error instead of PeerLost) — jobs that want the clean exit run so.
+                   PSB_NVLS="0")
         env.update(extra_env or {})
         procs.append(subprocess.Popen([sys.executable, WORKER, phase, ckpt], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
