@@ -32,7 +32,7 @@ run ours 30 X=1 --
 run ours_2000 2000 X=1 --
 run nccl 30 X=1 -- --impl nccl
 run nccl_2000 2000 X=1 -- --impl nccl
-if [ "$N" -ge 4 ]; then run split32 30 PSB_SPLIT_MB=32 --; fi
+if [ "$N" -ge 4 ] && [ -z "$NO_SPLIT32" ]; then run split32 30 PSB_SPLIT_MB=32 --; fi
 run resnet50 20 X=1 -- --config resnet50 --optimizer adamw
 if [ -n "$GPT2" ]; then run gpt2m 10 X=1 -- --config gpt2m --optimizer adamw; fi
 if [ "$N" -gt 1 ] && [ -z "$NO_FUSED" ]; then

@@ -835,7 +835,7 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
     const double t_gemm = 2.0 * M * N * (double)K / 1.5e15;
     const double t_link = (double)(world - 1) / world * N * (double)K * 2.0 / 700e9;
     const double r = t_link / t_gemm;
-    p.gather_ctas = r < 0.15 ? 8 : r < 0.4 ? 16 : r < 0.8 ? 24 : 32;
+    p.gather_ctas = r < 0.15 ? 8 : r < 0.3 ? 16 : 32;
     if (const char* e = getenv("PSB_GATHER_CTAS")) {
       const int v = atoi(e);
       if (v >= 2 && v <= 64) p.gather_ctas = v & ~1;
