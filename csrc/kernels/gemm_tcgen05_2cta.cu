@@ -39,6 +39,8 @@ constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
 // replica on the bulk-copy engine, G_STAGES in flight per gather CTA (see gather_role).
 constexpr int G_CHUNK = 16384;
 constexpr int G_STAGES = 11;   // 176 KB of the CTA's dynamic shared memory
+constexpr int G_CHUNK_LDG = 8192;   // register-path gather: 8 KB items, one warp each
+constexpr int G_WARPS_LDG = THREADS / 32;
 constexpr int G_PEND = 96;     // stores whose completion has not been published yet (batch = half)
 constexpr int CLC_SLOTS = 4;   // responses in flight: the producer runs up to ~3 tiles ahead
 constexpr int CLC_OFF = 256;   // byte offset of the CLC ring inside the 512-byte barrier area
@@ -238,6 +240,7 @@ struct Params {
   int M, N, K;
   int out_dtype;
   int fused, gather_ctas, rank, world;
+  int gather_tma;                // gather CTAs use the TMA ring (else 16-byte peer loads)
   const char* w_peer[PSB_MAX_PEERS];
   char* w_local;
   uint32_t* tile_flags;
@@ -390,6 +393,71 @@ __device__ void gather_role(const Params& p, int gidx, uint8_t* smem, const Peer
   }
 }
 
+// Register-path gather (the round-1 mechanism, still the faster one from 4 GPUs up, where the
+// remote tiles come from several owners at once — fused_gemm_{4,8}gpu.jsonl): items (8 KB pieces of the remote slices, in owner order) are dealt round-robin to all gather
+// warps of the grid.  After its stores a warp makes them visible (membar + release) and bumps
+// the arrival counter of the piece's N-tile; a tile is complete at tile_bytes / G_CHUNK_LDG.
+__device__ void gather_role_ldg(const Params& p, int gidx) {
+  const size_t slice_bytes = (size_t)(p.N / p.world) * p.K * 2;
+  const size_t chunks_per_slice = slice_bytes / G_CHUNK_LDG;
+  const size_t tile_bytes = (size_t)BN * p.K * 2;
+  const size_t n_remote = chunks_per_slice * (size_t)(p.world - 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const size_t worker = (size_t)gidx * G_WARPS_LDG + warp;
+  const size_t workers = (size_t)p.gather_ctas * G_WARPS_LDG;
+  uint32_t waited = p.skip_wait ? 0xffffffffu : 0u;
+  const uint32_t target = p.skip_wait ? 0u : *p.epoch;
+  constexpr int V = G_CHUNK_LDG / 512;
+  auto locate = [&](size_t c) -> size_t {  // byte offset of item c; waits for its owner once
+    const int ord = (int)(c / chunks_per_slice);
+    const int owner = (p.rank + 1 + ord) % p.world;
+    if (!((waited >> owner) & 1u)) {
+      if (lane == 0) wait_ge_sys(p.version_pad + owner, target);  // owner's slice is final
+      __syncwarp();
+      waited |= 1u << owner;
+    }
+    return (size_t)owner * slice_bytes + (c - (size_t)ord * chunks_per_slice) * G_CHUNK_LDG;
+  };
+  auto load = [&](size_t off, uint4 (&v)[V]) {
+    const char* src = p.w_peer[off / slice_bytes] + off + lane * 16;
+#pragma unroll
+    for (int k = 0; k < V; ++k) v[k] = ld_stream_16(src + k * 512);
+  };
+  auto store = [&](size_t off, const uint4 (&v)[V]) {
+    char* dst = p.w_local + off + lane * 16;
+#pragma unroll
+    for (int k = 0; k < V; ++k) st_stream_16(dst + k * 512, v[k]);
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) red_release_gpu_add(p.tile_flags + off / tile_bytes, 1u);
+  };
+  // two items in flight per warp: the loads of the next one are issued before the stores and
+  // the fence of the current one
+  uint4 va[V], vb[V];
+  size_t c = worker;
+  if (c >= n_remote) return;
+  size_t off_a = locate(c), off_b = 0;
+  load(off_a, va);
+  while (true) {
+    const bool more_b = c + workers < n_remote;
+    if (more_b) {
+      off_b = locate(c + workers);
+      load(off_b, vb);
+    }
+    store(off_a, va);
+    if (!more_b) break;
+    c += workers;
+    const bool more_a = c + workers < n_remote;
+    if (more_a) {
+      off_a = locate(c + workers);
+      load(off_a, va);
+    }
+    store(off_b, vb);
+    if (!more_a) break;
+    c += workers;
+  }
+}
+
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     gemm2_bf16_kernel(const __grid_constant__ CUtensorMap map_a,
@@ -416,7 +484,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   const int gather_clusters = p.fused ? p.gather_ctas >> 1 : 0;
 
   if (cluster_id < gather_clusters) {  // both CTAs of a gather cluster copy, independently
-    gather_role(p, blockIdx.x, smem, peers, &map_b);
+    if (p.gather_tma) gather_role(p, blockIdx.x, smem, peers, &map_b);
+    else gather_role_ldg(p, blockIdx.x);
     return;
   }
 
@@ -487,7 +556,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       const int n_per_rank = p.fused ? num_n / p.world : 0;
-      const uint32_t chunks_per_tile = p.fused ? 2u * (uint32_t)(p.K / BK) : 0;  // boxes, see gather_role
+      const uint32_t chunks_per_tile =  // arrivals that complete a tile: TMA boxes or 8 KB items
+          !p.fused ? 0u : p.gather_tma ? 2u * (uint32_t)(p.K / BK)
+                                       : (uint32_t)((size_t)BN * p.K * 2 / G_CHUNK_LDG);
       int cs = 0, issued = 0;
       uint32_t cph = 0;
       auto clc_issue = [&](int q) {  // leader only: query number q goes to slot q % CLC_SLOTS
@@ -830,12 +901,16 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
   p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
   p.skip_wait = skip_wait;
   if (fused) {
-    // SMs for the gather ring vs the tensor cores (measured at N = 2, fused_gemm_2gpu_g*.jsonl:
-    // a gather CTA sustains ~10-17 GB/s next to the running GEMM).
+    // Gather mechanism and SM split, from measurements (profiles/r2/fused_gemm_*): with ONE owner
+    // to read from (N = 2) the TMA ring is the faster gather (0.207 vs 0.246 ms on 4096x8192x4096);
+    // from 4 GPUs up the register-path copiers are (8 GPUs: 0.221 vs 0.279 ms).
     const double t_gemm = 2.0 * M * N * (double)K / 1.5e15;
     const double t_link = (double)(world - 1) / world * N * (double)K * 2.0 / 700e9;
     const double r = t_link / t_gemm;
-    p.gather_ctas = r < 0.15 ? 8 : r < 0.3 ? 16 : 32;
+    p.gather_tma = world <= 2;
+    if (const char* e = getenv("PSB_GATHER")) p.gather_tma = e[0] == 't';
+    if (p.gather_tma) p.gather_ctas = r < 0.15 ? 8 : r < 0.3 ? 16 : 32;
+    else p.gather_ctas = r < 0.15 ? 16 : r < 0.4 ? 24 : r < 0.8 ? 40 : 64;
     if (const char* e = getenv("PSB_GATHER_CTAS")) {
       const int v = atoi(e);
       if (v >= 2 && v <= 64) p.gather_ctas = v & ~1;

@@ -362,14 +362,17 @@ int psb_abort_word_destroy(uint32_t* host_word);
 // psb_gemm_allgather_bf16: W is row-sharded over the peers (rank r owns rows
 // [r*N/world, (r+1)*N/world)).  The all-gather of W runs INSIDE the GEMM kernel: a few CTAs
 // do no math and stream the remote row-slices from the owners' replicas over NVLink into the
-// local replica through a shared-memory ring on the bulk-copy engine (cp.async.bulk peer ->
-// smem -> local HBM, 176 KB in flight per CTA), bumping an arrival counter per 256-row
-// N-tile; the math clusters start on the locally owned tiles and acquire a tile's counter
-// before their TMA loads touch it.  The gathered W stays in the local replica for the
-// backward pass.  (B tiles are not fed to the MMA straight from the peer: a peer TMA load
-// takes ~4 us, the ring of the MMA pipeline covers ~1.6 us, and every W tile is needed by
-// M/256 row blocks — fetched once, shared through L2.)  Optional GELU epilogue as in
-// psb_gemm_bf16.  No counterpart in the reference (north-star item).
+// local replica, bumping an arrival counter per 256-row N-tile; the math clusters start on the
+// locally owned tiles and acquire a tile's counter before their TMA loads touch it.  Two gather
+// mechanisms, chosen from measurements (PSB_GATHER=tma|ldg overrides): with one owner to read
+// from (2 GPUs) a shared-memory ring on the TMA unit — tensor-map loads on the OWNER's map
+// (peer -> smem, 11 x 16 KB in flight per CTA) and TMA stores into the local replica; from
+// 4 GPUs up warp copiers with 16-byte peer loads (two 8 KB items in flight per warp).  The
+// gathered W stays in the local replica for the backward pass.  (B tiles are not fed to the
+// MMA straight from the peer: a peer TMA load takes ~4 us, the ring of the MMA pipeline covers
+// ~1.6 us, and every W tile is needed by M/256 row blocks — fetched once, shared through L2.)
+// Optional GELU epilogue as in psb_gemm_bf16.  No counterpart in the reference (north-star
+// item).
 // ---------------------------------------------------------------------------
 // kernel variant: 1 (default) = CTA pair per 256x256 tile (tcgen05.mma.cta_group::2),
 // 0 = one CTA per 128x256 tile (cta_group::1).  Also PSB_GEMM_VARIANT=1cta|2cta.
