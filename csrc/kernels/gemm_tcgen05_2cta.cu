@@ -901,13 +901,14 @@ int gemm2_launch(const void* x, const void* w, void* y, const float* bias, int M
   p.w_local = w_local, p.tile_flags = tile_flags, p.version_pad = version_pad, p.epoch = epoch;
   p.skip_wait = skip_wait;
   if (fused) {
-    // Gather mechanism and SM split, from measurements (profiles/r2/fused_gemm_*): with ONE owner
-    // to read from (N = 2) the TMA ring is the faster gather (0.207 vs 0.246 ms on 4096x8192x4096);
-    // from 4 GPUs up the register-path copiers are (8 GPUs: 0.221 vs 0.279 ms).
+    // Gather mechanism and SM split, from measurements (profiles/r2/fused_gemm_*): the register-
+    // path copiers are the default — level with the TMA ring at 2 GPUs (4096x8192x4096: 0.213 vs
+    // 0.207 ms; 1024 and 16384 rows: 0.100 / 0.762 vs 0.113 / 0.790) and faster from 4 GPUs up
+    // (8 GPUs: 0.221 vs 0.279 ms).  PSB_GATHER=tma selects the TMA ring.
     const double t_gemm = 2.0 * M * N * (double)K / 1.5e15;
     const double t_link = (double)(world - 1) / world * N * (double)K * 2.0 / 700e9;
     const double r = t_link / t_gemm;
-    p.gather_tma = world <= 2;
+    p.gather_tma = 0;
     if (const char* e = getenv("PSB_GATHER")) p.gather_tma = e[0] == 't';
     if (p.gather_tma) p.gather_ctas = r < 0.15 ? 8 : r < 0.3 ? 16 : 32;
     else p.gather_ctas = r < 0.15 ? 16 : r < 0.4 ? 24 : r < 0.8 ? 40 : 64;

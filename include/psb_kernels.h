@@ -364,10 +364,11 @@ int psb_abort_word_destroy(uint32_t* host_word);
 // do no math and stream the remote row-slices from the owners' replicas over NVLink into the
 // local replica, bumping an arrival counter per 256-row N-tile; the math clusters start on the
 // locally owned tiles and acquire a tile's counter before their TMA loads touch it.  Two gather
-// mechanisms, chosen from measurements (PSB_GATHER=tma|ldg overrides): with one owner to read
-// from (2 GPUs) a shared-memory ring on the TMA unit — tensor-map loads on the OWNER's map
-// (peer -> smem, 11 x 16 KB in flight per CTA) and TMA stores into the local replica; from
-// 4 GPUs up warp copiers with 16-byte peer loads (two 8 KB items in flight per warp).  The
+// mechanisms (PSB_GATHER=ldg|tma): warp copiers with 16-byte peer loads, two 8 KB items in
+// flight per warp — the default, as fast or faster at every GPU count measured — and a
+// shared-memory ring on the TMA unit: tensor-map loads on the OWNER's map (peer -> smem,
+// 11 x 16 KB in flight per CTA) and TMA stores into the local replica (level at 2 GPUs, slower
+// from 4 up, profiles/r2/fused_gemm_*).  The
 // gathered W stays in the local replica for the backward pass.  (B tiles are not fed to the
 // MMA straight from the peer: a peer TMA load takes ~4 us, the ring of the MMA pipeline covers
 // ~1.6 us, and every W tile is needed by M/256 row blocks — fetched once, shared through L2.)
