@@ -209,6 +209,12 @@ void Server::serve_conn(int fd) {
         conn->erase(req.id);
         continue;
       }
+      if (inflight->load() >= (int)h2::kMaxConcurrentStreams) {  // above what we advertised
+        conn->send_rst(req.id, 7 /*REFUSED_STREAM*/);
+        conn->erase(req.id);
+        req = h2::Stream();
+        continue;
+      }
       auto st = std::make_shared<h2::Stream>(std::move(req));
       req = h2::Stream();
       (*inflight)++;

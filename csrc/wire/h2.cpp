@@ -108,6 +108,7 @@ bool Conn::handshake() {
     put32(s, v);
   };
   if (!server_) setting(2, 0);  // ENABLE_PUSH = 0
+  else setting(3, kMaxConcurrentStreams);  // MAX_CONCURRENT_STREAMS: bounds the handler threads
   setting(4, kOurWindow);       // INITIAL_WINDOW_SIZE
   setting(5, kOurMaxFrame);     // MAX_FRAME_SIZE
   if (!write_frame(SETTINGS, 0, 0, s.data(), s.size())) return false;
@@ -221,7 +222,7 @@ bool Conn::pump() {
   if (len && !read_exact(&p[0], len)) return false;
   const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
 
-  std::lock_guard<std::mutex> lk(state_mu_);
+  std::unique_lock<std::mutex> lk(state_mu_);
   if (hdr_sid_ != 0 && type != CONTINUATION) {  // header block must be contiguous
     send_goaway(1);
     return fail();
@@ -245,16 +246,19 @@ bool Conn::pump() {
           st->body.append(p, off, n);
         }
       }
-      if (len > 0) {  // replenish both windows by what the frame consumed
-        std::string wu;
-        put32(wu, static_cast<uint32_t>(len));
-        if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
-        if (st && !(flags & END_STREAM) && !write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4))
-          return false;
-      }
+      const bool stream_wu = st && !(flags & END_STREAM);
       if (st && (flags & END_STREAM)) {
         st->remote_closed = true;
         completed_.push_back(sid);
+      }
+      if (len > 0) {  // replenish both windows by what the frame consumed
+        // The socket write happens WITHOUT state_mu_: a peer that stops reading can then stall
+        // this reader, but not the handler threads that need the lock to send their responses.
+        lk.unlock();
+        std::string wu;
+        put32(wu, static_cast<uint32_t>(len));
+        if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
+        if (stream_wu && !write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4)) return false;
       }
       break;
     }
@@ -268,6 +272,10 @@ bool Conn::pump() {
       if (flags & PRIO) off += 5;
       if (off + pad > len) return fail();
       hdr_block_.assign(p, off, len - off - pad);
+      if (hdr_block_.size() > kMaxHeaderBlock) {
+        send_goaway(11 /*ENHANCE_YOUR_CALM*/);
+        return fail();
+      }
       if (flags & END_HEADERS) return on_headers_block(sid, flags);
       hdr_sid_ = sid;
       hdr_flags_ = flags;
@@ -276,6 +284,10 @@ bool Conn::pump() {
     case CONTINUATION: {
       if (hdr_sid_ != sid) return fail();
       hdr_block_.append(p);
+      if (hdr_block_.size() > kMaxHeaderBlock) {  // CONTINUATION frames are not a memory reservoir
+        send_goaway(11 /*ENHANCE_YOUR_CALM*/);
+        return fail();
+      }
       if (flags & END_HEADERS) {
         uint8_t f = hdr_flags_;
         hdr_sid_ = 0;

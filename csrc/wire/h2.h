@@ -31,6 +31,11 @@ enum FrameType : uint8_t {
 };
 enum Flags : uint8_t { END_STREAM = 0x1, ACK = 0x1, END_HEADERS = 0x4, PADDED = 0x8, PRIO = 0x20 };
 
+// Limits a server advertises / enforces: any peer on the port could otherwise make it spawn
+// handler threads or buffer header fragments without bound.
+constexpr uint32_t kMaxConcurrentStreams = 128;  // SETTINGS_MAX_CONCURRENT_STREAMS
+constexpr size_t kMaxHeaderBlock = 64 * 1024;    // HEADERS + CONTINUATION fragments of one block
+
 struct Stream {
   uint32_t id = 0;
   std::vector<hpack::Header> headers;   // request headers (server) / response headers (client)
