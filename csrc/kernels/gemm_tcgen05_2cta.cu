@@ -34,7 +34,10 @@ constexpr int EPI_WARPS = 8;   // two warps per TMEM lane quarter, each takes ha
                                // GELU / dGELU epilogues and for short-K tiles
 constexpr int THREADS = 32 * (2 + EPI_WARPS);
 constexpr int TMEM_COLS = 512;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 512;
+constexpr int BAR_BYTES = 1024;                 // mbarriers, TMEM slot, CLC ring
+constexpr int EPI_BUF = 32 * 64;                // one staged piece: 32 rows x 32 bf16 columns
+constexpr int EPI_STAGE_BYTES = EPI_WARPS * 2 * EPI_BUF;  // two pieces in flight per epilogue warp
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + BAR_BYTES + EPI_STAGE_BYTES;
 // Gather (fused all-gather mode): pieces of G_CHUNK bytes travel peer -> shared memory -> local
 // replica on the bulk-copy engine, G_STAGES in flight per gather CTA (see gather_role).
 constexpr int G_CHUNK = 16384;
@@ -241,6 +244,7 @@ struct Params {
   int out_dtype;
   int fused, gather_ctas, rank, world;
   int gather_tma;                // gather CTAs use the TMA ring (else 16-byte peer loads)
+  int tma_store;                 // bf16 outputs leave through shared memory + TMA stores (map_y / map_z)
   const char* w_peer[PSB_MAX_PEERS];
   char* w_local;
   uint32_t* tile_flags;
@@ -462,7 +466,9 @@ template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     gemm2_bf16_kernel(const __grid_constant__ CUtensorMap map_a,
                       const __grid_constant__ CUtensorMap map_b,
-                      const __grid_constant__ PeerMaps peers, const Params p) {
+                      const __grid_constant__ PeerMaps peers,
+                      const __grid_constant__ CUtensorMap map_y,
+                      const __grid_constant__ CUtensorMap map_z, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
@@ -473,8 +479,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   uint8_t* clc_resp = smem + STAGES * STAGE_BYTES + CLC_OFF;  // CLC_SLOTS x 16 bytes
+  uint8_t* epi_stage = smem + STAGES * STAGE_BYTES + BAR_BYTES;  // 1024-aligned
   uint64_t* clc_full = reinterpret_cast<uint64_t*>(clc_resp + CLC_SLOTS * 16);
   uint64_t* clc_empty = clc_full + CLC_SLOTS;
+  uint64_t* zbar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + 512);  // one per epilogue warp
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -504,6 +512,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
       mbar_init(&clc_full[i], 1);    // the issuer's expect_tx; the response completes the bytes
       mbar_init(&clc_empty[i], 2 + 2 * EPI_WARPS);  // readers besides the issuer: MMA, peer producer, epilogue warps
     }
+    for (int i = 0; i < EPI_WARPS; ++i) mbar_init(&zbar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
   }
@@ -660,14 +669,35 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
     int it = 0;
     int cs = 0;
     uint32_t cph = 0;
+    int kbuf = 0;  // staged pieces issued by this warp (buffer = kbuf & 1)
+    uint32_t zphase = 0;  // parity of the warp's Z barrier (dGELU)
     for (int t = first; t < num_tiles; ++it) {
       int m_blk, n_blk;
       decode(t, m_blk, n_blk);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
+      const int row0w = m_blk * BM + (int)cta * 128 + quarter * 32;  // first row of this warp
+      const int row = row0w + lane;
+      const bool row_ok = row < p.M;
+      // dGELU: the pre-activation Z of a piece does not depend on the accumulator.  With the
+      // staged epilogue it arrives by TMA (the aux_in tensor map rides in the map_z slot): the
+      // first piece's load is issued before the wait for the MMA, each next one as soon as the
+      // lanes have taken the current piece out of the warp's Z buffer — a DRAM round trip hidden
+      // behind the math and the store of the piece before.  (Register prefetch with LDG is not
+      // an option: the proxy fence of the store path waits for every outstanding load.)
+      uint8_t* const zbuf = epi_stage + ((warp - 2) * 2) * EPI_BUF;        // dGELU: Z in
+      uint8_t* const obuf = epi_stage + ((warp - 2) * 2 + 1) * EPI_BUF;    // dGELU: result out
+      const bool z_tma = EPI == EPI_DGELU && p.tma_store;
+      auto z_issue = [&](int c) {
+        if (lane == 0) {
+          mbar_expect_tx(&zbar[warp - 2], EPI_BUF);
+          tma_load_2d(&map_z, &zbar[warp - 2], zbuf, n_blk * BN + c * 32, row0w);
+        }
+      };
+      const bool tile_rows = row0w < p.M;
+      if (z_tma && tile_rows && n_blk * BN + half * kChunks * 32 < p.N) z_issue(half * kChunks);
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row = m_blk * BM + (int)cta * 128 + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
 #pragma unroll 1
       for (int c = half * kChunks; c < (half + 1) * kChunks; ++c) {
@@ -675,7 +705,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
         tmem_ld32(taddr + c * 32, r);
         tmem_ld_wait();
         const int col0 = n_blk * BN + c * 32;
-        if (row < p.M && col0 < p.N) {
+        // bf16 output through shared memory: the lane's 32 values (one row) go into a 64-byte row
+        // of a 2 KB piece (16-byte chunks XOR-swizzled with the row, the TMA 64B pattern, so the
+        // eight lanes of a store phase hit distinct banks), then ONE TMA store writes the 32 x 32
+        // piece; rows / columns beyond M / N are clipped by the tensor map.  Direct stores from
+        // registers cost 32 different cache lines per warp instruction.
+        auto stage_store = [&](const CUtensorMap* map, const float* v) {
+          uint8_t* buf = z_tma ? obuf : epi_stage + ((warp - 2) * 2 + (kbuf & 1)) * EPI_BUF;
+          ++kbuf;
+          if (lane == 0) {
+            if (z_tma) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          }
+          __syncwarp();  // the store that used this buffer before has read it
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint4 pk = pack8(v + q * 8);
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
+                             smem_u32(buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4))),
+                         "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w)
+                         : "memory");
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) tma_store_2d(map, buf, col0, row0w);
+        };
+        const bool active = p.tma_store ? (row0w < p.M && col0 < p.N) : (row_ok && col0 < p.N);
+        if (active) {
           float f[32];
 #pragma unroll
           for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(r[k]);
@@ -697,36 +753,67 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
 #pragma unroll
             for (int k = 0; k < 32; ++k) f[k] = __bfloat162float(__float2bfloat16_rn(f[k]));
             if (p.aux_out) {
-              __nv_bfloat16* z = p.aux_out + (size_t)row * p.N + col0;
-              if (full_cols) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) st_stream_16(z + q * 8, pack8(f + q * 8));
+              if (p.tma_store) {
+                stage_store(&map_z, f);
               } else {
+                __nv_bfloat16* z = p.aux_out + (size_t)row * p.N + col0;
+                if (full_cols) {
 #pragma unroll
-                for (int k = 0; k < 32; ++k)
-                  if (col0 + k < p.N) z[k] = __float2bfloat16_rn(f[k]);
+                  for (int q = 0; q < 4; ++q) st_stream_16(z + q * 8, pack8(f + q * 8));
+                } else {
+#pragma unroll
+                  for (int k = 0; k < 32; ++k)
+                    if (col0 + k < p.N) z[k] = __float2bfloat16_rn(f[k]);
+                }
               }
             }
 #pragma unroll
             for (int k = 0; k < 32; ++k) f[k] = gelu_tanh(f[k]);
           }
           if constexpr (EPI == EPI_DGELU) {
-            const __nv_bfloat16* z = p.aux_in + (size_t)row * p.N + col0;
-            if (full_cols) {
+            if (z_tma) {
+              // rows / columns beyond the matrix arrive as zeros and leave clipped
+              mbar_wait(&zbar[warp - 2], zphase);
+              zphase ^= 1u;
+              uint4 zq[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(zq[q].x), "=r"(zq[q].y), "=r"(zq[q].z), "=r"(zq[q].w)
+                             : "r"(smem_u32(zbuf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4))));
+              __syncwarp();  // every lane has its row: the buffer may be refilled
+              const int cn = c + 1;
+              if (cn < (half + 1) * kChunks && n_blk * BN + cn * 32 < p.N) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                z_issue(cn);
+              }
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 float zz[8];
-                unpack8(ld_stream_16(z + q * 8), zz);
+                unpack8(zq[q], zz);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) f[q * 8 + k] *= dgelu_tanh(zz[k]);
               }
-            } else {
+            } else if (row_ok) {
+              const __nv_bfloat16* z = p.aux_in + (size_t)row * p.N + col0;
+              if (full_cols) {
 #pragma unroll
-              for (int k = 0; k < 32; ++k)
-                if (col0 + k < p.N) f[k] *= dgelu_tanh(__bfloat162float(z[k]));
+                for (int q = 0; q < 4; ++q) {
+                  float zz[8];
+                  unpack8(ld_stream_16(z + q * 8), zz);
+#pragma unroll
+                  for (int k = 0; k < 8; ++k) f[q * 8 + k] *= dgelu_tanh(zz[k]);
+                }
+              } else {
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                  if (col0 + k < p.N) f[k] *= dgelu_tanh(__bfloat162float(z[k]));
+              }
             }
           }
-          if (p.out_dtype == PSB_BF16) {
+          if (p.tma_store) {
+            stage_store(&map_y, f);
+          } else if (p.out_dtype == PSB_BF16) {
             __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.y) + (size_t)row * p.N + col0;
             if (col0 + 32 <= p.N) {
 #pragma unroll
@@ -763,6 +850,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
         t += step;
       }
     }
+    // the staged pieces must have left shared memory (and landed) before the CTA goes away
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
 
   tc_fence_before();
@@ -826,13 +915,39 @@ static int make_map_mn(CUtensorMap* map, const void* base, uint64_t red, uint64_
   return 0;
 }
 
+// Output (or Z) as the epilogue stores it: 32 x 32 bf16 pieces, 64-byte rows, 64B swizzle
+static int make_map_out(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols) {
+  EncodeTiledFn enc = get_encode();
+  PSB_REQUIRE(enc, PSB_EUNSUPPORTED, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t elem[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, elem, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PSB_REQUIRE(r == CUDA_SUCCESS, PSB_EINVAL, "cuTensorMapEncodeTiled (output) failed with CUresult %d",
+              (int)r);
+  return 0;
+}
+
+// PSB_GEMM_TMA_STORE=0: bf16 outputs are stored straight from registers (the round-1 epilogue)
+static bool tma_store_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("PSB_GEMM_TMA_STORE");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 template <int EPI>
 static int launch_epi(const CUtensorMap& map_a, const CUtensorMap& map_b, const PeerMaps& peers,
-                      const Params& p, int clusters, cudaStream_t s) {
+                      const CUtensorMap& map_y, const CUtensorMap& map_z, const Params& p,
+                      int clusters, cudaStream_t s) {
   // per launch, not once per process: the attribute belongs to the current device's context
   PSB_CUDA_OK(cudaFuncSetAttribute(gemm2_bf16_kernel<EPI>,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-  gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, peers, p);
+  gemm2_bf16_kernel<EPI><<<clusters * 2, THREADS, SMEM_BYTES, s>>>(map_a, map_b, peers, map_y, map_z, p);
   PSB_LAUNCH_OK(EPI == EPI_NONE ? "gemm_bf16_tcgen05_2cta"
                                 : EPI == EPI_GELU ? "gemm_bf16_tcgen05_2cta_gelu"
                                                   : "gemm_bf16_tcgen05_2cta_dgelu");
@@ -873,10 +988,19 @@ static int launch(const void* a, const void* b, const Params& p, int epi, cudaSt
     q.clc = 1;
     clusters = num_tiles;  // one pair per tile; running pairs cancel and absorb the rest
   }
+  CUtensorMap map_y = map_a, map_z = map_a;  // placeholders unless the TMA-store epilogue is on
+  q.tma_store = p.out_dtype == PSB_BF16 && tma_store_enabled();
+  if (q.tma_store) {
+    if (int rc = make_map_out(&map_y, p.y, p.M, p.N)) return rc;
+    if (epi == EPI_GELU && p.aux_out)
+      if (int rc = make_map_out(&map_z, p.aux_out, p.M, p.N)) return rc;
+    if (epi == EPI_DGELU)  // the epilogue's Z input travels by TMA through the same slot
+      if (int rc = make_map_out(&map_z, p.aux_in, p.M, p.N)) return rc;
+  }
   switch (epi) {
-    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, peers, q, clusters, s);
-    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, peers, q, clusters, s);
-    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, peers, q, clusters, s);
+    case EPI_NONE: return launch_epi<EPI_NONE>(map_a, map_b, peers, map_y, map_z, q, clusters, s);
+    case EPI_GELU: return launch_epi<EPI_GELU>(map_a, map_b, peers, map_y, map_z, q, clusters, s);
+    case EPI_DGELU: return launch_epi<EPI_DGELU>(map_a, map_b, peers, map_y, map_z, q, clusters, s);
   }
   PSB_REQUIRE(false, PSB_EINVAL, "gemm: unknown epilogue %d", epi);
   return 0;
