@@ -244,6 +244,7 @@ struct Params {
   int out_dtype;
   int fused, gather_ctas, rank, world;
   int gather_tma;                // gather CTAs use the TMA ring (else 16-byte peer loads)
+  int group_m;                   // row blocks per tile-walk group (L2 reuse of the A panels)
   int tma_store;                 // bf16 outputs leave through shared memory + TMA stores (map_y / map_z)
   const char* w_peer[PSB_MAX_PEERS];
   char* w_local;
@@ -543,7 +544,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
   // next owner's slice overlaps the math on this one); inside a region tiles are walked in
   // groups of kGroupM row-blocks so that one wave of 74 clusters touches ~8 A panels and ~9 W
   // panels (L2-resident) instead of streaming all of X once per N-tile.
-  constexpr int kGroupM = 8;
+  const int kGroupM = p.group_m;
   const int region_n = p.fused ? num_n / p.world : num_n;
   const int tiles_per_region = num_m * region_n;
   auto decode = [&](int t, int& m_blk, int& n_blk) {
@@ -987,6 +988,11 @@ static int launch(const void* a, const void* b, const Params& p, int epi, cudaSt
   } else if (clc_enabled()) {
     q.clc = 1;
     clusters = num_tiles;  // one pair per tile; running pairs cancel and absorb the rest
+  }
+  q.group_m = 8;
+  if (const char* e = getenv("PSB_GEMM_GROUPM")) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= 64) q.group_m = v;
   }
   CUtensorMap map_y = map_a, map_z = map_a;  // placeholders unless the TMA-store epilogue is on
   q.tma_store = p.out_dtype == PSB_BF16 && tma_store_enabled();
