@@ -11,8 +11,10 @@ LIB = os.path.join(ROOT, "parameter_server_distributed_b200", "_native", "libpsb
 
 SECTIONS = [
     ("gemm2_bf16_kernelILi0E",
-     ["UTCHMMA", "UTMALDG", "UGETNEXTWORKID", "UTCBAR", "LDTM", "UTCATOMSWS", "SYNCS.ARRIVE.TRANS64.RED"],
-     "CTA-pair tcgen05 GEMM (plain epilogue): TMA loads, UMMA issue, commit, TMEM loads, cluster launch control"),
+     ["UTCHMMA", "UTMALDG", "UGETNEXTWORKID", "UTCBAR", "LDTM", "UTCATOMSWS", "SYNCS.ARRIVE.TRANS64.RED",
+      "UTMASTG", "FENCE.VIEW.ASYNC"],
+     "CTA-pair tcgen05 GEMM (plain epilogue): TMA loads, UMMA issue, commit, TMEM loads, cluster launch "
+     "control, and the staged epilogue (STS into the swizzled piece, proxy fence, UTMASTG)"),
     ("gemm2_bf16_kernelILi2E", ["MUFU.TANH", "LDG.E.128", "UTCHMMA"],
      "same kernel, dX*dGELU epilogue: tanh.approx and the 16-byte loads of Z"),
     ("push_fused_kernelILi3ELi1ELi8E",

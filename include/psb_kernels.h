@@ -238,10 +238,11 @@ typedef struct PsbPush {
   int32_t grid;                     // CTAs (0 = auto)
   PsbOptim opt;
   const uint64_t* grad_off;         // optional device array [world]: byte offset added to grad[w]
+                                    // (async mode: which slot of worker w's gradient ring to read)
   int32_t block;                    // threads per CTA of the register-path kernel (0 = 512).  256
                                     // lets a K1 CTA share an SM with a CTA of the tcgen05 GEMM
-                                    // (32 K + 24 K registers), so an overlapped push really overlaps
-                                    // (which slot of the worker's gradient ring to read)
+                                    // (32 K + 24 K registers); measured slower than taking turns
+                                    // (profiles/overlap_matrix_1gpu.txt), kept as an experiment knob
   const void* grad_mc;              // PSB_PUSH_NVLS: multicast address of this bucket's gradient buffer
   void* param_mc;                   // PSB_PUSH_NVLS: multicast address of this bucket's bf16 replica
 } PsbPush;
@@ -405,6 +406,10 @@ int psb_gemm_allgather_bf16(const PsbGemmAG* args, psb_stream_t stream);
 // forward  Y  = X · W^T      : trans_a 0, trans_b 0
 // dX           = dY · W       : trans_a 0, trans_b 1
 // dW           = dY^T · X     : trans_a 1, trans_b 1   (A = dY [batch,N_out], B = X [batch,K_in])
+// bf16 outputs (Y and Z) leave the kernel through shared memory: every epilogue warp packs its
+// 32 x 32 piece into a swizzled 2 KB buffer and one lane issues a TMA store; the dGELU input Z
+// arrives by TMA one piece ahead (PSB_GEMM_TMA_STORE=0: the older register-path epilogue; fp32
+// outputs always use it).
 // Epilogues (tanh-form GELU): PSB_EPI_GELU stores Z = acc + bias rounded to bf16 into aux_out
 // (optional) and gelu(Z) into Y; PSB_EPI_DGELU stores acc * gelu'(aux_in) — the activation
 // gradient of the PREVIOUS layer is applied by the dX GEMM of this one.  CTA-pair kernel only.
