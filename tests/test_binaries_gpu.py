@@ -67,3 +67,61 @@ def test_worker_fills_gradients_on_gpu(tmp_path):
     finally:
         ps.stop()
         co.stop()
+
+
+@pytest.mark.parametrize("kind", ["adam", "momentum"])
+def test_device_shard_checkpoint_carries_the_moments(tmp_path, kind):
+    """Save -> restart -> load -> continue on a --device server equals an uninterrupted run:
+    the optimizer moments live only in HBM and must travel through the checkpoint sidecar
+    (without them a resumed Adam runs late-step bias correction on zero moments)."""
+    ensure_binaries()
+    flags = [f"--optimizer={kind}", "--lr=0.05", "--device=0"]
+    rng = np.random.default_rng(1)
+    n, steps, cut = 3000, 8, 4
+    grads = [rng.standard_normal(n).astype(np.float32) for _ in range(steps)]
+
+    def serve(log):
+        port = free_port()
+        p = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "1", "0", *flags], str(tmp_path),
+                 str(tmp_path / log))
+        assert wait_port(port)
+        return p, protos.Stub(grpc.insecure_channel(f"127.0.0.1:{port}"),
+                              "parameter_server.ParameterServer")
+
+    def push(stub, it):
+        r = stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+            worker_id=0, iteration=it, gradients=[M("parameter_server.Tensor")(
+                name="w", shape=[n], data=grads[it].tolist())]), timeout=20)
+        assert r.aggregation_complete
+
+    def pull(stub):
+        return np.array(stub.ServeParameters(M("parameter_server.PullRequest")(), timeout=20)
+                        .parameters[0].data, dtype=np.float32)
+
+    whole, stub = serve("whole.log")
+    try:
+        for it in range(steps):
+            push(stub, it)
+        expected = pull(stub)
+        assert "device shard disabled" not in whole.output()
+    finally:
+        whole.stop()
+    first, stub = serve("first.log")
+    try:
+        for it in range(cut):
+            push(stub, it)
+        assert stub.SaveCheckpoint(M("parameter_server.SaveCheckpointRequest")(
+            epoch=1, path="mid.ckpt"), timeout=20).success
+    finally:
+        first.stop()
+    assert (tmp_path / "mid.ckpt.psb").stat().st_size > 2 * n  # the sidecar holds real moments
+    second, stub = serve("second.log")
+    try:
+        assert stub.LoadCheckpoint(M("parameter_server.LoadCheckpointRequest")(path="mid.ckpt"),
+                                   timeout=20).success
+        for it in range(cut, steps):
+            push(stub, it)
+        got = pull(stub)
+    finally:
+        second.stop()
+    assert np.allclose(got, expected, atol=2e-5, rtol=1e-4), float(np.abs(got - expected).max())
