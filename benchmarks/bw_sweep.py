@@ -77,10 +77,10 @@ def main():
         elems = int(mb * (1 << 20) / 2)
         plan = plan_buckets([("vec", (elems,))], world, bucket_elems=1 << 62)
         # re-use the heap: reset the bump allocator past the signal pad
-        ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
+        ctx.fabric.reset_allocations()
         for grid in [int(g) for g in args.grids.split(",")]:
             be = DeviceBackend(ctx.fabric, plan, cfg, broadcast=True, push_grid=grid)
-            ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
+            ctx.fabric.reset_allocations()
             be.grad_flat.normal_()
             S = plan.total_elems * 2
             link_bytes = (world - 1) / world * S

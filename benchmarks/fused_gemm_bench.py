@@ -64,7 +64,7 @@ def main():
     for M, N, K in shapes:
         if N % (256 * world):
             continue
-        ctx.fabric._cursor, ctx.fabric._holes = ctx.fabric.pad.offset + ctx.fabric.pad.nbytes, []
+        ctx.fabric.reset_allocations()
         buf = ctx.fabric.alloc(N * K * 2, align=4096)
         wt = buf.view(torch.bfloat16).view(N, K)
         torch.manual_seed(7)

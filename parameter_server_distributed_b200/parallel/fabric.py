@@ -73,6 +73,61 @@ class SymBuffer:
         self.fabric._free(self)
 
 
+class HeapAllocator:
+    """Deterministic first-fit sub-allocator of one heap segment (offsets only, no memory).
+
+    Every rank runs its own instance; ranks that issue the same sequence of ``alloc`` / ``free``
+    calls get the same offsets, which is what makes the heap symmetric.  Freed ranges are merged
+    with their neighbours and a free range at the end lowers the high-water mark again."""
+
+    def __init__(self, capacity: int):
+        self.capacity = int(capacity)
+        self.cursor = 0
+        self.holes: List[List[int]] = []  # free ranges [offset, nbytes] below the cursor, sorted
+
+    def alloc(self, nbytes: int, align: int = 256) -> int:
+        nbytes = int(nbytes)
+        for i, (lo, size) in enumerate(self.holes):
+            off = (lo + align - 1) // align * align
+            if off + nbytes <= lo + size:
+                rest = []
+                if off > lo:
+                    rest.append([lo, off - lo])
+                if off + nbytes < lo + size:
+                    rest.append([off + nbytes, lo + size - off - nbytes])
+                self.holes[i:i + 1] = rest
+                return off
+        off = (self.cursor + align - 1) // align * align
+        if off + nbytes > self.capacity:
+            raise MemoryError(f"symmetric heap exhausted: need {off + nbytes} of {self.capacity} B")
+        if off > self.cursor:
+            self.holes.append([self.cursor, off - self.cursor])
+        self.cursor = off + nbytes
+        return off
+
+    def free(self, offset: int, nbytes: int) -> None:
+        if nbytes <= 0:
+            return
+        self.holes.append([int(offset), int(nbytes)])
+        self.holes.sort()
+        merged: List[List[int]] = []
+        for lo, size in self.holes:
+            if merged and merged[-1][0] + merged[-1][1] >= lo:
+                merged[-1][1] = max(merged[-1][1], lo + size - merged[-1][0])
+            else:
+                merged.append([lo, size])
+        if merged and merged[-1][0] + merged[-1][1] >= self.cursor:  # trailing hole: shrink
+            self.cursor = merged.pop()[0]
+        self.holes = merged
+
+    def reset(self, keep: int) -> None:
+        """Forget every allocation above ``keep`` bytes (benchmarks re-using one heap)."""
+        self.cursor, self.holes = int(keep), []
+
+    def largest_free(self) -> int:
+        return max([self.capacity - self.cursor] + [size for _, size in self.holes])
+
+
 class _Control:
     """What the fabric needs from the job's control plane while it comes up."""
 
@@ -163,8 +218,7 @@ class Fabric:
                     self._build_ipc(exchange if exchange is not None else (
                         (lambda h: control.gather_obj("fabric/heap", h)) if control else None))
         self.heap_u8 = _wrap(self.heap_base[rank], self.heap_bytes, self.device)
-        self._cursor = 0
-        self._holes: List[List[int]] = []  # free ranges [offset, nbytes] below the cursor, sorted
+        self._heap = HeapAllocator(self.heap_bytes)
         self.pad = self.alloc(self.pad_bytes(), align=4096)
         self._barrier_seq = torch.zeros(64, dtype=torch.int32, device=self.device)
         self._cfab = PsbFabric()
@@ -317,48 +371,20 @@ class Fabric:
 
     # ------------------------------------------------------------------ allocation
     def alloc(self, nbytes: int, align: int = 256) -> SymBuffer:
-        """Sub-allocate ``nbytes`` at the same offset on every rank.  First fit in the ranges
-        that were freed, else at the end; deterministic, so ranks that issue the same sequence
-        of ``alloc`` / ``free`` calls stay symmetric."""
-        nbytes = int(nbytes)
-        for i, (lo, size) in enumerate(self._holes):
-            off = (lo + align - 1) // align * align
-            if off + nbytes <= lo + size:
-                rest = []
-                if off > lo:
-                    rest.append([lo, off - lo])
-                if off + nbytes < lo + size:
-                    rest.append([off + nbytes, lo + size - off - nbytes])
-                self._holes[i:i + 1] = rest
-                return SymBuffer(self, off, nbytes)
-        off = (self._cursor + align - 1) // align * align
-        if off + nbytes > self.heap_bytes:
-            raise MemoryError(f"symmetric heap exhausted: need {off + nbytes} of {self.heap_bytes} B")
-        if off > self._cursor:
-            self._holes.append([self._cursor, off - self._cursor])
-        self._cursor = off + nbytes
-        return SymBuffer(self, off, nbytes)
+        """Sub-allocate ``nbytes`` at the same offset on every rank (``HeapAllocator``)."""
+        return SymBuffer(self, self._heap.alloc(nbytes, align), int(nbytes))
 
     def _free(self, buf: SymBuffer) -> None:
-        if buf.nbytes <= 0:
-            return
-        self._holes.append([buf.offset, buf.nbytes])
-        self._holes.sort()
-        merged: List[List[int]] = []
-        for lo, size in self._holes:
-            if merged and merged[-1][0] + merged[-1][1] >= lo:
-                merged[-1][1] = max(merged[-1][1], lo + size - merged[-1][0])
-            else:
-                merged.append([lo, size])
-        if merged and merged[-1][0] + merged[-1][1] >= self._cursor:  # trailing hole: shrink
-            self._cursor = merged.pop()[0]
-        self._holes = merged
+        self._heap.free(buf.offset, buf.nbytes)
         buf.nbytes = 0
 
     def free_bytes(self) -> int:
         """Largest allocation that is certain to succeed (same value on every rank)."""
-        tail = self.heap_bytes - self._cursor
-        return max([tail] + [size for _, size in self._holes])
+        return self._heap.largest_free()
+
+    def reset_allocations(self) -> None:
+        """Drop everything but the signal pad (benchmarks that rebuild backends on one heap)."""
+        self._heap.reset(self.pad.offset + self.pad.nbytes)
 
     def all_gather(self, t: torch.Tensor) -> List[torch.Tensor]:
         """Copies of every rank's ``t`` (same shape / dtype everywhere), through the symmetric

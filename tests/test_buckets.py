@@ -78,3 +78,32 @@ def test_row_split_gives_contiguous_unpadded_buckets():
     assert [r for r, *_ in rngs] == [0, 1] * 4
     seen = {s.name for b in plan.buckets for s in b.slots}
     assert "first.bias" in seen and "last.weight" in seen and "first.weight" not in seen
+
+
+def test_heap_allocator_is_deterministic_and_reuses_freed_ranges():
+    """The symmetric heap's sub-allocator (offsets only): first fit, merge on free, shrink at the
+    end — and two instances fed the same calls agree, which is what keeps the heap symmetric."""
+    from parameter_server_distributed_b200.parallel.fabric import HeapAllocator
+    a, b = HeapAllocator(1 << 20), HeapAllocator(1 << 20)
+    log = []
+    for h in (a, b):
+        p = h.alloc(1000, 4096)
+        g = h.alloc(100_000, 4096)
+        q = h.alloc(50_000, 256)
+        h.free(g, 100_000)
+        r = h.alloc(60_000, 4096)          # fits into the hole g left
+        s = h.alloc(30_000, 256)           # so does this, behind r
+        t = h.alloc(200_000, 4096)         # this does not: goes to the end
+        log.append((p, g, q, r, s, t, h.cursor))
+    assert log[0] == log[1]
+    p, g, q, r, s, t, top = log[0]
+    assert p == 0 and g == 4096 and r == g and g + 60_000 <= s < g + 100_000 and t >= q + 50_000
+    spans = sorted([(p, 1000), (q, 50_000), (r, 60_000), (s, 30_000), (t, 200_000)])
+    assert all(x + n <= y for (x, n), (y, _) in zip(spans, spans[1:]))  # no overlap
+    a.free(t, 200_000)                     # trailing range: the high-water mark drops
+    assert a.cursor < top and a.largest_free() >= (1 << 20) - a.cursor
+    for off, n in ((s, 30_000), (r, 60_000), (q, 50_000), (p, 1000)):
+        a.free(off, n)
+    assert a.cursor == 0 and a.holes == []
+    with pytest.raises(MemoryError):
+        a.alloc((1 << 20) + 1)
