@@ -207,6 +207,7 @@ class Trainer:
         if self.checkpoint_every and not checkpoint_path:
             raise ValueError("checkpoint_every needs a checkpoint_path")
         self.steps = 0
+        self._prefetched = None
         self._dev_inputs = None
         self._loss_ring = None
         self._ring_i = 0
@@ -265,15 +266,9 @@ class Trainer:
         return loss.detach()
 
     # ------------------------------------------------------------------ end-to-end step
-    def step(self, *host_inputs: torch.Tensor) -> LossHandle:
-        """End-to-end iteration from (pinned) host tensors; returns a handle on the loss.
-
-        The H2D copy of step i runs on a copy stream into one of two device buffer sets, so it
-        overlaps the tail of step i-1; the loss goes back through a pinned ring."""
-        if self.device.type != "cuda":
-            loss = self.step_device(*host_inputs)
-            return LossHandle(loss.reshape(()).float(), None)
-        self._guard()
+    def _stage(self, host_inputs) -> tuple:
+        """Queue the H2D copy of one batch into the next device buffer set (copy stream);
+        returns ``(slot, copied_event)``."""
         if self._dev_inputs is None:
             self._dev_inputs = [[torch.empty(t.shape, dtype=t.dtype, device=self.device)
                                  for t in host_inputs] for _ in range(2)]
@@ -283,7 +278,6 @@ class Trainer:
             self._loss_ring = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(4)]
             self.h2d_bytes = sum(t.numel() * t.element_size() for t in host_inputs)
         slot = self._ring_i & 1
-        cur = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self._copy_stream):
             if self._consumed[slot] is not None:
                 self._copy_stream.wait_event(self._consumed[slot])  # step i-2 is done with it
@@ -291,6 +285,45 @@ class Trainer:
                 d.copy_(h, non_blocking=True)
             copied = torch.cuda.Event()
             copied.record(self._copy_stream)
+        return slot, copied
+
+    def prefetch(self, *host_inputs: torch.Tensor) -> None:
+        """Start the H2D copy of the NEXT step's batch now; the following ``step()`` (called
+        without arguments, or with these same tensors) uses it.  Call it right after ``step``
+        of the current batch: the copy then has the whole current step to finish in, instead of
+        the part of it that is left once the caller has read the previous loss — with eight
+        ranks sharing the host's memory system a 40 MB batch takes longer than that part."""
+        if self.device.type != "cuda":
+            self._prefetched = (None, None, host_inputs)
+            return
+        if self._prefetched is not None:
+            raise RuntimeError("prefetch() called twice without a step() in between")
+        # the buffer set the next step will use is the one after the step that is in flight
+        slot, copied = self._stage(host_inputs)
+        self._prefetched = (slot, copied, host_inputs)
+
+    def step(self, *host_inputs: torch.Tensor) -> LossHandle:
+        """End-to-end iteration from (pinned) host tensors; returns a handle on the loss.
+
+        The H2D copy of step i runs on a copy stream into one of two device buffer sets, so it
+        overlaps the tail of step i-1 (all of it after :meth:`prefetch`); the loss goes back
+        through a pinned ring."""
+        pre, self._prefetched = self._prefetched, None
+        if self.device.type != "cuda":
+            if pre is not None and not host_inputs:
+                host_inputs = pre[2]
+            loss = self.step_device(*host_inputs)
+            return LossHandle(loss.reshape(()).float(), None)
+        self._guard()
+        if pre is not None:
+            if host_inputs and any(a is not b for a, b in zip(host_inputs, pre[2])):
+                raise ValueError("step() got a different batch than the one that was prefetched")
+            slot, copied = pre[0], pre[1]
+        else:
+            if not host_inputs:
+                raise ValueError("step() without arguments needs a prefetch() first")
+            slot, copied = self._stage(host_inputs)
+        cur = torch.cuda.current_stream(self.device)
         cur.wait_event(copied)
         *xs, target = self._dev_inputs[slot]
         loss = self.loss_fn(self.model(*xs), target)

@@ -100,3 +100,33 @@ def test_second_engine_on_reused_heap_ranges_sees_clean_padding(ctx):
             got = tr.ps.grad_norm().item()
             assert abs(got - exp) < 3e-2 * exp, (rnd, got, exp)
             tr.ps.close()
+
+
+@pytest.mark.gpu
+def test_prefetched_batches_train_like_batches_passed_to_step(ctx):
+    """Trainer.prefetch(next batch) + step() is the same training as step(batch)."""
+    dev = ctx.device
+    cfg = MLPConfig(d_in=256, hidden=(512,), d_out=128)
+    gen = torch.Generator().manual_seed(3)
+    batches = [(torch.randn(64, 256, generator=gen).to(torch.bfloat16).pin_memory(),
+                torch.randn(64, 128, generator=gen).to(torch.bfloat16).pin_memory()) for _ in range(5)]
+    runs = []
+    for use_prefetch in (False, True):
+        torch.manual_seed(11)
+        model = MLP(cfg).to(dev, torch.bfloat16)
+        tr = psd.Trainer(model, mse_loss, ctx, psd.OptimConfig(kind="sgd", lr=0.05), bucket_mb=0.25)
+        losses = []
+        if use_prefetch:
+            tr.prefetch(*batches[0])
+            for i in range(len(batches)):
+                h = tr.step()
+                if i + 1 < len(batches):
+                    tr.prefetch(*batches[i + 1])
+                losses.append(h.item())
+            with pytest.raises(ValueError):
+                tr.step()  # nothing prefetched, nothing passed
+        else:
+            losses = [tr.step(*b).item() for b in batches]
+        runs.append(losses)
+        tr.ps.close()
+    assert runs[0] == runs[1], runs
