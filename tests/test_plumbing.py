@@ -196,3 +196,12 @@ def test_python_worker_example_against_cpp_servers(tmp_path):
     finally:
         ps.stop()
         co.stop()
+
+
+def test_eviction_script(tmp_path):
+    """scripts/test_eviction.sh: kill 1 of 3 workers, the others finish (shell-level T7)."""
+    r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "test_eviction.sh")],
+                       capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, ITERS="600", COORD_PORT=str(free_port()),
+                                PS_PORT=str(free_port())))
+    assert r.returncode == 0 and "PASS:" in r.stdout, r.stdout[-800:] + r.stderr[-400:]
