@@ -132,6 +132,11 @@ void ParameterServerCore::apply_locked(const std::vector<HostTensor>& g) {
     if (g[i].name != params_[i].name || g[i].shape != params_[i].shape) continue;  // positional
     update_tensor(i, g[i].data);
   }
+  if (dev_ && dev_->active() && !dev_->sync()) {
+    // the device lost this step: bring back what it still has and continue on the host
+    dev_->download_state(m_, v_);
+    dev_->download(params_);
+  }
   version_++;
 }
 

@@ -162,8 +162,9 @@ bool DeviceShard::update(size_t idx, const float* grad, size_t n, int64_t opt_st
   if (rc == 0)
     rc = im.optim_step(&o, s.master, s.m, s.v, s.grad, PSB_F32, nullptr, n, nullptr, s.step,
                        nullptr);
-  // the staged host gradient may be reused by the caller, so the copy must have finished
-  if (rc == 0) rc = im.stream_sync(nullptr);
+  // No synchronisation here: a copy from pageable host memory has left the caller's buffer
+  // when the call returns, and the update kernels of one step queue up behind each other;
+  // ParameterServerCore::apply_locked waits once per step (sync()).
   if (rc != 0) {
     // The device copy of this tensor can no longer be trusted as the newest one.  Bring back
     // what is still readable, then stop using the GPU: the host path continues from there.
@@ -174,6 +175,17 @@ bool DeviceShard::update(size_t idx, const float* grad, size_t n, int64_t opt_st
   }
   im.dirty = true;
   return true;
+}
+
+bool DeviceShard::sync() {
+  Impl& im = *impl_;
+  if (im.disabled) return true;
+  im.set_device(im.opt.device);
+  if (im.stream_sync(nullptr) == 0) return true;
+  std::cerr << "device shard: update step failed (" << im.last_error()
+            << "): falling back to the host copy" << std::endl;
+  im.failed_update = true;
+  return false;
 }
 
 bool DeviceShard::download(std::vector<HostTensor>& params) {

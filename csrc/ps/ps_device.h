@@ -20,7 +20,10 @@ class DeviceShard {
   // slots are released and the shard disables itself: update() then answers false and the
   // caller's host path takes over.  Returns whether the shard is usable.
   bool upload(const std::vector<HostTensor>& params);
+  // Queues copy + K3 for one tensor; sync() once per optimizer step waits for all of them
+  // (one stream synchronisation per push instead of one per tensor).
   bool update(size_t idx, const float* grad, size_t n, int64_t opt_step);
+  bool sync();
   // false: a copy failed and `params` may be stale (the caller keeps its host copy)
   bool download(std::vector<HostTensor>& params);
   // Optimizer moments for the checkpoint sidecar: device -> host before a save, host -> device
