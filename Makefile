@@ -55,10 +55,13 @@ $(BIN)/psb_pbtool: $(call obj,csrc/selftest/pbtool.cpp)
 kernels:
 	python -c "from parameter_server_distributed_b200 import _build; print(_build.build_kernels())"
 
+# The sanitizer runtimes (libtsan / libasan) ship with the distribution's compiler; a g++ from
+# elsewhere on PATH or in $CXX may not have them, so these targets prefer /usr/bin/g++.
+SAN_CXX ?= $(if $(wildcard /usr/bin/g++),/usr/bin/g++,$(CXX))
 tsan:
-	$(MAKE) SAN=thread binaries
+	$(MAKE) SAN=thread CXX=$(SAN_CXX) binaries
 asan:
-	$(MAKE) SAN=address binaries
+	$(MAKE) SAN=address CXX=$(SAN_CXX) binaries
 
 clean:
 	rm -rf build parameter_server_distributed_b200/_native/*.so parameter_server_distributed_b200/_native/*.stamp

@@ -2,6 +2,7 @@
 #include "ps_core.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -52,6 +53,7 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
     st.seen[worker_id] = true;
     st.aggregated = true;
     prune_locked();
+    changed_.notify_all();
     return true;
   }
 
@@ -91,6 +93,7 @@ void ParameterServerCore::aggregate_locked(IterState& st, const std::vector<Host
   apply_locked(mean);
   st.aggregated = true;
   st.staged.clear();  // the reference keeps every copy forever
+  changed_.notify_all();
 }
 
 void ParameterServerCore::prune_locked() {
@@ -105,6 +108,7 @@ void ParameterServerCore::prune_locked() {
 int ParameterServerCore::set_total_workers(int n) {
   std::lock_guard<std::mutex> lk(mu_);
   total_workers_.store(n);
+  changed_.notify_all();  // the SSP gate depends on the count; sync completions notify below
   int completed = 0;
   if (opt_.mode != PsMode::kSync) return 0;
   const size_t need = static_cast<size_t>(std::max(1, n));
@@ -192,8 +196,7 @@ std::vector<HostTensor> ParameterServerCore::serve_parameters(int32_t /*iteratio
   return params_;
 }
 
-bool ParameterServerCore::check_sync_status(int32_t iteration, int32_t& workers_received) {
-  std::lock_guard<std::mutex> lk(mu_);
+bool ParameterServerCore::sync_status_locked(int32_t iteration, int32_t& workers_received) {
   auto it = iters_.find(iteration);
   if (it == iters_.end()) {
     workers_received = 0;
@@ -203,8 +206,24 @@ bool ParameterServerCore::check_sync_status(int32_t iteration, int32_t& workers_
   return it->second.aggregated;
 }
 
-bool ParameterServerCore::staleness_ok(int32_t /*worker_id*/, int32_t iteration) {
+bool ParameterServerCore::check_sync_status(int32_t iteration, int32_t& workers_received) {
   std::lock_guard<std::mutex> lk(mu_);
+  return sync_status_locked(iteration, workers_received);
+}
+
+bool ParameterServerCore::wait_sync_status(int32_t iteration, int32_t& workers_received) {
+  std::unique_lock<std::mutex> lk(mu_);
+  if (sync_status_locked(iteration, workers_received) || opt_.long_poll_ms <= 0) {
+    return sync_status_locked(iteration, workers_received);
+  }
+  changed_.wait_for(lk, std::chrono::milliseconds(opt_.long_poll_ms), [&] {
+    int32_t r = 0;
+    return sync_status_locked(iteration, r);
+  });
+  return sync_status_locked(iteration, workers_received);
+}
+
+bool ParameterServerCore::staleness_ok_locked(int32_t iteration) {
   if (opt_.mode == PsMode::kAsync) return true;
   if (opt_.mode == PsMode::kSync) {
     auto it = iters_.find(iteration);
@@ -216,6 +235,20 @@ bool ParameterServerCore::staleness_ok(int32_t /*worker_id*/, int32_t iteration)
     for (const auto& kv : clocks_) slowest = std::min(slowest, kv.second);
   }
   return iteration - (slowest + 1) <= opt_.staleness;
+}
+
+bool ParameterServerCore::staleness_ok(int32_t /*worker_id*/, int32_t iteration) {
+  std::lock_guard<std::mutex> lk(mu_);
+  return staleness_ok_locked(iteration);
+}
+
+bool ParameterServerCore::wait_staleness_ok(int32_t /*worker_id*/, int32_t iteration) {
+  std::unique_lock<std::mutex> lk(mu_);
+  if (opt_.mode == PsMode::kSsp && opt_.long_poll_ms > 0 && !staleness_ok_locked(iteration)) {
+    changed_.wait_for(lk, std::chrono::milliseconds(opt_.long_poll_ms),
+                      [&] { return staleness_ok_locked(iteration); });
+  }
+  return staleness_ok_locked(iteration);
 }
 
 // ---- checkpoints: SURVEY App. B (raw little-endian structs, size_t = 8 bytes, no padding) ----

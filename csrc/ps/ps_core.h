@@ -12,6 +12,7 @@
 #pragma once
 
 #include <atomic>
+#include <condition_variable>
 #include <cstdint>
 #include <map>
 #include <mutex>
@@ -39,6 +40,11 @@ struct PsOptions {
   float weight_decay = 0.0f;
   int keep_iterations = 1024;   // iteration states retained for status queries
   int device = -1;              // >= 0: keep master weights in HBM and update with K3
+  // Status queries that would answer "not yet" are held this long for the answer to change
+  // (CheckSyncStatus in sync mode, the staleness gate of ServeParameters in SSP mode), so a
+  // waiting worker learns of the completion when it happens instead of at its next poll.
+  // 0 = answer at once like the reference (src/parameter_server_service.cpp:77-90).
+  int long_poll_ms = 25;
 };
 
 class DeviceShard;  // ps_device.cpp (dlopen of libpsb_kernels.so)
@@ -53,6 +59,10 @@ class ParameterServerCore {
   bool receive_gradients(int32_t worker_id, int32_t iteration, const std::vector<HostTensor>& grads);
   std::vector<HostTensor> serve_parameters(int32_t iteration);
   bool check_sync_status(int32_t iteration, int32_t& workers_received);
+  // The same answers, but a negative one is held up to options().long_poll_ms for the state
+  // to change (an iteration aggregates, a clock advances, the membership changes).
+  bool wait_sync_status(int32_t iteration, int32_t& workers_received);
+  bool wait_staleness_ok(int32_t worker_id, int32_t iteration);
   // SSP / async: is a worker allowed to start clock `iteration`?
   bool staleness_ok(int32_t worker_id, int32_t iteration);
   bool save_checkpoint(int32_t epoch, const std::string& path);
@@ -76,7 +86,11 @@ class ParameterServerCore {
 
   std::atomic<int> total_workers_;
   PsOptions opt_;
+  bool sync_status_locked(int32_t iteration, int32_t& workers_received);
+  bool staleness_ok_locked(int32_t iteration);
+
   std::mutex mu_;  // guards everything below (single lock: no ordering hazards)
+  std::condition_variable changed_;  // an iteration aggregated / a clock or the membership moved
   std::vector<HostTensor> params_;
   std::vector<std::vector<float>> m_, v_;
   int64_t opt_step_ = 0;

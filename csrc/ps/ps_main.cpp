@@ -6,6 +6,8 @@
 //   --momentum=F --beta1=F --beta2=F --eps=F --weight-decay=F  --device=N (HBM-resident shard)
 //   --coordinator=host:port  --membership-poll-ms=N   follow the coordinator's worker registry:
 //       an evicted worker no longer blocks the sync barrier (PSB_COORDINATOR, PSB_MEMBERSHIP_POLL_MS)
+//   --long-poll-ms=N   hold a "not ready" status answer up to N ms for the barrier to open
+//       (default 25; 0 = answer at once like the reference) (PSB_LONG_POLL_MS)
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -35,6 +37,7 @@ int main(int argc, char** argv) {
   if (const char* e = env("PSB_OPTIMIZER")) opt.optimizer = e;
   if (const char* e = env("PSB_LR")) opt.lr = std::strtof(e, nullptr);
   if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
+  if (const char* e = env("PSB_LONG_POLL_MS")) opt.long_poll_ms = std::atoi(e);
   std::string coordinator;
   int membership_poll_ms = 1000;
   if (const char* e = env("PSB_COORDINATOR")) coordinator = e;
@@ -54,6 +57,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "eps", v)) opt.eps = std::strtof(v.c_str(), nullptr);
     else if (flag(a, "weight-decay", v)) opt.weight_decay = std::strtof(v.c_str(), nullptr);
     else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
+    else if (flag(a, "long-poll-ms", v)) opt.long_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "coordinator", v)) coordinator = v;
     else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
     else if (a.rfind("--", 0) == 0) {

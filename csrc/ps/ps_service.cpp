@@ -61,7 +61,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
       int32_t received = 0;
       out.ready = core_.check_sync_status(in.iteration, received);
     } else {
-      out.ready = core_.staleness_ok(in.worker_id, in.iteration);
+      out.ready = core_.wait_staleness_ok(in.worker_id, in.iteration);
     }
     for (auto& t : core_.serve_parameters(in.iteration)) out.parameters.push_back(to_pb(std::move(t)));
     resp = out.encode();
@@ -72,7 +72,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SyncStatusRequest"};
     pb::SyncStatusResponse out;
     out.iteration = in.iteration;
-    out.ready = core_.check_sync_status(in.iteration, out.workers_received);
+    out.ready = core_.wait_sync_status(in.iteration, out.workers_received);
     out.total_workers = core_.get_total_workers();
     resp = out.encode();
     return Status{};

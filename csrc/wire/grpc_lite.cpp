@@ -16,6 +16,7 @@
 
 #include <chrono>
 #include <cstring>
+#include <deque>
 
 #include "h2.h"
 
@@ -99,8 +100,59 @@ bool split_host_port(const std::string& s, std::string& host, int& port) {
   return true;
 }
 
+// ------------------------------------------------------------------------------ HandlerPool
+// Request handlers run on pooled threads: waking an idle thread costs a futex, creating one per
+// RPC costs a clone + stack mapping + teardown.  Handlers may block for long (Barrier, the
+// long-polled status queries), so the pool grows whenever no thread is idle — it is bounded by
+// what the connections admit (kMaxConcurrentStreams each), not by a fixed size that could
+// deadlock a barrier — and idle threads retire after a few seconds.
+class HandlerPool : public std::enable_shared_from_this<HandlerPool> {
+ public:
+  void submit(std::function<void()> fn) {
+    std::unique_lock<std::mutex> lk(mu_);
+    q_.push_back(std::move(fn));
+    if (idle_ > 0) {
+      lk.unlock();
+      cv_.notify_one();
+      return;
+    }
+    ++threads_;
+    lk.unlock();
+    auto self = shared_from_this();
+    std::thread([self] { self->run(); }).detach();
+  }
+  int threads() {
+    std::lock_guard<std::mutex> lk(mu_);
+    return threads_;
+  }
+
+ private:
+  void run() {
+    std::unique_lock<std::mutex> lk(mu_);
+    while (true) {
+      if (q_.empty()) {
+        ++idle_;
+        const bool got = cv_.wait_for(lk, std::chrono::seconds(5), [&] { return !q_.empty(); });
+        --idle_;
+        if (!got) break;
+      }
+      std::function<void()> fn = std::move(q_.front());
+      q_.pop_front();
+      lk.unlock();
+      fn();
+      fn = nullptr;
+      lk.lock();
+    }
+    --threads_;
+  }
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::deque<std::function<void()>> q_;
+  int idle_ = 0, threads_ = 0;
+};
+
 // ------------------------------------------------------------------------------ Server
-Server::Server() {}
+Server::Server() : pool_(std::make_shared<HandlerPool>()) {}
 Server::~Server() { shutdown(); }
 
 void Server::add(const std::string& path, Handler h) { handlers_[path] = std::move(h); }
@@ -197,8 +249,8 @@ void Server::accept_loop() {
 
 void Server::serve_conn(int fd) {
   // The reader (this thread) only pumps frames; every completed request runs on its own
-  // handler thread so RPCs multiplexed on one connection (gRPC shares connections between
-  // channels of a process) never wait for each other — e.g. two Barrier calls.
+  // pooled handler thread so RPCs multiplexed on one connection (gRPC shares connections
+  // between channels of a process) never wait for each other — e.g. two Barrier calls.
   auto conn = std::make_shared<h2::Conn>(fd, /*is_server=*/true, /*threaded=*/true);
   if (!conn->handshake()) return;
   auto inflight = std::make_shared<std::atomic<int>>(0);
@@ -218,7 +270,7 @@ void Server::serve_conn(int fd) {
       auto st = std::make_shared<h2::Stream>(std::move(req));
       req = h2::Stream();
       (*inflight)++;
-      std::thread([this, conn, st, inflight] {
+      pool_->submit([this, conn, st, inflight] {
         const uint32_t sid = st->id;
         const std::string* path = find_header(st->headers, ":path");
         const std::string* ctype = find_header(st->headers, "content-type");
@@ -243,11 +295,10 @@ void Server::serve_conn(int fd) {
         if (!status.message.empty())
           trailers.push_back({"grpc-message", percent_encode(status.message)});
         bool ok;
-        if (status.ok()) {
-          ok = conn->send_headers(sid, {{":status", "200"}, {"content-type", "application/grpc"}},
-                                  false) &&
-               conn->send_data(sid, frame_message(response), false) &&
-               conn->send_headers(sid, trailers, true);
+        if (status.ok()) {  // HEADERS + DATA + trailers leave in one write when small
+          const std::vector<hpack::Header> hs = {{":status", "200"},
+                                                 {"content-type", "application/grpc"}};
+          ok = conn->send_message(sid, &hs, frame_message(response), &trailers);
         } else {  // trailers-only response
           std::vector<hpack::Header> hs = {{":status", "200"},
                                            {"content-type", "application/grpc"}};
@@ -257,7 +308,7 @@ void Server::serve_conn(int fd) {
         conn->erase(sid);
         if (!ok) conn->mark_dead();
         (*inflight)--;
-      }).detach();
+      });
     }
   }
   conn->mark_dead();
@@ -317,7 +368,10 @@ Status Channel::call(const std::string& path, const std::string& request, std::s
     const bool fresh = !conn_ || !conn_->alive();
     if (fresh && !connect_locked(timeout_ms))
       return {UNAVAILABLE, "failed to connect to " + host_ + ":" + std::to_string(port_)};
-    set_timeouts(conn_->fd(), timeout_ms);
+    if (fresh || timeout_ms != socket_timeout_ms_) {  // two setsockopt calls saved per RPC
+      set_timeouts(conn_->fd(), timeout_ms);
+      socket_timeout_ms_ = timeout_ms;
+    }
     h2::Conn& c = *conn_;
     const uint32_t sid = c.next_stream_id();
     c.open_stream(sid);
@@ -326,7 +380,7 @@ Status Channel::call(const std::string& path, const std::string& request, std::s
         {":authority", host_ + ":" + std::to_string(port_)},
         {"content-type", "application/grpc"}, {"te", "trailers"},
         {"user-agent", "psb-grpc-lite/0.1"}};
-    bool sent = c.send_headers(sid, hs, false) && c.send_data(sid, frame_message(request), true);
+    bool sent = c.send_message(sid, &hs, frame_message(request), nullptr);
     bool done = false;
     h2::Stream got, tmp;
     h2::Stream* st = &got;

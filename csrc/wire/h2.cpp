@@ -15,6 +15,12 @@ const char kPreface[] = "PRI * HTTP/2.0\r\n\r\nSM\r\n\r\n";
 constexpr size_t kPrefaceLen = 24;
 constexpr uint32_t kOurWindow = 0x7fffffff;  // we never want to be the flow-control bottleneck
 constexpr uint32_t kOurMaxFrame = 1 << 20;
+// Both receive windows are opened to 2^31-1 at the handshake; they are replenished lazily, once
+// this much has been consumed, instead of after every DATA frame (two extra frames per RPC in
+// each direction for no benefit at that window size).
+constexpr int64_t kWindowUpdateThreshold = 1 << 26;
+constexpr size_t kReadBuf = 64 * 1024;
+constexpr size_t kCoalesceMax = 256 * 1024;
 
 void put32(std::string& s, uint32_t v) {
   char b[4] = {static_cast<char>(v >> 24), static_cast<char>(v >> 16), static_cast<char>(v >> 8),
@@ -29,6 +35,7 @@ uint32_t get32(const uint8_t* p) {
 Conn::Conn(int fd, bool is_server, bool threaded)
     : fd_(fd), server_(is_server), threaded_(threaded) {
   next_sid_ = is_server ? 2 : 1;
+  rbuf_.resize(kReadBuf);
 }
 
 void Conn::mark_dead() {
@@ -43,15 +50,31 @@ Conn::~Conn() {
 bool Conn::read_exact(void* buf, size_t n) {
   uint8_t* p = static_cast<uint8_t*>(buf);
   while (n > 0) {
-    ssize_t r = ::recv(fd_, p, n, 0);
+    if (rpos_ < rlen_) {  // serve from the buffer first
+      size_t k = rlen_ - rpos_;
+      if (k > n) k = n;
+      memcpy(p, rbuf_.data() + rpos_, k);
+      rpos_ += k;
+      p += k;
+      n -= k;
+      continue;
+    }
+    // large remainder: straight into the caller's memory; otherwise refill the buffer
+    const bool direct = n >= rbuf_.size();
+    ssize_t r = direct ? ::recv(fd_, p, n, 0) : ::recv(fd_, rbuf_.data(), rbuf_.size(), 0);
     if (r == 0) { mark_dead(); return false; }
     if (r < 0) {
       if (errno == EINTR) continue;
       mark_dead();  // includes SO_RCVTIMEO expiry
       return false;
     }
-    p += r;
-    n -= static_cast<size_t>(r);
+    if (direct) {
+      p += r;
+      n -= static_cast<size_t>(r);
+    } else {
+      rpos_ = 0;
+      rlen_ = static_cast<size_t>(r);
+    }
   }
   return true;
 }
@@ -246,19 +269,38 @@ bool Conn::pump() {
           st->body.append(p, off, n);
         }
       }
-      const bool stream_wu = st && !(flags & END_STREAM);
+      // Replenish the windows by what was consumed — lazily (kWindowUpdateThreshold).
+      uint32_t stream_inc = 0, conn_inc = 0;
+      if (st && !(flags & END_STREAM)) {
+        st->recv_unacked += static_cast<int64_t>(len);
+        if (st->recv_unacked >= kWindowUpdateThreshold) {
+          stream_inc = static_cast<uint32_t>(st->recv_unacked);
+          st->recv_unacked = 0;
+        }
+      }
       if (st && (flags & END_STREAM)) {
         st->remote_closed = true;
         completed_.push_back(sid);
       }
-      if (len > 0) {  // replenish both windows by what the frame consumed
+      conn_recv_unacked_ += static_cast<int64_t>(len);
+      if (conn_recv_unacked_ >= kWindowUpdateThreshold) {
+        conn_inc = static_cast<uint32_t>(conn_recv_unacked_);
+        conn_recv_unacked_ = 0;
+      }
+      if (conn_inc || stream_inc) {
         // The socket write happens WITHOUT state_mu_: a peer that stops reading can then stall
         // this reader, but not the handler threads that need the lock to send their responses.
         lk.unlock();
         std::string wu;
-        put32(wu, static_cast<uint32_t>(len));
-        if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
-        if (stream_wu && !write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4)) return false;
+        if (conn_inc) {
+          put32(wu, conn_inc);
+          if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
+        }
+        if (stream_inc) {
+          wu.clear();
+          put32(wu, stream_inc);
+          if (!write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4)) return false;
+        }
       }
       break;
     }
@@ -384,6 +426,57 @@ bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
     off += n;
   }
   return true;
+}
+
+void Conn::append_frame(std::string& out, uint8_t type, uint8_t flags, uint32_t sid,
+                        const char* payload, size_t n) {
+  const char h[9] = {static_cast<char>(n >> 16), static_cast<char>(n >> 8), static_cast<char>(n),
+                     static_cast<char>(type), static_cast<char>(flags),
+                     static_cast<char>((sid >> 24) & 0x7f), static_cast<char>(sid >> 16),
+                     static_cast<char>(sid >> 8), static_cast<char>(sid)};
+  out.append(h, 9);
+  if (n) out.append(payload, n);
+}
+
+bool Conn::send_message(uint32_t sid, const std::vector<hpack::Header>* hs, const std::string& data,
+                        const std::vector<hpack::Header>* trailers) {
+  std::string hblock, tblock;
+  if (hs) enc_.encode(*hs, hblock);
+  if (trailers) enc_.encode(*trailers, tblock);
+  uint32_t max_frame = 0;
+  bool coalesce = data.size() <= kCoalesceMax;
+  if (coalesce) {
+    std::lock_guard<std::mutex> lk(state_mu_);
+    max_frame = peer_max_frame_;
+    Stream* st = find(sid);
+    const int64_t need = static_cast<int64_t>(data.size());
+    coalesce = st && !st->reset && hblock.size() <= max_frame && tblock.size() <= max_frame &&
+               conn_send_window_ >= need && st->send_window >= need;
+    if (coalesce) {  // reserve the whole body now
+      conn_send_window_ -= need;
+      st->send_window -= need;
+    }
+  }
+  if (!coalesce) {
+    if (hs && !send_headers(sid, *hs, false)) return false;
+    if (!send_data(sid, data, trailers == nullptr)) return false;
+    return trailers ? send_headers(sid, *trailers, true) : true;
+  }
+  std::string out;
+  out.reserve(hblock.size() + data.size() + tblock.size() + 64);
+  if (hs) append_frame(out, HEADERS, END_HEADERS, sid, hblock.data(), hblock.size());
+  size_t off = 0;
+  do {
+    size_t n = data.size() - off;
+    if (n > max_frame) n = max_frame;
+    const bool last = off + n == data.size();
+    append_frame(out, DATA, (last && !trailers) ? END_STREAM : 0, sid, data.data() + off, n);
+    off += n;
+  } while (off < data.size());
+  if (trailers)
+    append_frame(out, HEADERS, END_HEADERS | END_STREAM, sid, tblock.data(), tblock.size());
+  std::lock_guard<std::mutex> wl(write_mu_);
+  return write_all(out.data(), out.size());
 }
 
 bool Conn::send_rst(uint32_t sid, uint32_t code) {

@@ -45,6 +45,7 @@ struct Stream {
   bool remote_closed = false;
   bool reset = false;
   int64_t send_window = 65535;
+  int64_t recv_unacked = 0;  // DATA bytes received and not yet returned by a WINDOW_UPDATE
 };
 
 // One HTTP/2 connection over a connected TCP socket.
@@ -66,6 +67,13 @@ class Conn {
   bool send_headers(uint32_t sid, const std::vector<hpack::Header>& h, bool end_stream);
   // Sends `data` as DATA frames, honouring flow control (pumps incoming frames while blocked).
   bool send_data(uint32_t sid, const std::string& data, bool end_stream);
+  // One unary message in ONE socket write when it is small and the flow-control windows allow:
+  // [HEADERS(hs)] + DATA(data) + [HEADERS(trailers), END_STREAM]; `hs` may be null (headers
+  // already sent), `trailers` null means END_STREAM goes on the last DATA frame.  Three writes
+  // become one segment — a unary RPC is latency-bound by syscalls and wake-ups, not by bytes.
+  // Falls back to send_headers / send_data for large bodies.
+  bool send_message(uint32_t sid, const std::vector<hpack::Header>* hs, const std::string& data,
+                    const std::vector<hpack::Header>* trailers);
   bool send_rst(uint32_t sid, uint32_t code);
   bool send_goaway(uint32_t code);
   uint32_t next_stream_id() { uint32_t s = next_sid_; next_sid_ += 2; return s; }
@@ -82,6 +90,8 @@ class Conn {
   bool write_frame_locked(uint8_t type, uint8_t flags, uint32_t sid, const void* payload,
                           size_t n);  // write_mu_ held
   bool fail();
+  void append_frame(std::string& out, uint8_t type, uint8_t flags, uint32_t sid, const char* payload,
+                    size_t n);
   bool on_headers_block(uint32_t sid, uint8_t flags);
   bool on_settings(const std::string& p, uint8_t flags);
   Stream* find(uint32_t id);  // state_mu_ held
@@ -106,6 +116,10 @@ class Conn {
   uint32_t peer_max_frame_ = 16384;
   uint32_t next_sid_ = 1;
   uint32_t last_peer_sid_ = 0;
+  int64_t conn_recv_unacked_ = 0;  // reader thread only
+  // reader-side buffer: one recv() usually brings every frame of a small response
+  std::vector<uint8_t> rbuf_;
+  size_t rpos_ = 0, rlen_ = 0;
 };
 
 }  // namespace h2
@@ -123,6 +137,8 @@ struct Status {
 };
 
 using Handler = std::function<Status(const std::string& request, std::string& response)>;
+
+class HandlerPool;  // grpc_lite.cpp
 
 class Server {
  public:
@@ -147,6 +163,7 @@ class Server {
   std::mutex conns_mu_;
   std::vector<int> conn_fds_;
   std::atomic<int> active_{0};
+  std::shared_ptr<HandlerPool> pool_;
 };
 
 // Client channel: one persistent connection, one unary call at a time, reconnects on failure.
@@ -164,6 +181,7 @@ class Channel {
   int port_;
   std::mutex mu_;
   std::unique_ptr<h2::Conn> conn_;
+  int socket_timeout_ms_ = -1;
 };
 
 // helpers shared by binaries

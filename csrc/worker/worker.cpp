@@ -104,6 +104,7 @@ Worker::Worker(int worker_id, const std::string& coordinator_address,
       worker_address_(worker_address), worker_port_(worker_port), opt_(opt) {
   coord_.reset(new Channel(coordinator_address_));
   coord_hb_.reset(new Channel(coordinator_address_));
+  sim_rng_ = 0x9E3779B97F4A7C15ull * static_cast<uint64_t>(worker_id + 1) + opt_.sim_seed;
   if (opt_.device >= 0) {
     dev_ = DeviceFill::create(opt_.device);
     if (!dev_) std::cerr << "worker " << worker_id_ << ": GPU fill unavailable, using host" << std::endl;
@@ -303,6 +304,16 @@ bool Worker::load_checkpoint_from_server(const std::string& checkpoint_path, int
 }
 
 std::vector<TensorLite> Worker::compute_gradients(const std::vector<TensorLite>& params) {
+  if (opt_.compute_ms > 0.0) {
+    // xorshift per worker: the same run sees the same stragglers in every mode
+    sim_rng_ ^= sim_rng_ << 13;
+    sim_rng_ ^= sim_rng_ >> 7;
+    sim_rng_ ^= sim_rng_ << 17;
+    const double u = static_cast<double>(sim_rng_ >> 11) / 9007199254740992.0;
+    const double ms = opt_.compute_ms * (u < opt_.straggle_prob ? opt_.straggle_factor : 1.0);
+    // sleeping, not spinning: the host thread of a GPU worker is idle while the device works
+    std::this_thread::sleep_for(std::chrono::microseconds(static_cast<int64_t>(ms * 1000.0)));
+  }
   if (grad_fn_) return grad_fn_(params);
   std::vector<TensorLite> grads = params;
   for (auto& t : grads) {

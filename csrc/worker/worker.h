@@ -41,6 +41,13 @@ struct WorkerOptions {
   int max_retries = 3;            // reference: 3 (src/worker.cpp:335)
   int device = -1;                // >= 0: synthetic gradients filled on this GPU (K7)
   float synthetic_grad = 0.01f;   // reference: 0.01f (src/worker.cpp:316-320)
+  // Simulated compute time of one iteration (benchmarks/straggler_host.sh): the gradient step
+  // takes compute_ms, and with probability straggle_prob an iteration takes straggle_factor
+  // times as long (a transient straggler; drawn from a per-worker deterministic sequence).
+  double compute_ms = 0.0;
+  double straggle_prob = 0.0;
+  double straggle_factor = 1.0;
+  uint64_t sim_seed = 0;
 };
 
 class Worker {
@@ -95,6 +102,7 @@ class Worker {
   std::unique_ptr<grpc_lite::Channel> ps_;
   std::string ps_channel_target_;
   bool last_push_ok_ = false;
+  uint64_t sim_rng_ = 0;
   std::function<std::vector<TensorLite>(const std::vector<TensorLite>&)> grad_fn_;
   struct DeviceFill;
   DeviceFill* dev_ = nullptr;

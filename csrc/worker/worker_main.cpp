@@ -3,7 +3,10 @@
 //   worker_main [coordinator=localhost:50052] [worker_id=0] [iterations=1] [worker_addr=""]
 //               [worker_port=0] [checkpoint_path=""]
 // Extensions: --mode=sync|async|ssp  --device=N  --heartbeat-ms=N  --sync-timeout-ms=N
-// (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS).
+// (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS), and for the straggler
+// benchmark --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N --quiet (simulated
+// compute time per iteration; no per-iteration log line, one summary line at the end).
+#include <chrono>
 #include <cstdlib>
 #include <iostream>
 #include <string>
@@ -24,6 +27,7 @@ int main(int argc, char** argv) {
   std::string worker_addr, checkpoint_path;
   int32_t worker_port = 0;
   psb::WorkerOptions opt;
+  bool quiet = false;
   if (const char* e = std::getenv("PSB_MODE")) opt.mode = e;
   if (const char* e = std::getenv("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = std::getenv("PSB_HEARTBEAT_MS")) opt.heartbeat_ms = std::atoi(e);
@@ -35,6 +39,11 @@ int main(int argc, char** argv) {
     else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
     else if (flag(a, "heartbeat-ms", v)) opt.heartbeat_ms = std::atoi(v.c_str());
     else if (flag(a, "sync-timeout-ms", v)) opt.sync_timeout_ms = std::atoi(v.c_str());
+    else if (flag(a, "compute-ms", v)) opt.compute_ms = std::atof(v.c_str());
+    else if (flag(a, "straggle-prob", v)) opt.straggle_prob = std::atof(v.c_str());
+    else if (flag(a, "straggle-factor", v)) opt.straggle_factor = std::atof(v.c_str());
+    else if (flag(a, "seed", v)) opt.sim_seed = std::strtoull(v.c_str(), nullptr, 10);
+    else if (a == "--quiet") quiet = true;
     else if (a.rfind("--", 0) == 0 && a.size() > 2) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;
@@ -62,10 +71,19 @@ int main(int argc, char** argv) {
                 << std::endl;  // continue from scratch, like the reference
     }
   }
+  const auto t0 = std::chrono::steady_clock::now();
+  int completed = 0;
   for (int it = 0; it < iterations; ++it) {
     bool done = w.run_iteration(it);
-    std::cout << "worker " << worker_id << " iter " << it << " done=" << (done ? "true" : "false")
-              << std::endl;
+    completed += done ? 1 : 0;
+    if (!quiet)
+      std::cout << "worker " << worker_id << " iter " << it << " done=" << (done ? "true" : "false")
+                << std::endl;
+  }
+  if (quiet || opt.compute_ms > 0.0) {
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    std::cout << "worker " << worker_id << " summary iterations=" << iterations << " done=" << completed
+              << " elapsed_ms=" << ms << " mode=" << opt.mode << std::endl;
   }
   return 0;
 }

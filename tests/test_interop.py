@@ -289,3 +289,44 @@ def test_barrier_membership_follows_eviction(servers):
     finally:
         stop.set()
         t.join()
+
+
+def test_status_query_is_held_until_the_barrier_opens(tmp_path):
+    """--long-poll-ms: a CheckSyncStatus that would say "not ready" waits for the completing
+    push instead of making the worker poll again (reference: answers at once,
+    /root/reference/src/parameter_server_service.cpp:77-90, worker sleeps 50 ms between polls,
+    src/worker.cpp:372-395).  A negative answer still comes back after the hold time."""
+    ps_port = free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0", "--long-poll-ms=1500"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    try:
+        assert wait_port(ps_port)
+        ch = grpc.insecure_channel(f"127.0.0.1:{ps_port}")
+        stub = protos.Stub(ch, "parameter_server.ParameterServer")
+        T = M("parameter_server.Tensor")
+        grad = [T(name="weight", shape=[4], data=[0.5] * 4, dtype=0)]
+        push = lambda w: stub.ReceiveGradients(M("parameter_server.GradientUpdate")(
+            worker_id=w, iteration=0, gradients=grad), timeout=5)
+        assert not push(0).aggregation_complete
+        got = {}
+
+        def waiter():
+            t0 = time.time()
+            got["resp"] = stub.CheckSyncStatus(
+                M("parameter_server.SyncStatusRequest")(iteration=0), timeout=10)
+            got["dt"] = time.time() - t0
+
+        th = threading.Thread(target=waiter)
+        th.start()
+        time.sleep(0.3)
+        assert th.is_alive(), "the negative answer was not held"
+        assert push(1).aggregation_complete
+        th.join(timeout=5)
+        assert got["resp"].ready and got["resp"].workers_received == 2
+        assert got["dt"] < 1.2, f"woken by the timeout, not by the completion ({got['dt']:.2f}s)"
+        # nothing will complete iteration 5: the hold time bounds the wait
+        t0 = time.time()
+        s = stub.CheckSyncStatus(M("parameter_server.SyncStatusRequest")(iteration=5), timeout=10)
+        assert not s.ready and 1.2 < time.time() - t0 < 4.0
+    finally:
+        ps.stop()

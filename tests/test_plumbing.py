@@ -205,3 +205,22 @@ def test_eviction_script(tmp_path):
                        env=dict(os.environ, ITERS="600", COORD_PORT=str(free_port()),
                                 PS_PORT=str(free_port())))
     assert r.returncode == 0 and "PASS:" in r.stdout, r.stdout[-800:] + r.stderr[-400:]
+
+
+def test_straggler_benchmark_modes_agree_on_the_work_done(tmp_path):
+    """benchmarks/straggler_host.py: every worker completes all of its iterations in sync, SSP
+    and async mode with simulated compute time and transient stragglers (timing is reported, not
+    asserted — this box's scheduler is part of it)."""
+    import json
+    import subprocess
+    import sys
+    out = tmp_path / "s.jsonl"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "benchmarks", "straggler_host.py"),
+                        "--workers", "3", "--iters", "40", "--compute-ms", "2", "--scenarios",
+                        "transient", "--out", str(out)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-500:]
+    rows = [json.loads(l) for l in open(out)]
+    assert [x["mode"] for x in rows] == ["sync", "ssp", "async"]
+    for x in rows:
+        assert len(x["worker_ms"]) == 3 and x["job_ms"] >= 40 * 2
