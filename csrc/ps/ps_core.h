@@ -43,7 +43,7 @@ struct PsOptions {
   // Status queries that would answer "not yet" are held this long for the answer to change
   // (CheckSyncStatus in sync mode, the staleness gate of ServeParameters in SSP mode), so a
   // waiting worker learns of the completion when it happens instead of at its next poll.
-  // 0 = answer at once like the reference (src/parameter_server_service.cpp:77-90).
+  // 0 = answer at once like the reference (src/parameter_server_service.cpp:85-96).
   int long_poll_ms = 25;
 };
 

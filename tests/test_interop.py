@@ -294,7 +294,7 @@ def test_barrier_membership_follows_eviction(servers):
 def test_status_query_is_held_until_the_barrier_opens(tmp_path):
     """--long-poll-ms: a CheckSyncStatus that would say "not ready" waits for the completing
     push instead of making the worker poll again (reference: answers at once,
-    /root/reference/src/parameter_server_service.cpp:77-90, worker sleeps 50 ms between polls,
+    /root/reference/src/parameter_server_service.cpp:85-96, worker sleeps 50 ms between polls,
     src/worker.cpp:372-395).  A negative answer still comes back after the hold time."""
     ps_port = free_port()
     ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0", "--long-poll-ms=1500"],
