@@ -9,5 +9,14 @@ from . import _lib
 from .ops.native import OptimConfig
 from .trainer import Context, Trainer, init
 
+
+def __getattr__(name):  # host-plane client: needs grpcio, so imported on first use
+    if name in ("RemoteParameterServer", "RemoteTrainer"):
+        from .control import remote
+        return getattr(remote, name)
+    raise AttributeError(name)
+
+
 __version__ = "0.1.0"
-__all__ = ["OptimConfig", "Context", "Trainer", "init", "_lib"]
+__all__ = ["OptimConfig", "Context", "Trainer", "init", "RemoteParameterServer", "RemoteTrainer",
+           "_lib"]

@@ -1,0 +1,236 @@
+"""Worker-side client of the host plane: train a torch model through the gRPC parameter server.
+
+The reference's worker is a C++ process whose "gradients" are a constant
+(/root/reference/src/worker.cpp:316-329) — its protocol, though, is a complete synchronous
+data-parallel step: register with the coordinator (:159-186), discover the parameter server
+(:141-157), then per iteration pull (:240-252) -> compute -> push (:254-272) -> poll the sync
+status (:274-287, :366-395).  This module speaks that protocol from Python (grpcio, message
+classes from ``protos``; no codegen) against ``build/bin/coordinator`` and
+``build/bin/parameter_server`` — or against the reference's own binaries, the wire is the
+same — with real gradients of a ``torch.nn.Module``.
+
+Two layers:
+
+* :class:`RemoteParameterServer` — registration, heartbeats, ``pull`` / ``push`` / ``wait`` /
+  checkpoints as numpy dictionaries;
+* :class:`RemoteTrainer` — ``step(*inputs)`` on a model: pull, load, forward, backward, push,
+  wait.  ``mode`` is the server's mode: ``sync`` waits for the barrier, ``async`` never waits,
+  ``ssp`` waits at the pull until the slowest worker is within the server's bound.
+
+This is the slow path by construction (parameters cross TCP as ``repeated float`` every step);
+the HBM data plane is ``psd.Trainer``.  It exists so that a deployment built around a central
+parameter-server process keeps working, with any worker that can produce gradients.
+"""
+from __future__ import annotations
+
+import socket
+import threading
+import time
+from typing import Callable, Dict, Iterable, List, Optional, Tuple
+
+import numpy as np
+
+from . import protos
+
+IDLE, TRAINING, CHECKPOINTING, ERROR = 0, 1, 2, 3
+
+
+class RemoteParameterServer:
+    """One worker's connection to the coordinator and the parameter server."""
+
+    def __init__(self, coordinator: str, worker_id: int, *, address: str = "",
+                 port: int = 0, hostname: Optional[str] = None, heartbeat_s: float = 5.0,
+                 rpc_timeout_s: float = 30.0, ps_address: Optional[str] = None):
+        import grpc
+        self.worker_id = int(worker_id)
+        self.timeout = rpc_timeout_s
+        unlimited = [("grpc.max_receive_message_length", -1), ("grpc.max_send_message_length", -1)]
+        self._coord_ch = grpc.insecure_channel(coordinator)
+        self.coord = protos.Stub(self._coord_ch, "coordinator.Coordinator")
+        self._info = protos.msg("coordinator.WorkerInfo")(
+            worker_id=self.worker_id, address=address or "127.0.0.1", port=port,
+            hostname=hostname or socket.gethostname())
+        reg = self._retry(lambda: self.coord.RegisterWorker(self._info, timeout=self.timeout))
+        if not reg.success:
+            raise RuntimeError(f"registration refused: {reg.message}")
+        self.total_workers = reg.total_workers
+        if ps_address is None:
+            where = self.coord.GetParameterServerAddress(
+                protos.msg("coordinator.GetPSAddressRequest")(), timeout=self.timeout)
+            # the reference coordinator answers host-only addresses with port 0
+            ps_address = f"{where.address}:{where.port or 50051}"
+        self.ps_address = ps_address
+        self._ps_ch = grpc.insecure_channel(ps_address, options=unlimited)
+        self.ps = protos.Stub(self._ps_ch, "parameter_server.ParameterServer")
+        self.status = IDLE
+        self.evictions = 0
+        self._stop = threading.Event()
+        self._hb = threading.Thread(target=self._heartbeat_loop, args=(heartbeat_s,), daemon=True)
+        self._hb.start()
+
+    # ------------------------------------------------------------------ plumbing
+    def _retry(self, fn: Callable, attempts: int = 5):
+        """Exponential back-off like the reference's query_with_retry (src/worker.cpp:129-139)."""
+        import grpc
+        for a in range(attempts):
+            try:
+                return fn()
+            except grpc.RpcError:
+                if a + 1 == attempts:
+                    raise
+                time.sleep(0.1 * 2 ** a)
+
+    def _heartbeat_loop(self, period: float) -> None:
+        import grpc
+        HB = protos.msg("coordinator.HeartbeatRequest")
+        while not self._stop.wait(period):
+            try:
+                r = self.coord.Heartbeat(HB(worker_id=self.worker_id, status=self.status),
+                                         timeout=self.timeout)
+                if not r.success:  # evicted (a long stall): come back, as the C++ worker does
+                    self.evictions += 1
+                    self.coord.RegisterWorker(self._info, timeout=self.timeout)
+            except grpc.RpcError:
+                pass  # coordinator away: keep trying at the next beat
+
+    def close(self) -> None:
+        self._stop.set()
+        self._hb.join(timeout=2)
+        self._coord_ch.close()
+        self._ps_ch.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ------------------------------------------------------------------ protocol
+    def pull(self, iteration: int) -> Tuple[Dict[str, np.ndarray], bool]:
+        """ServeParameters: ({name: fp32 array shaped like the server's tensor}, ready)."""
+        r = self.ps.ServeParameters(protos.msg("parameter_server.PullRequest")(
+            worker_id=self.worker_id, iteration=iteration), timeout=self.timeout)
+        out = {}
+        for t in r.parameters:
+            a = np.asarray(t.data, dtype=np.float32)
+            out[t.name] = a.reshape(tuple(t.shape)) if len(t.shape) else a
+        return out, bool(r.ready)
+
+    def push(self, iteration: int, grads: Iterable[Tuple[str, np.ndarray]]) -> Tuple[bool, int, int]:
+        """ReceiveGradients: (aggregation_complete, workers_received, total_workers).  Order
+        matters: the server matches tensors by position and checks name + shape."""
+        req = protos.msg("parameter_server.GradientUpdate")(worker_id=self.worker_id,
+                                                            iteration=iteration)
+        for name, g in grads:
+            g = np.ascontiguousarray(g, dtype=np.float32)
+            t = req.gradients.add()
+            t.name = name
+            t.shape.extend(g.shape)
+            t.dtype = 0
+            t.data.extend(g.reshape(-1))
+        r = self._retry(lambda: self.ps.ReceiveGradients(req, timeout=self.timeout), attempts=3)
+        if not r.success:
+            raise RuntimeError(f"push refused: {r.message}")
+        return bool(r.aggregation_complete), r.workers_received, r.total_workers
+
+    def wait(self, iteration: int, timeout_s: float = 10.0, poll_s: float = 0.0) -> bool:
+        """CheckSyncStatus until the iteration is aggregated.  This framework's server holds a
+        negative answer (``--long-poll-ms``), so polling back to back costs nothing; against the
+        reference's server pass ``poll_s=0.05`` (its worker's own interval)."""
+        Req = protos.msg("parameter_server.SyncStatusRequest")
+        end = time.monotonic() + timeout_s
+        while True:
+            if self.ps.CheckSyncStatus(Req(iteration=iteration), timeout=self.timeout).ready:
+                return True
+            if time.monotonic() >= end:
+                return False
+            if poll_s:
+                time.sleep(poll_s)
+
+    def save_checkpoint(self, epoch: int, path: str = "") -> str:
+        r = self.ps.SaveCheckpoint(protos.msg("parameter_server.SaveCheckpointRequest")(
+            epoch=epoch, path=path), timeout=max(self.timeout, 120))
+        if not r.success:
+            raise RuntimeError(r.message)
+        return r.checkpoint_path
+
+    def load_checkpoint(self, path: str) -> int:
+        r = self.ps.LoadCheckpoint(protos.msg("parameter_server.LoadCheckpointRequest")(path=path),
+                                   timeout=max(self.timeout, 120))
+        if not r.success:
+            raise RuntimeError(r.message)
+        return r.epoch
+
+    def live_workers(self) -> List[int]:
+        r = self.coord.ListWorkers(protos.msg("coordinator.ListWorkersRequest")(),
+                                   timeout=self.timeout)
+        return sorted(w.worker_id for w in r.workers)
+
+
+class RemoteTrainer:
+    """Data-parallel training of ``model`` with the parameter server as the only optimizer.
+
+    The server owns the weights and applies ``--optimizer`` / ``--lr`` to the mean gradient of
+    an iteration; this process holds a replica that it overwrites from every pull.  An empty
+    server adopts the first aggregate as its model (reference semantics): every
+    worker therefore pushes its initial weights as iteration 0 — with identically seeded
+    workers their mean is that initialisation — and training starts at iteration 1.
+    """
+
+    def __init__(self, model, loss_fn, ps: RemoteParameterServer, *, mode: str = "sync",
+                 sync_timeout_s: float = 10.0, start_iteration: Optional[int] = None):
+        import torch
+        if mode not in ("sync", "async", "ssp"):
+            raise ValueError(mode)
+        self.torch = torch
+        self.model, self.loss_fn, self.ps, self.mode = model, loss_fn, ps, mode
+        self.sync_timeout_s = sync_timeout_s
+        self.names = [n for n, p in model.named_parameters() if p.requires_grad]
+        self.params = [p for _, p in model.named_parameters() if p.requires_grad]
+        self.skipped = 0  # iterations whose barrier did not open in time (reference: moves on)
+        have, _ = ps.pull(0)
+        if start_iteration is not None:
+            self.iteration = start_iteration
+        elif have:
+            self.iteration = 1  # server already has a model (another worker, or a checkpoint)
+        else:
+            init = [(n, p.detach().float().cpu().numpy()) for n, p in zip(self.names, self.params)]
+            done, _, _ = ps.push(0, init)
+            if not done and mode == "sync":
+                ps.wait(0, sync_timeout_s)
+            self.iteration = 1
+
+    def _load(self, pulled: Dict[str, np.ndarray]) -> None:
+        torch = self.torch
+        with torch.no_grad():
+            for n, p in zip(self.names, self.params):
+                a = pulled.get(n)
+                if a is not None and a.size == p.numel():
+                    p.copy_(torch.from_numpy(a).view_as(p))
+
+    def step(self, *inputs):
+        """One iteration; returns the loss tensor of this worker's batch."""
+        ps, it = self.ps, self.iteration
+        ps.status = TRAINING
+        pulled, ready = ps.pull(it)
+        if self.mode == "ssp":  # the server's staleness gate (held server-side, no sleep needed)
+            end = time.monotonic() + self.sync_timeout_s
+            while not ready and time.monotonic() < end:
+                pulled, ready = ps.pull(it)
+        self._load(pulled)
+        for p in self.params:
+            p.grad = None
+        loss = self.loss_fn(self.model, *inputs)
+        loss.backward()
+        grads = [(n, (p.grad if p.grad is not None else self.torch.zeros_like(p))
+                  .detach().float().cpu().numpy()) for n, p in zip(self.names, self.params)]
+        done, _, _ = ps.push(it, grads)
+        if not done and self.mode == "sync" and not ps.wait(it, self.sync_timeout_s):
+            self.skipped += 1
+        ps.status = IDLE
+        self.iteration = it + 1
+        return loss.detach()
+
+    def sync_model(self) -> None:
+        """Overwrite the local replica with the server's current weights."""
+        self._load(self.ps.pull(self.iteration)[0])
