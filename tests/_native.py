@@ -6,7 +6,8 @@ import sys
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-BIN = os.path.join(ROOT, "build", "bin")
+# PSB_TEST_BIN=build/bin-address (or bin-thread) runs the same tests on the sanitizer binaries
+BIN = os.path.abspath(os.environ.get("PSB_TEST_BIN") or os.path.join(ROOT, "build", "bin"))
 
 
 def ensure_binaries():
