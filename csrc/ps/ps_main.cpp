@@ -6,6 +6,8 @@
 //   --momentum=F --beta1=F --beta2=F --eps=F --weight-decay=F  --device=N (HBM-resident shard)
 //   --coordinator=host:port  --membership-poll-ms=N   follow the coordinator's worker registry:
 //       an evicted worker no longer blocks the sync barrier (PSB_COORDINATOR, PSB_MEMBERSHIP_POLL_MS)
+//   --resume=PATH|latest   load this checkpoint (latest: the newest checkpoint_epoch_*.ckpt in the
+//       working directory) before serving, so a restarted server carries on (PSB_RESUME)
 //   --long-poll-ms=N   hold a "not ready" status answer up to N ms for the barrier to open
 //       (default 25; 0 = answer at once like the reference) (PSB_LONG_POLL_MS)
 #include <cstdlib>
@@ -38,8 +40,9 @@ int main(int argc, char** argv) {
   if (const char* e = env("PSB_LR")) opt.lr = std::strtof(e, nullptr);
   if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = env("PSB_LONG_POLL_MS")) opt.long_poll_ms = std::atoi(e);
-  std::string coordinator;
+  std::string coordinator, resume;
   int membership_poll_ms = 1000;
+  if (const char* e = env("PSB_RESUME")) resume = e;
   if (const char* e = env("PSB_COORDINATOR")) coordinator = e;
   if (const char* e = env("PSB_MEMBERSHIP_POLL_MS")) membership_poll_ms = std::atoi(e);
   std::vector<std::string> pos;
@@ -60,6 +63,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "long-poll-ms", v)) opt.long_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "coordinator", v)) coordinator = v;
     else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
+    else if (flag(a, "resume", v)) resume = v;
     else if (a.rfind("--", 0) == 0) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;
@@ -68,6 +72,7 @@ int main(int argc, char** argv) {
   if (pos.size() > 0) listen = pos[0];
   if (pos.size() > 1) total_workers = std::stoi(pos[1]);
   if (pos.size() > 2) checkpoint_interval = std::stoi(pos[2]);
-  psb::run_server(listen, total_workers, checkpoint_interval, opt, coordinator, membership_poll_ms);
+  psb::run_server(listen, total_workers, checkpoint_interval, opt, coordinator, membership_poll_ms,
+                  resume);
   return 0;
 }

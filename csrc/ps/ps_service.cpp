@@ -1,6 +1,8 @@
 // ps_service.cpp — see ps_service.h.
 #include "ps_service.h"
 
+#include <dirent.h>
+
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
@@ -184,9 +186,32 @@ void ParameterServerService::shutdown() {
   }
 }
 
+std::string latest_checkpoint(const std::string& dir) {
+  std::string best;
+  long best_epoch = -1;
+  DIR* d = ::opendir(dir.empty() ? "." : dir.c_str());
+  if (!d) return best;
+  const std::string pre = "checkpoint_epoch_", suf = ".ckpt";
+  while (dirent* e = ::readdir(d)) {
+    const std::string n = e->d_name;
+    if (n.size() <= pre.size() + suf.size() || n.compare(0, pre.size(), pre) != 0 ||
+        n.compare(n.size() - suf.size(), suf.size(), suf) != 0)
+      continue;
+    const std::string num = n.substr(pre.size(), n.size() - pre.size() - suf.size());
+    if (num.find_first_not_of("0123456789") != std::string::npos) continue;
+    const long epoch = std::strtol(num.c_str(), nullptr, 10);
+    if (epoch > best_epoch) {
+      best_epoch = epoch;
+      best = (dir.empty() ? std::string() : dir + "/") + n;
+    }
+  }
+  ::closedir(d);
+  return best;
+}
+
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
                 const PsOptions& opt, const std::string& coordinator_address,
-                int membership_poll_ms) {
+                int membership_poll_ms, const std::string& resume) {
   int scan_ms = 5000;
   if (const char* e = std::getenv("PSB_CHECKPOINT_SCAN_MS")) scan_ms = std::atoi(e);
   ParameterServerService svc(total_workers, checkpoint_interval, opt, scan_ms);
@@ -195,6 +220,22 @@ void run_server(const std::string& server_address, int total_workers, int checkp
     std::exit(1);
   }
   std::cout << "parameter server listening on " << server_address << std::endl;
+  if (!resume.empty()) {
+    // A restarted server (supervisor, scale_workers.sh) picks its model up again by itself; the
+    // reference comes back empty unless a worker passes CHECKPOINT_PATH
+    // (/root/reference/scripts/scale_workers.sh:137-144, scripts/start_worker.sh:22-23).
+    const std::string path = resume == "latest" ? latest_checkpoint("") : resume;
+    int32_t epoch = 0;
+    if (path.empty()) {
+      std::cout << "resume: no checkpoint_epoch_*.ckpt here, starting empty" << std::endl;
+    } else if (svc.core().load_checkpoint(path, epoch)) {
+      std::cout << "resumed from " << path << " (epoch " << epoch << ", iteration "
+                << svc.core().get_current_iteration() << ")" << std::endl;
+    } else {
+      std::cerr << "resume: failed to load " << path << std::endl;
+      std::exit(1);
+    }
+  }
   if (checkpoint_interval > 0)
     std::cout << "periodic checkpointing every " << checkpoint_interval << " iterations"
               << std::endl;

@@ -46,6 +46,9 @@ class ParameterServerService {
 // (include/parameter_server_service.h:5, src/parameter_server_service.cpp:177-191).
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
                 const PsOptions& opt = PsOptions(), const std::string& coordinator_address = "",
-                int membership_poll_ms = 1000);
+                int membership_poll_ms = 1000, const std::string& resume = "");
+
+// Newest periodic checkpoint ("checkpoint_epoch_<E>.ckpt", largest E) in `dir`; "" if none.
+std::string latest_checkpoint(const std::string& dir);
 
 }  // namespace psb

@@ -174,3 +174,82 @@ def test_ensure_coordinator_rendezvous(tmp_path, monkeypatch):
     c0.close()
     assert not os.listdir(tmp_path), os.listdir(tmp_path)
     assert proc.poll() is not None, "the coordinator launched by rank 0 outlived it"
+
+
+def test_parameter_server_restart_resumes_from_its_latest_checkpoint(tmp_path):
+    """The other half of T7: the parameter server dies (SIGKILL) mid-run and a supervisor starts
+    it again with --resume=latest.  The model continues from the newest periodic checkpoint and
+    the workers — which only saw some RPCs fail — carry on against the new process.  The
+    reference's restarted server is empty until somebody passes CHECKPOINT_PATH to a worker
+    (/root/reference/scripts/scale_workers.sh:137-144, scripts/start_worker.sh:22-23)."""
+    from parameter_server_distributed_b200.utils.checkpoint import read_reference_file
+    ps_port, co_port = free_port(), free_port()
+    env = {"PSB_CHECKPOINT_SCAN_MS": "50"}
+    argv = [f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "20", "--resume=latest"]
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    ps = Proc(argv, str(tmp_path), str(tmp_path / "ps1.log"), env=env)
+    ps2 = None
+    workers = []
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        assert "resume: no checkpoint_epoch_*.ckpt here, starting empty" in ps.output()
+        iters = 1200
+        for wid in range(2):
+            workers.append(Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(wid), str(iters),
+                                 "--heartbeat-ms=200", "--sync-timeout-ms=3000", "--compute-ms=1"],
+                                str(tmp_path), str(tmp_path / f"w{wid}.log")))
+        def saved_epochs():  # the checkpoint thread may skip epochs when iterations fly by
+            return [int(e) for e in re.findall(r"saved checkpoint: checkpoint_epoch_(\d+)\.ckpt",
+                                               ps.output())]
+
+        end = time.time() + 30
+        while time.time() < end and not any(e >= 5 for e in saved_epochs()):
+            time.sleep(0.02)
+        assert any(e >= 5 for e in saved_epochs()), ps.output()[-300:]
+        assert max(saved_epochs()) < 40, "the run was nearly over before the kill"
+        ps.p.send_signal(signal.SIGKILL)
+        ps.p.wait(timeout=5)
+        ps.f.close()
+        time.sleep(0.3)  # the workers meet a dead port for a moment
+        ps2 = Proc(argv, str(tmp_path), str(tmp_path / "ps2.log"), env=env)
+        assert wait_port(ps_port)
+        m = re.search(r"resumed from (checkpoint_epoch_(\d+)\.ckpt) \(epoch (\d+), iteration (\d+)\)",
+                      ps2.output())
+        end = time.time() + 5
+        while m is None and time.time() < end:
+            time.sleep(0.05)
+            m = re.search(r"resumed from (checkpoint_epoch_(\d+)\.ckpt) \(epoch (\d+), iteration (\d+)\)",
+                          ps2.output())
+        assert m, ps2.output()[-300:]
+        assert int(m.group(2)) >= 5 and int(m.group(4)) >= 100
+        for w in workers:
+            w.p.wait(timeout=180)
+        for wid in range(2):
+            lines = _done_lines(workers[wid].output())
+            assert len(lines) == iters
+            lost = [i for i, ok in lines if not ok]
+            assert len(lost) <= 20, f"worker {wid} lost {len(lost)} iterations: {lost[:8]}"
+            assert all(ok for i, ok in lines if i > (lost[-1] if lost else 0))
+        # the model went on from the checkpoint: weight = 0.01 - 0.01 * (#aggregations - 1), so
+        # a server that restarted empty would end near -0.01 * (iterations after the restart)
+        def newest_checkpoint():
+            files = sorted(tmp_path.glob("checkpoint_epoch_*.ckpt"),
+                           key=lambda p: int(p.stem.split("_")[-1]))
+            return read_reference_file(str(files[-1]))
+
+        epoch, iteration, tensors = newest_checkpoint()
+        end = time.time() + 10  # the checkpoint thread scans every 50 ms; give it a moment
+        while iteration < iters - 25 and time.time() < end:
+            time.sleep(0.1)
+            epoch, iteration, tensors = newest_checkpoint()
+        w = float(tensors[0][2].reshape(-1)[0])
+        assert iteration >= iters - 25
+        assert w < -0.01 * (iters - 60), (w, iteration)
+    finally:
+        for w in workers:
+            w.stop()
+        ps.stop() if ps.p.poll() is None else None
+        if ps2:
+            ps2.stop()
+        co.stop()
