@@ -16,7 +16,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
                                        int scan_period_ms, int timeout_s)
     : core_(ps_host, ps_port), scan_period_ms_(scan_period_ms), timeout_s_(timeout_s) {
   const std::string base = "/coordinator.Coordinator/";
-  server_.add(base + "RegisterWorker", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "RegisterWorker", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::WorkerInfo in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed WorkerInfo"};
     WorkerEntry e;
@@ -27,7 +27,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "Heartbeat", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "Heartbeat", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::HeartbeatRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed HeartbeatRequest"};
     pb::HeartbeatResponse out;
@@ -38,7 +38,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "ListWorkers", [this](const std::string&, std::string& resp) {
+  server_.add(base + "ListWorkers", [this](std::string_view, grpc_lite::Reply& resp) {
     pb::ListWorkersResponse out;
     for (const auto& w : core_.list_workers()) {
       pb::WorkerInfo wi;
@@ -49,7 +49,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "GetParameterServerAddress", [this](const std::string&, std::string& resp) {
+  server_.add(base + "GetParameterServerAddress", [this](std::string_view, grpc_lite::Reply& resp) {
     pb::GetPSAddressResponse out;
     core_.get_parameter_server_address(out.address, out.port);
     resp = out.encode();
@@ -58,7 +58,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
 
   // ---- extension service (proto/psb_ext.proto)
   const std::string ext = "/psb.CoordinatorExt/";
-  server_.add(ext + "RegisterShard", [this](const std::string& req, std::string& resp) {
+  server_.add(ext + "RegisterShard", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::ShardInfo in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed ShardInfo"};
     core_.register_shard({in.shard_id, in.address, in.device - 1});
@@ -67,7 +67,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = ack.encode();
     return Status{};
   });
-  server_.add(ext + "GetShardMap", [this](const std::string&, std::string& resp) {
+  server_.add(ext + "GetShardMap", [this](std::string_view, grpc_lite::Reply& resp) {
     pb::ShardMapResponse out;
     for (const auto& s : core_.shard_map()) {
       pb::ShardInfo si;
@@ -78,7 +78,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(ext + "Barrier", [this](const std::string& req, std::string& resp) {
+  server_.add(ext + "Barrier", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::BarrierRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed BarrierRequest"};
     pb::BarrierResponse out;
@@ -87,7 +87,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(ext + "UpdateClock", [this](const std::string& req, std::string& resp) {
+  server_.add(ext + "UpdateClock", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::ClockRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed ClockRequest"};
     pb::ClockResponse out;
@@ -95,7 +95,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = out.encode();
     return Status{};
   });
-  server_.add(ext + "PutHandle", [this](const std::string& req, std::string& resp) {
+  server_.add(ext + "PutHandle", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::HandleBlob in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed HandleBlob"};
     core_.put_handle(in.key, in.rank, in.blob);
@@ -104,7 +104,7 @@ CoordinatorService::CoordinatorService(const std::string& ps_host, int32_t ps_po
     resp = ack.encode();
     return Status{};
   });
-  server_.add(ext + "GetHandles", [this](const std::string& req, std::string& resp) {
+  server_.add(ext + "GetHandles", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::HandleQuery in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed HandleQuery"};
     pb::HandleList out;

@@ -7,13 +7,50 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <thread>
 
 #include "ps_device.h"
 
 namespace psb {
 
+namespace {
+// Element-wise loops over large tensors run on a few threads.  Every element is still computed
+// by the same expression in the same order (the sum over workers is ascending in worker id per
+// element), so results do not depend on the thread count.  Threads are created per call: the
+// loops this is used for run for milliseconds.
+constexpr size_t kParallelGrain = 1 << 16;
+
+template <class F>
+void parallel_for(size_t n, int max_threads, F&& body) {  // body(lo, hi)
+  size_t t = n / kParallelGrain;
+  if (t > static_cast<size_t>(max_threads)) t = static_cast<size_t>(max_threads);
+  if (t <= 1) {
+    body(size_t{0}, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  th.reserve(t - 1);
+  const size_t step = (n + t - 1) / t;
+  for (size_t k = 1; k < t; ++k) {
+    const size_t lo = k * step, hi = std::min(n, lo + step);
+    if (lo >= hi) break;
+    th.emplace_back([&body, lo, hi] { body(lo, hi); });
+  }
+  body(size_t{0}, std::min(n, step));
+  for (auto& x : th) x.join();
+}
+
+int resolve_threads(int requested) {
+  int t = requested > 0 ? requested : static_cast<int>(std::thread::hardware_concurrency());
+  if (t < 1) t = 1;
+  return t > 16 ? 16 : t;
+}
+}  // namespace
+
+
 ParameterServerCore::ParameterServerCore(int total_workers, const PsOptions& opt)
     : total_workers_(total_workers), opt_(opt) {
+  opt_.threads = resolve_threads(opt_.threads);
   if (opt_.device >= 0) dev_ = DeviceShard::create(opt_);  // nullptr if CUDA is unavailable
 }
 
@@ -30,6 +67,11 @@ void ParameterServerCore::initialize_parameters(const std::vector<HostTensor>& i
 
 bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration,
                                             const std::vector<HostTensor>& grads) {
+  return receive_gradients(worker_id, iteration, std::vector<HostTensor>(grads));
+}
+
+bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration,
+                                            std::vector<HostTensor>&& grads) {
   std::lock_guard<std::mutex> lk(mu_);
   if (iteration > current_iteration_.load()) current_iteration_.store(iteration);
 
@@ -43,10 +85,13 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
       apply_locked(grads);  // bootstrap from the unscaled tensor, as in sync mode
     } else {
       const float share = 1.0f / static_cast<float>(std::max(1, total_workers_.load()));
-      std::vector<HostTensor> scaled = grads;
-      for (auto& t : scaled)
-        for (auto& x : t.data) x *= share;
-      apply_locked(scaled);
+      for (auto& t : grads) {  // ours to scale in place
+        float* x = t.data.data();
+        parallel_for(t.data.size(), opt_.threads, [x, share](size_t lo, size_t hi) {
+          for (size_t j = lo; j < hi; ++j) x[j] *= share;
+        });
+      }
+      apply_locked(grads);
     }
     clocks_[worker_id] = iteration;
     IterState& st = iters_[iteration];
@@ -59,11 +104,11 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
 
   IterState& st = iters_[iteration];
   if (st.aggregated) return true;  // idempotent retry after completion
-  st.staged[worker_id] = grads;    // a re-push from the same worker overwrites its slot
+  st.staged[worker_id] = std::move(grads);  // a re-push from the same worker overwrites its slot
   st.seen[worker_id] = true;
   if (st.staged.size() < static_cast<size_t>(std::max(1, total_workers_.load()))) return false;
   // names / shapes / dtypes come from the completing push
-  aggregate_locked(st, grads);
+  aggregate_locked(st, worker_id);
   prune_locked();
   return true;
 }
@@ -71,28 +116,43 @@ bool ParameterServerCore::receive_gradients(int32_t worker_id, int32_t iteration
 // Mean over the staged contributions in ascending worker id (deterministic summation order),
 // shaped like `tmpl`; shorter contributions are truncated element-wise (reference semantics,
 // src/parameter_server.cpp:40-63).
-void ParameterServerCore::aggregate_locked(IterState& st, const std::vector<HostTensor>& tmpl) {
-  const size_t count = st.staged.size();
-  std::vector<HostTensor> mean(tmpl.size());
-  for (size_t i = 0; i < tmpl.size(); ++i) {
-    HostTensor& a = mean[i];
-    a.name = tmpl[i].name;
-    a.shape = tmpl[i].shape;
-    a.dtype = tmpl[i].dtype;
-    const size_t n = tmpl[i].data.size();
-    a.data.assign(n, 0.0f);
-    for (const auto& kv : st.staged) {
-      if (i >= kv.second.size()) continue;
-      const std::vector<float>& g = kv.second[i].data;
-      const size_t lim = std::min(n, g.size());
-      for (size_t j = 0; j < lim; ++j) a.data[j] += g[j];
+void ParameterServerCore::aggregate_locked(IterState& st, int32_t shape_from) {
+  const float div = static_cast<float>(st.staged.size());
+  // The mean is written over the staged gradient of worker `shape_from` (we own that memory):
+  // no third model-sized buffer, no page faults on the completing push.  Element j of the
+  // output is stored after every read of element j, so summing in place is safe.
+  std::vector<HostTensor> mean = std::move(st.staged[shape_from]);
+  std::vector<std::pair<const float*, size_t>> src;  // per tensor: every worker's (data, size)
+  for (size_t i = 0; i < mean.size(); ++i) {
+    const size_t n = mean[i].data.size();
+    float* out = mean[i].data.data();
+    src.clear();
+    for (const auto& kv : st.staged) {  // ascending worker id
+      if (kv.first == shape_from) {
+        src.emplace_back(out, n);
+      } else if (i < kv.second.size()) {
+        const std::vector<float>& g = kv.second[i].data;
+        src.emplace_back(g.data(), std::min(n, g.size()));
+      }
     }
-    const float div = static_cast<float>(count);
-    for (size_t j = 0; j < n; ++j) a.data[j] /= div;
+    parallel_for(n, opt_.threads, [&src, out, div](size_t lo, size_t hi) {
+      constexpr size_t kBlock = 2048;  // sum block-wise: streams every source, keeps `acc` in L1
+      float acc[kBlock];
+      for (size_t b = lo; b < hi; b += kBlock) {
+        const size_t e = std::min(hi, b + kBlock);
+        for (size_t j = b; j < e; ++j) acc[j - b] = 0.0f;  // the sum starts from 0.0f (reference)
+        for (const auto& s : src) {
+          const size_t lim = std::min(e, s.second);
+          const float* g = s.first;
+          for (size_t j = b; j < lim; ++j) acc[j - b] += g[j];
+        }
+        for (size_t j = b; j < e; ++j) out[j] = acc[j - b] / div;
+      }
+    });
   }
-  apply_locked(mean);
   st.aggregated = true;
   st.staged.clear();  // the reference keeps every copy forever
+  apply_locked(mean);
   changed_.notify_all();
 }
 
@@ -115,8 +175,7 @@ int ParameterServerCore::set_total_workers(int n) {
   for (auto& kv : iters_) {  // ascending iteration
     IterState& st = kv.second;
     if (st.aggregated || st.staged.empty() || st.staged.size() < need) continue;
-    const std::vector<HostTensor> tmpl = st.staged.rbegin()->second;  // copy: staged is cleared
-    aggregate_locked(st, tmpl);
+    aggregate_locked(st, st.staged.rbegin()->first);
     ++completed;
   }
   return completed;
@@ -156,44 +215,63 @@ void ParameterServerCore::update_tensor(size_t idx, const std::vector<float>& g)
   }
   const std::string& kind = opt_.optimizer;
   const float lr = opt_.lr, wd = opt_.weight_decay;
+  float* pp = p.data();
+  const float* gg = g.data();
+  const int nt = opt_.threads;
   if (kind == "sgd") {
     if (lr == 1.0f && wd == 0.0f) {
-      for (size_t j = 0; j < n; ++j) p[j] -= g[j];  // the reference's exact expression
+      parallel_for(n, nt, [pp, gg](size_t lo, size_t hi) {
+        for (size_t k = lo; k < hi; ++k) pp[k] -= gg[k];  // the reference's exact expression
+      });
     } else {
-      for (size_t j = 0; j < n; ++j) p[j] -= lr * (g[j] + wd * p[j]);
+      parallel_for(n, nt, [pp, gg, lr, wd](size_t lo, size_t hi) {
+        for (size_t k = lo; k < hi; ++k) pp[k] -= lr * (gg[k] + wd * pp[k]);
+      });
     }
     return;
   }
   if (m_[idx].size() != p.size()) m_[idx].assign(p.size(), 0.0f);
-  std::vector<float>& m = m_[idx];
+  float* m = m_[idx].data();
   if (kind == "momentum") {
-    for (size_t j = 0; j < n; ++j) {
-      m[j] = opt_.momentum * m[j] + (g[j] + wd * p[j]);
-      p[j] -= lr * m[j];
-    }
+    const float mu = opt_.momentum;
+    parallel_for(n, nt, [pp, gg, m, lr, wd, mu](size_t lo, size_t hi) {
+      for (size_t k = lo; k < hi; ++k) {
+        m[k] = mu * m[k] + (gg[k] + wd * pp[k]);
+        pp[k] -= lr * m[k];
+      }
+    });
     return;
   }
   if (v_[idx].size() != p.size()) v_[idx].assign(p.size(), 0.0f);
-  std::vector<float>& v = v_[idx];
+  float* v = v_[idx].data();
   const bool decoupled = kind == "adamw";
-  const float b1 = opt_.beta1, b2 = opt_.beta2;
+  const float b1 = opt_.beta1, b2 = opt_.beta2, eps = opt_.eps;
   const float bias1 = 1.0f - std::pow(b1, static_cast<float>(opt_step_));
   const float bias2 = 1.0f - std::pow(b2, static_cast<float>(opt_step_));
-  for (size_t j = 0; j < n; ++j) {
-    float gj = g[j];
-    if (decoupled) p[j] *= 1.0f - lr * wd;
-    else gj += wd * p[j];
-    m[j] = b1 * m[j] + (1.0f - b1) * gj;
-    v[j] = b2 * v[j] + (1.0f - b2) * gj * gj;
-    const float denom = std::sqrt(v[j]) / std::sqrt(bias2) + opt_.eps;
-    p[j] -= (lr / bias1) * (m[j] / denom);
-  }
+  parallel_for(n, nt, [=](size_t lo, size_t hi) {
+    for (size_t k = lo; k < hi; ++k) {
+      float gj = gg[k];
+      if (decoupled) pp[k] *= 1.0f - lr * wd;
+      else gj += wd * pp[k];
+      m[k] = b1 * m[k] + (1.0f - b1) * gj;
+      v[k] = b2 * v[k] + (1.0f - b2) * gj * gj;
+      const float denom = std::sqrt(v[k]) / std::sqrt(bias2) + eps;
+      pp[k] -= (lr / bias1) * (m[k] / denom);
+    }
+  });
 }
 
 std::vector<HostTensor> ParameterServerCore::serve_parameters(int32_t /*iteration*/) {
   std::lock_guard<std::mutex> lk(mu_);
   if (dev_) dev_->download(params_);
   return params_;
+}
+
+void ParameterServerCore::with_parameters(
+    const std::function<void(const std::vector<HostTensor>&, int64_t)>& fn) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (dev_) dev_->download(params_);
+  fn(params_, version_.load());
 }
 
 bool ParameterServerCore::sync_status_locked(int32_t iteration, int32_t& workers_received) {

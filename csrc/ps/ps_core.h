@@ -14,6 +14,7 @@
 #include <atomic>
 #include <condition_variable>
 #include <cstdint>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -40,6 +41,7 @@ struct PsOptions {
   float weight_decay = 0.0f;
   int keep_iterations = 1024;   // iteration states retained for status queries
   int device = -1;              // >= 0: keep master weights in HBM and update with K3
+  int threads = 0;              // host aggregation / update threads (0 = hardware, capped at 16)
   // Status queries that would answer "not yet" are held this long for the answer to change
   // (CheckSyncStatus in sync mode, the staleness gate of ServeParameters in SSP mode), so a
   // waiting worker learns of the completion when it happens instead of at its next poll.
@@ -57,7 +59,14 @@ class ParameterServerCore {
   void initialize_parameters(const std::vector<HostTensor>& initial);
   // Returns true when `iteration` is (now or already) aggregated.
   bool receive_gradients(int32_t worker_id, int32_t iteration, const std::vector<HostTensor>& grads);
+  // The same, taking ownership: the service hands over the tensors it decoded, so staging a
+  // push is a pointer move (the reference copies twice: proto -> tensor -> staging map,
+  // src/parameter_server_service.cpp:35-42, src/parameter_server.cpp:32).
+  bool receive_gradients(int32_t worker_id, int32_t iteration, std::vector<HostTensor>&& grads);
   std::vector<HostTensor> serve_parameters(int32_t iteration);
+  // Runs `fn(parameters, version)` on the current model under the lock, without copying it
+  // (the service encodes a pull response straight from the weights, once per version).
+  void with_parameters(const std::function<void(const std::vector<HostTensor>&, int64_t)>& fn);
   bool check_sync_status(int32_t iteration, int32_t& workers_received);
   // The same answers, but a negative one is held up to options().long_poll_ms for the state
   // to change (an iteration aggregates, a clock advances, the membership changes).
@@ -79,7 +88,7 @@ class ParameterServerCore {
  private:
   struct IterState;
   void apply_locked(const std::vector<HostTensor>& mean_grads);
-  void aggregate_locked(IterState& st, const std::vector<HostTensor>& tmpl);
+  void aggregate_locked(IterState& st, int32_t shape_from);  // names / shapes of that worker's push
   void prune_locked();
   void update_tensor(size_t idx, const std::vector<float>& g);
   bool write_file(int32_t epoch, const std::string& path);

@@ -8,6 +8,8 @@
 //       an evicted worker no longer blocks the sync barrier (PSB_COORDINATOR, PSB_MEMBERSHIP_POLL_MS)
 //   --resume=PATH|latest   load this checkpoint (latest: the newest checkpoint_epoch_*.ckpt in the
 //       working directory) before serving, so a restarted server carries on (PSB_RESUME)
+//   --threads=N   host threads for aggregation and update of large tensors (default: all cores,
+//       at most 16; results do not depend on it) (PSB_THREADS)
 //   --long-poll-ms=N   hold a "not ready" status answer up to N ms for the barrier to open
 //       (default 25; 0 = answer at once like the reference) (PSB_LONG_POLL_MS)
 #include <cstdlib>
@@ -16,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include "../common/memtune.h"
 #include "ps_service.h"
 
 static bool flag(const std::string& arg, const char* key, std::string& val) {
@@ -26,6 +29,7 @@ static bool flag(const std::string& arg, const char* key, std::string& val) {
 }
 
 int main(int argc, char** argv) {
+  psb::retain_freed_memory();
   std::string listen = "0.0.0.0:50051";
   int total_workers = 2, checkpoint_interval = 10;
   psb::PsOptions opt;
@@ -40,6 +44,7 @@ int main(int argc, char** argv) {
   if (const char* e = env("PSB_LR")) opt.lr = std::strtof(e, nullptr);
   if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = env("PSB_LONG_POLL_MS")) opt.long_poll_ms = std::atoi(e);
+  if (const char* e = env("PSB_THREADS")) opt.threads = std::atoi(e);
   std::string coordinator, resume;
   int membership_poll_ms = 1000;
   if (const char* e = env("PSB_RESUME")) resume = e;
@@ -61,6 +66,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "weight-decay", v)) opt.weight_decay = std::strtof(v.c_str(), nullptr);
     else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
     else if (flag(a, "long-poll-ms", v)) opt.long_poll_ms = std::atoi(v.c_str());
+    else if (flag(a, "threads", v)) opt.threads = std::atoi(v.c_str());
     else if (flag(a, "coordinator", v)) coordinator = v;
     else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "resume", v)) resume = v;

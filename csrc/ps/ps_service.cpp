@@ -38,14 +38,15 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     : core_(total_workers, opt), checkpoint_interval_(checkpoint_interval),
       scan_ms_(checkpoint_scan_ms), configured_workers_(total_workers) {
   const std::string base = "/parameter_server.ParameterServer/";
-  server_.add(base + "ReceiveGradients", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "ReceiveGradients", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::GradientUpdate in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed GradientUpdate"};
     std::vector<HostTensor> grads;
     grads.reserve(in.gradients.size());
     for (auto& t : in.gradients) grads.push_back(from_pb(std::move(t)));  // one move, no copies
     pb::PushResponse out;
-    out.aggregation_complete = core_.receive_gradients(in.worker_id, in.iteration, grads);
+    out.aggregation_complete =
+        core_.receive_gradients(in.worker_id, in.iteration, std::move(grads));
     out.success = true;
     out.message = "gradients received";
     out.iteration = in.iteration;
@@ -54,7 +55,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "ServeParameters", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "ServeParameters", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::PullRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed PullRequest"};
     pb::ParameterUpdate out;
@@ -65,11 +66,11 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     } else {
       out.ready = core_.wait_staleness_ok(in.worker_id, in.iteration);
     }
-    for (auto& t : core_.serve_parameters(in.iteration)) out.parameters.push_back(to_pb(std::move(t)));
-    resp = out.encode();
+    resp = out.encode();  // iteration + ready; the tensors follow from the shared encoding
+    resp.shared_tail = encoded_parameters();
     return Status{};
   });
-  server_.add(base + "CheckSyncStatus", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "CheckSyncStatus", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::SyncStatusRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SyncStatusRequest"};
     pb::SyncStatusResponse out;
@@ -79,7 +80,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "SaveCheckpoint", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "SaveCheckpoint", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::SaveCheckpointRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SaveCheckpointRequest"};
     std::string path = in.path;
@@ -95,7 +96,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     resp = out.encode();
     return Status{};
   });
-  server_.add(base + "LoadCheckpoint", [this](const std::string& req, std::string& resp) {
+  server_.add(base + "LoadCheckpoint", [this](std::string_view req, grpc_lite::Reply& resp) {
     pb::LoadCheckpointRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed LoadCheckpointRequest"};
     pb::LoadCheckpointResponse out;
@@ -119,6 +120,42 @@ ParameterServerService::~ParameterServerService() { shutdown(); }
 
 // Same policy as the reference (src/parameter_server_service.cpp:150-169): every scan,
 // epoch = current_iteration / interval; save when a new epoch started and iteration > 0.
+std::shared_ptr<const std::string> ParameterServerService::encoded_parameters() {
+  std::lock_guard<std::mutex> lk(serve_mu_);  // single flight: concurrent pulls wait for one encode
+  if (serve_cache_ && serve_cache_version_ == core_.version()) return serve_cache_;
+  auto bytes = std::make_shared<std::string>();
+  int64_t version = -1;
+  core_.with_parameters([&](const std::vector<HostTensor>& params, int64_t v) {
+    version = v;
+    size_t total = 0;
+    std::vector<size_t> sizes(params.size());
+    pb::Tensor shell;  // for the size / header arithmetic only; the floats are never copied into it
+    for (size_t i = 0; i < params.size(); ++i) {
+      shell.name = params[i].name;
+      shell.shape = params[i].shape;
+      shell.dtype = params[i].dtype;
+      const size_t n = params[i].data.size();
+      const size_t data_field = n ? 1 + pb::varint_size(n * 4) + n * 4 : 0;
+      sizes[i] = shell.encoded_size() + data_field;
+      total += 1 + pb::varint_size(sizes[i]) + sizes[i];
+    }
+    pb::Writer w;
+    w.buf.reserve(total);
+    for (size_t i = 0; i < params.size(); ++i) {
+      w.tag(2, pb::kLen);
+      w.varint(sizes[i]);
+      w.str(1, params[i].name);
+      w.packed_i32(2, params[i].shape);
+      w.packed_f32(3, params[i].data.data(), params[i].data.size());
+      w.i32(4, params[i].dtype);
+    }
+    *bytes = std::move(w.buf);
+  });
+  serve_cache_ = std::move(bytes);
+  serve_cache_version_ = version;
+  return serve_cache_;
+}
+
 void ParameterServerService::periodic_checkpoint() {
   int32_t last_epoch = -1;
   int waited = 0;

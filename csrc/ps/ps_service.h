@@ -4,6 +4,8 @@
 
 #include <atomic>
 #include <string>
+#include <memory>
+#include <mutex>
 #include <thread>
 
 #include "../wire/h2.h"
@@ -32,6 +34,15 @@ class ParameterServerService {
  private:
   void periodic_checkpoint();
   void membership_loop(std::string coordinator_address, int poll_ms);
+  // `repeated Tensor parameters = 2` of ParameterUpdate, encoded for the current model version.
+  // In sync mode every worker pulls the same weights between two updates: they are encoded
+  // once (straight from the core's tensors) and every response is sent from this buffer.  The
+  // reference converts float by float into a fresh proto for each pull
+  // (src/parameter_server_service.cpp:61-83).
+  std::shared_ptr<const std::string> encoded_parameters();
+  std::mutex serve_mu_;
+  std::shared_ptr<const std::string> serve_cache_;
+  int64_t serve_cache_version_ = -1;
   ParameterServerCore core_;
   grpc_lite::Server server_;
   int checkpoint_interval_;

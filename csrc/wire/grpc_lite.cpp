@@ -25,20 +25,8 @@ namespace grpc_lite {
 
 namespace {
 
-std::string frame_message(const std::string& msg) {
-  std::string out;
-  out.reserve(msg.size() + 5);
-  out.push_back(0);
-  uint32_t n = static_cast<uint32_t>(msg.size());
-  char b[4] = {static_cast<char>(n >> 24), static_cast<char>(n >> 16), static_cast<char>(n >> 8),
-               static_cast<char>(n)};
-  out.append(b, 4);
-  out.append(msg);
-  return out;
-}
-
-// Extracts the single message of a unary body.  Returns false on framing errors.
-bool unframe_message(const std::string& body, std::string& msg, std::string& err) {
+// Locates the single message of a unary body (a view into `body`).  False on framing errors.
+bool unframe_message(const std::string& body, std::string_view& msg, std::string& err) {
   if (body.size() < 5) {
     err = "missing gRPC message frame";
     return false;
@@ -53,7 +41,7 @@ bool unframe_message(const std::string& body, std::string& msg, std::string& err
     err = "gRPC message length does not match the body";
     return false;
   }
-  msg.assign(body, 5, n);
+  msg = std::string_view(body.data() + 5, n);
   return true;
 }
 
@@ -275,12 +263,13 @@ void Server::serve_conn(int fd) {
         const std::string* path = find_header(st->headers, ":path");
         const std::string* ctype = find_header(st->headers, "content-type");
         Status status;
-        std::string response;
+        Reply response;
         if (!path || !ctype || ctype->rfind("application/grpc", 0) != 0) {
           status = {UNKNOWN, "not a gRPC request"};
         } else {
           auto it = handlers_.find(*path);
-          std::string request, err;
+          std::string_view request;
+          std::string err;
           if (it == handlers_.end()) status = {UNIMPLEMENTED, "unknown method " + *path};
           else if (!unframe_message(st->body, request, err)) status = {INTERNAL, err};
           else {
@@ -298,7 +287,8 @@ void Server::serve_conn(int fd) {
         if (status.ok()) {  // HEADERS + DATA + trailers leave in one write when small
           const std::vector<hpack::Header> hs = {{":status", "200"},
                                                  {"content-type", "application/grpc"}};
-          ok = conn->send_message(sid, &hs, frame_message(response), &trailers);
+          ok = conn->send_message(sid, &hs, response.body, &trailers, /*grpc_prefix=*/true,
+                                  response.shared_tail.get());
         } else {  // trailers-only response
           std::vector<hpack::Header> hs = {{":status", "200"},
                                            {"content-type", "application/grpc"}};
@@ -380,7 +370,7 @@ Status Channel::call(const std::string& path, const std::string& request, std::s
         {":authority", host_ + ":" + std::to_string(port_)},
         {"content-type", "application/grpc"}, {"te", "trailers"},
         {"user-agent", "psb-grpc-lite/0.1"}};
-    bool sent = c.send_message(sid, &hs, frame_message(request), nullptr);
+    bool sent = c.send_message(sid, &hs, request, nullptr, /*grpc_prefix=*/true);
     bool done = false;
     h2::Stream got, tmp;
     h2::Stream* st = &got;
@@ -411,7 +401,13 @@ Status Channel::call(const std::string& path, const std::string& request, std::s
       else status = {std::atoi(gs->c_str()), gm ? *gm : std::string()};
       if (status.ok()) {
         std::string err;
-        if (!unframe_message(st->body, response, err)) status = {INTERNAL, err};
+        std::string_view msg;
+        if (!unframe_message(st->body, msg, err)) {
+          status = {INTERNAL, err};
+        } else {  // hand the receive buffer over; dropping the 5-byte header is a warm memmove
+          response = std::move(st->body);
+          response.erase(0, 5);
+        }
       }
     }
     c.erase(sid);

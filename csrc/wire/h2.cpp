@@ -230,6 +230,81 @@ bool Conn::on_headers_block(uint32_t sid, uint8_t flags) {
   return true;
 }
 
+// An unpadded DATA frame: the payload is received straight into the stream's body — no
+// intermediate frame buffer, and the body is sized once from the gRPC message header at its
+// start, so a 400 MB tensor message is written exactly once on its way in.  Only the reader
+// thread touches the body of a stream that is still open (take_completed moves it out after
+// END_STREAM), so the socket read happens without state_mu_.
+bool Conn::on_data(uint32_t sid, uint8_t flags, size_t len) {
+  Stream* st = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(state_mu_);
+    if (hdr_sid_ != 0) {  // header block must be contiguous
+      send_goaway(1);
+      return fail();
+    }
+    st = find(sid);
+    if (st && st->reset) st = nullptr;
+    if (st && st->body.size() + len > max_message_bytes + 5) {
+      send_rst(sid, 11 /*ENHANCE_YOUR_CALM*/);
+      st->reset = true;
+      st = nullptr;
+    }
+  }
+  if (st) {
+    std::string& body = st->body;
+    const size_t old = body.size();
+    body.resize(old + len);
+    if (len && !read_exact(&body[old], len)) return false;
+    if (old < 5 && body.size() >= 5) {
+      const uint8_t* b = reinterpret_cast<const uint8_t*>(body.data());
+      const size_t want = 5 + static_cast<size_t>(get32(b + 1));
+      if (want > body.size() && want <= max_message_bytes + 5) body.reserve(want);
+    }
+  } else if (len) {  // nobody wants it: drain
+    char scratch[16384];
+    for (size_t left = len; left > 0;) {
+      const size_t k = left < sizeof(scratch) ? left : sizeof(scratch);
+      if (!read_exact(scratch, k)) return false;
+      left -= k;
+    }
+  }
+  uint32_t stream_inc = 0, conn_inc = 0;
+  {
+    std::lock_guard<std::mutex> lk(state_mu_);
+    st = find(sid);  // may have been erased meanwhile only if it was not ours to fill
+    if (st && !(flags & END_STREAM)) {
+      st->recv_unacked += static_cast<int64_t>(len);
+      if (st->recv_unacked >= kWindowUpdateThreshold) {
+        stream_inc = static_cast<uint32_t>(st->recv_unacked);
+        st->recv_unacked = 0;
+      }
+    }
+    if (st && (flags & END_STREAM)) {
+      st->remote_closed = true;
+      completed_.push_back(sid);
+    }
+    conn_recv_unacked_ += static_cast<int64_t>(len);
+    if (conn_recv_unacked_ >= kWindowUpdateThreshold) {
+      conn_inc = static_cast<uint32_t>(conn_recv_unacked_);
+      conn_recv_unacked_ = 0;
+    }
+  }
+  // The window updates go out WITHOUT state_mu_: a peer that stops reading can then stall this
+  // reader, but not the handler threads that need the lock to send their responses.
+  std::string wu;
+  if (conn_inc) {
+    put32(wu, conn_inc);
+    if (!write_frame(WINDOW_UPDATE, 0, 0, wu.data(), 4)) return false;
+  }
+  if (stream_inc) {
+    wu.clear();
+    put32(wu, stream_inc);
+    if (!write_frame(WINDOW_UPDATE, 0, sid, wu.data(), 4)) return false;
+  }
+  return true;
+}
+
 bool Conn::pump() {
   if (!alive_) return false;
   uint8_t h[9];
@@ -241,6 +316,7 @@ bool Conn::pump() {
     send_goaway(6 /*FRAME_SIZE_ERROR*/);
     return fail();
   }
+  if (type == DATA && !(flags & PADDED)) return on_data(sid, flags, len);
   std::string p(len, '\0');
   if (len && !read_exact(&p[0], len)) return false;
   const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data());
@@ -391,9 +467,13 @@ bool Conn::send_headers(uint32_t sid, const std::vector<hpack::Header>& hs, bool
 }
 
 bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
+  return send_data(sid, data.data(), data.size(), end_stream);
+}
+
+bool Conn::send_data(uint32_t sid, const char* data, size_t size, bool end_stream) {
   size_t off = 0;
-  if (data.empty()) return write_frame(DATA, end_stream ? END_STREAM : 0, sid, nullptr, 0);
-  while (off < data.size()) {
+  if (size == 0) return write_frame(DATA, end_stream ? END_STREAM : 0, sid, nullptr, 0);
+  while (off < size) {
     size_t n = 0;
     {
       std::unique_lock<std::mutex> lk(state_mu_);
@@ -403,7 +483,7 @@ bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
         if (!st || st->reset) return false;
         int64_t win = conn_send_window_ < st->send_window ? conn_send_window_ : st->send_window;
         if (win > 0) {
-          n = data.size() - off;
+          n = size - off;
           if (n > static_cast<size_t>(win)) n = static_cast<size_t>(win);
           if (n > peer_max_frame_) n = peer_max_frame_;
           conn_send_window_ -= static_cast<int64_t>(n);
@@ -420,8 +500,8 @@ bool Conn::send_data(uint32_t sid, const std::string& data, bool end_stream) {
         }
       }
     }
-    const bool last = off + n == data.size();
-    if (!write_frame(DATA, (last && end_stream) ? END_STREAM : 0, sid, data.data() + off, n))
+    const bool last = off + n == size;
+    if (!write_frame(DATA, (last && end_stream) ? END_STREAM : 0, sid, data + off, n))
       return false;
     off += n;
   }
@@ -439,17 +519,24 @@ void Conn::append_frame(std::string& out, uint8_t type, uint8_t flags, uint32_t 
 }
 
 bool Conn::send_message(uint32_t sid, const std::vector<hpack::Header>* hs, const std::string& data,
-                        const std::vector<hpack::Header>* trailers) {
+                        const std::vector<hpack::Header>* trailers, bool grpc_prefix,
+                        const std::string* tail) {
   std::string hblock, tblock;
   if (hs) enc_.encode(*hs, hblock);
   if (trailers) enc_.encode(*trailers, tblock);
+  const size_t tail_n = tail ? tail->size() : 0;
+  const size_t msg_n = data.size() + tail_n;
+  char prefix[5] = {0, static_cast<char>(msg_n >> 24), static_cast<char>(msg_n >> 16),
+                    static_cast<char>(msg_n >> 8), static_cast<char>(msg_n)};
+  const size_t prefix_n = grpc_prefix ? 5 : 0;
+  const size_t body_n = prefix_n + msg_n;
   uint32_t max_frame = 0;
-  bool coalesce = data.size() <= kCoalesceMax;
+  bool coalesce = body_n <= kCoalesceMax;
   if (coalesce) {
     std::lock_guard<std::mutex> lk(state_mu_);
     max_frame = peer_max_frame_;
     Stream* st = find(sid);
-    const int64_t need = static_cast<int64_t>(data.size());
+    const int64_t need = static_cast<int64_t>(body_n);
     coalesce = st && !st->reset && hblock.size() <= max_frame && tblock.size() <= max_frame &&
                conn_send_window_ >= need && st->send_window >= need;
     if (coalesce) {  // reserve the whole body now
@@ -458,21 +545,36 @@ bool Conn::send_message(uint32_t sid, const std::vector<hpack::Header>* hs, cons
     }
   }
   if (!coalesce) {
+    // large body: frames go out straight from the caller's buffers, piece by piece
     if (hs && !send_headers(sid, *hs, false)) return false;
-    if (!send_data(sid, data, trailers == nullptr)) return false;
+    const bool end = trailers == nullptr;
+    if (prefix_n && !send_data(sid, prefix, prefix_n, end && msg_n == 0)) return false;
+    if ((!data.empty() || (!prefix_n && !tail_n)) &&
+        !send_data(sid, data.data(), data.size(), end && tail_n == 0))
+      return false;
+    if (tail_n && !send_data(sid, tail->data(), tail_n, end)) return false;
     return trailers ? send_headers(sid, *trailers, true) : true;
   }
   std::string out;
-  out.reserve(hblock.size() + data.size() + tblock.size() + 64);
+  out.reserve(hblock.size() + body_n + tblock.size() + 64);
   if (hs) append_frame(out, HEADERS, END_HEADERS, sid, hblock.data(), hblock.size());
+  std::string body;
+  const std::string* src = &data;
+  if (prefix_n || tail_n) {  // small: one contiguous body is simplest
+    body.reserve(body_n);
+    body.append(prefix, prefix_n);
+    body.append(data);
+    if (tail_n) body.append(*tail);
+    src = &body;
+  }
   size_t off = 0;
   do {
-    size_t n = data.size() - off;
+    size_t n = src->size() - off;
     if (n > max_frame) n = max_frame;
-    const bool last = off + n == data.size();
-    append_frame(out, DATA, (last && !trailers) ? END_STREAM : 0, sid, data.data() + off, n);
+    const bool last = off + n == src->size();
+    append_frame(out, DATA, (last && !trailers) ? END_STREAM : 0, sid, src->data() + off, n);
     off += n;
-  } while (off < data.size());
+  } while (off < src->size());
   if (trailers)
     append_frame(out, HEADERS, END_HEADERS | END_STREAM, sid, tblock.data(), tblock.size());
   std::lock_guard<std::mutex> wl(write_mu_);

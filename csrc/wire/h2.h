@@ -17,6 +17,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <string_view>
 #include <thread>
 #include <vector>
 
@@ -67,13 +68,18 @@ class Conn {
   bool send_headers(uint32_t sid, const std::vector<hpack::Header>& h, bool end_stream);
   // Sends `data` as DATA frames, honouring flow control (pumps incoming frames while blocked).
   bool send_data(uint32_t sid, const std::string& data, bool end_stream);
+  bool send_data(uint32_t sid, const char* data, size_t size, bool end_stream);
   // One unary message in ONE socket write when it is small and the flow-control windows allow:
   // [HEADERS(hs)] + DATA(data) + [HEADERS(trailers), END_STREAM]; `hs` may be null (headers
   // already sent), `trailers` null means END_STREAM goes on the last DATA frame.  Three writes
   // become one segment — a unary RPC is latency-bound by syscalls and wake-ups, not by bytes.
   // Falls back to send_headers / send_data for large bodies.
+  // `grpc_prefix`: put the 5-byte gRPC message header (flag 0 + big-endian length) in front of
+  // the body here, so that callers never build a framed copy of a large message; `tail` is a
+  // second piece of the same body (e.g. a cached encoding shared between responses).
   bool send_message(uint32_t sid, const std::vector<hpack::Header>* hs, const std::string& data,
-                    const std::vector<hpack::Header>* trailers);
+                    const std::vector<hpack::Header>* trailers, bool grpc_prefix = false,
+                    const std::string* tail = nullptr);
   bool send_rst(uint32_t sid, uint32_t code);
   bool send_goaway(uint32_t code);
   uint32_t next_stream_id() { uint32_t s = next_sid_; next_sid_ += 2; return s; }
@@ -93,6 +99,7 @@ class Conn {
   void append_frame(std::string& out, uint8_t type, uint8_t flags, uint32_t sid, const char* payload,
                     size_t n);
   bool on_headers_block(uint32_t sid, uint8_t flags);
+  bool on_data(uint32_t sid, uint8_t flags, size_t len);
   bool on_settings(const std::string& p, uint8_t flags);
   Stream* find(uint32_t id);  // state_mu_ held
 
@@ -136,7 +143,20 @@ struct Status {
   bool ok() const { return code == OK; }
 };
 
-using Handler = std::function<Status(const std::string& request, std::string& response)>;
+// What a handler returns: the encoded response message, optionally continued by a shared,
+// immutable piece (`shared_tail`) that is sent straight from that buffer — protobuf fields may
+// arrive in any order, so "small fields, then the big cached repeated field" is one message.
+struct Reply {
+  std::string body;
+  std::shared_ptr<const std::string> shared_tail;
+  Reply& operator=(std::string encoded) {
+    body = std::move(encoded);
+    return *this;
+  }
+};
+
+// `request` is a view into the connection's receive buffer (valid for the call).
+using Handler = std::function<Status(std::string_view request, Reply& response)>;
 
 class HandlerPool;  // grpc_lite.cpp
 

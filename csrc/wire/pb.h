@@ -19,6 +19,15 @@ namespace pb {
 
 enum WireType { kVarint = 0, kFixed64 = 1, kLen = 2, kFixed32 = 5 };
 
+inline size_t varint_size(uint64_t v) {
+  size_t n = 1;
+  while (v >= 0x80) {
+    v >>= 7;
+    ++n;
+  }
+  return n;
+}
+
 class Writer {
  public:
   std::string buf;

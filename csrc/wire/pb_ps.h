@@ -12,6 +12,20 @@ struct Tensor {
   std::vector<float> data;
   int32_t dtype = 0;  // 0 = float32, 1 = float64 (payload is float32 either way)
 
+  // Exact number of bytes encode_into() appends: lets a message with many large tensors be
+  // written into one buffer reserved once (no per-tensor staging copy, no growth copies).
+  size_t encoded_size() const {
+    size_t n = 0;
+    if (!name.empty()) n += 1 + varint_size(name.size()) + name.size();
+    if (!shape.empty()) {
+      size_t packed = 0;
+      for (int32_t x : shape) packed += varint_size(static_cast<uint64_t>(static_cast<int64_t>(x)));
+      n += 1 + varint_size(packed) + packed;
+    }
+    if (!data.empty()) n += 1 + varint_size(data.size() * 4) + data.size() * 4;
+    if (dtype != 0) n += 1 + varint_size(static_cast<uint64_t>(static_cast<int64_t>(dtype)));
+    return n;
+  }
   void encode_into(Writer& w) const {
     w.str(1, name);
     w.packed_i32(2, shape);
@@ -60,12 +74,21 @@ struct Tensor {
   }
 };
 
-inline void encode_tensors(Writer& w, int field, const std::vector<Tensor>& ts) {
+inline size_t tensors_encoded_size(const std::vector<Tensor>& ts) {
+  size_t total = 0;
   for (const auto& t : ts) {
-    Writer inner;
-    inner.buf.reserve(t.data.size() * 4 + t.name.size() + 32);
-    t.encode_into(inner);
-    w.msg(field, inner.buf);
+    const size_t n = t.encoded_size();
+    total += 1 + varint_size(n) + n;  // field numbers here are < 16: one tag byte
+  }
+  return total;
+}
+
+inline void encode_tensors(Writer& w, int field, const std::vector<Tensor>& ts) {
+  w.buf.reserve(w.buf.size() + tensors_encoded_size(ts) + 32);
+  for (const auto& t : ts) {
+    w.tag(field, kLen);  // embedded message: always written, even when empty
+    w.varint(t.encoded_size());
+    t.encode_into(w);
   }
 }
 

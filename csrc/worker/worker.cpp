@@ -18,11 +18,6 @@ using grpc_lite::Channel;
 using grpc_lite::Status;
 
 namespace {
-pb::Tensor to_pb(const TensorLite& t) {
-  pb::Tensor p;
-  p.name = t.name, p.shape = t.shape, p.data = t.data, p.dtype = t.dtype;
-  return p;
-}
 TensorLite from_pb(pb::Tensor&& p) {
   TensorLite t;
   t.name = std::move(p.name), t.shape = std::move(p.shape), t.data = std::move(p.data);
@@ -261,11 +256,24 @@ std::vector<TensorLite> Worker::pull_parameters(int iteration, bool* ready) {
 
 bool Worker::push_gradients(int iteration, const std::vector<TensorLite>& grads,
                             int& workers_received, int& total_workers) {
+  return push_gradients(iteration, std::vector<TensorLite>(grads), workers_received,
+                        total_workers);
+}
+
+// Takes the gradients over: they go into the request without a copy, and the request is encoded
+// into one buffer reserved once (the reference appends float by float, src/worker.cpp:40-52).
+bool Worker::push_gradients(int iteration, std::vector<TensorLite>&& grads,
+                            int& workers_received, int& total_workers) {
   pb::GradientUpdate req;
   req.worker_id = worker_id_;
   req.iteration = iteration;
   req.gradients.reserve(grads.size());
-  for (const auto& g : grads) req.gradients.push_back(to_pb(g));
+  for (auto& g : grads) {
+    pb::Tensor p;
+    p.name = std::move(g.name), p.shape = std::move(g.shape), p.data = std::move(g.data);
+    p.dtype = g.dtype;
+    req.gradients.push_back(std::move(p));
+  }
   std::string resp;
   Status s = ps_channel().call("/parameter_server.ParameterServer/ReceiveGradients", req.encode(),
                                resp, 30000);
@@ -303,7 +311,7 @@ bool Worker::load_checkpoint_from_server(const std::string& checkpoint_path, int
   return true;
 }
 
-std::vector<TensorLite> Worker::compute_gradients(const std::vector<TensorLite>& params) {
+std::vector<TensorLite> Worker::compute_gradients(std::vector<TensorLite>&& params) {
   if (opt_.compute_ms > 0.0) {
     // xorshift per worker: the same run sees the same stragglers in every mode
     sim_rng_ ^= sim_rng_ << 13;
@@ -315,7 +323,7 @@ std::vector<TensorLite> Worker::compute_gradients(const std::vector<TensorLite>&
     std::this_thread::sleep_for(std::chrono::microseconds(static_cast<int64_t>(ms * 1000.0)));
   }
   if (grad_fn_) return grad_fn_(params);
-  std::vector<TensorLite> grads = params;
+  std::vector<TensorLite> grads = std::move(params);  // same names and shapes: filled in place
   for (auto& t : grads) {
     if (dev_ && dev_->run(t.data, opt_.synthetic_grad)) continue;
     for (auto& v : t.data) v = opt_.synthetic_grad;
@@ -325,8 +333,13 @@ std::vector<TensorLite> Worker::compute_gradients(const std::vector<TensorLite>&
 
 bool Worker::run_iteration(int iteration) {
   current_status_ = pb::TRAINING;
+  using clk = std::chrono::steady_clock;
+  auto since = [](clk::time_point t) {
+    return std::chrono::duration<double, std::milli>(clk::now() - t).count();
+  };
   for (int attempt = 0; attempt < opt_.max_retries; ++attempt) {
     bool ready = true;
+    const auto t_pull = clk::now();
     std::vector<TensorLite> params = pull_parameters(iteration, &ready);
     if (opt_.mode == "ssp") {
       // bounded staleness: wait until the slowest worker is within the bound
@@ -348,11 +361,25 @@ bool Worker::run_iteration(int iteration) {
       w.data.assign(100, 0.0f);
       params.push_back(std::move(w));
     }
-    std::vector<TensorLite> grads = compute_gradients(params);
+    const double pull_ms = since(t_pull);
+    const auto t_compute = clk::now();
+    std::vector<TensorLite> grads = compute_gradients(std::move(params));
+    const double compute_ms = since(t_compute);
     int received = 0, total = 0;
-    bool complete = push_gradients(iteration, grads, received, total);
+    const auto t_push = clk::now();
+    bool complete = push_gradients(iteration, std::move(grads), received, total);
+    const double push_ms = since(t_push);
+    const auto t_wait = clk::now();
+    auto trace = [&](bool done) {
+      if (!opt_.trace) return;
+      std::cout << "worker " << worker_id_ << " trace iter " << iteration << " pull_ms=" << pull_ms
+                << " compute_ms=" << compute_ms << " push_ms=" << push_ms
+                << " wait_ms=" << since(t_wait) << " done=" << (done ? "true" : "false")
+                << std::endl;
+    };
     if (complete) {
       current_status_ = pb::IDLE;
+      trace(true);
       return true;
     }
     if (!last_push_ok_) {  // transport failure: back off and try the whole step again
@@ -366,6 +393,7 @@ bool Worker::run_iteration(int iteration) {
     while (std::chrono::steady_clock::now() < deadline) {
       if (check_sync_ready(iteration, received, total)) {
         current_status_ = pb::IDLE;
+        trace(true);
         return true;
       }
       sleep_ms(backoff);

@@ -48,6 +48,7 @@ struct WorkerOptions {
   double straggle_prob = 0.0;
   double straggle_factor = 1.0;
   uint64_t sim_seed = 0;
+  bool trace = false;             // per-iteration pull / compute / push / wait times on stdout
 };
 
 class Worker {
@@ -67,6 +68,8 @@ class Worker {
   std::vector<TensorLite> pull_parameters(int iteration, bool* ready = nullptr);
   bool push_gradients(int iteration, const std::vector<TensorLite>& grads, int& workers_received,
                       int& total_workers);
+  bool push_gradients(int iteration, std::vector<TensorLite>&& grads, int& workers_received,
+                      int& total_workers);
   bool check_sync_ready(int iteration, int& workers_received, int& total_workers);
   std::vector<std::string> discover_peer_workers();
   const std::string& ps_address() const { return ps_address_; }
@@ -81,7 +84,7 @@ class Worker {
   bool query_with_retry(const std::function<bool()>& query, int max_retries = 5);
   void send_heartbeat();
   void heartbeat_loop();
-  std::vector<TensorLite> compute_gradients(const std::vector<TensorLite>& params);
+  std::vector<TensorLite> compute_gradients(std::vector<TensorLite>&& params);
   grpc_lite::Channel& ps_channel();
 
   int worker_id_;

@@ -5,13 +5,15 @@
 // Extensions: --mode=sync|async|ssp  --device=N  --heartbeat-ms=N  --sync-timeout-ms=N
 // (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS), and for the straggler
 // benchmark --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N --quiet (simulated
-// compute time per iteration; no per-iteration log line, one summary line at the end).
+// compute time per iteration; no per-iteration log line, one summary line at the end), and
+// --trace (pull / compute / push / wait milliseconds of every iteration).
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
 #include <string>
 #include <vector>
 
+#include "../common/memtune.h"
 #include "worker.h"
 
 static bool flag(const std::string& arg, const char* key, std::string& val) {
@@ -22,6 +24,7 @@ static bool flag(const std::string& arg, const char* key, std::string& val) {
 }
 
 int main(int argc, char** argv) {
+  psb::retain_freed_memory();
   std::string coordinator_addr = "localhost:50052";
   int worker_id = 0, iterations = 1;
   std::string worker_addr, checkpoint_path;
@@ -44,6 +47,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "straggle-factor", v)) opt.straggle_factor = std::atof(v.c_str());
     else if (flag(a, "seed", v)) opt.sim_seed = std::strtoull(v.c_str(), nullptr, 10);
     else if (a == "--quiet") quiet = true;
+    else if (a == "--trace") opt.trace = true;
     else if (a.rfind("--", 0) == 0 && a.size() > 2) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;

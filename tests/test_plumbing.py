@@ -224,3 +224,49 @@ def test_straggler_benchmark_modes_agree_on_the_work_done(tmp_path):
     assert [x["mode"] for x in rows] == ["sync", "ssp", "async"]
     for x in rows:
         assert len(x["worker_ms"]) == 3 and x["job_ms"] >= 40 * 2
+
+
+def test_multi_megabyte_model_through_cpp_worker_and_server(tmp_path):
+    """6 MB of parameters resumed from a checkpoint, two C++ workers x 3 iterations: every pull is
+    a response sent from the server's shared per-version encoding in several DATA frames, every
+    push is received straight into the stream body and moved into the staging map.  The weights
+    must come out as init - 3 x 0.01 exactly as with the 100-float model."""
+    from parameter_server_distributed_b200.utils.checkpoint import write_reference_file
+    rng = np.random.default_rng(5)
+    init = [("big.weight", (1024, 1024), rng.standard_normal(1024 * 1024).astype(np.float32)),
+            ("big.bias", (1024,), rng.standard_normal(1024).astype(np.float32)),
+            ("tail.weight", (512, 1024), rng.standard_normal(512 * 1024).astype(np.float32))]
+    write_reference_file(str(tmp_path / "init.ckpt"), 0, 0, init)
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0", "--resume=init.ckpt"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    workers = []
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        for wid in range(2):
+            workers.append(Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(wid), "3",
+                                 "--trace"], str(tmp_path), str(tmp_path / f"w{wid}.log")))
+        for w in workers:
+            assert w.p.wait(timeout=120) == 0
+        for w in workers:
+            out = w.output()
+            assert out.count("done=true") >= 3 and "pull_ms=" in out, out[-300:]
+        stub = protos.Stub(grpc.insecure_channel(
+            f"127.0.0.1:{ps_port}", options=[("grpc.max_receive_message_length", -1)]),
+            "parameter_server.ParameterServer")
+        r = stub.ServeParameters(protos.msg("parameter_server.PullRequest")(worker_id=0, iteration=9),
+                                 timeout=30)
+        assert [t.name for t in r.parameters] == [n for n, _, _ in init]
+        for t, (_, shape, a) in zip(r.parameters, init):
+            assert tuple(t.shape) == shape
+            exp = a
+            for _ in range(3):
+                exp = exp - np.float32(0.01)
+            np.testing.assert_array_equal(np.asarray(t.data, dtype=np.float32), exp)
+    finally:
+        for w in workers:
+            w.stop()
+        ps.stop()
+        co.stop()

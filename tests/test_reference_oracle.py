@@ -87,3 +87,31 @@ def test_reference_coordinator_returns_host_only_address_we_return_dialable():
     assert lib.ref_coord_register(c, 1, buf, 64) == 2
     assert lib.ref_coord_register(c, 1, buf, 64) == 2  # overwrite allowed
     lib.ref_coord_destroy(c)
+
+
+def test_threaded_aggregation_is_bit_identical_on_large_tensors(tmp_path):
+    """benchmarks/host_core_bench: both cores in one process on a 2.2 M-parameter cut of the
+    MLP, two workers — large enough for the threaded, in-place mean + update of ps_core.cpp.
+    The binary exits non-zero unless the parameters are bit-identical; the same holds for
+    every thread count (each element is computed by the same expression in the same order)."""
+    import json
+    import subprocess
+    ref_src = os.path.join(ROOT, "baseline", "_ref", "src", "parameter_server.cpp")
+    if not os.path.exists(ref_src):
+        pytest.skip("baseline/_ref sources absent")
+    exe = str(tmp_path / "host_core_bench")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-pthread", "-I",
+                    os.path.join(ROOT, "baseline", "_ref", "include"),
+                    os.path.join(ROOT, "benchmarks", "host_core_bench.cpp"), ref_src,
+                    os.path.join(ROOT, "csrc", "ps", "ps_core.cpp"),
+                    os.path.join(ROOT, "csrc", "ps", "ps_device.cpp"), "-ldl", "-o", exe],
+                   check=True, cwd=ROOT)
+    for workers in (2, 5):
+        r = subprocess.run([exe, str(workers), "4", "0.02"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        row = json.loads(r.stdout)
+        assert row["params"] > 2_000_000
+        if workers == 2:
+            assert row["bit_identical"] and row["max_abs_diff"] == 0
+        else:  # the reference's summation order is that of an unordered_map
+            assert row["max_abs_diff"] < 1e-7

@@ -45,11 +45,12 @@ def plane(tmp_path, request):
 
 def _run_workers(coord, steps, mode="sync"):
     out, errs = {}, []
+    models = [_model() for _ in range(2)]  # seeded here: torch's global RNG is not per thread
 
     def work(w):
         try:
             with psd.RemoteParameterServer(coord, w, heartbeat_s=0.2) as ps:
-                tr = psd.RemoteTrainer(_model(), _loss, ps, mode=mode)
+                tr = psd.RemoteTrainer(models[w], _loss, ps, mode=mode)
                 losses = [float(tr.step(x, y)) for x, y in _batches(w, steps)]
                 tr.sync_model()
                 out[w] = (losses, [p.detach().clone() for p in tr.params], tr.skipped,
