@@ -6,6 +6,9 @@
 //   --momentum=F --beta1=F --beta2=F --eps=F --weight-decay=F  --device=N (HBM-resident shard)
 //   --coordinator=host:port  --membership-poll-ms=N   follow the coordinator's worker registry:
 //       an evicted worker no longer blocks the sync barrier (PSB_COORDINATOR, PSB_MEMBERSHIP_POLL_MS)
+//   --shard-id=I [--advertise=host:port]   one of several parameter servers: registers in the
+//       coordinator's shard map (needs --coordinator); workers run with --shards=N and split the
+//       model's tensors over the shards (PSB_SHARD_ID, PSB_ADVERTISE)
 //   --resume=PATH|latest   load this checkpoint (latest: the newest checkpoint_epoch_*.ckpt in the
 //       working directory) before serving, so a restarted server carries on (PSB_RESUME)
 //   --threads=N   host threads for aggregation and update of large tensors (default: all cores,
@@ -45,7 +48,10 @@ int main(int argc, char** argv) {
   if (const char* e = env("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = env("PSB_LONG_POLL_MS")) opt.long_poll_ms = std::atoi(e);
   if (const char* e = env("PSB_THREADS")) opt.threads = std::atoi(e);
-  std::string coordinator, resume;
+  std::string coordinator, resume, advertise;
+  int shard_id = -1;
+  if (const char* e = env("PSB_SHARD_ID")) shard_id = std::atoi(e);
+  if (const char* e = env("PSB_ADVERTISE")) advertise = e;
   int membership_poll_ms = 1000;
   if (const char* e = env("PSB_RESUME")) resume = e;
   if (const char* e = env("PSB_COORDINATOR")) coordinator = e;
@@ -70,6 +76,8 @@ int main(int argc, char** argv) {
     else if (flag(a, "coordinator", v)) coordinator = v;
     else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "resume", v)) resume = v;
+    else if (flag(a, "shard-id", v)) shard_id = std::atoi(v.c_str());
+    else if (flag(a, "advertise", v)) advertise = v;
     else if (a.rfind("--", 0) == 0) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;
@@ -79,6 +87,6 @@ int main(int argc, char** argv) {
   if (pos.size() > 1) total_workers = std::stoi(pos[1]);
   if (pos.size() > 2) checkpoint_interval = std::stoi(pos[2]);
   psb::run_server(listen, total_workers, checkpoint_interval, opt, coordinator, membership_poll_ms,
-                  resume);
+                  resume, shard_id, advertise);
   return 0;
 }

@@ -9,6 +9,7 @@
 #include <sstream>
 
 #include "../wire/pb.h"
+#include "../wire/pb_ext.h"
 
 namespace psb {
 
@@ -211,6 +212,35 @@ void ParameterServerService::membership_loop(std::string coordinator_address, in
   }
 }
 
+void ParameterServerService::announce_shard(const std::string& coordinator_address, int shard_id,
+                                            const std::string& advertise, int poll_ms) {
+  if (coordinator_address.empty() || shard_id < 0 || shard_thread_.joinable()) return;
+  shard_thread_ = std::thread([this, coordinator_address, shard_id, advertise, poll_ms] {
+    grpc_lite::Channel coord(coordinator_address);
+    pb::ShardInfo me;
+    me.shard_id = shard_id;
+    me.address = advertise;
+    me.device = 0;  // host shard
+    bool announced = false;
+    int waited = poll_ms;
+    while (running_) {
+      if (waited < poll_ms) {
+        std::this_thread::sleep_for(std::chrono::milliseconds(20));
+        waited += 20;
+        continue;
+      }
+      waited = 0;
+      std::string resp;
+      Status s = coord.call("/psb.CoordinatorExt/RegisterShard", me.encode(), resp, 2000);
+      pb::Ack ack;
+      const bool ok = s.ok() && ack.decode(resp) && ack.success;
+      if (ok && !announced)
+        std::cout << "registered as shard " << shard_id << " at " << advertise << std::endl;
+      announced = announced || ok;  // repeated: a restarted coordinator learns the map again
+    }
+  });
+}
+
 int ParameterServerService::listen(const std::string& address) { return server_.listen(address); }
 void ParameterServerService::serve_forever() { server_.serve_forever(); }
 void ParameterServerService::start() { server_.start(); }
@@ -220,6 +250,7 @@ void ParameterServerService::shutdown() {
     server_.shutdown();
     if (checkpoint_thread_.joinable()) checkpoint_thread_.join();
     if (membership_thread_.joinable()) membership_thread_.join();
+    if (shard_thread_.joinable()) shard_thread_.join();
   }
 }
 
@@ -248,7 +279,8 @@ std::string latest_checkpoint(const std::string& dir) {
 
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
                 const PsOptions& opt, const std::string& coordinator_address,
-                int membership_poll_ms, const std::string& resume) {
+                int membership_poll_ms, const std::string& resume, int shard_id,
+                const std::string& advertise) {
   int scan_ms = 5000;
   if (const char* e = std::getenv("PSB_CHECKPOINT_SCAN_MS")) scan_ms = std::atoi(e);
   ParameterServerService svc(total_workers, checkpoint_interval, opt, scan_ms);
@@ -276,6 +308,21 @@ void run_server(const std::string& server_address, int total_workers, int checkp
   if (checkpoint_interval > 0)
     std::cout << "periodic checkpointing every " << checkpoint_interval << " iterations"
               << std::endl;
+  if (shard_id >= 0) {
+    if (coordinator_address.empty()) {
+      std::cerr << "--shard-id needs --coordinator" << std::endl;
+      std::exit(2);
+    }
+    std::string adv = advertise;
+    if (adv.empty()) {  // the listen address, made dialable
+      std::string host;
+      int port = 0;
+      grpc_lite::split_host_port(server_address, host, port);
+      if (host.empty() || host == "0.0.0.0" || host == "[::]") host = "127.0.0.1";
+      adv = host + ":" + std::to_string(port);
+    }
+    svc.announce_shard(coordinator_address, shard_id, adv, membership_poll_ms);
+  }
   if (!coordinator_address.empty()) {
     svc.follow_membership(coordinator_address, membership_poll_ms);
     std::cout << "following worker membership of coordinator " << coordinator_address << std::endl;

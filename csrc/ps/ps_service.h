@@ -24,6 +24,13 @@ class ParameterServerService {
   // (SURVEY D9); this uses the reference's own ListWorkers RPC, so it also works against a
   // reference coordinator.
   void follow_membership(const std::string& coordinator_address, int poll_ms = 1000);
+  // Host-plane sharding: announce this process as shard `shard_id` at `advertise` (dialable
+  // host:port) in the coordinator's shard map (psb.CoordinatorExt/RegisterShard) and keep the
+  // entry fresh; workers started with --shards=N split the model's tensors over the N shards
+  // they find there.  The reference has exactly one parameter server
+  // (src/coordinator_main.cpp:9-21 knows a single address).
+  void announce_shard(const std::string& coordinator_address, int shard_id,
+                      const std::string& advertise, int poll_ms = 1000);
   ~ParameterServerService();
   int listen(const std::string& address);
   void serve_forever();
@@ -49,6 +56,7 @@ class ParameterServerService {
   int scan_ms_;
   std::thread checkpoint_thread_;
   std::thread membership_thread_;
+  std::thread shard_thread_;
   int configured_workers_;
   std::atomic<bool> running_{true};
 };
@@ -57,7 +65,8 @@ class ParameterServerService {
 // (include/parameter_server_service.h:5, src/parameter_server_service.cpp:177-191).
 void run_server(const std::string& server_address, int total_workers, int checkpoint_interval,
                 const PsOptions& opt = PsOptions(), const std::string& coordinator_address = "",
-                int membership_poll_ms = 1000, const std::string& resume = "");
+                int membership_poll_ms = 1000, const std::string& resume = "", int shard_id = -1,
+                const std::string& advertise = "");
 
 // Newest periodic checkpoint ("checkpoint_epoch_<E>.ckpt", largest E) in `dir`; "" if none.
 std::string latest_checkpoint(const std::string& dir);

@@ -11,6 +11,7 @@
 
 #include "../../include/psb_kernels.h"
 #include "../wire/pb.h"
+#include "../wire/pb_ext.h"
 
 namespace psb {
 
@@ -121,6 +122,7 @@ bool Worker::initialize() {
   if (initialized_) return true;
   if (!discover_parameter_server()) return false;
   if (!register_with_coordinator()) return false;
+  if (opt_.shards > 1 && !discover_shards()) return false;
   initialized_ = true;
   current_status_ = pb::IDLE;
   return true;
@@ -157,6 +159,55 @@ bool Worker::discover_parameter_server() {
     else ps_address_ = out.address + ":" + std::to_string(out.port);
     return true;
   });
+}
+
+// Host-plane sharding: the coordinator's shard map (psb.CoordinatorExt/GetShardMap) names the
+// parameter servers started with --shard-id; tensor k of the model lives on shard k % N.  Waits
+// until all N have registered (they may still be starting).
+bool Worker::discover_shards() {
+  const auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(30);
+  while (std::chrono::steady_clock::now() < deadline) {
+    std::string resp;
+    Status s = coord_->call("/psb.CoordinatorExt/GetShardMap", std::string(), resp, 5000);
+    pb::ShardMapResponse out;
+    if (s.ok() && out.decode(resp)) {
+      std::vector<std::string> addrs(static_cast<size_t>(opt_.shards));
+      int found = 0;
+      for (const auto& sh : out.shards) {
+        if (sh.shard_id < 0 || sh.shard_id >= opt_.shards) continue;
+        if (sh.address.rfind("hbm://", 0) == 0) continue;  // a GPU-plane shard, not a server
+        if (addrs[static_cast<size_t>(sh.shard_id)].empty()) ++found;
+        addrs[static_cast<size_t>(sh.shard_id)] = sh.address;
+      }
+      if (found == opt_.shards) {
+        shard_addrs_ = std::move(addrs);
+        shard_ch_.clear();
+        for (const auto& a : shard_addrs_) shard_ch_.emplace_back(new Channel(a));
+        return true;
+      }
+    }
+    sleep_ms(100);
+  }
+  std::cerr << "worker " << worker_id_ << ": fewer than " << opt_.shards
+            << " parameter-server shards registered with the coordinator" << std::endl;
+  return false;
+}
+
+grpc_lite::Channel& Worker::shard_channel(int s) {
+  return shard_addrs_.empty() ? ps_channel() : *shard_ch_[static_cast<size_t>(s)];
+}
+
+bool Worker::for_each_shard(const std::function<bool(int)>& fn) {
+  const int n = num_shards();
+  if (n == 1) return fn(0);
+  std::vector<char> ok(static_cast<size_t>(n), 0);
+  std::vector<std::thread> th;
+  for (int s = 1; s < n; ++s) th.emplace_back([&, s] { ok[static_cast<size_t>(s)] = fn(s); });
+  ok[0] = fn(0);
+  for (auto& t : th) t.join();
+  for (char c : ok)
+    if (!c) return false;
+  return true;
 }
 
 bool Worker::register_with_coordinator() {
@@ -242,15 +293,38 @@ std::vector<TensorLite> Worker::pull_parameters(int iteration, bool* ready) {
   pb::PullRequest req;
   req.worker_id = worker_id_;
   req.iteration = iteration;
-  std::string resp;
-  Status s = ps_channel().call("/parameter_server.ParameterServer/ServeParameters", req.encode(),
-                               resp, 30000);
-  pb::ParameterUpdate out;
-  if (!s.ok() || !out.decode(resp)) return {};
-  if (ready) *ready = out.ready;
+  const std::string encoded = req.encode();
+  const int n = num_shards();
+  std::vector<std::vector<TensorLite>> parts(static_cast<size_t>(n));
+  std::vector<char> part_ready(static_cast<size_t>(n), 0);
+  const bool ok = for_each_shard([&](int s) {
+    std::string resp;
+    Status st = shard_channel(s).call("/parameter_server.ParameterServer/ServeParameters", encoded,
+                                      resp, 30000);
+    pb::ParameterUpdate out;
+    if (!st.ok() || !out.decode(resp)) return false;
+    part_ready[static_cast<size_t>(s)] = out.ready;
+    auto& mine = parts[static_cast<size_t>(s)];
+    mine.reserve(out.parameters.size());
+    for (auto& t : out.parameters) mine.push_back(from_pb(std::move(t)));
+    return true;
+  });
+  if (!ok) return {};
+  if (ready) {
+    *ready = true;
+    for (char r : part_ready) *ready = *ready && r;
+  }
+  if (n == 1) return std::move(parts[0]);
+  // tensor k lives on shard k % n as that shard's tensor k / n: interleave them back
+  size_t total = 0;
+  for (const auto& p : parts) total += p.size();
   std::vector<TensorLite> params;
-  params.reserve(out.parameters.size());
-  for (auto& t : out.parameters) params.push_back(from_pb(std::move(t)));
+  params.reserve(total);
+  for (size_t k = 0; k < total; ++k) {
+    auto& p = parts[k % static_cast<size_t>(n)];
+    if (k / static_cast<size_t>(n) >= p.size()) return {};  // shards disagree about the model
+    params.push_back(std::move(p[k / static_cast<size_t>(n)]));
+  }
   return params;
 }
 
@@ -264,50 +338,75 @@ bool Worker::push_gradients(int iteration, const std::vector<TensorLite>& grads,
 // into one buffer reserved once (the reference appends float by float, src/worker.cpp:40-52).
 bool Worker::push_gradients(int iteration, std::vector<TensorLite>&& grads,
                             int& workers_received, int& total_workers) {
-  pb::GradientUpdate req;
-  req.worker_id = worker_id_;
-  req.iteration = iteration;
-  req.gradients.reserve(grads.size());
-  for (auto& g : grads) {
+  const int n = num_shards();
+  std::vector<pb::GradientUpdate> reqs(static_cast<size_t>(n));
+  for (auto& r : reqs) {
+    r.worker_id = worker_id_;
+    r.iteration = iteration;
+  }
+  for (size_t k = 0; k < grads.size(); ++k) {
+    TensorLite& g = grads[k];
     pb::Tensor p;
     p.name = std::move(g.name), p.shape = std::move(g.shape), p.data = std::move(g.data);
     p.dtype = g.dtype;
-    req.gradients.push_back(std::move(p));
+    reqs[k % static_cast<size_t>(n)].gradients.push_back(std::move(p));
   }
-  std::string resp;
-  Status s = ps_channel().call("/parameter_server.ParameterServer/ReceiveGradients", req.encode(),
-                               resp, 30000);
-  pb::PushResponse out;
-  last_push_ok_ = s.ok() && out.decode(resp);
+  std::vector<pb::PushResponse> outs(static_cast<size_t>(n));
+  last_push_ok_ = for_each_shard([&](int s) {
+    std::string resp;
+    Status st = shard_channel(s).call("/parameter_server.ParameterServer/ReceiveGradients",
+                                      reqs[static_cast<size_t>(s)].encode(), resp, 30000);
+    return st.ok() && outs[static_cast<size_t>(s)].decode(resp);
+  });
   if (!last_push_ok_) return false;
-  workers_received = out.workers_received;
-  total_workers = out.total_workers;
-  return out.aggregation_complete;
+  bool complete = true;
+  workers_received = outs[0].workers_received;
+  total_workers = outs[0].total_workers;
+  for (const auto& o : outs) {  // the iteration is done when every shard has aggregated it
+    complete = complete && o.aggregation_complete;
+    workers_received = std::min(workers_received, o.workers_received);
+  }
+  return complete;
 }
 
 bool Worker::check_sync_ready(int iteration, int& workers_received, int& total_workers) {
   pb::SyncStatusRequest req;
   req.iteration = iteration;
-  std::string resp;
-  Status s = ps_channel().call("/parameter_server.ParameterServer/CheckSyncStatus", req.encode(),
-                               resp, 5000);
-  pb::SyncStatusResponse out;
-  if (!s.ok() || !out.decode(resp)) return false;
-  workers_received = out.workers_received;
-  total_workers = out.total_workers;
-  return out.ready;
+  const std::string encoded = req.encode();
+  const int n = num_shards();
+  bool ready = true;
+  for (int s = 0; s < n && ready; ++s) {  // each answer is long-polled by its server
+    std::string resp;
+    Status st = shard_channel(s).call("/parameter_server.ParameterServer/CheckSyncStatus", encoded,
+                                      resp, 5000);
+    pb::SyncStatusResponse out;
+    if (!st.ok() || !out.decode(resp)) return false;
+    workers_received = s == 0 ? out.workers_received
+                              : std::min(workers_received, out.workers_received);
+    total_workers = out.total_workers;
+    ready = out.ready;
+  }
+  return ready;
 }
 
 bool Worker::load_checkpoint_from_server(const std::string& checkpoint_path, int32_t& epoch) {
   if (!initialized_ && ps_address_.empty() && !discover_parameter_server()) return false;
+  if (opt_.shards > 1 && shard_addrs_.empty() && !discover_shards()) return false;
   pb::LoadCheckpointRequest req;
-  req.path = checkpoint_path;
-  std::string resp;
-  Status s = ps_channel().call("/parameter_server.ParameterServer/LoadCheckpoint", req.encode(),
-                               resp, 60000);
-  pb::LoadCheckpointResponse out;
-  if (!s.ok() || !out.decode(resp) || !out.success) return false;
-  epoch = out.epoch;  // the parameters now live in the server; the next pull returns them
+  req.path = checkpoint_path;  // every shard resolves it in its own working directory
+  const std::string encoded = req.encode();
+  std::vector<int32_t> epochs(static_cast<size_t>(num_shards()), 0);
+  const bool ok = for_each_shard([&](int sh) {
+    std::string resp;
+    Status s = shard_channel(sh).call("/parameter_server.ParameterServer/LoadCheckpoint", encoded,
+                                      resp, 60000);
+    pb::LoadCheckpointResponse out;
+    if (!s.ok() || !out.decode(resp) || !out.success) return false;
+    epochs[static_cast<size_t>(sh)] = out.epoch;
+    return true;
+  });
+  if (!ok) return false;
+  epoch = epochs[0];  // the parameters now live in the servers; the next pull returns them
   return true;
 }
 

@@ -48,6 +48,7 @@ struct WorkerOptions {
   double straggle_prob = 0.0;
   double straggle_factor = 1.0;
   uint64_t sim_seed = 0;
+  int shards = 0;                 // > 1: the model's tensors are split over this many PS shards
   bool trace = false;             // per-iteration pull / compute / push / wait times on stdout
 };
 
@@ -80,6 +81,11 @@ class Worker {
 
  private:
   bool discover_parameter_server();
+  bool discover_shards();
+  int num_shards() const { return shard_addrs_.empty() ? 1 : static_cast<int>(shard_addrs_.size()); }
+  grpc_lite::Channel& shard_channel(int s);
+  // run fn(shard) for every shard (in parallel when there are several); true iff all returned true
+  bool for_each_shard(const std::function<bool(int)>& fn);
   bool register_with_coordinator();
   bool query_with_retry(const std::function<bool()>& query, int max_retries = 5);
   void send_heartbeat();
@@ -104,6 +110,8 @@ class Worker {
   std::unique_ptr<grpc_lite::Channel> coord_hb_;  // heartbeats use their own connection
   std::unique_ptr<grpc_lite::Channel> ps_;
   std::string ps_channel_target_;
+  std::vector<std::string> shard_addrs_;                      // by shard id; empty = single server
+  std::vector<std::unique_ptr<grpc_lite::Channel>> shard_ch_;
   bool last_push_ok_ = false;
   uint64_t sim_rng_ = 0;
   std::function<std::vector<TensorLite>(const std::vector<TensorLite>&)> grad_fn_;

@@ -6,7 +6,9 @@
 // (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS), and for the straggler
 // benchmark --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N --quiet (simulated
 // compute time per iteration; no per-iteration log line, one summary line at the end), and
-// --trace (pull / compute / push / wait milliseconds of every iteration).
+// --trace (pull / compute / push / wait milliseconds of every iteration);
+// --shards=N: the model's tensors are split over the N parameter servers that registered with
+// --shard-id (tensor k on shard k % N); PSB_SHARDS.
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
@@ -35,6 +37,7 @@ int main(int argc, char** argv) {
   if (const char* e = std::getenv("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = std::getenv("PSB_HEARTBEAT_MS")) opt.heartbeat_ms = std::atoi(e);
   if (const char* e = std::getenv("PSB_SYNC_TIMEOUT_MS")) opt.sync_timeout_ms = std::atoi(e);
+  if (const char* e = std::getenv("PSB_SHARDS")) opt.shards = std::atoi(e);
   std::vector<std::string> pos;
   for (int i = 1; i < argc; ++i) {
     std::string a = argv[i], v;
@@ -48,6 +51,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "seed", v)) opt.sim_seed = std::strtoull(v.c_str(), nullptr, 10);
     else if (a == "--quiet") quiet = true;
     else if (a == "--trace") opt.trace = true;
+    else if (flag(a, "shards", v)) opt.shards = std::atoi(v.c_str());
     else if (a.rfind("--", 0) == 0 && a.size() > 2) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;

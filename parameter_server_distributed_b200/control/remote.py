@@ -40,7 +40,10 @@ class RemoteParameterServer:
 
     def __init__(self, coordinator: str, worker_id: int, *, address: str = "",
                  port: int = 0, hostname: Optional[str] = None, heartbeat_s: float = 5.0,
-                 rpc_timeout_s: float = 30.0, ps_address: Optional[str] = None):
+                 rpc_timeout_s: float = 30.0, ps_address: Optional[str] = None, shards: int = 0):
+        """``shards > 1``: the model is split over that many parameter servers, the ones started
+        with ``--shard-id=0..N-1 --coordinator=...`` (tensor k lives on shard k % N, as in the C++
+        worker's ``--shards=N``); their addresses come from the coordinator's shard map."""
         import grpc
         self.worker_id = int(worker_id)
         self.timeout = rpc_timeout_s
@@ -60,8 +63,18 @@ class RemoteParameterServer:
             # the reference coordinator answers host-only addresses with port 0
             ps_address = f"{where.address}:{where.port or 50051}"
         self.ps_address = ps_address
-        self._ps_ch = grpc.insecure_channel(ps_address, options=unlimited)
-        self.ps = protos.Stub(self._ps_ch, "parameter_server.ParameterServer")
+        if shards > 1:
+            addrs = self._discover_shards(shards)
+        else:
+            addrs = [ps_address]
+        self.shard_addresses = addrs
+        self._ps_chs = [grpc.insecure_channel(a, options=unlimited) for a in addrs]
+        self._stubs = [protos.Stub(ch, "parameter_server.ParameterServer") for ch in self._ps_chs]
+        self.ps = self._stubs[0]
+        self._pool = None
+        if len(addrs) > 1:
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(max_workers=len(addrs))
         self.status = IDLE
         self.evictions = 0
         self._stop = threading.Event()
@@ -69,6 +82,25 @@ class RemoteParameterServer:
         self._hb.start()
 
     # ------------------------------------------------------------------ plumbing
+    def _discover_shards(self, n: int, timeout_s: float = 30.0) -> List[str]:
+        ext = protos.Stub(self._coord_ch, "psb.CoordinatorExt")
+        end = time.monotonic() + timeout_s
+        while True:
+            sm = ext.GetShardMap(protos.msg("psb.ShardMapRequest")(), timeout=self.timeout)
+            found = {s.shard_id: s.address for s in sm.shards
+                     if 0 <= s.shard_id < n and not s.address.startswith("hbm://")}
+            if len(found) == n:
+                return [found[i] for i in range(n)]
+            if time.monotonic() >= end:
+                raise RuntimeError(f"{len(found)} of {n} parameter-server shards registered")
+            time.sleep(0.1)
+
+    def _each_shard(self, fn):
+        """[fn(shard_index, stub) for every shard], in parallel when there are several."""
+        if self._pool is None:
+            return [fn(0, self._stubs[0])]
+        return list(self._pool.map(lambda a: fn(*a), enumerate(self._stubs)))
+
     def _retry(self, fn: Callable, attempts: int = 5):
         """Exponential back-off like the reference's query_with_retry (src/worker.cpp:129-139)."""
         import grpc
@@ -97,7 +129,10 @@ class RemoteParameterServer:
         self._stop.set()
         self._hb.join(timeout=2)
         self._coord_ch.close()
-        self._ps_ch.close()
+        for ch in self._ps_chs:
+            ch.close()
+        if self._pool is not None:
+            self._pool.shutdown(wait=False)
 
     def __enter__(self):
         return self
@@ -108,30 +143,39 @@ class RemoteParameterServer:
     # ------------------------------------------------------------------ protocol
     def pull(self, iteration: int) -> Tuple[Dict[str, np.ndarray], bool]:
         """ServeParameters: ({name: fp32 array shaped like the server's tensor}, ready)."""
-        r = self.ps.ServeParameters(protos.msg("parameter_server.PullRequest")(
-            worker_id=self.worker_id, iteration=iteration), timeout=self.timeout)
+        req = protos.msg("parameter_server.PullRequest")(worker_id=self.worker_id,
+                                                         iteration=iteration)
+        resps = self._each_shard(lambda i, stub: stub.ServeParameters(req, timeout=self.timeout))
+        n = len(resps)
+        total = sum(len(r.parameters) for r in resps)
         out = {}
-        for t in r.parameters:
+        for k in range(total):  # tensor k is shard (k % n)'s tensor k // n
+            t = resps[k % n].parameters[k // n]
             a = np.asarray(t.data, dtype=np.float32)
             out[t.name] = a.reshape(tuple(t.shape)) if len(t.shape) else a
-        return out, bool(r.ready)
+        return out, all(bool(r.ready) for r in resps)
 
     def push(self, iteration: int, grads: Iterable[Tuple[str, np.ndarray]]) -> Tuple[bool, int, int]:
         """ReceiveGradients: (aggregation_complete, workers_received, total_workers).  Order
         matters: the server matches tensors by position and checks name + shape."""
-        req = protos.msg("parameter_server.GradientUpdate")(worker_id=self.worker_id,
-                                                            iteration=iteration)
-        for name, g in grads:
+        n = len(self._stubs)
+        reqs = [protos.msg("parameter_server.GradientUpdate")(worker_id=self.worker_id,
+                                                              iteration=iteration)
+                for _ in range(n)]
+        for k, (name, g) in enumerate(grads):
             g = np.ascontiguousarray(g, dtype=np.float32)
-            t = req.gradients.add()
+            t = reqs[k % n].gradients.add()
             t.name = name
             t.shape.extend(g.shape)
             t.dtype = 0
             t.data.extend(g.reshape(-1))
-        r = self._retry(lambda: self.ps.ReceiveGradients(req, timeout=self.timeout), attempts=3)
-        if not r.success:
-            raise RuntimeError(f"push refused: {r.message}")
-        return bool(r.aggregation_complete), r.workers_received, r.total_workers
+        rs = self._each_shard(lambda i, stub: self._retry(
+            lambda: stub.ReceiveGradients(reqs[i], timeout=self.timeout), attempts=3))
+        for r in rs:
+            if not r.success:
+                raise RuntimeError(f"push refused: {r.message}")
+        return (all(bool(r.aggregation_complete) for r in rs),
+                min(r.workers_received for r in rs), rs[0].total_workers)
 
     def wait(self, iteration: int, timeout_s: float = 10.0, poll_s: float = 0.0) -> bool:
         """CheckSyncStatus until the iteration is aggregated.  This framework's server holds a
@@ -140,7 +184,8 @@ class RemoteParameterServer:
         Req = protos.msg("parameter_server.SyncStatusRequest")
         end = time.monotonic() + timeout_s
         while True:
-            if self.ps.CheckSyncStatus(Req(iteration=iteration), timeout=self.timeout).ready:
+            if all(stub.CheckSyncStatus(Req(iteration=iteration), timeout=self.timeout).ready
+                   for stub in self._stubs):
                 return True
             if time.monotonic() >= end:
                 return False
@@ -148,18 +193,20 @@ class RemoteParameterServer:
                 time.sleep(poll_s)
 
     def save_checkpoint(self, epoch: int, path: str = "") -> str:
-        r = self.ps.SaveCheckpoint(protos.msg("parameter_server.SaveCheckpointRequest")(
-            epoch=epoch, path=path), timeout=max(self.timeout, 120))
-        if not r.success:
-            raise RuntimeError(r.message)
-        return r.checkpoint_path
+        req = protos.msg("parameter_server.SaveCheckpointRequest")(epoch=epoch, path=path)
+        rs = self._each_shard(lambda i, stub: stub.SaveCheckpoint(req, timeout=max(self.timeout, 120)))
+        for r in rs:  # every shard writes `path` relative to its own working directory
+            if not r.success:
+                raise RuntimeError(r.message)
+        return rs[0].checkpoint_path
 
     def load_checkpoint(self, path: str) -> int:
-        r = self.ps.LoadCheckpoint(protos.msg("parameter_server.LoadCheckpointRequest")(path=path),
-                                   timeout=max(self.timeout, 120))
-        if not r.success:
-            raise RuntimeError(r.message)
-        return r.epoch
+        req = protos.msg("parameter_server.LoadCheckpointRequest")(path=path)
+        rs = self._each_shard(lambda i, stub: stub.LoadCheckpoint(req, timeout=max(self.timeout, 120)))
+        for r in rs:
+            if not r.success:
+                raise RuntimeError(r.message)
+        return rs[0].epoch
 
     def live_workers(self) -> List[int]:
         r = self.coord.ListWorkers(protos.msg("coordinator.ListWorkersRequest")(),

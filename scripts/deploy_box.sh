@@ -6,6 +6,7 @@
 # workers, each through its start_*.sh script with logs and pidfiles under $RUN_DIR.
 #
 #   WORKER_COUNT=3 ITERATIONS=100 CHECKPOINT_INTERVAL=10 scripts/deploy_box.sh
+#   PS_SHARDS=2 WORKER_COUNT=4 scripts/deploy_box.sh   # model split over 2 parameter servers
 #   MODE=gpu GPUS=8 scripts/deploy_box.sh [script.py args...]   # HBM data plane: torchrun, 1 rank/GPU
 set -euo pipefail
 
@@ -17,6 +18,7 @@ CHECKPOINT_INTERVAL="${CHECKPOINT_INTERVAL:-10}"
 COORDINATOR_PORT="${COORDINATOR_PORT:-50052}"
 PS_PORT="${PS_PORT:-50051}"
 MODE="${MODE:-host}"
+PS_SHARDS="${PS_SHARDS:-1}"
 mkdir -p "$RUN_DIR"
 
 echo "[1/4] building"
@@ -48,12 +50,28 @@ echo "[2/4] starting coordinator on :$COORDINATOR_PORT"
 COORDINATOR_PORT="$COORDINATOR_PORT" PS_ADDRESS="127.0.0.1:$PS_PORT" BINARY_PATH="$BIN/coordinator" \
   LOG_FILE="$RUN_DIR/coordinator.log" PID_FILE="$RUN_DIR/coordinator.pid" \
   bash "$ROOT/scripts/start_coordinator.sh"
+if [ "$PS_SHARDS" -gt 1 ]; then
+  echo "[3/4] starting $PS_SHARDS parameter-server shards on :$PS_PORT, :$((PS_PORT + 10)), .. for $WORKER_COUNT workers"
+  for s in $(seq 0 $((PS_SHARDS - 1))); do
+    mkdir -p "$RUN_DIR/shard_$s"   # every shard checkpoints into its own directory
+    # shard s listens on PS_PORT + 10 s (PS_PORT + 1 is the coordinator's default port)
+    SHARD_PORT="$((PS_PORT + 10 * s))"
+    PS_PORT="$SHARD_PORT" TOTAL_WORKERS="$WORKER_COUNT" CHECKPOINT_INTERVAL="$CHECKPOINT_INTERVAL" \
+      COORDINATOR_ADDR="127.0.0.1:$COORDINATOR_PORT" SHARD_ID="$s" \
+      ADVERTISE_ADDR="127.0.0.1:$SHARD_PORT" \
+      BINARY_PATH="$BIN/parameter_server" LOG_FILE="$RUN_DIR/parameter_server_$s.log" \
+      PID_FILE="$RUN_DIR/parameter_server_$s.pid" PS_WORKDIR="$RUN_DIR/shard_$s" \
+      PS_FLAGS="${PS_FLAGS:-}" bash "$ROOT/scripts/start_parameter_server.sh"
+  done
+  WORKER_FLAGS="${WORKER_FLAGS:-} --shards=$PS_SHARDS"
+else
 echo "[3/4] starting parameter server on :$PS_PORT for $WORKER_COUNT workers"
 PS_PORT="$PS_PORT" TOTAL_WORKERS="$WORKER_COUNT" CHECKPOINT_INTERVAL="$CHECKPOINT_INTERVAL" \
   COORDINATOR_ADDR="127.0.0.1:$COORDINATOR_PORT" \
   BINARY_PATH="$BIN/parameter_server" LOG_FILE="$RUN_DIR/parameter_server.log" \
   PID_FILE="$RUN_DIR/parameter_server.pid" PS_WORKDIR="$RUN_DIR" PS_FLAGS="${PS_FLAGS:-}" \
   bash "$ROOT/scripts/start_parameter_server.sh"
+fi
 sleep 0.5
 echo "[4/4] starting $WORKER_COUNT workers x $ITERATIONS iterations"
 for i in $(seq 0 $((WORKER_COUNT - 1))); do

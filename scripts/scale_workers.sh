@@ -68,6 +68,7 @@ case "${1:-status}" in
   stop)
     for id in $(workers); do stop_pid "$RUN_DIR/worker_$id.pid"; done
     stop_pid "$RUN_DIR/parameter_server.pid"; stop_pid "$RUN_DIR/coordinator.pid"
+    for f in "$RUN_DIR"/parameter_server_*.pid; do [ -f "$f" ] && stop_pid "$f"; done  # PS_SHARDS > 1
     echo "stopped" ;;
   *) echo "usage: $0 up N | down N | status | stop"; exit 2 ;;
 esac

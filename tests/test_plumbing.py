@@ -270,3 +270,105 @@ def test_multi_megabyte_model_through_cpp_worker_and_server(tmp_path):
             w.stop()
         ps.stop()
         co.stop()
+
+
+def test_cpp_workers_over_two_parameter_server_shards(tmp_path):
+    """worker_main --shards=2: three tensors resumed from per-shard checkpoints (a, c on shard 0;
+    b on shard 1), two C++ workers x 4 iterations; every tensor ends at init - 4 x 0.01 and the
+    workers report done=true throughout (each iteration needs both shards' barriers)."""
+    from parameter_server_distributed_b200.utils.checkpoint import write_reference_file
+    rng = np.random.default_rng(11)
+    tensors = [("a", (64, 32)), ("b", (300,)), ("c", (8, 8, 4))]
+    init = {n: rng.standard_normal(int(np.prod(s))).astype(np.float32) for n, s in tensors}
+    co_port = free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", "127.0.0.1:1"], str(tmp_path),
+              str(tmp_path / "co.log"))
+    procs, ports = [], []
+    try:
+        assert wait_port(co_port)
+        for sid in range(2):
+            d = tmp_path / f"s{sid}"
+            d.mkdir()
+            mine = [(n, s, init[n]) for k, (n, s) in enumerate(tensors) if k % 2 == sid]
+            write_reference_file(str(d / "init.ckpt"), 0, 0, mine)
+            port = free_port()
+            ports.append(port)
+            procs.append(Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "2", "0",
+                               "--resume=init.ckpt", f"--coordinator=127.0.0.1:{co_port}",
+                               f"--shard-id={sid}", "--membership-poll-ms=100"], str(d),
+                              str(d / "ps.log")))
+        for p in ports:
+            assert wait_port(p)
+        workers = [Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(w), "4", "--shards=2",
+                         "--heartbeat-ms=200"], str(tmp_path), str(tmp_path / f"w{w}.log"))
+                   for w in range(2)]
+        procs += workers
+        for w in workers:
+            assert w.p.wait(timeout=60) == 0
+            assert w.output().count("done=true") == 4, w.output()[-300:]
+        got = {}
+        for port in ports:
+            stub = protos.Stub(grpc.insecure_channel(f"127.0.0.1:{port}"),
+                               "parameter_server.ParameterServer")
+            r = stub.ServeParameters(protos.msg("parameter_server.PullRequest")(worker_id=0, iteration=9),
+                                     timeout=10)
+            for t in r.parameters:
+                got[t.name] = (tuple(t.shape), np.asarray(t.data, dtype=np.float32))
+        assert sorted(got) == ["a", "b", "c"]
+        for n, s in tensors:
+            exp = init[n]
+            for _ in range(4):
+                exp = exp - np.float32(0.01)
+            assert got[n][0] == s
+            np.testing.assert_array_equal(got[n][1], exp)
+    finally:
+        for p in procs:
+            p.stop()
+        co.stop()
+
+
+def _wait_for(pred, timeout):
+    end = time.time() + timeout
+    while time.time() < end:
+        if pred():
+            return True
+        time.sleep(0.1)
+    return pred()
+
+
+@pytest.mark.parametrize("shards", [1, 2])
+def test_deploy_box_and_scale_workers_scripts(tmp_path, shards):
+    """S5 / S6 on one box: deploy_box.sh (host mode; PS_SHARDS=2 splits the model over two
+    parameter servers), then scale_workers.sh up 3 — checkpoint, server restart with the new
+    worker count, the first new worker reloads the checkpoint — and stop."""
+    run = tmp_path / "run"
+    co_port = free_port()
+    ps_port = free_port()
+    env = dict(os.environ, RUN_DIR=str(run), COORDINATOR_PORT=str(co_port), PS_PORT=str(ps_port),
+               WORKER_COUNT="2", ITERATIONS="30", CHECKPOINT_INTERVAL="0", PS_SHARDS=str(shards))
+    r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "deploy_box.sh")], env=env,
+                       capture_output=True, text=True, timeout=300)
+    try:
+        assert r.returncode == 0, r.stdout[-500:] + r.stderr[-500:]
+
+        def done(wid, n):
+            p = run / f"worker_{wid}.log"
+            return p.exists() and p.read_text().count("done=true") >= n
+
+        assert _wait_for(lambda: done(0, 30) and done(1, 30), 60), (run / "worker_0.log").read_text()[-300:]
+        if shards == 2:
+            assert "registered as shard 1" in (run / "parameter_server_1.log").read_text()
+            return
+        env["ITERATIONS"] = "10"
+        r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "scale_workers.sh"), "up", "3"],
+                           env=env, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0 and "scaled to 3 workers" in r.stdout, r.stdout + r.stderr
+        assert (run / "scale.ckpt").exists()
+        assert _wait_for(lambda: all(done(w, 10) for w in range(3)), 60)
+        assert "loaded checkpoint from scale.ckpt" in (run / "worker_0.log").read_text()
+        st = subprocess.run(["bash", os.path.join(ROOT, "scripts", "scale_workers.sh"), "status"],
+                            env=env, capture_output=True, text=True, timeout=30)
+        assert "parameter_server: running" in st.stdout and "coordinator: running" in st.stdout
+    finally:
+        subprocess.run(["bash", os.path.join(ROOT, "scripts", "scale_workers.sh"), "stop"], env=env,
+                       capture_output=True, text=True, timeout=60)

@@ -120,3 +120,83 @@ def test_checkpoint_round_trip_through_the_python_client(plane):
         for k in before:
             np.testing.assert_array_equal(before[k], after[k])
         assert before["0.weight"].shape == (16, 8)
+
+
+# ------------------------------------------------------------------ host-plane sharding
+@pytest.fixture()
+def sharded_plane(tmp_path):
+    """coordinator + two parameter servers that register as shards 0 and 1 (own working dirs)."""
+    co_port = free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", "127.0.0.1:1"], str(tmp_path),
+              str(tmp_path / "co.log"))
+    assert wait_port(co_port)
+    servers, ports = [], []
+    for sid in range(2):
+        d = tmp_path / f"shard{sid}"
+        d.mkdir()
+        port = free_port()
+        ports.append(port)
+        servers.append(Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "2", "0",
+                             "--optimizer=sgd", "--lr=0.1", f"--coordinator=127.0.0.1:{co_port}",
+                             f"--shard-id={sid}", "--membership-poll-ms=100"], str(d),
+                            str(d / "ps.log")))
+    for p in ports:
+        assert wait_port(p)
+    yield f"127.0.0.1:{co_port}", ports, servers, tmp_path
+    for s in servers:
+        s.stop()
+    co.stop()
+
+
+def test_model_split_over_two_parameter_server_shards(sharded_plane):
+    """tensor k lives on shard k % 2; two Python workers train through both shards and end
+    exactly where the single-process oracle ends; each shard holds (and checkpoints) its half."""
+    from parameter_server_distributed_b200.utils.checkpoint import read_reference_file
+    coord, ports, servers, tmp = sharded_plane
+    steps = 6
+    out, errs = {}, []
+    models = [_model() for _ in range(2)]
+
+    def work(w):
+        try:
+            with psd.RemoteParameterServer(coord, w, heartbeat_s=0.2, shards=2) as ps:
+                assert ps.shard_addresses == [f"127.0.0.1:{p}" for p in ports]
+                tr = psd.RemoteTrainer(models[w], _loss, ps)
+                for x, y in _batches(w, steps):
+                    tr.step(x, y)
+                tr.sync_model()
+                if w == 0:
+                    ps.save_checkpoint(3, "half.ckpt")
+                out[w] = ([p.detach().clone() for p in tr.params], tr.skipped)
+        except BaseException as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    ts = [threading.Thread(target=work, args=(w,)) for w in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    assert not errs, errs
+    oracle = _model()
+    params = list(oracle.parameters())
+    b = [_batches(w, steps) for w in range(2)]
+    for s in range(steps):
+        gs = []
+        for w in range(2):
+            for p in params:
+                p.grad = None
+            _loss(oracle, *b[w][s]).backward()
+            gs.append([p.grad.clone() for p in params])
+        with torch.no_grad():
+            for i, p in enumerate(params):
+                p -= 0.1 * (gs[0][i] + gs[1][i]) / 2
+    for w in range(2):
+        got, skipped = out[w]
+        assert skipped == 0
+        for a, e in zip(got, params):
+            assert torch.allclose(a, e, atol=2e-6), (a - e).abs().max()
+    names = [[t[0] for t in read_reference_file(str(tmp / f"shard{s}" / "half.ckpt"))[2]]
+             for s in range(2)]
+    assert names == [["0.weight", "2.weight"], ["0.bias", "2.bias"]]
+    for s in servers:
+        assert "registered as shard" in s.output()
