@@ -4,6 +4,7 @@
 // Also the program the TSAN / ASAN builds run (`make tsan && build/bin-thread/psb_selftest`).
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <fstream>
 #include <iostream>
 #include <thread>
@@ -60,9 +61,114 @@ static int hpack_rfc_vectors() {
   return 0;
 }
 
+// The threaded aggregation / optimizer loops of ps_core.cpp give the same bits for every thread
+// count: three workers push 300 k-element tensors (above the parallel grain) for three
+// iterations, once with 1 thread and once with 5, for every optimizer.
+static int threads_do_not_change_results() {
+  using namespace psb;
+  for (const char* kind : {"sgd", "momentum", "adam", "adamw"}) {
+    std::vector<std::vector<HostTensor>> results;
+    for (int threads : {1, 5}) {
+      PsOptions opt;
+      opt.optimizer = kind;
+      opt.lr = 0.01f;
+      opt.weight_decay = 0.1f;
+      opt.threads = threads;
+      ParameterServerCore core(3, opt);
+      uint32_t seed = 12345;
+      for (int it = 0; it < 4; ++it) {
+        for (int w = 0; w < 3; ++w) {
+          std::vector<HostTensor> g(2);
+          g[0].name = "big", g[0].shape = {300, 1000};
+          g[1].name = "small", g[1].shape = {17};
+          g[0].data.resize(300000), g[1].data.resize(17);
+          for (auto& t : g)
+            for (auto& x : t.data) {
+              seed = seed * 1664525u + 1013904223u;
+              x = (static_cast<int32_t>(seed >> 9) - (1 << 22)) * (1.0f / (1 << 22));
+            }
+          const bool done = core.receive_gradients(w, it, std::move(g));
+          CHECK(done == (w == 2));
+        }
+      }
+      results.push_back(core.serve_parameters(0));
+    }
+    CHECK(results[0].size() == 2 && results[1].size() == 2);
+    for (size_t i = 0; i < 2; ++i)
+      CHECK(results[0][i].data.size() == results[1][i].data.size() &&
+            memcmp(results[0][i].data.data(), results[1][i].data.data(),
+                   results[0][i].data.size() * sizeof(float)) == 0);
+  }
+  return 0;
+}
+
+// Two parameter servers register as shards 0 and 1; two workers with shards = 2 split a
+// three-tensor model over them (tensor k on shard k % 2) and run five iterations.
+static int sharded_parameter_servers() {
+  using namespace psb;
+  CoordinatorService coord("127.0.0.1", 1, 100, 30);
+  const int coord_port = coord.listen("127.0.0.1:0");
+  CHECK(coord_port > 0);
+  coord.start();
+  const std::string caddr = "127.0.0.1:" + std::to_string(coord_port);
+  ParameterServerService s0(2, 0, PsOptions()), s1(2, 0, PsOptions());
+  const int p0 = s0.listen("127.0.0.1:0"), p1 = s1.listen("127.0.0.1:0");
+  CHECK(p0 > 0 && p1 > 0);
+  s0.start();
+  s1.start();
+  s0.announce_shard(caddr, 0, "127.0.0.1:" + std::to_string(p0), 50);
+  s1.announce_shard(caddr, 1, "127.0.0.1:" + std::to_string(p1), 50);
+  auto model = [](float v) {
+    std::vector<HostTensor> m(3);
+    const char* names[3] = {"a", "b", "c"};
+    for (int k = 0; k < 3; ++k) {
+      m[k].name = names[k];
+      m[k].shape = {4 + k};
+      m[k].data.assign(static_cast<size_t>(4 + k), v + k);
+    }
+    return m;
+  };
+  {  // tensors a, c on shard 0; b on shard 1
+    std::vector<HostTensor> m = model(1.0f);
+    s0.core().initialize_parameters({m[0], m[2]});
+    s1.core().initialize_parameters({m[1]});
+  }
+  bool ok[2] = {true, true};
+  auto run = [&](int id) {
+    WorkerOptions wo;
+    wo.heartbeat_ms = 50;
+    wo.shards = 2;
+    Worker w(id, caddr, "", 0, wo);
+    if (!w.initialize()) {
+      ok[id] = false;
+      return;
+    }
+    bool ready = false;
+    std::vector<TensorLite> pulled = w.pull_parameters(0, &ready);
+    ok[id] = pulled.size() == 3 && pulled[0].name == "a" && pulled[1].name == "b" &&
+             pulled[2].name == "c" && pulled[1].data.size() == 5;
+    for (int it = 0; it < 5; ++it) ok[id] = ok[id] && w.run_iteration(it);
+  };
+  std::thread t0(run, 0), t1(run, 1);
+  t0.join();
+  t1.join();
+  CHECK(ok[0] && ok[1]);
+  auto a = s0.core().serve_parameters(0), b = s1.core().serve_parameters(0);
+  CHECK(a.size() == 2 && b.size() == 1 && a[1].name == "c" && b[0].name == "b");
+  for (float v : a[0].data) CHECK(std::fabs(v - (1.0f - 0.05f)) < 1e-6f);
+  for (float v : b[0].data) CHECK(std::fabs(v - (2.0f - 0.05f)) < 1e-6f);
+  for (float v : a[1].data) CHECK(std::fabs(v - (3.0f - 0.05f)) < 1e-6f);
+  coord.shutdown();
+  s0.shutdown();
+  s1.shutdown();
+  return 0;
+}
+
 int main() {
   using namespace psb;
   if (hpack_rfc_vectors() != 0) return 1;
+  if (threads_do_not_change_results() != 0) return 1;
+  if (sharded_parameter_servers() != 0) return 1;
   ParameterServerService ps(2, 0, PsOptions());
   int ps_port = ps.listen("127.0.0.1:0");
   CHECK(ps_port > 0);
