@@ -152,6 +152,11 @@ std::shared_ptr<const std::string> ParameterServerService::encoded_parameters() 
     }
     *bytes = std::move(w.buf);
   });
+  static const bool keep = [] {  // PSB_SERVE_CACHE=0: do not hold a second copy of the model
+    const char* e = std::getenv("PSB_SERVE_CACHE");
+    return !(e && e[0] == '0');
+  }();
+  if (!keep) return bytes;
   serve_cache_ = std::move(bytes);
   serve_cache_version_ = version;
   return serve_cache_;
