@@ -7,6 +7,7 @@
 #
 #   WORKER_COUNT=3 ITERATIONS=100 CHECKPOINT_INTERVAL=10 scripts/deploy_box.sh
 #   PS_SHARDS=2 WORKER_COUNT=4 scripts/deploy_box.sh   # model split over 2 parameter servers
+#   PS_SHARDS=8 PS_ON_GPUS=1 scripts/deploy_box.sh     # ... shard s keeps its weights in the HBM of GPU s
 #   MODE=gpu GPUS=8 scripts/deploy_box.sh [script.py args...]   # HBM data plane: torchrun, 1 rank/GPU
 set -euo pipefail
 
@@ -61,7 +62,8 @@ if [ "$PS_SHARDS" -gt 1 ]; then
       ADVERTISE_ADDR="127.0.0.1:$SHARD_PORT" \
       BINARY_PATH="$BIN/parameter_server" LOG_FILE="$RUN_DIR/parameter_server_$s.log" \
       PID_FILE="$RUN_DIR/parameter_server_$s.pid" PS_WORKDIR="$RUN_DIR/shard_$s" \
-      PS_FLAGS="${PS_FLAGS:-}" bash "$ROOT/scripts/start_parameter_server.sh"
+      PS_FLAGS="${PS_FLAGS:-}$([ "${PS_ON_GPUS:-0}" = 1 ] && echo " --device=$s")" \
+      bash "$ROOT/scripts/start_parameter_server.sh"
   done
   WORKER_FLAGS="${WORKER_FLAGS:-} --shards=$PS_SHARDS"
 else
