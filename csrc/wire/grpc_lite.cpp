@@ -99,7 +99,11 @@ class HandlerPool : public std::enable_shared_from_this<HandlerPool> {
   void submit(std::function<void()> fn) {
     std::unique_lock<std::mutex> lk(mu_);
     q_.push_back(std::move(fn));
-    if (idle_ > 0) {
+    // One thread per queued task: a task may block until a LATER task has run (two Barrier
+    // calls of the same barrier), so it must never wait behind another one.  An idle thread
+    // that was notified is still counted in idle_ until it wakes up — hence the comparison
+    // with the queue length instead of `idle_ > 0`.
+    if (q_.size() <= static_cast<size_t>(idle_)) {
       lk.unlock();
       cv_.notify_one();
       return;

@@ -186,3 +186,34 @@ def test_garbage_does_not_take_the_server_down(tmp_path):
         assert still_serves(port)
     finally:
         co.stop()
+
+
+def test_burst_of_interdependent_calls_after_the_pool_has_idle_threads(tmp_path):
+    """40 Barrier calls of ONE barrier (expected = 40) in a single write, on a server whose
+    handler pool already has idle threads: every call needs its own thread at the same time —
+    a request queued behind another one would deadlock the barrier until its timeout."""
+    co, port = coordinator(tmp_path)
+    try:
+        for _ in range(3):
+            assert still_serves(port)  # leaves idle pooled threads behind
+        s = connect(port)
+        hb = request_headers("/psb.CoordinatorExt/Barrier")
+        out = b""
+        k = 40
+        for i in range(k):
+            sid = 1 + 2 * i
+            body = grpc_body(M("psb.BarrierRequest")(name="all", worker_id=i, generation=0,
+                                                     expected=k, timeout_ms=6000))
+            out += frame(HEADERS, 0x4, sid, hb) + frame(DATA, 0x1, sid, body)
+        t0 = time.time()
+        s.sendall(out)
+        fr = read_frames(s, lambda f: sum(t == HEADERS and fl & 1 for t, fl, _, _ in f) >= k,
+                         timeout=12)
+        dt = time.time() - t0
+        bodies = [p for t, _, _, p in fr if t == DATA and len(p) >= 5]
+        released = [M("psb.BarrierResponse").FromString(p[5:]).released for p in bodies]
+        assert len(released) == k and all(released), (len(released), sum(released))
+        assert dt < 4.0, f"the barrier opened only after {dt:.1f}s"
+        s.close()
+    finally:
+        co.stop()
