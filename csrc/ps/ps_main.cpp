@@ -31,7 +31,27 @@ static bool flag(const std::string& arg, const char* key, std::string& val) {
   return true;
 }
 
+static const char kUsage[] =
+    "usage: parameter_server [listen=0.0.0.0:50051] [total_workers=2] [checkpoint_interval=10] [flags]\n"
+    "  --mode=sync|async|ssp      barrier per iteration | apply every push | bounded staleness\n"
+    "  --staleness=N              SSP bound (clocks a worker may run ahead)\n"
+    "  --optimizer=sgd|momentum|adam|adamw  --lr=F --momentum=F --beta1=F --beta2=F --eps=F\n"
+    "  --weight-decay=F           server-side update (default: sgd, lr 1 = the reference's p -= mean)\n"
+    "  --device=N                 keep master weights and optimizer state in the HBM of GPU N\n"
+    "  --threads=N                host threads for aggregation / update of large tensors\n"
+    "  --coordinator=host:port    follow the worker registry: an evicted worker stops blocking\n"
+    "  --membership-poll-ms=N     ... polled this often (1000)\n"
+    "  --shard-id=I [--advertise=host:port]  one of several servers; registers in the shard map\n"
+    "  --resume=PATH|latest       load a checkpoint before serving\n"
+    "  --long-poll-ms=N           hold a 'not ready' status answer up to N ms (25)\n"
+    "  Every flag has a PSB_* environment twin (PSB_MODE, PSB_OPTIMIZER, ...).\n";
+
 int main(int argc, char** argv) {
+  for (int i = 1; i < argc; ++i)
+    if (!std::strcmp(argv[i], "--help") || !std::strcmp(argv[i], "-h")) {
+      std::cout << kUsage;
+      return 0;
+    }
   psb::retain_freed_memory();
   std::string listen = "0.0.0.0:50051";
   int total_workers = 2, checkpoint_interval = 10;

@@ -11,6 +11,7 @@
 // --shard-id (tensor k on shard k % N); PSB_SHARDS.
 #include <chrono>
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 #include <string>
 #include <vector>
@@ -25,7 +26,23 @@ static bool flag(const std::string& arg, const char* key, std::string& val) {
   return true;
 }
 
+static const char kUsage[] =
+    "usage: worker_main [coordinator=localhost:50052] [worker_id=0] [iterations=1] [worker_addr]\n"
+    "                   [worker_port=0] [checkpoint_path] [flags]\n"
+    "  --mode=sync|async|ssp   wait for the barrier | never wait | wait at the staleness gate\n"
+    "  --shards=N              the model's tensors are split over N parameter servers\n"
+    "  --device=N              synthetic gradients are filled on GPU N\n"
+    "  --heartbeat-ms=N (5000) --sync-timeout-ms=N (10000)\n"
+    "  --trace                 pull / compute / push / wait milliseconds of every iteration\n"
+    "  --quiet                 no per-iteration line, one summary line at the end\n"
+    "  --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N   simulated compute time\n";
+
 int main(int argc, char** argv) {
+  for (int i = 1; i < argc; ++i)
+    if (!std::strcmp(argv[i], "--help") || !std::strcmp(argv[i], "-h")) {
+      std::cout << kUsage;
+      return 0;
+    }
   psb::retain_freed_memory();
   std::string coordinator_addr = "localhost:50052";
   int worker_id = 0, iterations = 1;

@@ -372,3 +372,18 @@ def test_deploy_box_and_scale_workers_scripts(tmp_path, shards):
     finally:
         subprocess.run(["bash", os.path.join(ROOT, "scripts", "scale_workers.sh"), "stop"], env=env,
                        capture_output=True, text=True, timeout=60)
+
+
+def test_binaries_explain_themselves():
+    """--help prints the positional contract of the reference binaries plus the extension flags
+    (the reference has no --help: SURVEY §5.6) and exits 0 without starting anything."""
+    for exe, words in (("coordinator", ["usage: coordinator", "PSB_STALE_TIMEOUT_S"]),
+                       ("parameter_server", ["total_workers=2", "--resume=PATH|latest", "--shard-id"]),
+                       ("worker_main", ["iterations=1", "--shards=N", "--trace"])):
+        r = subprocess.run([f"{BIN}/{exe}", "--help"], capture_output=True, text=True, timeout=10)
+        assert r.returncode == 0
+        for w in words:
+            assert w in r.stdout, (exe, w)
+    r = subprocess.run([f"{BIN}/parameter_server", "127.0.0.1:1", "2", "0", "--no-such-flag=1"],
+                       capture_output=True, text=True, timeout=10)
+    assert r.returncode == 2 and "unknown flag" in r.stderr
