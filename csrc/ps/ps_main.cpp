@@ -44,6 +44,7 @@ static const char kUsage[] =
     "  --shard-id=I [--advertise=host:port]  one of several servers; registers in the shard map\n"
     "  --resume=PATH|latest       load a checkpoint before serving\n"
     "  --long-poll-ms=N           hold a 'not ready' status answer up to N ms (25)\n"
+    "  --stats-every-s=N          one JSON line of counters on stdout every N seconds\n"
     "  Every flag has a PSB_* environment twin (PSB_MODE, PSB_OPTIMIZER, ...).\n";
 
 int main(int argc, char** argv) {
@@ -93,6 +94,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "device", v)) opt.device = std::atoi(v.c_str());
     else if (flag(a, "long-poll-ms", v)) opt.long_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "threads", v)) opt.threads = std::atoi(v.c_str());
+    else if (flag(a, "stats-every-s", v)) setenv("PSB_STATS_EVERY_S", v.c_str(), 1);
     else if (flag(a, "coordinator", v)) coordinator = v;
     else if (flag(a, "membership-poll-ms", v)) membership_poll_ms = std::atoi(v.c_str());
     else if (flag(a, "resume", v)) resume = v;

@@ -46,8 +46,13 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     grads.reserve(in.gradients.size());
     for (auto& t : in.gradients) grads.push_back(from_pb(std::move(t)));  // one move, no copies
     pb::PushResponse out;
+    const auto t0 = std::chrono::steady_clock::now();
     out.aggregation_complete =
         core_.receive_gradients(in.worker_id, in.iteration, std::move(grads));
+    push_us_ += static_cast<uint64_t>(std::chrono::duration_cast<std::chrono::microseconds>(
+                                          std::chrono::steady_clock::now() - t0).count());
+    pushes_++;
+    bytes_in_ += req.size();
     out.success = true;
     out.message = "gradients received";
     out.iteration = in.iteration;
@@ -69,6 +74,8 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     }
     resp = out.encode();  // iteration + ready; the tensors follow from the shared encoding
     resp.shared_tail = encoded_parameters();
+    pulls_++;
+    bytes_out_ += resp.body.size() + resp.shared_tail->size();
     return Status{};
   });
   server_.add(base + "CheckSyncStatus", [this](std::string_view req, grpc_lite::Reply& resp) {
@@ -77,6 +84,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     pb::SyncStatusResponse out;
     out.iteration = in.iteration;
     out.ready = core_.wait_sync_status(in.iteration, out.workers_received);
+    status_polls_++;
     out.total_workers = core_.get_total_workers();
     resp = out.encode();
     return Status{};
@@ -246,6 +254,31 @@ void ParameterServerService::announce_shard(const std::string& coordinator_addre
   });
 }
 
+std::string ParameterServerService::stats_json() {
+  const uint64_t pushes = pushes_.load();
+  std::ostringstream o;
+  o << "{\"iteration\": " << core_.get_current_iteration() << ", \"version\": " << core_.version()
+    << ", \"total_workers\": " << core_.get_total_workers() << ", \"pushes\": " << pushes
+    << ", \"pulls\": " << pulls_.load() << ", \"status_polls\": " << status_polls_.load()
+    << ", \"bytes_in\": " << bytes_in_.load() << ", \"bytes_out\": " << bytes_out_.load()
+    << ", \"push_ms_mean\": " << (pushes ? push_us_.load() / 1000.0 / pushes : 0.0) << "}";
+  return o.str();
+}
+
+void ParameterServerService::log_stats_every(int every_s) {
+  if (every_s <= 0 || stats_thread_.joinable()) return;
+  stats_thread_ = std::thread([this, every_s] {
+    int waited = 0;
+    while (running_) {
+      std::this_thread::sleep_for(std::chrono::milliseconds(50));
+      waited += 50;
+      if (waited < every_s * 1000) continue;
+      waited = 0;
+      std::cout << "stats " << stats_json() << std::endl;
+    }
+  });
+}
+
 int ParameterServerService::listen(const std::string& address) { return server_.listen(address); }
 void ParameterServerService::serve_forever() { server_.serve_forever(); }
 void ParameterServerService::start() { server_.start(); }
@@ -256,6 +289,7 @@ void ParameterServerService::shutdown() {
     if (checkpoint_thread_.joinable()) checkpoint_thread_.join();
     if (membership_thread_.joinable()) membership_thread_.join();
     if (shard_thread_.joinable()) shard_thread_.join();
+    if (stats_thread_.joinable()) stats_thread_.join();
   }
 }
 
@@ -313,6 +347,7 @@ void run_server(const std::string& server_address, int total_workers, int checkp
   if (checkpoint_interval > 0)
     std::cout << "periodic checkpointing every " << checkpoint_interval << " iterations"
               << std::endl;
+  if (const char* e = std::getenv("PSB_STATS_EVERY_S")) svc.log_stats_every(std::atoi(e));
   if (shard_id >= 0) {
     if (coordinator_address.empty()) {
       std::cerr << "--shard-id needs --coordinator" << std::endl;

@@ -37,6 +37,11 @@ class ParameterServerService {
   void start();
   void shutdown();
   ParameterServerCore& core() { return core_; }
+  // Observability (the reference prints nothing but its start-up lines): one JSON
+  // line on stdout every `every_s` seconds — iteration, model version, live worker count, RPC
+  // and byte counters, mean time of a push inside the core.  --stats-every-s / PSB_STATS_EVERY_S.
+  void log_stats_every(int every_s);
+  std::string stats_json();
 
  private:
   void periodic_checkpoint();
@@ -57,6 +62,9 @@ class ParameterServerService {
   std::thread checkpoint_thread_;
   std::thread membership_thread_;
   std::thread shard_thread_;
+  std::thread stats_thread_;
+  std::atomic<uint64_t> pushes_{0}, pulls_{0}, status_polls_{0}, bytes_in_{0}, bytes_out_{0},
+      push_us_{0};
   int configured_workers_;
   std::atomic<bool> running_{true};
 };

@@ -387,3 +387,27 @@ def test_binaries_explain_themselves():
     r = subprocess.run([f"{BIN}/parameter_server", "127.0.0.1:1", "2", "0", "--no-such-flag=1"],
                        capture_output=True, text=True, timeout=10)
     assert r.returncode == 2 and "unknown flag" in r.stderr
+
+
+def test_parameter_server_stats_line(tmp_path):
+    """--stats-every-s: one JSON line of counters per period (the reference prints nothing after
+    its start-up lines)."""
+    import json
+    ps_port, co_port = free_port(), free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "1", "0", "--stats-every-s=1"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "50", "--quiet"],
+                           capture_output=True, text=True, timeout=60, cwd=tmp_path)
+        assert "done=50" in w.stdout
+        assert _wait_for(lambda: "stats {" in ps.output(), 5)
+        line = [l for l in ps.output().splitlines() if l.startswith("stats ")][-1]
+        st = json.loads(line[len("stats "):])
+        assert st["pushes"] == 50 and st["pulls"] == 50 and st["iteration"] == 49
+        assert st["bytes_in"] > 50 * 400 and st["total_workers"] == 1
+    finally:
+        ps.stop()
+        co.stop()
