@@ -403,9 +403,12 @@ def test_parameter_server_stats_line(tmp_path):
         w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "50", "--quiet"],
                            capture_output=True, text=True, timeout=60, cwd=tmp_path)
         assert "done=50" in w.stdout
-        assert _wait_for(lambda: "stats {" in ps.output(), 5)
-        line = [l for l in ps.output().splitlines() if l.startswith("stats ")][-1]
-        st = json.loads(line[len("stats "):])
+        def last():
+            lines = [l for l in ps.output().splitlines() if l.startswith("stats ")]
+            return json.loads(lines[-1][len("stats "):]) if lines else None
+
+        assert _wait_for(lambda: (last() or {}).get("pushes") == 50, 8), ps.output()[-300:]
+        st = last()
         assert st["pushes"] == 50 and st["pulls"] == 50 and st["iteration"] == 49
         assert st["bytes_in"] > 50 * 400 and st["total_workers"] == 1
     finally:
