@@ -47,3 +47,27 @@ def test_periodic_checkpoints_are_written_atomically(tmp_path):
     epoch, it = tr.load_checkpoint(path)
     assert (epoch, it) == (2, 5)  # written after step 6 = iteration index 5
     assert os.path.exists(path + ".psb")  # AdamW moments ride in the sidecar
+
+
+def test_learning_rate_schedule_through_set_lr():
+    """ps.set_lr between steps == the same schedule applied by torch.optim.SGD."""
+    cfg = MLPConfig(d_in=16, hidden=(32,), d_out=4)
+    torch.manual_seed(3)
+    model = MLP(cfg)
+    ref = MLP(cfg)
+    ref.load_state_dict(model.state_dict())
+    tr = psd.Trainer(model, mse_loss, _ctx(), psd.OptimConfig(kind="sgd", lr=0.2), bucket_mb=0.001)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.2)
+    gen = torch.Generator().manual_seed(4)
+    for step in range(5):
+        lr = 0.2 * (0.5 ** step)
+        tr.ps.set_lr(lr)
+        for g in opt.param_groups:
+            g["lr"] = lr
+        x, y = torch.randn(8, 16, generator=gen), torch.randn(8, 4, generator=gen)
+        tr.step(x, y)
+        opt.zero_grad()
+        mse_loss(ref(x), y).backward()
+        opt.step()
+    for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(a, b, atol=1e-6), n
