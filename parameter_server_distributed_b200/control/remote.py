@@ -35,6 +35,134 @@ from . import protos
 IDLE, TRAINING, CHECKPOINTING, ERROR = 0, 1, 2, 3
 
 
+# ---------------------------------------------------------------------- tensor messages in numpy
+# The protobuf runtime moves `repeated float` through Python one element at a time: a 109 M-
+# parameter model takes 17 s to pull and 33 s to push that way.  The two tensor-carrying messages
+# are therefore written and read here, with the float payload going through numpy as one block
+# (same bytes: proto3 packed floats are little-endian IEEE, proto/parameter_server.proto:13-24;
+# tests/test_remote_trainer.py checks both directions against the protobuf runtime).
+def _varint(v: int) -> bytes:
+    v &= (1 << 64) - 1  # negative int32 are sign-extended to 10 bytes, as protobuf does
+    out = bytearray()
+    while v >= 0x80:
+        out.append((v & 0x7F) | 0x80)
+        v >>= 7
+    out.append(v)
+    return bytes(out)
+
+
+def _read_varint(buf, pos: int) -> Tuple[int, int]:
+    v = shift = 0
+    while True:
+        b = buf[pos]
+        pos += 1
+        v |= (b & 0x7F) << shift
+        if not b & 0x80:
+            return v, pos
+        shift += 7
+        if shift > 63:
+            raise ValueError("varint too long")
+
+
+def _int32(v: int) -> int:
+    v &= 0xFFFFFFFF
+    return v - (1 << 32) if v & 0x80000000 else v
+
+
+def encode_gradient_update(worker_id: int, iteration: int,
+                           grads: Iterable[Tuple[str, np.ndarray]]) -> bytes:
+    """parameter_server.GradientUpdate{worker_id=1, iteration=2, repeated Tensor gradients=3}."""
+    parts: List[bytes] = []
+    if worker_id:
+        parts += [b"\x08", _varint(worker_id)]
+    if iteration:
+        parts += [b"\x10", _varint(iteration)]
+    for name, g in grads:
+        g = np.require(g, dtype="<f4", requirements="C")  # keeps 0-d arrays 0-d
+        t: List[bytes] = []
+        nm = name.encode()
+        if nm:
+            t += [b"\x0a", _varint(len(nm)), nm]
+        if g.ndim:
+            shape = b"".join(_varint(d) for d in g.shape)
+            t += [b"\x12", _varint(len(shape)), shape]
+        if g.size:
+            t += [b"\x1a", _varint(g.size * 4), g.reshape(-1).data.cast("B")]
+        parts += [b"\x1a", _varint(sum(len(x) for x in t))] + t
+    return b"".join(parts)
+
+
+def decode_parameter_update(buf: bytes) -> Tuple[int, bool, List[Tuple[str, Tuple[int, ...], np.ndarray]]]:
+    """parameter_server.ParameterUpdate -> (iteration, ready, [(name, shape, fp32 array)]).  The
+    arrays are read-only views into ``buf`` (no copy); unknown fields are skipped."""
+    mv = memoryview(buf)
+    iteration, ready, tensors = 0, False, []
+
+    def skip(wt: int, pos: int) -> int:
+        if wt == 0:
+            return _read_varint(mv, pos)[1]
+        if wt == 1:
+            return pos + 8
+        if wt == 2:
+            n, pos = _read_varint(mv, pos)
+            return pos + n
+        if wt == 5:
+            return pos + 4
+        raise ValueError(f"unsupported wire type {wt}")
+
+    pos, end = 0, len(mv)
+    while pos < end:
+        tag, pos = _read_varint(mv, pos)
+        field, wt = tag >> 3, tag & 7
+        if field == 1 and wt == 0:
+            v, pos = _read_varint(mv, pos)
+            iteration = _int32(v)
+        elif field == 3 and wt == 0:
+            v, pos = _read_varint(mv, pos)
+            ready = bool(v)
+        elif field == 2 and wt == 2:
+            n, pos = _read_varint(mv, pos)
+            tend = pos + n
+            name, shape, chunks = "", [], []
+            while pos < tend:
+                ttag, pos = _read_varint(mv, pos)
+                tf, twt = ttag >> 3, ttag & 7
+                if tf == 1 and twt == 2:
+                    k, pos = _read_varint(mv, pos)
+                    name = bytes(mv[pos:pos + k]).decode()
+                    pos += k
+                elif tf == 2 and twt == 2:
+                    k, pos = _read_varint(mv, pos)
+                    send = pos + k
+                    while pos < send:
+                        d, pos = _read_varint(mv, pos)
+                        shape.append(_int32(d))
+                elif tf == 2 and twt == 0:
+                    d, pos = _read_varint(mv, pos)
+                    shape.append(_int32(d))
+                elif tf == 3 and twt == 2:
+                    k, pos = _read_varint(mv, pos)
+                    if k % 4:
+                        raise ValueError("packed float field of odd length")
+                    chunks.append(np.frombuffer(mv, dtype="<f4", count=k // 4, offset=pos))
+                    pos += k
+                elif tf == 3 and twt == 5:
+                    chunks.append(np.frombuffer(mv, dtype="<f4", count=1, offset=pos))
+                    pos += 4
+                else:
+                    pos = skip(twt, pos)
+            if pos != tend:
+                raise ValueError("tensor message overruns its length")
+            data = chunks[0] if len(chunks) == 1 else (
+                np.concatenate(chunks) if chunks else np.zeros(0, dtype="<f4"))
+            tensors.append((name, tuple(shape), data))
+        else:
+            pos = skip(wt, pos)
+    if pos != end:
+        raise ValueError("message overruns its length")
+    return iteration, ready, tensors
+
+
 class RemoteParameterServer:
     """One worker's connection to the coordinator and the parameter server."""
 
@@ -70,6 +198,10 @@ class RemoteParameterServer:
         self.shard_addresses = addrs
         self._ps_chs = [grpc.insecure_channel(a, options=unlimited) for a in addrs]
         self._stubs = [protos.Stub(ch, "parameter_server.ParameterServer") for ch in self._ps_chs]
+        raw = dict(request_serializer=lambda b: b, response_deserializer=lambda b: b)
+        base = "/parameter_server.ParameterServer/"
+        self._raw_pull = [ch.unary_unary(base + "ServeParameters", **raw) for ch in self._ps_chs]
+        self._raw_push = [ch.unary_unary(base + "ReceiveGradients", **raw) for ch in self._ps_chs]
         self.ps = self._stubs[0]
         self._pool = None
         if len(addrs) > 1:
@@ -142,35 +274,31 @@ class RemoteParameterServer:
 
     # ------------------------------------------------------------------ protocol
     def pull(self, iteration: int) -> Tuple[Dict[str, np.ndarray], bool]:
-        """ServeParameters: ({name: fp32 array shaped like the server's tensor}, ready)."""
-        req = protos.msg("parameter_server.PullRequest")(worker_id=self.worker_id,
-                                                         iteration=iteration)
-        resps = self._each_shard(lambda i, stub: stub.ServeParameters(req, timeout=self.timeout))
+        """ServeParameters: ({name: fp32 array shaped like the server's tensor}, ready).  The
+        arrays are read-only views of the response buffers."""
+        req = protos.msg("parameter_server.PullRequest")(
+            worker_id=self.worker_id, iteration=iteration).SerializeToString()
+        resps = self._each_shard(lambda i, stub: decode_parameter_update(
+            self._raw_pull[i](req, timeout=self.timeout)))
         n = len(resps)
-        total = sum(len(r.parameters) for r in resps)
+        total = sum(len(r[2]) for r in resps)
         out = {}
         for k in range(total):  # tensor k is shard (k % n)'s tensor k // n
-            t = resps[k % n].parameters[k // n]
-            a = np.asarray(t.data, dtype=np.float32)
-            out[t.name] = a.reshape(tuple(t.shape)) if len(t.shape) else a
-        return out, all(bool(r.ready) for r in resps)
+            name, shape, a = resps[k % n][2][k // n]
+            out[name] = a.reshape(shape) if shape else a
+        return out, all(r[1] for r in resps)
 
     def push(self, iteration: int, grads: Iterable[Tuple[str, np.ndarray]]) -> Tuple[bool, int, int]:
         """ReceiveGradients: (aggregation_complete, workers_received, total_workers).  Order
         matters: the server matches tensors by position and checks name + shape."""
         n = len(self._stubs)
-        reqs = [protos.msg("parameter_server.GradientUpdate")(worker_id=self.worker_id,
-                                                              iteration=iteration)
-                for _ in range(n)]
-        for k, (name, g) in enumerate(grads):
-            g = np.ascontiguousarray(g, dtype=np.float32)
-            t = reqs[k % n].gradients.add()
-            t.name = name
-            t.shape.extend(g.shape)
-            t.dtype = 0
-            t.data.extend(g.reshape(-1))
-        rs = self._each_shard(lambda i, stub: self._retry(
-            lambda: stub.ReceiveGradients(reqs[i], timeout=self.timeout), attempts=3))
+        parts: List[List[Tuple[str, np.ndarray]]] = [[] for _ in range(n)]
+        for k, item in enumerate(grads):
+            parts[k % n].append(item)
+        reqs = [encode_gradient_update(self.worker_id, iteration, p) for p in parts]
+        Resp = protos.msg("parameter_server.PushResponse")
+        rs = self._each_shard(lambda i, stub: Resp.FromString(self._retry(
+            lambda: self._raw_push[i](reqs[i], timeout=self.timeout), attempts=3)))
         for r in rs:
             if not r.success:
                 raise RuntimeError(f"push refused: {r.message}")
@@ -248,8 +376,10 @@ class RemoteTrainer:
             self.iteration = 1
 
     def _load(self, pulled: Dict[str, np.ndarray]) -> None:
+        import warnings
         torch = self.torch
-        with torch.no_grad():
+        with torch.no_grad(), warnings.catch_warnings():
+            warnings.simplefilter("ignore")  # the views are read-only; they are only read from
             for n, p in zip(self.names, self.params):
                 a = pulled.get(n)
                 if a is not None and a.size == p.numel():

@@ -200,3 +200,40 @@ def test_model_split_over_two_parameter_server_shards(sharded_plane):
     assert names == [["0.weight", "2.weight"], ["0.bias", "2.bias"]]
     for s in servers:
         assert "registered as shard" in s.output()
+
+
+def test_numpy_codec_agrees_with_the_protobuf_runtime():
+    """control/remote.py writes GradientUpdate and reads ParameterUpdate itself (float payload as
+    one numpy block); both must be what the protobuf runtime writes / reads."""
+    from parameter_server_distributed_b200.control import protos, remote
+    rng = np.random.default_rng(0)
+    grads = [("layer.weight", rng.standard_normal((3, 5)).astype(np.float32)),
+             ("scalar", np.float32(2.5) * np.ones((), np.float32)),
+             ("empty", np.zeros((0, 4), np.float32)),
+             ("", rng.standard_normal(7).astype(np.float32))]
+    for wid, it in ((0, 0), (3, 17), (-1, 2 ** 31 - 1)):
+        raw = remote.encode_gradient_update(wid, it, grads)
+        m = protos.msg("parameter_server.GradientUpdate").FromString(raw)
+        assert (m.worker_id, m.iteration, len(m.gradients)) == (wid, it, 4)
+        for t, (name, g) in zip(m.gradients, grads):
+            assert t.name == name and list(t.shape) == list(g.shape) and t.dtype == 0
+            np.testing.assert_array_equal(np.asarray(t.data, np.float32), g.reshape(-1))
+        # byte-identical with the runtime's own serialisation of the same message
+        assert raw == m.SerializeToString()
+    T = protos.msg("parameter_server.Tensor")
+    upd = protos.msg("parameter_server.ParameterUpdate")(
+        iteration=9, ready=True, parameters=[
+            T(name="a", shape=[2, 3], data=[1, 2, 3, 4, 5, 6], dtype=0),
+            T(name="b", shape=[], data=[], dtype=1),
+            T(name="c", shape=[4], data=[0.5, -1.5, 2.5, 1e-30])])
+    it, ready, ts = remote.decode_parameter_update(upd.SerializeToString())
+    assert (it, ready) == (9, True) and [t[0] for t in ts] == ["a", "b", "c"]
+    assert ts[0][1] == (2, 3) and ts[1][1] == () and ts[1][2].size == 0
+    np.testing.assert_array_equal(ts[0][2], np.arange(1, 7, dtype=np.float32))
+    np.testing.assert_array_equal(ts[2][2], np.array([0.5, -1.5, 2.5, 1e-30], np.float32))
+    # fields in another order (the C++ server sends iteration / ready first, tensors last)
+    head = protos.msg("parameter_server.ParameterUpdate")(iteration=4, ready=True).SerializeToString()
+    tail = protos.msg("parameter_server.ParameterUpdate")(parameters=upd.parameters).SerializeToString()
+    assert remote.decode_parameter_update(head + tail)[0:2] == (4, True)
+    with pytest.raises((ValueError, IndexError)):
+        remote.decode_parameter_update(upd.SerializeToString()[:-3])
