@@ -253,3 +253,54 @@ def test_parameter_server_restart_resumes_from_its_latest_checkpoint(tmp_path):
         if ps2:
             ps2.stop()
         co.stop()
+
+
+def test_coordinator_restart_rebuilds_its_soft_state(tmp_path):
+    """The coordinator keeps nothing on disk: after a crash and restart the workers' next
+    heartbeat is refused (unknown id), they register again, and a sharded parameter server
+    announces itself again — registry and shard map are back without touching the job."""
+    ps_port, co_port = free_port(), free_port()
+    coargs = [f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"]
+    co = Proc(coargs, str(tmp_path), str(tmp_path / "co1.log"), env=FAST)
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0",
+               f"--coordinator=127.0.0.1:{co_port}", "--shard-id=0", "--membership-poll-ms=100"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    co2 = None
+    workers = []
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        for wid in range(2):
+            workers.append(Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(wid), "100000",
+                                 "--heartbeat-ms=100", "--compute-ms=2", "--quiet"], str(tmp_path),
+                                str(tmp_path / f"w{wid}.log")))
+        probe = cc.CoordinatorClient(f"127.0.0.1:{co_port}", 99, 3, heartbeat_ms=100)
+        end = time.time() + 10
+        while time.time() < end and probe.list_workers() != [0, 1, 99]:
+            time.sleep(0.05)
+        assert probe.list_workers() == [0, 1, 99]
+        assert [s[0] for s in probe.shard_map()[0]] == [0]
+        co.p.send_signal(signal.SIGKILL)
+        co.p.wait(timeout=5)
+        time.sleep(0.3)
+        co2 = Proc(coargs, str(tmp_path), str(tmp_path / "co2.log"), env=FAST)
+        assert wait_port(co_port)
+        fresh = cc.CoordinatorClient(f"127.0.0.1:{co_port}", 98, 4, heartbeat_ms=100)
+        end = time.time() + 10
+        while time.time() < end and not (set(fresh.list_workers()) >= {0, 1, 99}
+                                         and fresh.shard_map()[0]):
+            time.sleep(0.05)
+        assert set(fresh.list_workers()) >= {0, 1, 99}, fresh.list_workers()
+        shards, _ = fresh.shard_map()
+        assert [(s[0], s[1]) for s in shards] == [(0, f"127.0.0.1:{ps_port}")]
+        assert probe.evictions() >= 1  # it found itself unknown and registered again
+        for w in workers:
+            assert w.p.poll() is None, "a worker died with the coordinator"
+        probe.close()
+        fresh.close()
+    finally:
+        for w in workers:
+            w.stop()
+        ps.stop()
+        co.stop() if co.p.poll() is None else None
+        if co2:
+            co2.stop()
