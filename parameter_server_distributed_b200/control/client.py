@@ -182,9 +182,37 @@ class CoordinatorClient:
         self._check(self.lib.psbc_update_clock(self._h, clock, C.byref(lo)), "UpdateClock")
         return lo.value
 
+    # ------------------------------------------------------------------ blobs
+    def put(self, key: str, blob: bytes) -> None:
+        buf = (C.c_char * max(1, len(blob))).from_buffer_copy(blob or b"\0")
+        self._check(self.lib.psbc_put(self._h, key.encode(), buf, len(blob)), "PutHandle")
+
+    def get(self, key: str, rank: int, cap: int = 1 << 16) -> Optional[bytes]:
+        """Rank ``rank``'s blob of ``key`` (None when absent)."""
+        out = (C.c_char * cap)()
+        n = C.c_size_t()
+        self._check(self.lib.psbc_get(self._h, key.encode(), rank, out, cap, C.byref(n)), "GetHandles")
+        return bytes(out[:n.value]) if n.value else None
+
     # ------------------------------------------------------------------ teardown
-    def close(self) -> None:
+    _BYE = "psb/bye"
+
+    def close(self, linger_s: float = 10.0) -> None:
+        """Leave the job.  Every rank says goodbye (a marker in the coordinator's blob store)
+        before it disconnects; the rank that LAUNCHED the coordinator keeps it alive until all
+        ``world`` ranks have said so (or ``linger_s`` has passed) — otherwise a peer that is
+        still reading the answer of its last barrier would find the coordinator gone."""
         if self._h:
+            try:
+                self.put(self._BYE, b"1")
+                if self._proc is not None and self.world > 1:
+                    end = time.time() + linger_s
+                    while time.time() < end and self._proc.poll() is None:
+                        if all(self.get(self._BYE, r) for r in range(self.world)):
+                            break
+                        time.sleep(0.02)
+            except ControlError:
+                pass  # coordinator already gone: nothing to wait for
             self.lib.psbc_close(self._h)
             self._h = None
         if self._proc is not None:

@@ -304,3 +304,50 @@ def test_coordinator_restart_rebuilds_its_soft_state(tmp_path):
         co.stop() if co.p.poll() is None else None
         if co2:
             co2.stop()
+
+
+def _init_rank(rank, world, port, rdv, q):
+    try:
+        os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world),
+                          MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), PSB_RENDEZVOUS_DIR=rdv,
+                          PSB_HEARTBEAT_MS="100")
+        os.environ.pop("PSB_COORDINATOR", None)
+        import parameter_server_distributed_b200 as psd
+        ctx = psd.init(control="coordinator")  # no GPU here: control plane only, fabric is None
+        assert ctx.coord is not None and ctx.world == world and ctx.fabric is None
+        ctx.barrier("up")
+        objs = ctx.all_gather_object({"rank": rank, "blob": "x" * (50 * rank)}, key="t")
+        mx = [ctx.reduce_max(float(rank * (i + 1)), key="m") for i in range(3)]
+        workers = ctx.coord.list_workers()
+        ctx.barrier("down")
+        ctx.close()
+        q.put((rank, [o["rank"] for o in objs], mx, workers))
+    except BaseException as e:  # noqa: BLE001
+        q.put((rank, "error", repr(e)))
+
+
+def test_psd_init_bootstraps_ranks_through_a_coordinator_it_launches(tmp_path):
+    """The torchrun path of the GPU benchmark, minus the GPUs: nobody started a coordinator,
+    rank 0's psd.init() launches the binary, the others find it through the rendezvous file, and
+    the host collectives of Context (barrier, all_gather_object, reduce_max) run through it."""
+    world, port = 4, free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_init_rank, args=(r, world, port, str(tmp_path), q))
+          for r in range(world)]
+    for p in ps:
+        p.start()
+    res = {}
+    for _ in range(world):
+        r = q.get(timeout=120)
+        assert r[1] != "error", r
+        res[r[0]] = r
+    for p in ps:
+        p.join(timeout=20)
+        assert p.exitcode == 0
+    for rank in range(world):
+        _, ranks, mx, workers = res[rank]
+        assert ranks == list(range(world))
+        assert mx == [float((world - 1) * (i + 1)) for i in range(3)]
+        assert workers == list(range(world))
+    assert not os.listdir(tmp_path), os.listdir(tmp_path)  # the rendezvous file is gone
