@@ -351,3 +351,49 @@ def test_psd_init_bootstraps_ranks_through_a_coordinator_it_launches(tmp_path):
         assert mx == [float((world - 1) * (i + 1)) for i in range(3)]
         assert workers == list(range(world))
     assert not os.listdir(tmp_path), os.listdir(tmp_path)  # the rendezvous file is gone
+
+
+def _fd_rank(rank, world, addr, q):
+    try:
+        from parameter_server_distributed_b200.parallel import fabric as fb
+        c = cc.CoordinatorClient(addr, rank, world, heartbeat_ms=100)
+        ctl = fb._Control(lambda key, obj: c.allgather_object(key, obj), lambda name: c.barrier(name))
+        mine = []
+        for k in range(2):  # two descriptors per rank, like heap segment + signal pad
+            fd = os.memfd_create(f"psb_test_{rank}_{k}")
+            os.write(fd, f"rank {rank} segment {k}".encode())
+            mine.append(fd)
+        fds = fb._exchange_fds(ctl, rank, world, mine)
+        seen = []
+        for r in range(world):
+            row = []
+            for fd in fds[r]:
+                row.append(os.pread(fd, 64, 0).decode())  # the offset is shared between ranks
+            seen.append(row)
+        c.barrier("done")
+        c.close()
+        q.put((rank, seen))
+    except BaseException as e:  # noqa: BLE001
+        q.put((rank, "error", repr(e)))
+
+
+def test_file_descriptors_travel_between_ranks(tmp_path):
+    """The VMM heap's bootstrap step without a GPU: every rank's POSIX descriptors (here memfds)
+    reach every peer over Unix sockets whose paths were exchanged through the coordinator
+    (parallel/fabric.py: _exchange_fds, the route of cuMemExportToShareableHandle fds)."""
+    proc, addr = cc.spawn_coordinator(env=FAST, log_path=str(tmp_path / "co.log"))
+    try:
+        world = 4
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        ps = [ctx.Process(target=_fd_rank, args=(r, world, addr, q)) for r in range(world)]
+        for p in ps:
+            p.start()
+        for _ in range(world):
+            r = q.get(timeout=120)
+            assert r[1] != "error", r
+            assert r[1] == [[f"rank {o} segment {k}" for k in range(2)] for o in range(world)]
+        for p in ps:
+            p.join(timeout=20)
+    finally:
+        cc._stop(proc)
