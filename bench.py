@@ -47,6 +47,11 @@ def parse():
     ap.add_argument("--push", default="auto", choices=["auto", "tma", "ldg", "nvls"],
                     help="K1 variant: auto = bulk-copy kernel on 32 SMs for overlapped buckets, "
                          "register-path kernel on all SMs for the last one")
+    ap.add_argument("--straggler-rank", type=int, default=-1,
+                    help="experiment: this rank's GPU is held up before some of its steps "
+                         "(device-timed loop only); adds sum-of-rank rates to the JSON line")
+    ap.add_argument("--straggler-ms", type=float, default=0.0, help="... by this long")
+    ap.add_argument("--straggler-prob", type=float, default=1.0, help="... with this probability")
     return ap.parse_args()
 
 
@@ -161,12 +166,20 @@ def run_ours(args):
     with ClockSampler(ctx.local_rank) as clocks:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        straggle = args.straggler_ms > 0 and ctx.rank == args.straggler_rank
+        if straggle:  # cycles of torch.cuda._sleep at the current SM clock
+            import random
+            rng = random.Random(1234)
+            cycles = int(args.straggler_ms * 1.9e6)  # ~1.9 GHz SM clock
         for i in range(args.steps):
+            if straggle and rng.random() < args.straggler_prob:
+                torch.cuda._sleep(cycles)
             loss = trainer.step_device(dev_x[i % n_host], dev_y[i % n_host])
         e1.record()
         host_barrier(ctx)
         dev_ms = e0.elapsed_time(e1)
     launches = _lib.launch_count() - launches0
+    own_dev_ms = dev_ms
     dev_ms = max_over_ranks(dev_ms, ctx)
     final_loss = float(loss.item())
 
@@ -212,6 +225,9 @@ def run_ours(args):
     if args.mode != "sync":
         ps.drain()  # apply what is still in flight so every rank ends with the same model
 
+    rank_ms = None
+    if args.straggler_ms > 0:  # collective: every rank contributes its own device time
+        rank_ms = ctx.all_gather_object(float(own_dev_ms), key="straggler_ms")
     global_batch = B * world
     value = global_batch * args.steps / (dev_ms / 1e3)
     e2e_value = global_batch * args.steps / (e2e_ms / 1e3)
@@ -249,6 +265,13 @@ def run_ours(args):
             "clocks": clocks.summary(),
             "final_loss": final_loss, "e2e_final_loss": e2e_loss,
         }
+        if rank_ms is not None:
+            # with a straggler the job-level number (max over ranks) hides what async / SSP buy:
+            # the other ranks' own rates; report both
+            out["straggler"] = {"rank": args.straggler_rank, "ms": args.straggler_ms,
+                                "prob": args.straggler_prob, "rank_ms_per_step":
+                                    [m / args.steps for m in rank_ms],
+                                "sum_of_rank_rates": sum(B * args.steps / (m / 1e3) for m in rank_ms)}
         print(json.dumps(out), flush=True)
     host_barrier(ctx)
     ctx.close()
