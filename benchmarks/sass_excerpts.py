@@ -28,6 +28,38 @@ SECTIONS = [
      "fused all-gather GEMM, gather role: TMA loads on the OWNER's tensor map (UTMALDG.2D without "
      ".2CTA), TMA stores into the local replica (UTMASTG.2D), batched arrival counters"),
     ("colsum_bf16_kernel", ["LDG", "STG", "ATOM", "BAR"], "bias-gradient column sum"),
+    ("pull_allgather_kernel", ["LD.E.STRONG.SYS", "LDG.E.128", "LDG.E.NA", "STG.E.128", "CCTL", "MEMBAR",
+                               "NANOSLEEP"],
+     "K2 pull all-gather: version wait (ld.acquire.sys = LD.E.STRONG.SYS in a NANOSLEEP back-off loop), "
+     "16-byte peer loads that bypass L1, 16-byte stores into the local replica; the seqlock variant "
+     "re-reads the version after the copy"),
+    ("wait_versions_kernel", ["LD.E.STRONG.SYS", "NANOSLEEP", "BPT.TRAP", "LD.E.STRONG"],
+     "K9 version wait: one warp spins on the owners' version words (acquire at system scope), polls the "
+     "host-mapped abort word, traps when the watchdog expires"),
+    ("device_barrier_kernel", ["ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "MEMBAR", "NANOSLEEP"],
+     "K9 device barrier over the signal pad: release store of the epoch into every peer's pad, acquire "
+     "spin on the own pad"),
+    ("push_ready_kernel", ["ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "MEMBAR", "NANOSLEEP"],
+     "READY handshake of a bucket taken off the SMs that run K1 (round 2): post the own flag to every "
+     "owner, wait for all workers' flags"),
+    ("norm_allreduce_kernel", ["ST.E.STRONG.SYS", "LD.E.STRONG.SYS", "MUFU.RSQ", "MUFU.SQRT", "FMNMX",
+                               "MEMBAR"],
+     "K4 cross-shard gradient norm: every rank posts its partial sum of squares into every pad, spins "
+     "for the others, sums in rank order (bit-identical on every rank) and derives the clip coefficient"),
+    ("sumsq_partial_kernelILi1E", ["LDG.E.128", "SHFL", "FFMA", "STG"],
+     "K4 partial sum of squares of a bf16 buffer (16-byte loads, warp shuffles, one partial per CTA)"),
+    ("optim_kernelILi3ELi1ELb1E", ["LDG.E.128", "STG.E.128", "MUFU.RSQ", "MUFU.RCP", "MUFU.SQRT", "F2FP"],
+     "K3 stand-alone flat-shard AdamW, bf16 gradients, bf16 emit: 16-byte loads of g / p / m / v, one pass, "
+     "packed bf16 conversion of the new weights"),
+    ("bcast_slice_nvls_kernel", ["STG.E.128.STRONG.SYS", "ST.E.STRONG.SYS", "MEMBAR", "LDG.E.128"],
+     "K2 over NVLS: the owner stores its updated slice once to the multicast address (multimem.st), the "
+     "switch replicates it into all replicas"),
+    ("async_gate_kernel", ["LD.E.STRONG.SYS", "NANOSLEEP", "ISETP"],
+     "async / SSP gate: blocks the stream until the ring slot of the next clock is free on every owner "
+     "and (SSP) the slowest worker is within the staleness bound"),
+    ("async_plan_kernel", ["LD.E.STRONG.SYS", "ST.E", "STG"],
+     "async / SSP owner plan: per bucket, which workers have an unapplied clock (mask) and where their "
+     "gradient ring slot is (offset)"),
 ]
 MNEMONICS = (r"\b(LDTM|SYNCS|UBLKCP|UCGABAR|UTCATOMSWS|UTCBAR|UTCHMMA|UTMALDG|UTMASTG|UTMACCTL|"
              r"UGETNEXTWORKID|UTMACMDFLUSH|LDGMC|LDG\.E[A-Z0-9.]*256|STG\.E[A-Z0-9.]*256)[A-Za-z0-9_.]*")
