@@ -105,6 +105,27 @@ def main() -> int:
     with open(os.path.join(ROOT, "profiles", "sass_mnemonics.txt"), "w") as f:
         for k in sorted(counts):
             f.write(f"{counts[k]:7d} {k}\n")
+    # registers / static shared memory / stack of every kernel (dynamic shared memory is set at
+    # launch: 197 KB for the CTA-pair GEMM, see gemm_tcgen05_2cta.cu SMEM_BYTES)
+    res = subprocess.run(["cuobjdump", "-res-usage", LIB], capture_output=True, text=True, check=True).stdout
+    rows, name = [], None
+    for line in res.split("\n"):
+        m = re.match(r"\s*Function (\S+):", line)
+        if m:
+            name = m.group(1)
+            continue
+        m = re.match(r"\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", line)
+        if m and name:
+            rows.append((name, *map(int, m.groups())))
+            name = None
+    demangled = subprocess.run(["c++filt"], input="\n".join(r[0] for r in rows), capture_output=True,
+                               text=True, check=True).stdout.split("\n")
+    with open(os.path.join(ROOT, "profiles", "kernel_resources.txt"), "w") as f:
+        f.write("# `cuobjdump -res-usage` of libpsb_kernels.so (sm_100a): registers per thread, stack bytes,\n"
+                "# static shared bytes, local bytes.  Regenerate with `python benchmarks/sass_excerpts.py`.\n")
+        f.write(f"{'REG':>4} {'STACK':>6} {'SHARED':>7} {'LOCAL':>6}  kernel\n")
+        for (n, reg, stack, shared, local), d in sorted(zip(rows, demangled), key=lambda x: x[1]):
+            f.write(f"{reg:4d} {stack:6d} {shared:7d} {local:6d}  {re.sub(r'\(.*', '', d)[:100]}\n")
     return 0
 
 
