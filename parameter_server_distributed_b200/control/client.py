@@ -23,7 +23,7 @@ import struct
 import subprocess
 import time
 from pathlib import Path
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Optional, Tuple
 
 ROOT = Path(__file__).resolve().parents[2]
 LIB_PATH = Path(__file__).resolve().parents[1] / "_native" / "libpsb_control.so"

@@ -11,7 +11,7 @@ are plain PyTorch.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Optional, Sequence
+from typing import Sequence
 
 import torch
 import torch.nn as nn

@@ -22,7 +22,7 @@ those fields now drive ``parameter_server --mode=async|ssp``.  This module is th
 from __future__ import annotations
 
 import ctypes as C
-from typing import Iterable, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -161,7 +161,6 @@ class AsyncParameterServer(ShardedParameterServer):
         """CPU tensors / gloo: collectives are blocking, so every worker's gradient of this
         clock arrives at once; owners apply them one after the other in rank order, each scaled
         by 1/N — the arithmetic of the device path when nobody is ahead."""
-        import torch.distributed as dist
         be = self.backend
         cfg = OptimConfig(**{**self.optim.__dict__, "grad_scale": 1.0})
         for b, bk in enumerate(self.plan.buckets):
