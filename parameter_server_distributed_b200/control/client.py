@@ -208,7 +208,8 @@ class CoordinatorClient:
                 if self._proc is not None and self.world > 1:
                     end = time.time() + linger_s
                     while time.time() < end and self._proc.poll() is None:
-                        if all(self.get(self._BYE, r) for r in range(self.world)):
+                        live = set(self.list_workers())  # an evicted (dead) rank is not waited for
+                        if all(self.get(self._BYE, r) for r in range(self.world) if r in live):
                             break
                         time.sleep(0.02)
             except ControlError:
