@@ -135,3 +135,44 @@ def test_malformed_input_is_rejected():
     r = subprocess.run([f"{BIN}/psb_pbtool", "parameter_server.Tensor"], input=b"\x0a\x05ab",
                        capture_output=True)
     assert r.returncode == 3
+
+
+def test_decoders_never_crash_on_mutated_messages():
+    """Bit flips, truncations and random tails of valid encodings: the hand-written decoders
+    either accept (exit 0) or reject (exit 3) — never a signal.  The servers feed them bytes
+    from the network."""
+    import random
+    T = protos.msg("parameter_server.Tensor")
+    seeds = {
+        "parameter_server.GradientUpdate": protos.msg("parameter_server.GradientUpdate")(
+            worker_id=3, iteration=7, gradients=[T(name="w", shape=[2, 3], data=[1, 2, 3, 4, 5, 6]),
+                                                 T(name="b", shape=[3], data=[0.5, 1.5, 2.5], dtype=1)]
+        ).SerializeToString(),
+        "parameter_server.ParameterUpdate": protos.msg("parameter_server.ParameterUpdate")(
+            iteration=9, ready=True, parameters=[T(name="p", shape=[4], data=[1, 2, 3, 4])]
+        ).SerializeToString(),
+        "coordinator.ListWorkersResponse": protos.msg("coordinator.ListWorkersResponse")(
+            total_workers=2, workers=[protos.msg("coordinator.WorkerInfo")(
+                worker_id=i, address="10.0.0.%d" % i, port=5000 + i, hostname="h%d" % i)
+                for i in range(2)]).SerializeToString(),
+    }
+    rng = random.Random(7)
+    codes = set()
+    for name, good in seeds.items():
+        for _ in range(60):
+            b = bytearray(good)
+            kind = rng.randrange(4)
+            if kind == 0:
+                for _ in range(rng.randrange(1, 4)):
+                    b[rng.randrange(len(b))] ^= 1 << rng.randrange(8)
+            elif kind == 1:
+                del b[rng.randrange(1, len(b)):]
+            elif kind == 2:
+                b += bytes(rng.getrandbits(8) for _ in range(rng.randrange(1, 12)))
+            else:
+                i = rng.randrange(len(b))
+                b[i:i] = bytes([0xFF] * rng.randrange(1, 11))  # runaway varints / huge lengths
+            r = subprocess.run([f"{BIN}/psb_pbtool", name], input=bytes(b), capture_output=True)
+            assert r.returncode in (0, 3), (name, bytes(b).hex(), r.returncode)
+            codes.add(r.returncode)
+    assert codes == {0, 3}  # the mutations do produce both outcomes
