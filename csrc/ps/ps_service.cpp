@@ -66,6 +66,10 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed PullRequest"};
     pb::ParameterUpdate out;
     out.iteration = in.iteration;
+    // A negative iteration asks "where is the job?": the answer carries the newest iteration any
+    // worker has pushed, so a worker that was restarted (or joins late) continues there instead
+    // of at 0 (the reference's workers always start at 0, scripts/scale_workers.sh:113).
+    if (in.iteration < 0) out.iteration = core_.get_current_iteration();
     if (core_.options().mode == PsMode::kSync) {
       int32_t received = 0;
       out.ready = core_.check_sync_status(in.iteration, received);

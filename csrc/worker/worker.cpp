@@ -369,6 +369,18 @@ bool Worker::push_gradients(int iteration, std::vector<TensorLite>&& grads,
   return complete;
 }
 
+int Worker::server_iteration() {
+  pb::PullRequest req;
+  req.worker_id = worker_id_;
+  req.iteration = -1;
+  std::string resp;
+  Status st = shard_channel(0).call("/parameter_server.ParameterServer/ServeParameters",
+                                    req.encode(), resp, 30000);
+  pb::ParameterUpdate out;
+  if (!st.ok() || !out.decode(resp)) return -1;
+  return out.iteration;
+}
+
 bool Worker::check_sync_ready(int iteration, int& workers_received, int& total_workers) {
   pb::SyncStatusRequest req;
   req.iteration = iteration;

@@ -72,6 +72,9 @@ class Worker {
   bool push_gradients(int iteration, std::vector<TensorLite>&& grads, int& workers_received,
                       int& total_workers);
   bool check_sync_ready(int iteration, int& workers_received, int& total_workers);
+  // The newest iteration any worker has pushed to the server (shard 0), -1 if it cannot be
+  // asked: where a restarted or late worker joins the job (worker_main --join).
+  int server_iteration();
   std::vector<std::string> discover_peer_workers();
   const std::string& ps_address() const { return ps_address_; }
   // Replace the synthetic gradient source (default: every element = 0.01).

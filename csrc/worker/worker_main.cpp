@@ -6,9 +6,11 @@
 // (or PSB_MODE / PSB_DEVICE / PSB_HEARTBEAT_MS / PSB_SYNC_TIMEOUT_MS), and for the straggler
 // benchmark --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N --quiet (simulated
 // compute time per iteration; no per-iteration log line, one summary line at the end), and
-// --trace (pull / compute / push / wait milliseconds of every iteration);
+// --trace (pull / compute / push / wait milliseconds of every iteration); --join (start at the
+// iteration the job has reached instead of 0: a worker that was restarted);
 // --shards=N: the model's tensors are split over the N parameter servers that registered with
 // --shard-id (tensor k on shard k % N); PSB_SHARDS.
+#include <algorithm>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -33,6 +35,7 @@ static const char kUsage[] =
     "  --shards=N              the model's tensors are split over N parameter servers\n"
     "  --device=N              synthetic gradients are filled on GPU N\n"
     "  --heartbeat-ms=N (5000) --sync-timeout-ms=N (10000)\n"
+    "  --join                  start at the iteration the job has reached (a restarted worker)\n"
     "  --trace                 pull / compute / push / wait milliseconds of every iteration\n"
     "  --quiet                 no per-iteration line, one summary line at the end\n"
     "  --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N   simulated compute time\n";
@@ -49,7 +52,7 @@ int main(int argc, char** argv) {
   std::string worker_addr, checkpoint_path;
   int32_t worker_port = 0;
   psb::WorkerOptions opt;
-  bool quiet = false;
+  bool quiet = false, join = false;
   if (const char* e = std::getenv("PSB_MODE")) opt.mode = e;
   if (const char* e = std::getenv("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = std::getenv("PSB_HEARTBEAT_MS")) opt.heartbeat_ms = std::atoi(e);
@@ -68,6 +71,7 @@ int main(int argc, char** argv) {
     else if (flag(a, "seed", v)) opt.sim_seed = std::strtoull(v.c_str(), nullptr, 10);
     else if (a == "--quiet") quiet = true;
     else if (a == "--trace") opt.trace = true;
+    else if (a == "--join") join = true;
     else if (flag(a, "shards", v)) opt.shards = std::atoi(v.c_str());
     else if (a.rfind("--", 0) == 0 && a.size() > 2) {
       std::cerr << "unknown flag " << a << std::endl;
@@ -96,9 +100,14 @@ int main(int argc, char** argv) {
                 << std::endl;  // continue from scratch, like the reference
     }
   }
+  int first = 0;
+  if (join) {  // continue where the job is, not at iteration 0
+    first = std::max(0, w.server_iteration());
+    std::cout << "worker " << worker_id << " joining at iteration " << first << std::endl;
+  }
   const auto t0 = std::chrono::steady_clock::now();
   int completed = 0;
-  for (int it = 0; it < iterations; ++it) {
+  for (int it = first; it < iterations; ++it) {
     bool done = w.run_iteration(it);
     completed += done ? 1 : 0;
     if (!quiet)

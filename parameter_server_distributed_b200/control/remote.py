@@ -305,6 +305,13 @@ class RemoteParameterServer:
         return (all(bool(r.aggregation_complete) for r in rs),
                 min(r.workers_received for r in rs), rs[0].total_workers)
 
+    def server_iteration(self) -> int:
+        """Newest iteration any worker has pushed (shard 0); this framework's server answers a
+        pull with a negative iteration that way, the reference's echoes the request (-1)."""
+        req = protos.msg("parameter_server.PullRequest")(
+            worker_id=self.worker_id, iteration=-1).SerializeToString()
+        return decode_parameter_update(self._raw_pull[0](req, timeout=self.timeout))[0]
+
     def wait(self, iteration: int, timeout_s: float = 10.0, poll_s: float = 0.0) -> bool:
         """CheckSyncStatus until the iteration is aggregated.  This framework's server holds a
         negative answer (``--long-poll-ms``), so polling back to back costs nothing; against the
@@ -367,7 +374,9 @@ class RemoteTrainer:
         if start_iteration is not None:
             self.iteration = start_iteration
         elif have:
-            self.iteration = 1  # server already has a model (another worker, or a checkpoint)
+            # the server already has a model (other workers, or a checkpoint): join where the job
+            # is — a pull with a negative iteration is answered with the newest pushed iteration
+            self.iteration = max(1, ps.server_iteration())
         else:
             init = [(n, p.detach().float().cpu().numpy()) for n, p in zip(self.names, self.params)]
             done, _, _ = ps.push(0, init)

@@ -397,3 +397,52 @@ def test_file_descriptors_travel_between_ranks(tmp_path):
             p.join(timeout=20)
     finally:
         cc._stop(proc)
+
+
+def test_restarted_worker_joins_at_the_jobs_iteration(tmp_path):
+    """A worker dies, the barrier shrinks, a supervisor starts the worker again with --join: it
+    asks the server where the job is, continues there, the barrier grows back, and all three
+    finish.  (Started at iteration 0 — what the reference does, scripts/scale_workers.sh:113 —
+    it would push iterations nobody waits for any more.)"""
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"), env=FAST)
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "3", "0",
+               f"--coordinator=127.0.0.1:{co_port}", "--membership-poll-ms=100"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    iters = 4000
+    common = ["--heartbeat-ms=100", "--sync-timeout-ms=8000", "--compute-ms=1"]
+    workers, again = [], None
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        for wid in range(3):
+            workers.append(Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(wid), str(iters),
+                                 *common], str(tmp_path), str(tmp_path / f"w{wid}.log")))
+        end = time.time() + 20
+        while time.time() < end and len(_done_lines(workers[0].output())) < 50:
+            time.sleep(0.02)
+        workers[2].p.send_signal(signal.SIGKILL)
+        end = time.time() + 10
+        while time.time() < end and "total_workers 3 -> 2" not in ps.output():
+            time.sleep(0.05)
+        assert "membership: total_workers 3 -> 2" in ps.output()
+        again = Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "2", str(iters), "--join",
+                      *common], str(tmp_path), str(tmp_path / "w2b.log"))
+        for w in workers[:2] + [again]:
+            assert w.p.wait(timeout=180) == 0
+        m = re.search(r"worker 2 joining at iteration (\d+)", again.output())
+        assert m and 50 <= int(m.group(1)) < iters, again.output()[:200]
+        joined = int(m.group(1))
+        lines = _done_lines(again.output())
+        assert [i for i, _ in lines] == list(range(joined, iters))
+        assert sum(ok for _, ok in lines) >= len(lines) - 2, [i for i, ok in lines if not ok][:5]
+        for wid in (0, 1):
+            lines = _done_lines(workers[wid].output())
+            assert len(lines) == iters and all(ok for _, ok in lines)
+        assert re.search(r"membership: total_workers 2 -> 3 \(3 live\)", ps.output())
+        assert joined < iters - 100, "the job was over before the worker came back"
+    finally:
+        for w in workers + ([again] if again else []):
+            w.stop()
+        ps.stop()
+        co.stop()
