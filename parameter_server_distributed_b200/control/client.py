@@ -27,7 +27,7 @@ from typing import List, Optional, Tuple
 
 ROOT = Path(__file__).resolve().parents[2]
 LIB_PATH = Path(__file__).resolve().parents[1] / "_native" / "libpsb_control.so"
-COORDINATOR_BIN = ROOT / "build" / "bin" / "coordinator"
+COORDINATOR_BIN = Path(os.environ.get("PSB_COORDINATOR_BIN") or ROOT / "build" / "bin" / "coordinator")
 
 _LIB = None
 

@@ -9,6 +9,7 @@ import multiprocessing as mp
 import os
 import re
 import signal
+import struct
 import subprocess
 import time
 
@@ -446,3 +447,43 @@ def test_restarted_worker_joins_at_the_jobs_iteration(tmp_path):
             w.stop()
         ps.stop()
         co.stop()
+
+
+def test_eight_ranks_hammer_the_control_plane(tmp_path):
+    """8 clients (threads, each with its own native handle and connections) run 150 rounds of
+    barrier + all-gather + max-reduce + clock update against one coordinator: the control traffic
+    of an 8-GPU job, compressed.  Every round must see every rank's value of THAT round."""
+    import threading
+    proc, addr = cc.spawn_coordinator(env=FAST, log_path=str(tmp_path / "co.log"))
+    world, rounds = 8, 150
+    errs, clients = [], []
+    try:
+        clients = [cc.CoordinatorClient(addr, r, world, heartbeat_ms=50) for r in range(world)]
+
+        def work(r):
+            c = clients[r]
+            try:
+                for i in range(rounds):
+                    c.barrier("b")
+                    got = c.allgather("v", struct.pack("<ii", r, i))
+                    assert [struct.unpack("<ii", g) for g in got] == [(q, i) for q in range(world)]
+                    assert c.reduce_max("m", float(r + i)) == float(world - 1 + i)
+                    if i % 10 == 0:
+                        assert c.update_clock(i) <= i
+                        assert c.list_workers() == list(range(world))
+            except BaseException as e:  # noqa: BLE001
+                errs.append((r, repr(e)))
+
+        ts = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+        t0 = time.time()
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(timeout=120)
+        assert not errs, errs[:3]
+        assert all(not t.is_alive() for t in ts)
+        assert time.time() - t0 < 60
+    finally:
+        for c in clients:
+            c.close()
+        cc._stop(proc)
