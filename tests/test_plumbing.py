@@ -414,3 +414,38 @@ def test_parameter_server_stats_line(tmp_path):
     finally:
         ps.stop()
         co.stop()
+
+
+def test_async_pushes_of_a_multi_megabyte_model_are_applied_exactly_once(tmp_path):
+    """--mode=async, four C++ workers x 15 iterations on a 4 MB model, all at once: every push is
+    applied exactly once with share 1/4 (final = init - 60 x 0.0025) while pulls of the shared
+    per-version encoding race with the updates."""
+    from parameter_server_distributed_b200.utils.checkpoint import write_reference_file
+    rng = np.random.default_rng(6)
+    init = rng.standard_normal(1 << 20).astype(np.float32)
+    write_reference_file(str(tmp_path / "init.ckpt"), 0, 0, [("w", (1024, 1024), init)])
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "4", "0", "--mode=async",
+               "--resume=init.ckpt"], str(tmp_path), str(tmp_path / "ps.log"))
+    workers = []
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        workers = [Proc([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", str(w), "15", "--mode=async",
+                         "--quiet"], str(tmp_path), str(tmp_path / f"w{w}.log")) for w in range(4)]
+        for w in workers:
+            assert w.p.wait(timeout=120) == 0
+            assert "done=15" in w.output(), w.output()[-200:]
+        stub = protos.Stub(grpc.insecure_channel(
+            f"127.0.0.1:{ps_port}", options=[("grpc.max_receive_message_length", -1)]),
+            "parameter_server.ParameterServer")
+        r = stub.ServeParameters(protos.msg("parameter_server.PullRequest")(worker_id=0, iteration=99),
+                                 timeout=30)
+        got = np.asarray(r.parameters[0].data, dtype=np.float32)
+        np.testing.assert_allclose(got, init - np.float32(60 * 0.0025), atol=2e-5)
+    finally:
+        for w in workers:
+            w.stop()
+        ps.stop()
+        co.stop()
