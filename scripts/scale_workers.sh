@@ -45,7 +45,8 @@ restart_ps() {  # $1 = new worker count
 start_worker() {  # $1 = id, $2 = optional checkpoint
   WORKER_ID="$1" COORDINATOR_ADDR="127.0.0.1:$COORDINATOR_PORT" ITERATIONS="$ITERATIONS" \
     CHECKPOINT_PATH="${2:-}" BINARY_PATH="$BIN/worker_main" LOG_FILE="$RUN_DIR/worker_$1.log" \
-    PID_FILE="$RUN_DIR/worker_$1.pid" bash "$ROOT/scripts/start_worker.sh"
+    PID_FILE="$RUN_DIR/worker_$1.pid" WORKER_FLAGS="${WORKER_FLAGS:-}" \
+    bash "$ROOT/scripts/start_worker.sh"
 }
 
 case "${1:-status}" in

@@ -345,7 +345,8 @@ def test_deploy_box_and_scale_workers_scripts(tmp_path, shards):
     co_port = free_port()
     ps_port = free_port()
     env = dict(os.environ, RUN_DIR=str(run), COORDINATOR_PORT=str(co_port), PS_PORT=str(ps_port),
-               WORKER_COUNT="2", ITERATIONS="30", CHECKPOINT_INTERVAL="0", PS_SHARDS=str(shards))
+               WORKER_COUNT="2", ITERATIONS="30", CHECKPOINT_INTERVAL="0", PS_SHARDS=str(shards),
+               WORKER_FLAGS="--sync-timeout-ms=60000")  # a slow box must not turn into done=false
     r = subprocess.run(["bash", os.path.join(ROOT, "scripts", "deploy_box.sh")], env=env,
                        capture_output=True, text=True, timeout=300)
     try:
@@ -355,7 +356,7 @@ def test_deploy_box_and_scale_workers_scripts(tmp_path, shards):
             p = run / f"worker_{wid}.log"
             return p.exists() and p.read_text().count("done=true") >= n
 
-        assert _wait_for(lambda: done(0, 30) and done(1, 30), 60), (run / "worker_0.log").read_text()[-300:]
+        assert _wait_for(lambda: done(0, 30) and done(1, 30), 120), (run / "worker_0.log").read_text()[-300:]
         if shards == 2:
             assert "registered as shard 1" in (run / "parameter_server_1.log").read_text()
             return
@@ -364,7 +365,8 @@ def test_deploy_box_and_scale_workers_scripts(tmp_path, shards):
                            env=env, capture_output=True, text=True, timeout=120)
         assert r.returncode == 0 and "scaled to 3 workers" in r.stdout, r.stdout + r.stderr
         assert (run / "scale.ckpt").exists()
-        assert _wait_for(lambda: all(done(w, 10) for w in range(3)), 60)
+        assert _wait_for(lambda: all(done(w, 10) for w in range(3)), 120), "\n".join(
+            (run / f"worker_{w}.log").read_text()[-200:] for w in range(3))
         assert "loaded checkpoint from scale.ckpt" in (run / "worker_0.log").read_text()
         st = subprocess.run(["bash", os.path.join(ROOT, "scripts", "scale_workers.sh"), "status"],
                             env=env, capture_output=True, text=True, timeout=30)
