@@ -17,7 +17,17 @@ ITERATIONS="${ITERATIONS:-100}"
 CHECKPOINT_INTERVAL="${CHECKPOINT_INTERVAL:-10}"
 
 alive() { [ -f "$1" ] && kill -0 "$(cat "$1")" 2>/dev/null; }
-stop_pid() { if alive "$1"; then kill "$(cat "$1")" 2>/dev/null || true; fi; rm -f "$1"; }
+stop_pid() {  # TERM, then wait until the process is gone: its port must be free for a successor
+  if alive "$1"; then
+    local pid; pid="$(cat "$1")"
+    kill "$pid" 2>/dev/null || true
+    # (a zombie nobody reaps — containers without an init — still answers kill -0: read its state)
+    running() { kill -0 "$1" 2>/dev/null && ! grep -q '^State:[[:space:]]*Z' "/proc/$1/status" 2>/dev/null; }
+    for _ in $(seq 1 100); do running "$pid" || break; sleep 0.05; done
+    running "$pid" && kill -9 "$pid" 2>/dev/null || true
+  fi
+  rm -f "$1"
+}
 workers() { ls "$RUN_DIR"/worker_*.pid 2>/dev/null | sed 's/.*worker_\([0-9]*\)\.pid/\1/' | sort -n; }
 
 save_checkpoint() {
