@@ -101,24 +101,29 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, kind, broadcast, q, alt=False):
+def _worker(rank, world, port, kind, broadcast, q, alt=False, split_mb=None, big=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     torch.manual_seed(0)
-    m = MLP(CFG)
+    cfg = MLPConfig(d_in=256, hidden=(512,), d_out=64) if big else CFG
+    m = MLP(cfg)
     ref = copy.deepcopy(m)
     ps = ShardedParameterServer(list(m.named_parameters()), OptimConfig(kind=kind, lr=0.01),
-                                world=world, rank=rank, bucket_mb=0.005, broadcast=broadcast,
-                                alt_params=alt)
+                                world=world, rank=rank, bucket_mb=0.3 if big else 0.005,
+                                broadcast=broadcast,
+                                alt_params=alt, **({} if split_mb is None else {"split_mb": split_mb}))
+    if split_mb:
+        pieces = sum(len(getattr(s_, "pieces", None) or []) for s_ in ps.plan.slots.values())
+        assert pieces >= 2, "the row-split path was not taken"
     fwd = _SinkMLP(m) if alt else m  # with two replicas: sink layers that commit before dX
     opt = _torch_opt(kind, list(ref.parameters()))
     for g in opt.param_groups:
         g["weight_decay"] = 0.0
     gen = torch.Generator().manual_seed(123)
     for _ in range(3):
-        xs = torch.randn(world, 8, 32, generator=gen)
-        ys = torch.randn(world, 8, 8, generator=gen)
+        xs = torch.randn(world, 8, cfg.d_in, generator=gen)
+        ys = torch.randn(world, 8, cfg.d_out, generator=gen)
         mse_loss(fwd(xs[rank]), ys[rank]).backward()
         ps.step()
         # oracle: mean over workers of the per-worker gradients
@@ -143,6 +148,25 @@ def test_gloo_two_workers_match_mean_gradient(kind, broadcast, alt):
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err in res:
+        assert err < 5e-6, (rank, err)
+
+
+def test_gloo_four_workers_with_row_split_buckets():
+    """world = 4 with the first-produced tensors cut into row blocks (what the GPU engine does
+    from 4 ranks up so that the last bucket's push overlaps its own dW GEMM): same result as the
+    mean-gradient oracle."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 4, port, "adam", True, q, False, 0.125, True))
+             for r in range(4)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
