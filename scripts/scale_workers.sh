@@ -70,7 +70,11 @@ case "${1:-status}" in
     done
     echo "scaled to $TARGET workers" ;;
   status)
-    for f in coordinator parameter_server; do
+    SERVERS="parameter_server"
+    if ls "$RUN_DIR"/parameter_server_*.pid >/dev/null 2>&1; then  # PS_SHARDS > 1
+      SERVERS="$(ls "$RUN_DIR"/parameter_server_*.pid | sed 's/.*\/\(parameter_server_[0-9]*\)\.pid/\1/' | sort)"
+    fi
+    for f in coordinator $SERVERS; do
       alive "$RUN_DIR/$f.pid" && echo "$f: running (pid $(cat "$RUN_DIR/$f.pid"))" || echo "$f: stopped"
     done
     for id in $(workers); do
