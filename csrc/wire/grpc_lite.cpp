@@ -144,7 +144,15 @@ class HandlerPool : public std::enable_shared_from_this<HandlerPool> {
 };
 
 // ------------------------------------------------------------------------------ Server
-Server::Server() : pool_(std::make_shared<HandlerPool>()) {}
+Server::Server() : pool_(std::make_shared<HandlerPool>()) {
+  // grpc.health.v1.Health/Check — what load balancers, `grpc_health_probe` and Kubernetes gRPC
+  // probes call.  Every server built on this class answers SERVING (HealthCheckResponse
+  // {status = 1}) for any service name while it is accepting requests.
+  add("/grpc.health.v1.Health/Check", [](std::string_view, Reply& reply) {
+    reply.body.assign("\x08\x01", 2);
+    return Status{};
+  });
+}
 Server::~Server() { shutdown(); }
 
 void Server::add(const std::string& path, Handler h) { handlers_[path] = std::move(h); }

@@ -330,3 +330,17 @@ def test_status_query_is_held_until_the_barrier_opens(tmp_path):
         assert not s.ready and 1.2 < time.time() - t0 < 4.0
     finally:
         ps.stop()
+
+
+def test_standard_health_check_is_answered(servers):
+    """grpc.health.v1.Health/Check (load balancers, grpc_health_probe, Kubernetes gRPC probes):
+    both servers answer SERVING.  HealthCheckRequest{service = 1: string},
+    HealthCheckResponse{status = 1: enum, SERVING = 1} — encoded by hand, grpcio's health package
+    is not installed here."""
+    ps_port, co_port, _, _, _ = servers
+    for port in (ps_port, co_port):
+        ch = grpc.insecure_channel(f"127.0.0.1:{port}")
+        check = ch.unary_unary("/grpc.health.v1.Health/Check", request_serializer=lambda b: b,
+                               response_deserializer=lambda b: b)
+        assert check(b"", timeout=5) == b"\x08\x01"
+        assert check(b"\x0a\x10parameter_server", timeout=5) == b"\x08\x01"
