@@ -2,6 +2,8 @@
 #include "ps_service.h"
 
 #include <dirent.h>
+#include <pthread.h>
+#include <signal.h>
 
 #include <chrono>
 #include <cstdlib>
@@ -324,6 +326,13 @@ void run_server(const std::string& server_address, int total_workers, int checkp
                 const PsOptions& opt, const std::string& coordinator_address,
                 int membership_poll_ms, const std::string& resume, int shard_id,
                 const std::string& advertise) {
+  // SIGTERM / SIGINT are taken by one dedicated thread (below): blocked here, before any other
+  // thread exists, so that every thread of the process inherits the mask.
+  sigset_t stop_signals;
+  sigemptyset(&stop_signals);
+  sigaddset(&stop_signals, SIGTERM);
+  sigaddset(&stop_signals, SIGINT);
+  pthread_sigmask(SIG_BLOCK, &stop_signals, nullptr);
   int scan_ms = 5000;
   if (const char* e = std::getenv("PSB_CHECKPOINT_SCAN_MS")) scan_ms = std::atoi(e);
   ParameterServerService svc(total_workers, checkpoint_interval, opt, scan_ms);
@@ -371,7 +380,24 @@ void run_server(const std::string& server_address, int total_workers, int checkp
     svc.follow_membership(coordinator_address, membership_poll_ms);
     std::cout << "following worker membership of coordinator " << coordinator_address << std::endl;
   }
-  svc.serve_forever();
+  // A planned stop (systemctl stop, scale_workers.sh, Ctrl-C) writes a last checkpoint where the
+  // periodic ones go, so that --resume=latest continues from the very last update; the reference
+  // loses everything since its last periodic file (src/parameter_server_service.cpp:150-169).
+  std::thread stopper([&svc, stop_signals, checkpoint_interval] {
+    int sig = 0;
+    if (sigwait(&stop_signals, &sig) != 0) return;
+    std::cout << "signal " << sig << ": shutting down" << std::endl;
+    const int32_t iter = svc.core().get_current_iteration();
+    if (checkpoint_interval > 0 && svc.core().version() > 0) {
+      const int32_t epoch = iter / checkpoint_interval;
+      const std::string path = "checkpoint_epoch_" + std::to_string(epoch) + ".ckpt";
+      if (svc.core().save_checkpoint(epoch, path))
+        std::cout << "saved checkpoint: " << path << " (epoch " << epoch << ")" << std::endl;
+    }
+    svc.shutdown();
+  });
+  svc.serve_forever();  // returns once the stopper has shut the service down
+  stopper.join();
 }
 
 }  // namespace psb

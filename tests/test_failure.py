@@ -487,3 +487,39 @@ def test_eight_ranks_hammer_the_control_plane(tmp_path):
         for c in clients:
             c.close()
         cc._stop(proc)
+
+
+def test_planned_stop_writes_a_last_checkpoint(tmp_path):
+    """SIGTERM (systemctl stop, Ctrl-C): the parameter server saves where its periodic
+    checkpoints go, exits 0, and --resume=latest continues from the very last update."""
+    ps_port, co_port = free_port(), free_port()
+    argv = [f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "1", "1000", "--resume=latest"]
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    ps = Proc(argv, str(tmp_path), str(tmp_path / "ps1.log"))
+    ps2 = None
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "37", "--quiet"],
+                           capture_output=True, text=True, timeout=60, cwd=tmp_path)
+        assert "done=37" in w.stdout
+        assert not list(tmp_path.glob("*.ckpt")), "no periodic checkpoint is due yet (interval 1000)"
+        ps.p.send_signal(signal.SIGTERM)
+        assert ps.p.wait(timeout=20) == 0
+        out = ps.output()
+        assert "signal 15: shutting down" in out
+        assert "saved checkpoint: checkpoint_epoch_0.ckpt (epoch 0)" in out
+        ps2 = Proc(argv, str(tmp_path), str(tmp_path / "ps2.log"))
+        assert wait_port(ps_port)
+        end = time.time() + 5
+        while time.time() < end and "resumed from" not in ps2.output():
+            time.sleep(0.05)
+        assert "resumed from checkpoint_epoch_0.ckpt (epoch 0, iteration 36)" in ps2.output()
+        w = subprocess.run([f"{BIN}/worker_main", f"127.0.0.1:{co_port}", "0", "40", "--join", "--quiet"],
+                           capture_output=True, text=True, timeout=60, cwd=tmp_path)
+        assert "joining at iteration 36" in w.stdout and "done=4" in w.stdout, w.stdout
+    finally:
+        ps.stop() if ps.p.poll() is None else ps.f.close()
+        if ps2:
+            ps2.stop()
+        co.stop()
