@@ -523,3 +523,25 @@ def test_planned_stop_writes_a_last_checkpoint(tmp_path):
         if ps2:
             ps2.stop()
         co.stop()
+
+
+def test_c_example_of_the_control_abi(tmp_path):
+    """examples/control_client.c: include/psb_control.h used from plain C (two processes)."""
+    exe = str(tmp_path / "control_client")
+    native = os.path.join(os.path.dirname(cc.LIB_PATH), "")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"),
+                    os.path.join(root, "examples", "control_client.c"), "-L", native, "-lpsb_control",
+                    f"-Wl,-rpath,{native}", "-o", exe], check=True)
+    proc, addr = cc.spawn_coordinator(env=FAST, log_path=str(tmp_path / "co.log"))
+    try:
+        ps = [subprocess.Popen([exe, addr, str(r), "2"], stdout=subprocess.PIPE, text=True)
+              for r in range(2)]
+        outs = [p.communicate(timeout=60)[0] for p in ps]
+        for r, (p, out) in enumerate(zip(ps, outs)):
+            assert p.returncode == 0, out
+            assert f"rank {r}: rank 0 says 'hello from 0'" in out
+            assert f"rank {r}: rank 1 says 'hello from 1'" in out
+            assert f"rank {r}: 2 worker(s) registered" in out
+    finally:
+        cc._stop(proc)
