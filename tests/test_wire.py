@@ -1,6 +1,7 @@
 """T0: the hand-written proto3 codec (csrc/wire/pb.h) against the protobuf runtime built from
 proto/*.proto — golden bytes of SURVEY.md App. A, every message of both reference services and
 the extension service, unpacked repeated scalars, unknown fields, negative int32."""
+import os
 import struct
 import subprocess
 
@@ -176,3 +177,16 @@ def test_decoders_never_crash_on_mutated_messages():
             assert r.returncode in (0, 3), (name, bytes(b).hex(), r.returncode)
             codes.add(r.returncode)
     assert codes == {0, 3}  # the mutations do produce both outcomes
+
+
+def test_public_headers_are_plain_c(tmp_path):
+    """include/psb_kernels.h and include/psb_control.h are the C ABI: they must compile as C11
+    (pedantic) and as C++11 without anything else on the include path."""
+    src = tmp_path / "abi.c"
+    src.write_text('#include "psb_kernels.h"\n#include "psb_control.h"\nint main(void) { return 0; }\n')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    inc = os.path.join(root, "include")
+    for cmd in (["gcc", "-std=c11", "-Wall", "-Wextra", "-Wpedantic", "-Werror"],
+                ["g++", "-std=c++11", "-Wall", "-Wextra", "-Werror", "-x", "c++"]):
+        r = subprocess.run(cmd + ["-I", inc, "-fsyntax-only", str(src)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
