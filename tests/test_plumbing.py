@@ -3,6 +3,7 @@ config 1), server-side optimizers and async / SSP modes through the unchanged wi
 periodic checkpoints, resume from a checkpoint, and a missing worker."""
 import os
 import random
+import re
 import subprocess
 import time
 
@@ -174,6 +175,12 @@ def test_example_script_trains_and_checkpoints(tmp_path):
                        env=env)
     assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
     assert "checkpoint" in r.stdout and ckpt.exists() and ckpt.stat().st_size > 1000
+    # the same script in bounded-staleness mode (host emulation of the async engine)
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "train_mlp.py"), "--steps", "8",
+                        "--mode", "ssp"], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
+    first, last = re.search(r"loss ([0-9.]+) -> ([0-9.]+)", r.stdout).groups()
+    assert float(last) < float(first)
 
 
 def test_python_worker_example_against_cpp_servers(tmp_path):
