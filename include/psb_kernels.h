@@ -449,6 +449,56 @@ int psb_mse_fwd_bf16(const void* a, const void* b, size_t n, float* scratch, flo
 int psb_mse_bwd_bf16(const void* a, const void* b, const float* gout, size_t n, void* da,
                      psb_stream_t stream);
 
+// ---------------------------------------------------------------------------
+// K5 — sparse embedding push / pull (sparse.cu).  No counterpart in the reference: its Tensor
+// is a dense `repeated float` (proto/parameter_server.proto:19-24) and every push carries the
+// whole model (src/worker.cpp:253-275).  Here an embedding table of `vocab` rows x `dim`
+// columns is row-sharded over the ranks (rank r owns rows [r*rows_per_rank, (r+1)*rows_per_rank)):
+// fp32 master rows (+ m, v) stay with the owner, a bf16 copy of the shard lives in the symmetric
+// heap.  Workers move only the rows a batch touches.
+//
+//   pull   out[i, :] = table[owner(idx[i])][idx[i] - owner*rows_per_rank, :]   (bf16, peer loads;
+//          an index outside [0, vocab) yields a zero row — padding)
+//   push   every worker w stages {count, idx[count], grad[count, dim]} in its own heap range;
+//          between two device barriers (caller: psb_device_barrier) the owner runs
+//          psb_sparse_apply: (1) mark — every staged index it owns gets a slot in a compact
+//          accumulator (atomicCAS on slot[row], atomic counter), (2) accumulate — the staged
+//          gradient rows are read from the peers (only the rows this rank owns cross NVLink)
+//          and added in fp32 (float4 atomics: the order of a row's duplicates is not fixed, so
+//          sums of >2 contributions can differ in the last bit between runs), (3) apply — one
+//          warp per touched row: g * grad_scale through the same update as K1/K3
+//          (SGD / momentum / Adam(W), *lazy*: rows without a gradient keep their state),
+//          master + bf16 row written, accumulator row and slot cleared for the next step.
+// dim % 8 == 0 (16-byte vectors).  acc holds world*cap rows of dim floats and starts zeroed,
+// slot holds rows_per_rank int32 and starts at -1 (psb_sparse_init), n_touched starts at 0.
+// ---------------------------------------------------------------------------
+typedef struct PsbSparse {
+  PsbFabric fabric;
+  const void* table[PSB_MAX_PEERS];       // peer-mapped bf16 shard [rows_per_rank, dim]
+  const void* stage_idx[PSB_MAX_PEERS];   // peer-mapped int64 [cap]
+  const void* stage_grad[PSB_MAX_PEERS];  // peer-mapped [cap, dim] gradient rows (grad_dtype)
+  const void* stage_cnt[PSB_MAX_PEERS];   // peer-mapped uint32: entries staged by that worker
+  int64_t vocab;
+  int64_t rows_per_rank;
+  int32_t dim;
+  int32_t cap;          // staging capacity per worker (entries)
+  int32_t grad_dtype;   // PSB_F32 / PSB_BF16
+  int32_t reserved;
+  float* master;        // owner-local [rows_per_rank, dim]
+  float* m;             // optional (momentum / Adam)
+  float* v;             // optional (Adam)
+  int32_t* slot;        // [rows_per_rank], -1 = untouched
+  int32_t* touched;     // [world * cap] local rows that received a gradient this step
+  uint32_t* n_touched;  // device word
+  float* acc;           // [world * cap, dim] fp32 accumulator, zero between steps
+  const uint32_t* step; // device word: completed optimizer steps (Adam bias correction)
+  PsbOptim opt;
+} PsbSparse;
+int psb_sparse_init(int32_t* slot, int64_t rows, psb_stream_t stream);  // slot[:] = -1
+int psb_sparse_pull(const PsbSparse* s, const int64_t* idx, int64_t n, void* out_bf16,
+                    psb_stream_t stream);
+int psb_sparse_apply(const PsbSparse* s, psb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,6 +7,7 @@ peer memory, parameter pull an all-gather fused into the first tcgen05 GEMM.
 """
 from . import _lib
 from .ops.native import OptimConfig
+from .parallel.sparse import ShardedEmbedding
 from .trainer import Context, Trainer, init
 
 
@@ -18,5 +19,5 @@ def __getattr__(name):  # host-plane client: needs grpcio, so imported on first 
 
 
 __version__ = "0.1.0"
-__all__ = ["OptimConfig", "Context", "Trainer", "init", "RemoteParameterServer", "RemoteTrainer",
-           "_lib"]
+__all__ = ["OptimConfig", "Context", "Trainer", "init", "ShardedEmbedding",
+           "RemoteParameterServer", "RemoteTrainer", "_lib"]

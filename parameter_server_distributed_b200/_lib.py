@@ -95,6 +95,17 @@ class PsbGemm(C.Structure):
                 ("bias_dtype", C.c_int32), ("lda", C.c_int32), ("ldb", C.c_int32)]
 
 
+class PsbSparse(C.Structure):
+    _fields_ = [("fabric", PsbFabric), ("table", C.c_void_p * MAX_PEERS),
+                ("stage_idx", C.c_void_p * MAX_PEERS), ("stage_grad", C.c_void_p * MAX_PEERS),
+                ("stage_cnt", C.c_void_p * MAX_PEERS), ("vocab", C.c_int64),
+                ("rows_per_rank", C.c_int64), ("dim", C.c_int32), ("cap", C.c_int32),
+                ("grad_dtype", C.c_int32), ("reserved", C.c_int32), ("master", C.c_void_p),
+                ("m", C.c_void_p), ("v", C.c_void_p), ("slot", C.c_void_p),
+                ("touched", C.c_void_p), ("n_touched", C.c_void_p), ("acc", C.c_void_p),
+                ("step", C.c_void_p), ("opt", PsbOptim)]
+
+
 class PsbError(RuntimeError):
     pass
 
@@ -172,6 +183,9 @@ def _declare(lib) -> None:
         "psb_colsum_bf16": (i32, [vp, vp, i32, i32, i32, vp, vp]),
         "psb_mse_fwd_bf16": (i32, [vp, vp, sz, vp, vp, vp]),
         "psb_mse_bwd_bf16": (i32, [vp, vp, vp, sz, vp, vp]),
+        "psb_sparse_init": (i32, [vp, C.c_int64, vp]),
+        "psb_sparse_pull": (i32, [C.POINTER(PsbSparse), vp, C.c_int64, vp, vp]),
+        "psb_sparse_apply": (i32, [C.POINTER(PsbSparse), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -1,0 +1,185 @@
+"""K5 sparse embedding push / pull, host path (CPU tensors, gloo): the oracle of the kernels in
+csrc/kernels/sparse.cu and the proof that the shard / staging / mean logic is right without a GPU.
+Oracles are independent of the implementation: torch.nn.Embedding + torch.optim (dense SGD on
+the summed gradient, SparseAdam for the lazy Adam)."""
+import multiprocessing as mp
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+
+from parameter_server_distributed_b200 import OptimConfig
+from parameter_server_distributed_b200.parallel.sparse import ShardedEmbedding, _init_rows
+
+V, D = 1000, 16
+
+
+def test_init_is_independent_of_the_shard_layout():
+    whole = _init_rows(0, 9000, 8, 0.02, seed=3)
+    parts = torch.cat([_init_rows(lo, hi, 8, 0.02, seed=3)
+                       for lo, hi in ((0, 2250), (2250, 4500), (4500, 6750), (6750, 9000))])
+    assert torch.equal(whole, parts)
+    assert abs(whole.std().item() - 0.02) < 1e-3
+
+
+def test_pull_returns_rows_and_zero_rows_for_padding():
+    e = ShardedEmbedding(V, D, OptimConfig(kind="sgd", lr=0.1), capacity=64)
+    idx = torch.tensor([[0, 5, 999], [-1, 1000, 5]])
+    out = e.pull(idx)
+    assert out.shape == (2, 3, D) and out.dtype == torch.bfloat16
+    assert torch.equal(out[0, 1], e.master[5].to(torch.bfloat16))
+    assert torch.equal(out[0, 2], e.master[999].to(torch.bfloat16))
+    assert out[1, 0].abs().sum() == 0 and out[1, 1].abs().sum() == 0
+    assert torch.equal(out[1, 2], out[0, 1])
+
+
+def test_sgd_push_matches_dense_embedding_with_duplicates():
+    e = ShardedEmbedding(V, D, OptimConfig(kind="sgd", lr=0.5), capacity=256,
+                         grad_dtype=torch.float32)
+    ref = torch.nn.Embedding(V, D)
+    ref.weight.data.copy_(e.master)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.5)
+    gen = torch.Generator().manual_seed(0)
+    for _ in range(4):
+        idx = torch.randint(0, V, (200,), generator=gen)
+        idx[:20] = idx[20:40]  # duplicates are summed
+        w = torch.randn(200, D, generator=gen)
+        opt.zero_grad()
+        (ref(idx) * w).sum().backward()
+        opt.step()
+        e.push(idx, w)
+    assert (e.master - ref.weight.data).abs().max() < 1e-5
+    assert torch.equal(e.table, e.master.to(torch.bfloat16))
+
+
+def test_lazy_adam_matches_torch_sparse_adam():
+    e = ShardedEmbedding(V, D, OptimConfig(kind="adam", lr=0.01), capacity=256,
+                         grad_dtype=torch.float32)
+    ref = torch.nn.Embedding(V, D, sparse=True)
+    ref.weight.data.copy_(e.master)
+    opt = torch.optim.SparseAdam(ref.parameters(), lr=0.01)
+    gen = torch.Generator().manual_seed(1)
+    for _ in range(5):
+        idx = torch.randint(0, 50, (64,), generator=gen)  # small range: rows come back
+        w = torch.randn(64, D, generator=gen)
+        opt.zero_grad()
+        (ref(idx) * w).sum().backward()
+        opt.step()
+        e.push(idx, w)
+    # SparseAdam puts eps outside the bias correction: a difference of order eps
+    assert (e.master - ref.weight.data).abs().max() < 1e-5
+    untouched = torch.ones(V, dtype=torch.bool)
+    untouched[:50] = False
+    assert e.m[untouched].abs().sum() == 0 and e.v[untouched].abs().sum() == 0
+
+
+def test_lookup_collects_gradients_of_several_lookups_into_one_push():
+    e = ShardedEmbedding(V, D, OptimConfig(kind="sgd", lr=1.0), capacity=64,
+                         grad_dtype=torch.float32)
+    before = e.master.clone()
+    a, b = torch.tensor([1, 2, 2]), torch.tensor([[7], [1]])
+    loss = e.lookup(a).float().sum() + 2 * e.lookup(b).float().sum()
+    loss.backward()
+    e.apply_gradients()
+    want = before.clone()
+    want[1] -= 1 + 2
+    want[2] -= 2
+    want[7] -= 2
+    assert (e.master - want).abs().max() < 1e-6
+    assert e.steps == 1
+    e.apply_gradients()  # nothing pending: an empty push is still a (collective) step
+    assert e.steps == 2 and (e.master - want).abs().max() < 1e-6
+
+
+def test_capacity_and_shape_errors():
+    e = ShardedEmbedding(V, D, OptimConfig(), capacity=4)
+    with pytest.raises(ValueError, match="capacity"):
+        e.push(torch.arange(5), torch.zeros(5, D))
+    with pytest.raises(ValueError, match="one gradient row"):
+        e.push(torch.arange(3), torch.zeros(2, D))
+    with pytest.raises(ValueError, match="multiple of 8"):
+        ShardedEmbedding(V, 12, OptimConfig(), capacity=4)
+
+
+def test_state_dict_round_trip_continues_identically():
+    cfg = OptimConfig(kind="adamw", lr=0.01, weight_decay=0.1)
+    a = ShardedEmbedding(V, D, cfg, capacity=64, grad_dtype=torch.float32)
+    gen = torch.Generator().manual_seed(2)
+    batches = [(torch.randint(0, 30, (32,), generator=gen), torch.randn(32, D, generator=gen))
+               for _ in range(4)]
+    for i, g in batches[:2]:
+        a.push(i, g)
+    b = ShardedEmbedding(V, D, cfg, capacity=64, grad_dtype=torch.float32, seed=9)
+    b.load_state_dict(a.state_dict())
+    for i, g in batches[2:]:
+        a.push(i, g)
+        b.push(i, g)
+    assert torch.equal(a.master, b.master) and torch.equal(a.table, b.table)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, kind, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = OptimConfig(kind=kind, lr=0.05)
+    e = ShardedEmbedding(V + 3, D, cfg, capacity=128, rank=rank, world=world,
+                         grad_dtype=torch.float32)       # V + 3: the last shard is shorter
+    one = ShardedEmbedding(V + 3, D, cfg, capacity=128 * world, grad_dtype=torch.float32)
+    gen = torch.Generator().manual_seed(5)
+    for _ in range(3):
+        idx = torch.randint(0, V + 3, (world, 100), generator=gen)
+        idx[:, :10] = idx[0, :10]                          # rows pushed by every worker
+        g = torch.randn(world, 100, D, generator=gen)
+        e.push(idx[rank], g[rank])
+        one.push(idx.reshape(-1), g.reshape(-1, D) / world)  # oracle: one worker, mean gradient
+    full = e.full_table()
+    err = (full.float() - one.table.float()).abs().max().item()
+    own = (e.master[:e.hi - e.lo] - one.master[e.lo:e.hi]).abs().max().item()
+    q.put((rank, err, own))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("kind,world", [("sgd", 2), ("adam", 3)])
+def test_gloo_workers_match_one_worker_with_the_mean_gradient(kind, world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, kind, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err, own in res:
+        assert own < 1e-5, (rank, own)
+        assert err < 1e-2, (rank, err)   # bf16 rows
+
+
+@pytest.mark.parametrize("nproc", [1, 2])
+def test_example_trains_a_sharded_table_with_a_dense_tower(nproc):
+    """examples/train_embedding.py: ShardedEmbedding + EmbeddingMLP + the dense engine end to end
+    on the host path; exit code 0 means the loss went down."""
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = os.path.join(root, "examples", "train_embedding.py")
+    cmd = [sys.executable, script] if nproc == 1 else [
+        sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1",
+        "--nproc-per-node", str(nproc), script]
+    r = subprocess.run(cmd + ["--steps", "30"], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert r.returncode == 0, r.stdout[-600:] + r.stderr[-600:]
+    first, last = re.search(r"loss ([0-9.]+) -> ([0-9.]+)", r.stdout).groups()
+    assert float(last) < 0.8 * float(first)
