@@ -60,6 +60,18 @@ SECTIONS = [
     ("async_plan_kernel", ["LD.E.STRONG.SYS", "ST.E", "STG"],
      "async / SSP owner plan: per bucket, which workers have an unapplied clock (mask) and where their "
      "gradient ring slot is (offset)"),
+    ("sparse_pull_kernel", ["LDG.E.NA.128", "STG.E.NA.128", "LDG.E.64", "STG.E.128"],
+     "K5 sparse pull: a sub-warp per requested row, 16-byte loads that bypass L1 from the owner's bf16 "
+     "shard (a peer address over NVLink), 16-byte stores; zero rows for padding ids"),
+    ("sparse_mark_kernel", ["ATOMG", "LDG.E.64.STRONG.SYS", "LDG.E.STRONG.SYS", "STG.E"],
+     "K5 sparse push, mark: strong loads of the workers' staged counts / ids, atomicCAS claims the row, "
+     "an atomic counter hands out the accumulator slot"),
+    ("sparse_accumulate_kernelILi1E", ["REDG", "LDG.E.NA.128", "LDG.E.64.STRONG.SYS"],
+     "K5 sparse push, accumulate (bf16 gradients): staged rows read from the worker's heap range, added "
+     "into the slot's fp32 row with 16-byte vector reductions (REDG.E.ADD.F32x4)"),
+    ("sparse_apply_kernelILi3E", ["LDG.E.128", "STG.E.128", "MUFU.RSQ", "MUFU.SQRT", "F2FP"],
+     "K5 sparse push, apply (AdamW): one sub-warp per touched row - accumulator row read and zeroed, "
+     "master / m / v updated, bf16 row rewritten, slot released"),
 ]
 MNEMONICS = (r"\b(LDTM|SYNCS|UBLKCP|UCGABAR|UTCATOMSWS|UTCBAR|UTCHMMA|UTMALDG|UTMASTG|UTMACCTL|"
              r"UGETNEXTWORKID|UTMACMDFLUSH|LDGMC|LDG\.E[A-Z0-9.]*256|STG\.E[A-Z0-9.]*256)[A-Za-z0-9_.]*")
@@ -125,7 +137,7 @@ def main() -> int:
                 "# static shared bytes, local bytes.  Regenerate with `python benchmarks/sass_excerpts.py`.\n")
         f.write(f"{'REG':>4} {'STACK':>6} {'SHARED':>7} {'LOCAL':>6}  kernel\n")
         for (n, reg, stack, shared, local), d in sorted(zip(rows, demangled), key=lambda x: x[1]):
-            f.write(f"{reg:4d} {stack:6d} {shared:7d} {local:6d}  {re.sub(r'\(.*', '', d)[:100]}\n")
+            f.write(f"{reg:4d} {stack:6d} {shared:7d} {local:6d}  {re.sub(r'\(.*', '', d.replace('(anonymous namespace)::', ''))[:100]}\n")
     return 0
 
 
