@@ -13,7 +13,7 @@ endif
 
 WIRE_SRC := csrc/wire/hpack.cpp csrc/wire/h2.cpp csrc/wire/grpc_lite.cpp
 COORD_SRC := csrc/control/coordinator_core.cpp csrc/control/coordinator_service.cpp
-PS_SRC := csrc/ps/ps_core.cpp csrc/ps/ps_device.cpp csrc/ps/ps_service.cpp
+PS_SRC := csrc/ps/ps_core.cpp csrc/ps/ps_device.cpp csrc/ps/ps_sparse.cpp csrc/ps/ps_service.cpp
 WORKER_SRC := csrc/worker/worker.cpp
 HDRS := $(wildcard csrc/*/*.h) include/psb_kernels.h
 

@@ -38,7 +38,7 @@ pb::Tensor to_pb(HostTensor&& h) {
 
 ParameterServerService::ParameterServerService(int total_workers, int checkpoint_interval,
                                                const PsOptions& opt, int checkpoint_scan_ms)
-    : core_(total_workers, opt), checkpoint_interval_(checkpoint_interval),
+    : core_(total_workers, opt), sparse_(opt), checkpoint_interval_(checkpoint_interval),
       scan_ms_(checkpoint_scan_ms), configured_workers_(total_workers) {
   const std::string base = "/parameter_server.ParameterServer/";
   server_.add(base + "ReceiveGradients", [this](std::string_view req, grpc_lite::Reply& resp) {
@@ -102,6 +102,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     if (path.empty()) path = "checkpoint_epoch_" + std::to_string(in.epoch) + ".ckpt";
     pb::SaveCheckpointResponse out;
     out.success = core_.save_checkpoint(in.epoch, path);
+    if (out.success && !sparse_.empty()) out.success = sparse_.save(path + ".tables");
     if (out.success) {
       out.message = "checkpoint saved";
       out.checkpoint_path = path;
@@ -117,6 +118,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     pb::LoadCheckpointResponse out;
     int32_t epoch = 0;
     out.success = core_.load_checkpoint(in.path, epoch);
+    if (out.success) sparse_.load(in.path + ".tables");  // absent when the job has no tables
     if (out.success) {
       out.message = "checkpoint loaded";
       out.epoch = epoch;
@@ -125,6 +127,51 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
       out.message = "failed to load checkpoint";
     }
     resp = out.encode();
+    return Status{};
+  });
+  // ---- sparse embedding tables (proto/psb_ext.proto: service psb.ParameterServerExt)
+  const std::string ext = "/psb.ParameterServerExt/";
+  server_.add(ext + "CreateTable", [this](std::string_view req, grpc_lite::Reply& resp) {
+    pb::TableSpec in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed TableSpec"};
+    pb::Ack out;
+    out.success = sparse_.create(in.name, in.rows, in.dim, in.init_std, in.seed);
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(ext + "PushSparse", [this](std::string_view req, grpc_lite::Reply& resp) {
+    pb::SparsePush in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed SparsePush"};
+    std::vector<SparseGrad> grads;
+    grads.reserve(in.tables.size());
+    for (auto& t : in.tables) {
+      SparseGrad g;
+      g.name = std::move(t.name), g.dim = t.dim;
+      g.indices = std::move(t.indices), g.values = std::move(t.values);
+      grads.push_back(std::move(g));
+    }
+    pb::SparsePushResponse out;
+    std::string err;
+    out.aggregation_complete = sparse_.push(in.worker_id, in.iteration, std::move(grads),
+                                            core_.get_total_workers(), out.workers_received, err);
+    out.success = err.empty();
+    out.message = err.empty() ? "sparse gradients received" : err;
+    out.total_workers = core_.get_total_workers();
+    bytes_in_ += req.size();
+    resp = out.encode();
+    return Status{};
+  });
+  server_.add(ext + "PullRows", [this](std::string_view req, grpc_lite::Reply& resp) {
+    pb::RowsRequest in;
+    if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed RowsRequest"};
+    pb::RowsResponse out;
+    out.ready = sparse_.ready(in.iteration, core_.options().long_poll_ms);
+    if (!sparse_.rows(in.name, in.indices, out.values, out.dim)) {
+      out.ready = false;
+      out.message = "unknown table '" + in.name + "'";
+    }
+    resp = out.encode();
+    bytes_out_ += resp.body.size();
     return Status{};
   });
   if (checkpoint_interval_ > 0)
@@ -189,6 +236,7 @@ void ParameterServerService::periodic_checkpoint() {
     if (epoch > last_epoch && iter > 0) {
       const std::string path = "checkpoint_epoch_" + std::to_string(epoch) + ".ckpt";
       if (core_.save_checkpoint(epoch, path)) {
+        if (!sparse_.empty()) sparse_.save(path + ".tables");
         last_epoch = epoch;
         std::cout << "saved checkpoint: " << path << " (epoch " << epoch << ")" << std::endl;
       }
@@ -224,7 +272,7 @@ void ParameterServerService::membership_loop(std::string coordinator_address, in
     if (seen_full && live >= 1 && live < configured_workers_) target = live;
     const int cur = core_.get_total_workers();
     if (target != cur) {
-      const int completed = core_.set_total_workers(target);
+      const int completed = core_.set_total_workers(target) + sparse_.set_total_workers(target);
       std::cout << "membership: total_workers " << cur << " -> " << target << " (" << live
                 << " live), " << completed << " pending iteration(s) completed" << std::endl;
     }
@@ -350,6 +398,7 @@ void run_server(const std::string& server_address, int total_workers, int checkp
     if (path.empty()) {
       std::cout << "resume: no checkpoint_epoch_*.ckpt here, starting empty" << std::endl;
     } else if (svc.core().load_checkpoint(path, epoch)) {
+      svc.sparse().load(path + ".tables");
       std::cout << "resumed from " << path << " (epoch " << epoch << ", iteration "
                 << svc.core().get_current_iteration() << ")" << std::endl;
     } else {
@@ -391,6 +440,7 @@ void run_server(const std::string& server_address, int total_workers, int checkp
     if (checkpoint_interval > 0 && svc.core().version() > 0) {
       const int32_t epoch = iter / checkpoint_interval;
       const std::string path = "checkpoint_epoch_" + std::to_string(epoch) + ".ckpt";
+      if (!svc.sparse().empty()) svc.sparse().save(path + ".tables");
       if (svc.core().save_checkpoint(epoch, path))
         std::cout << "saved checkpoint: " << path << " (epoch " << epoch << ")" << std::endl;
     }

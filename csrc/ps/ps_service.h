@@ -10,6 +10,7 @@
 
 #include "../wire/h2.h"
 #include "ps_core.h"
+#include "ps_sparse.h"
 
 namespace psb {
 
@@ -37,6 +38,10 @@ class ParameterServerService {
   void start();
   void shutdown();
   ParameterServerCore& core() { return core_; }
+  // Sparse embedding tables (service psb.ParameterServerExt: CreateTable / PushSparse /
+  // PullRows); they follow the same membership and are saved next to every checkpoint
+  // (`<path>.tables`).  No counterpart in the reference.
+  SparseTables& sparse() { return sparse_; }
   // Observability (the reference prints nothing but its start-up lines): one JSON
   // line on stdout every `every_s` seconds — iteration, model version, live worker count, RPC
   // and byte counters, mean time of a push inside the core.  --stats-every-s / PSB_STATS_EVERY_S.
@@ -56,6 +61,7 @@ class ParameterServerService {
   std::shared_ptr<const std::string> serve_cache_;
   int64_t serve_cache_version_ = -1;
   ParameterServerCore core_;
+  SparseTables sparse_;
   grpc_lite::Server server_;
   int checkpoint_interval_;
   int scan_ms_;

@@ -54,6 +54,12 @@ int main(int argc, char** argv) {
       {"psb.HandleQuery", roundtrip<HandleQuery>},
       {"psb.HandleList", roundtrip<HandleList>},
       {"psb.Ack", roundtrip<Ack>},
+      {"psb.TableSpec", roundtrip<TableSpec>},
+      {"psb.SparseRows", roundtrip<SparseRows>},
+      {"psb.SparsePush", roundtrip<SparsePush>},
+      {"psb.SparsePushResponse", roundtrip<SparsePushResponse>},
+      {"psb.RowsRequest", roundtrip<RowsRequest>},
+      {"psb.RowsResponse", roundtrip<RowsResponse>},
   };
   auto it = table.find(argv[1]);
   if (it == table.end()) return 2;

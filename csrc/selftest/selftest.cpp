@@ -164,8 +164,62 @@ static int sharded_parameter_servers() {
   return 0;
 }
 
+// Sparse tables (ps_sparse.h): sync staging and completion, membership shrink completing a
+// pending iteration with the live worker's gradient alone, lazy updates, async once-per-clock,
+// save / load with optimizer state.
+static int sparse_tables() {
+  using namespace psb;
+  auto grad = [](std::vector<int64_t> idx, float v, int dim) {
+    SparseGrad g;
+    g.name = "emb", g.dim = dim, g.indices = std::move(idx);
+    g.values.assign(g.indices.size() * dim, v);
+    return std::vector<SparseGrad>{g};
+  };
+  PsOptions o;
+  o.optimizer = "momentum", o.lr = 0.5f, o.momentum = 0.5f;
+  SparseTables t(o);
+  CHECK(t.create("emb", 10, 2, 0.0f, 0) && t.create("emb", 10, 2, 0.5f, 9) && !t.create("emb", 10, 4, 0, 0));
+  CHECK(!t.create("", 1, 1, 0, 0) && !t.create("x", 0, 1, 0, 0));
+  int32_t got = 0, dim = 0;
+  std::string err;
+  std::vector<float> rows;
+  CHECK(!t.push(0, 0, grad({1, 1, 3, -1, 10}, 1.0f, 2), 2, got, err) && got == 1 && err.empty());
+  CHECK(!t.ready(0, 0) && t.ready(-1, 0));
+  CHECK(t.push(1, 0, grad({1}, 2.0f, 2), 2, got, err) && got == 2 && t.ready(0, 0));
+  CHECK(t.push(1, 0, grad({1}, 2.0f, 2), 2, got, err));  // idempotent after completion
+  CHECK(t.rows("emb", {1, 3, 0, -1, 10}, rows, dim) && dim == 2 && rows.size() == 10);
+  // row 1: (1 + 1 + 2) / 2 = 2 -> m = 2, p = -1; row 3: 1 / 2 -> m = .5, p = -.25; row 0 untouched
+  CHECK(std::fabs(rows[0] + 1.0f) < 1e-6f && std::fabs(rows[2] + 0.25f) < 1e-6f && rows[4] == 0.0f);
+  CHECK(rows[6] == 0.0f && rows[8] == 0.0f);
+  // a pending iteration completes when the membership shrinks to the worker that did push
+  CHECK(!t.push(0, 1, grad({3}, 1.0f, 2), 2, got, err) && !t.ready(1, 0));
+  CHECK(t.set_total_workers(1) == 1 && t.ready(1, 0));
+  CHECK(t.rows("emb", {3}, rows, dim));
+  CHECK(std::fabs(rows[0] - (-0.25f - 0.5f * (0.5f * 0.5f + 1.0f))) < 1e-6f);  // divisor = 1 pusher
+  // malformed pushes are rejected whole
+  CHECK(!t.push(0, 2, grad({1}, 1.0f, 4), 1, got, err) && !err.empty());
+  const std::string path = "/tmp/psb_selftest.tables";
+  CHECK(t.save(path));
+  SparseTables u(o);
+  CHECK(u.load(path));
+  std::vector<float> a, b;
+  err.clear();
+  CHECK(t.push(0, 5, grad({1, 3}, 1.0f, 2), 1, got, err) && u.push(0, 5, grad({1, 3}, 1.0f, 2), 1, got, err));
+  CHECK(t.rows("emb", {0, 1, 3}, a, dim) && u.rows("emb", {0, 1, 3}, b, dim) && a == b);  // state too
+  std::remove(path.c_str());
+  // async: a share of 1 / N at once, each clock once
+  PsOptions as;
+  as.mode = PsMode::kAsync, as.lr = 1.0f;
+  SparseTables v(as);
+  CHECK(v.create("emb", 4, 2, 0.0f, 0));
+  CHECK(v.push(0, 0, grad({2}, 1.0f, 2), 2, got, err) && v.push(0, 0, grad({2}, 1.0f, 2), 2, got, err));
+  CHECK(v.rows("emb", {2}, rows, dim) && std::fabs(rows[0] + 0.5f) < 1e-6f);
+  return 0;
+}
+
 int main() {
   using namespace psb;
+  if (sparse_tables() != 0) return 1;
   if (hpack_rfc_vectors() != 0) return 1;
   if (threads_do_not_change_results() != 0) return 1;
   if (sharded_parameter_servers() != 0) return 1;

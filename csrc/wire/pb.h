@@ -75,6 +75,17 @@ class Writer {
     varint(inner.buf.size());
     buf.append(inner.buf);
   }
+  void f32(int field, float v) {
+    if (v == 0.0f) return;
+    tag(field, kFixed32);
+    buf.append(reinterpret_cast<const char*>(&v), 4);
+  }
+  void packed_sfixed64(int field, const int64_t* data, size_t n) {
+    if (n == 0) return;
+    tag(field, kLen);
+    varint(n * 8);
+    buf.append(reinterpret_cast<const char*>(data), n * 8);  // little-endian host
+  }
   void packed_f32(int field, const float* data, size_t n) {
     if (n == 0) return;
     tag(field, kLen);
@@ -131,6 +142,16 @@ class Reader {
     uint32_t v;
     memcpy(&v, p_, 4);
     p_ += 4;
+    return v;
+  }
+  uint64_t fixed64() {
+    if (end_ - p_ < 8) {
+      ok_ = false;
+      return 0;
+    }
+    uint64_t v;
+    memcpy(&v, p_, 8);
+    p_ += 8;
     return v;
   }
   void skip(int wt) {

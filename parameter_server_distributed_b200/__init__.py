@@ -12,7 +12,7 @@ from .trainer import Context, Trainer, init
 
 
 def __getattr__(name):  # host-plane client: needs grpcio, so imported on first use
-    if name in ("RemoteParameterServer", "RemoteTrainer"):
+    if name in ("RemoteParameterServer", "RemoteTrainer", "RemoteEmbedding"):
         from .control import remote
         return getattr(remote, name)
     raise AttributeError(name)
@@ -20,4 +20,4 @@ def __getattr__(name):  # host-plane client: needs grpcio, so imported on first 
 
 __version__ = "0.1.0"
 __all__ = ["OptimConfig", "Context", "Trainer", "init", "ShardedEmbedding",
-           "RemoteParameterServer", "RemoteTrainer", "_lib"]
+           "RemoteParameterServer", "RemoteTrainer", "RemoteEmbedding", "_lib"]

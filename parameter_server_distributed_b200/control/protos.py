@@ -44,6 +44,11 @@ SERVICES = {
         "PutHandle": ("psb.HandleBlob", "psb.Ack"),
         "GetHandles": ("psb.HandleQuery", "psb.HandleList"),
     },
+    "psb.ParameterServerExt": {
+        "CreateTable": ("psb.TableSpec", "psb.Ack"),
+        "PushSparse": ("psb.SparsePush", "psb.SparsePushResponse"),
+        "PullRows": ("psb.RowsRequest", "psb.RowsResponse"),
+    },
 }
 
 

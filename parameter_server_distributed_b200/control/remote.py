@@ -163,6 +163,67 @@ def decode_parameter_update(buf: bytes) -> Tuple[int, bool, List[Tuple[str, Tupl
     return iteration, ready, tensors
 
 
+def encode_sparse_push(worker_id: int, iteration: int,
+                       tables: Iterable[Tuple[str, int, np.ndarray, np.ndarray]]) -> bytes:
+    """psb.SparsePush from (name, dim, int64 ids, fp32 values[len(ids), dim]) entries; ids and
+    values go out as packed sfixed64 / float blocks straight from numpy."""
+    out = bytearray()
+    if worker_id:
+        out += b"\x08" + _varint(worker_id)
+    if iteration:
+        out += b"\x10" + _varint(iteration)
+    for name, dim, ids, vals in tables:
+        ids = np.ascontiguousarray(ids, dtype="<i8").ravel()
+        vals = np.ascontiguousarray(vals, dtype="<f4").ravel()
+        if vals.size != ids.size * dim:
+            raise ValueError(f"table {name!r}: {vals.size} values for {ids.size} rows of {dim}")
+        body = bytearray()
+        nb = name.encode()
+        body += b"\x0a" + _varint(len(nb)) + nb
+        if dim:
+            body += b"\x10" + _varint(dim)
+        if ids.size:
+            body += b"\x1a" + _varint(ids.nbytes) + ids.tobytes()
+            body += b"\x22" + _varint(vals.nbytes) + vals.tobytes()
+        out += b"\x1a" + _varint(len(body)) + body
+    return bytes(out)
+
+
+def decode_rows_response(buf: bytes) -> Tuple[bool, int, np.ndarray, str]:
+    """psb.RowsResponse -> (ready, dim, fp32 values (flat, read-only view), message)."""
+    view = memoryview(buf)
+    pos, ready, dim, msg = 0, False, 0, ""
+    vals = np.empty(0, dtype="<f4")
+    singles: List[float] = []
+    while pos < len(buf):
+        tag, pos = _read_varint(view, pos)
+        field, wt = tag >> 3, tag & 7
+        if wt == 0:
+            v, pos = _read_varint(view, pos)
+            if field == 1:
+                ready = bool(v)
+            elif field == 2:
+                dim = _int32(v)
+        elif wt == 2:
+            n, pos = _read_varint(view, pos)
+            if field == 3:
+                vals = np.frombuffer(view[pos:pos + n], dtype="<f4")
+            elif field == 4:
+                msg = bytes(view[pos:pos + n]).decode(errors="replace")
+            pos += n
+        elif wt == 5:
+            if field == 3:  # an unpacked repeated float
+                singles.append(float(np.frombuffer(view[pos:pos + 4], dtype="<f4")[0]))
+            pos += 4
+        elif wt == 1:
+            pos += 8
+        else:
+            raise ValueError(f"unsupported wire type {wt}")
+    if singles:
+        vals = np.concatenate([vals, np.asarray(singles, dtype="<f4")])
+    return ready, dim, vals, msg
+
+
 class RemoteParameterServer:
     """One worker's connection to the coordinator and the parameter server."""
 
@@ -202,6 +263,11 @@ class RemoteParameterServer:
         base = "/parameter_server.ParameterServer/"
         self._raw_pull = [ch.unary_unary(base + "ServeParameters", **raw) for ch in self._ps_chs]
         self._raw_push = [ch.unary_unary(base + "ReceiveGradients", **raw) for ch in self._ps_chs]
+        ext = "/psb.ParameterServerExt/"
+        self._raw_push_sparse = [ch.unary_unary(ext + "PushSparse", **raw) for ch in self._ps_chs]
+        self._raw_pull_rows = [ch.unary_unary(ext + "PullRows", **raw) for ch in self._ps_chs]
+        self._ext_stubs = [protos.Stub(ch, "psb.ParameterServerExt") for ch in self._ps_chs]
+        self._tables: Dict[str, Tuple[int, int, int]] = {}  # name -> (rows, dim, rows per shard)
         self.ps = self._stubs[0]
         self._pool = None
         if len(addrs) > 1:
@@ -343,10 +409,138 @@ class RemoteParameterServer:
                 raise RuntimeError(r.message)
         return rs[0].epoch
 
+    # ------------------------------------------------------------------ sparse embedding tables
+    # No counterpart in the reference (dense Tensor only, proto/parameter_server.proto:19-24).
+    # A table is row-sharded over the parameter servers of the job: shard k holds rows
+    # [k * R, (k + 1) * R), R = ceil(rows / shards) — the layout of the GPU plane's
+    # ``ShardedEmbedding``.  With one server that is the whole table.
+    def create_table(self, name: str, rows: int, dim: int, init_std: float = 0.0,
+                     seed: int = 0) -> None:
+        """Idempotent: every worker may call it; the first call creates the table."""
+        n = len(self._stubs)
+        per = (rows + n - 1) // n
+        Spec = protos.msg("psb.TableSpec")
+
+        def one(i, _stub):
+            local = max(0, min(per, rows - i * per))
+            if local == 0:
+                return True
+            return self._ext_stubs[i].CreateTable(
+                Spec(name=name, rows=local, dim=dim, init_std=init_std, seed=seed + i),
+                timeout=self.timeout).success
+        if not all(self._each_shard(one)):
+            raise RuntimeError(f"table {name!r} exists with another shape")
+        self._tables[name] = (rows, dim, per)
+
+    def _split_rows(self, name: str, ids: np.ndarray):
+        rows, dim, per = self._tables[name]
+        ids = np.asarray(ids, dtype=np.int64).ravel()
+        valid = (ids >= 0) & (ids < rows)
+        shard = np.where(valid, ids // per, -1)
+        return rows, dim, per, ids, shard
+
+    def push_sparse(self, iteration: int,
+                    grads: Iterable[Tuple[str, np.ndarray, np.ndarray]]) -> bool:
+        """PushSparse of (table, ids, values[len(ids), dim]) entries; every worker calls it once
+        per iteration (sync mode counts pushers like the dense push), empty ids are fine.
+        Returns whether the iteration is applied on every shard."""
+        n = len(self._stubs)
+        parts: List[list] = [[] for _ in range(n)]
+        for name, ids, vals in grads:
+            rows, dim, per, ids, shard = self._split_rows(name, ids)
+            vals = np.asarray(vals, dtype=np.float32).reshape(-1, dim)
+            for k in range(n):
+                pick = shard == k
+                parts[k].append((name, dim, ids[pick] - k * per, vals[pick]))
+        reqs = [encode_sparse_push(self.worker_id, iteration, p) for p in parts]
+        Resp = protos.msg("psb.SparsePushResponse")
+        rs = self._each_shard(lambda i, stub: Resp.FromString(self._retry(
+            lambda: self._raw_push_sparse[i](reqs[i], timeout=self.timeout), attempts=3)))
+        for r in rs:
+            if not r.success:
+                raise RuntimeError(f"sparse push refused: {r.message}")
+        return all(bool(r.aggregation_complete) for r in rs)
+
+    def pull_rows(self, name: str, ids: np.ndarray, after_iteration: int = -1,
+                  timeout_s: float = 30.0) -> np.ndarray:
+        """Rows ``ids`` of ``name`` as fp32 ``[len(ids), dim]`` (zero rows for ids outside the
+        table), once the sparse pushes of ``after_iteration`` are applied (-1: at once)."""
+        rows, dim, per, ids, shard = self._split_rows(name, ids)
+        n = len(self._stubs)
+        Req = protos.msg("psb.RowsRequest")
+        out = np.zeros((ids.size, dim), dtype=np.float32)
+        end = time.monotonic() + timeout_s
+
+        def one(k, _stub):
+            pick = np.nonzero(shard == k)[0]
+            if pick.size == 0 and after_iteration < 0:
+                return
+            req = Req(worker_id=self.worker_id, iteration=after_iteration, name=name)
+            req.indices.extend((ids[pick] - k * per).tolist())
+            body = req.SerializeToString()
+            while True:
+                ready, d, vals, msg = decode_rows_response(
+                    self._raw_pull_rows[k](body, timeout=self.timeout))
+                if msg:
+                    raise RuntimeError(msg)
+                if ready:
+                    out[pick] = vals.reshape(-1, dim)
+                    return
+                if time.monotonic() >= end:
+                    raise TimeoutError(f"sparse iteration {after_iteration} not applied on shard {k}")
+        self._each_shard(one)
+        return out
+
     def live_workers(self) -> List[int]:
         r = self.coord.ListWorkers(protos.msg("coordinator.ListWorkersRequest")(),
                                    timeout=self.timeout)
         return sorted(w.worker_id for w in r.workers)
+
+
+class RemoteEmbedding:
+    """An embedding table on the host-plane parameter server(s), with autograd.
+
+    ``lookup(ids)`` pulls the rows (fp32) and is differentiable; ``apply_gradients(iteration)``
+    pushes the row gradients the backward passes collected — once per iteration on every worker,
+    like the dense push — and makes the next ``lookup`` wait for that iteration's update.  The
+    host-plane sibling of ``parallel.sparse.ShardedEmbedding``; the reference has no sparse path
+    (dense ``Tensor`` only, /root/reference/proto/parameter_server.proto:19-24)."""
+
+    def __init__(self, ps: "RemoteParameterServer", name: str, vocab: int, dim: int,
+                 init_std: float = 0.02, seed: int = 0):
+        self.ps, self.name, self.vocab, self.dim = ps, name, int(vocab), int(dim)
+        ps.create_table(name, vocab, dim, init_std=init_std, seed=seed)
+        self.after = -1          # iteration whose sparse pushes the next pull must include
+        self._pending: List[Tuple[np.ndarray, np.ndarray]] = []
+
+    def lookup(self, ids):
+        import torch
+        emb = self
+
+        class _Lookup(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, anchor):
+                ctx.ids = ids.detach().reshape(-1).cpu().numpy()
+                rows = emb.ps.pull_rows(emb.name, ctx.ids, after_iteration=emb.after)
+                return torch.from_numpy(rows).view(*ids.shape, emb.dim)
+
+            @staticmethod
+            def backward(ctx, g):
+                emb._pending.append((ctx.ids, g.reshape(-1, emb.dim).float().cpu().numpy()))
+                return None
+
+        return _Lookup.apply(torch.empty(0, requires_grad=True))
+
+    def apply_gradients(self, iteration: int) -> bool:
+        if self._pending:
+            ids = np.concatenate([i for i, _ in self._pending])
+            g = np.concatenate([g for _, g in self._pending])
+        else:
+            ids, g = np.empty(0, np.int64), np.empty((0, self.dim), np.float32)
+        self._pending = []
+        done = self.ps.push_sparse(iteration, [(self.name, ids, g)])
+        self.after = iteration
+        return done
 
 
 class RemoteTrainer:
@@ -360,8 +554,12 @@ class RemoteTrainer:
     """
 
     def __init__(self, model, loss_fn, ps: RemoteParameterServer, *, mode: str = "sync",
-                 sync_timeout_s: float = 10.0, start_iteration: Optional[int] = None):
+                 sync_timeout_s: float = 10.0, start_iteration: Optional[int] = None,
+                 tables: Iterable["RemoteEmbedding"] = ()):
+        """``tables``: embedding tables the model looks rows up in (``RemoteEmbedding``); their
+        row gradients are pushed after the dense ones, under the same iteration number."""
         import torch
+        self.tables = list(tables)
         if mode not in ("sync", "async", "ssp"):
             raise ValueError(mode)
         self.torch = torch
@@ -413,6 +611,8 @@ class RemoteTrainer:
         done, _, _ = ps.push(it, grads)
         if not done and self.mode == "sync" and not ps.wait(it, self.sync_timeout_s):
             self.skipped += 1
+        for t in self.tables:  # the next lookup waits (server side) for this iteration's rows
+            t.apply_gradients(it)
         ps.status = IDLE
         self.iteration = it + 1
         return loss.detach()

@@ -1,0 +1,208 @@
+"""Sparse embedding tables on the host plane: psb.ParameterServerExt (CreateTable / PushSparse /
+PullRows) answered by build/bin/parameter_server, driven by RemoteParameterServer.  The oracle
+is the host path of ShardedEmbedding (itself pinned to torch.nn.Embedding + torch.optim in
+tests/test_sparse_host.py) fed with the mean of the workers' gradients."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import parameter_server_distributed_b200 as psd
+from parameter_server_distributed_b200.control import protos
+from parameter_server_distributed_b200.control.remote import (decode_rows_response,
+                                                               encode_sparse_push)
+from tests._native import BIN, Proc, ensure_binaries, free_port, wait_port
+
+ensure_binaries()
+V, D, STEPS = 503, 8, 4
+
+
+def test_numpy_codec_matches_the_protobuf_runtime():
+    ids = np.array([5, 0, 2 ** 40, -1], dtype=np.int64)
+    vals = np.arange(8, dtype=np.float32).reshape(4, 2) - 3.5
+    mine = encode_sparse_push(3, 7, [("emb", 2, ids, vals), ("empty", 2, ids[:0], vals[:0])])
+    m = protos.msg("psb.SparsePush").FromString(mine)
+    assert (m.worker_id, m.iteration, len(m.tables)) == (3, 7, 2)
+    assert list(m.tables[0].indices) == ids.tolist() and list(m.tables[0].values) == vals.ravel().tolist()
+    assert m.tables[1].name == "empty" and len(m.tables[1].indices) == 0
+    assert m.SerializeToString() == mine            # byte-identical with the runtime's encoding
+    R = protos.msg("psb.RowsResponse")
+    ready, dim, got, msg = decode_rows_response(R(ready=True, dim=2, values=[1.5, -2.0]).SerializeToString())
+    assert ready and dim == 2 and got.tolist() == [1.5, -2.0] and msg == ""
+    assert decode_rows_response(R(message="no").SerializeToString())[3] == "no"
+
+
+def _batches(worker, world):
+    gen = torch.Generator().manual_seed(7)
+    out = []
+    for _ in range(STEPS):
+        idx = torch.randint(0, V, (world, 40), generator=gen)
+        idx[:, :5] = idx[0, :5].clone()      # rows pushed by every worker
+        idx[:, 5:8] = idx[:, 8:11].clone()   # duplicates inside one push
+        idx[:, -1] = -1                       # padding
+        idx[:, -2] = V                        # out of range
+        out.append((idx, torch.randn(world, 40, D, generator=gen)))
+    return out
+
+
+def _drive(coord, kind, lr, shards=0):
+    """Two worker threads: create, read the initial table, STEPS x (push, pull after it)."""
+    res, errs = {}, []
+
+    def work(w):
+        try:
+            with psd.RemoteParameterServer(coord, w, heartbeat_s=0.2, shards=shards) as ps:
+                ps.create_table("emb", V, D, init_std=0.1, seed=11)
+                init = ps.pull_rows("emb", np.arange(V))
+                last = None
+                for it, (idx, g) in enumerate(_batches(w, 2)):
+                    ps.push_sparse(it, [("emb", idx[w].numpy(), g[w].numpy())])
+                    last = ps.pull_rows("emb", idx[w].numpy(), after_iteration=it)
+                res[w] = (init, ps.pull_rows("emb", np.arange(-1, V + 1)), last)
+        except BaseException as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    ts = [threading.Thread(target=work, args=(w,)) for w in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=120)
+    assert not errs, errs
+    init, final, last = res[0]
+    assert np.array_equal(init, res[1][0]) and np.array_equal(final, res[1][1])
+    assert abs(float(init.std()) - 0.1) < 0.01
+    # oracle: one worker that pushes both workers' rows with the mean gradient
+    cfg = psd.OptimConfig(kind=kind, lr=lr)
+    one = psd.ShardedEmbedding(V, D, cfg, capacity=80, grad_dtype=torch.float32)
+    one.master.copy_(torch.from_numpy(init))
+    for idx, g in _batches(0, 2):
+        one.push(idx.reshape(-1), g.reshape(-1, D) / 2)
+    assert np.abs(final[1:-1] - one.master.numpy()).max() < 2e-5
+    assert not final[0].any() and not final[-1].any()          # ids -1 and V: zero rows
+    idx = _batches(0, 2)[-1][0][0].numpy()
+    assert np.array_equal(last[idx == -1], np.zeros((1, D), np.float32))
+    ok = (idx >= 0) & (idx < V)
+    assert np.array_equal(last[ok], final[1:-1][idx[ok]])     # the pull after the last push is final
+
+
+@pytest.fixture()
+def plane(tmp_path, request):
+    ps_port, co_port = free_port(), free_port()
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0", *request.param],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    assert wait_port(ps_port) and wait_port(co_port)
+    yield f"127.0.0.1:{co_port}", ps, tmp_path
+    ps.stop()
+    co.stop()
+
+
+@pytest.mark.parametrize("plane,kind,lr", [(["--optimizer=sgd", "--lr=0.5"], "sgd", 0.5),
+                                           (["--optimizer=adam", "--lr=0.01"], "adam", 0.01)],
+                         indirect=["plane"])
+def test_two_workers_through_the_cpp_server_match_the_oracle(plane, kind, lr):
+    _drive(plane[0], kind, lr)
+
+
+@pytest.mark.parametrize("plane", [["--optimizer=momentum", "--lr=0.05"]], indirect=True)
+def test_tables_survive_checkpoint_and_reload_and_reject_bad_pushes(plane):
+    coord, ps_proc, tmp = plane
+    with psd.RemoteParameterServer(coord, 0, heartbeat_s=0.2) as a, \
+            psd.RemoteParameterServer(coord, 1, heartbeat_s=0.2) as b:
+        a.create_table("emb", V, D, init_std=0.1)
+        b.create_table("emb", V, D)                       # same shape: fine
+        with pytest.raises(RuntimeError, match="another shape"):
+            b.create_table("emb", V, 2 * D)
+        ids, g = np.array([3, 4, 3]), np.ones((3, D), np.float32)
+        assert a.push_sparse(0, [("emb", ids, g)]) is False   # waits for worker 1
+        assert b.push_sparse(0, [("emb", ids[:0], g[:0])]) is True
+        # the dense model needs a pusher before a checkpoint exists (bootstrap)
+        for ps in (a, b):
+            ps.push(0, [("w", np.ones(4, np.float32))])
+        before = a.pull_rows("emb", np.arange(V), after_iteration=0)
+        path = a.save_checkpoint(1, str(tmp / "t.ckpt"))
+        assert (tmp / "t.ckpt.tables").exists()
+        a.push_sparse(1, [("emb", ids, g)])
+        b.push_sparse(1, [("emb", ids, g)])
+        moved = a.pull_rows("emb", ids, after_iteration=1)
+        assert np.abs(moved - before[ids]).max() > 1e-3
+        a.load_checkpoint(path)
+        assert np.array_equal(a.pull_rows("emb", np.arange(V)), before)
+        # momentum state came back too: the same push from the same state lands in the same place
+        a.push_sparse(0, [("emb", ids, g)])
+        b.push_sparse(0, [("emb", ids, g)])
+        assert np.allclose(a.pull_rows("emb", ids, after_iteration=0), moved, atol=1e-6)
+        # malformed pushes are refused as a whole
+        with pytest.raises(RuntimeError, match="unknown table"):
+            a._tables["nope"] = (V, D, V)
+            a.push_sparse(5, [("nope", ids, g)])
+
+
+def test_table_rows_split_over_two_parameter_server_shards(tmp_path):
+    """shards=2: rows [0, 252) on shard 0, [252, 503) on shard 1; same result as one server."""
+    co_port = free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", "127.0.0.1:1"], str(tmp_path),
+              str(tmp_path / "co.log"))
+    assert wait_port(co_port)
+    servers = []
+    try:
+        for sid in range(2):
+            d = tmp_path / f"shard{sid}"
+            d.mkdir()
+            port = free_port()
+            servers.append(Proc([f"{BIN}/parameter_server", f"127.0.0.1:{port}", "2", "0",
+                                 "--optimizer=adam", "--lr=0.01",
+                                 f"--coordinator=127.0.0.1:{co_port}", f"--shard-id={sid}",
+                                 "--membership-poll-ms=100"], str(d), str(d / "ps.log")))
+            assert wait_port(port)
+        _drive(f"127.0.0.1:{co_port}", "adam", 0.01, shards=2)
+    finally:
+        for s in servers:
+            s.stop()
+        co.stop()
+
+
+@pytest.mark.parametrize("plane", [["--optimizer=adam", "--lr=0.02"]], indirect=True)
+def test_remote_trainer_with_an_embedding_table_learns(plane):
+    """RemoteEmbedding + RemoteTrainer: a classifier over categorical ids, dense tower and table
+    both on the C++ server; two workers, the loss falls and both end with the same rows."""
+    coord = plane[0]
+    vocab, dim = 200, 8
+    score = torch.randn(vocab, generator=torch.Generator().manual_seed(1))
+    res, errs = {}, []
+    towers = []
+    for _ in range(2):
+        torch.manual_seed(0)
+        towers.append(torch.nn.Linear(3 * dim, 2))
+
+    def work(w):
+        try:
+            with psd.RemoteParameterServer(coord, w, heartbeat_s=0.2) as ps:
+                table = psd.RemoteEmbedding(ps, "ids", vocab, dim, init_std=0.1)
+
+                def loss_fn(model, ids, y):
+                    x = table.lookup(ids).reshape(ids.shape[0], -1)
+                    return torch.nn.functional.cross_entropy(model(x), y)
+
+                tr = psd.RemoteTrainer(towers[w], loss_fn, ps, tables=[table])
+                gen = torch.Generator().manual_seed(50 + w)
+                losses = []
+                for _ in range(40):
+                    ids = torch.randint(0, vocab, (64, 3), generator=gen)
+                    losses.append(float(tr.step(ids, (score[ids].sum(1) > 0).long())))
+                res[w] = (losses, ps.pull_rows("ids", np.arange(vocab), after_iteration=table.after))
+        except BaseException as e:  # noqa: BLE001
+            errs.append(repr(e))
+
+    ts = [threading.Thread(target=work, args=(w,)) for w in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=180)
+    assert not errs, errs
+    for w in range(2):
+        losses = res[w][0]
+        assert sum(losses[-5:]) / 5 < 0.8 * sum(losses[:5]) / 5, losses
+    assert np.array_equal(res[0][1], res[1][1])

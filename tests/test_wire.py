@@ -94,6 +94,19 @@ def _samples():
         ("psb.HandleList", m("psb.HandleList")(
             handles=[m("psb.HandleBlob")(key="k", rank=1, blob=b"\x00\xff")])),
         ("psb.Ack", m("psb.Ack")(success=True)),
+        ("psb.TableSpec", m("psb.TableSpec")(name="emb", rows=1 << 33, dim=64, init_std=0.02, seed=-5)),
+        ("psb.SparseRows", m("psb.SparseRows")(name="emb", dim=2, indices=[0, -1, 1 << 40],
+                                               values=[1.5, -2.0, 0.0, 3e-8, 1e30, -0.0])),
+        ("psb.SparsePush", m("psb.SparsePush")(worker_id=2, iteration=9, tables=[
+            m("psb.SparseRows")(name="a", dim=1, indices=[7], values=[0.25]),
+            m("psb.SparseRows")(name="empty", dim=8)])),
+        ("psb.SparsePushResponse", m("psb.SparsePushResponse")(
+            success=True, message="sparse gradients received", aggregation_complete=True,
+            workers_received=2, total_workers=2)),
+        ("psb.RowsRequest", m("psb.RowsRequest")(worker_id=1, iteration=-1, name="emb",
+                                                 indices=[5, 5, 0])),
+        ("psb.RowsResponse", m("psb.RowsResponse")(ready=True, dim=2, values=[1.0, 2.0, 3.0, 4.0],
+                                                   message="m")),
     ]
 
 
@@ -156,6 +169,11 @@ def test_decoders_never_crash_on_mutated_messages():
             total_workers=2, workers=[protos.msg("coordinator.WorkerInfo")(
                 worker_id=i, address="10.0.0.%d" % i, port=5000 + i, hostname="h%d" % i)
                 for i in range(2)]).SerializeToString(),
+        "psb.SparsePush": protos.msg("psb.SparsePush")(worker_id=1, iteration=3, tables=[
+            protos.msg("psb.SparseRows")(name="emb", dim=2, indices=[4, 9], values=[1, 2, 3, 4])]
+        ).SerializeToString(),
+        "psb.RowsRequest": protos.msg("psb.RowsRequest")(
+            worker_id=1, iteration=2, name="emb", indices=[1, 2, 3]).SerializeToString(),
     }
     rng = random.Random(7)
     codes = set()
