@@ -132,6 +132,9 @@ def run_nccl(args) -> int:
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    # same host placement as the other arm: pinned batches next to the GPU
+    from parameter_server_distributed_b200.utils.numa import bind_to_gpu_node
+    numa = bind_to_gpu_node(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
@@ -253,7 +256,7 @@ def run_nccl(args) -> int:
             "config": {"model": f"{wl.label} ({wl.nparams / 1e6:.1f}M params)", "global_batch": gb,
                        "seq_len": wl.seq_len, "parallelism": f"dp{world} / {world} PS shards (ZeRO-1)",
                        "optimizer": args.optimizer, "bucket_mb": args.bucket_mb,
-                       "layer_gemms": "library (cuBLAS)",
+                       "layer_gemms": "library (cuBLAS)", "numa_bind": numa,
                        "push_pull": "ncclReduceScatter + torch.optim on the fp32 shard + ncclAllGather, "
                                     "bucketed, overlapped with backward",
                        "l2": "working set exceeds the 126 MB L2; inputs rotate over 4 batches"},

@@ -250,6 +250,7 @@ def run_ours(args):
                        "pull": args.pull, "bucket_mb": args.bucket_mb,
                        "layer_gemms": "own tcgen05 kernel" if _linear.ENABLED else "library",
                        "alt_param_replicas": bool(getattr(ps, "_alt", False)),
+                       "numa_bind": ctx.numa,  # process pinned to the GPU's node (null: not done)
                        "control_plane": ("C++ coordinator (register / heartbeat / shard map / handle "
                                          "exchange / barriers)" if ctx.coord is not None
                                          else "single rank" if world == 1 else "torch.distributed"),

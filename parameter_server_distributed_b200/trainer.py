@@ -31,6 +31,7 @@ class Context:
     fabric: Optional[Fabric]
     coord: Optional[object] = None   # control.client.CoordinatorClient
     abort: Optional[object] = None   # utils.elastic.AbortWord
+    numa: Optional[dict] = None      # utils.numa.bind_to_gpu_node: where this process was bound
 
     # ---- host-side collectives of the control plane (small, off the training path)
     def barrier(self, name: str = "host") -> None:
@@ -106,9 +107,12 @@ def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
         control = "coordinator" if want and _client.available() else "dist"
     if control not in ("coordinator", "dist"):
         raise ValueError(f"unknown control plane {control!r}")
+    numa = None
     if cuda:
         torch.cuda.set_device(local_rank)
         device = torch.device("cuda", local_rank)
+        from .utils.numa import bind_to_gpu_node
+        numa = bind_to_gpu_node(local_rank)  # before the first pinned allocation (PSB_NUMA_BIND=0: off)
         if spin_timeout_s is None and "PSB_SPIN_TIMEOUT_S" in os.environ:
             spin_timeout_s = float(os.environ["PSB_SPIN_TIMEOUT_S"])
         if spin_timeout_s is not None:
@@ -130,7 +134,7 @@ def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
             coord.watch(world, abort.host_ptr)
         else:
             fabric = None
-        return Context(rank, world, local_rank, device, fabric, coord, abort)
+        return Context(rank, world, local_rank, device, fabric, coord, abort, numa)
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
@@ -139,7 +143,7 @@ def init(heap_bytes: int = 4 << 30, backend: Optional[str] = None,
         kw = {"device_id": device} if (cuda and backend == "nccl") else {}
         dist.init_process_group(backend, rank=rank, world_size=world, **kw)
     fabric = Fabric.from_process_group(device, heap_bytes) if cuda else None
-    return Context(rank, world, local_rank, device, fabric)
+    return Context(rank, world, local_rank, device, fabric, numa=numa)
 
 
 class LossHandle:

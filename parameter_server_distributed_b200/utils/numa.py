@@ -1,0 +1,91 @@
+"""Keep a rank on the NUMA node of its GPU.
+
+Every step a rank copies its batch from pinned host memory to the GPU (``Trainer.step``); with
+eight ranks on a two-socket box, pinned buffers that happen to sit on the other socket cross the
+inter-socket link on every copy and the end-to-end rate falls behind the device-timed one (round
+1: 0.21 ms/step at 8 GPUs against 0.05 at one).  Binding the process to the CPUs of the GPU's
+node *before* the first pinned allocation puts those pages — and the threads that drive the GPU —
+next to it.  The reference pins nothing (its tensors are ``std::vector``s copied with blocking
+``cudaMemcpy``, /root/reference/src/worker.cpp:408-448).
+
+Best effort by design: any missing piece of information (no sysfs, one node, a cpuset that does
+not intersect, ``PSB_NUMA_BIND=0``) leaves the process as it was.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Set
+
+
+def _parse_cpulist(text: str) -> Set[int]:
+    cpus: Set[int] = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_numa_node(device_index: int, sysfs: str = "/sys") -> Optional[int]:
+    """NUMA node of CUDA device ``device_index`` (after CUDA_VISIBLE_DEVICES), or None."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"{sysfs}/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        return node if node >= 0 else None
+    except Exception:
+        return None
+
+
+def node_cpus(node: int, sysfs: str = "/sys") -> Set[int]:
+    try:
+        with open(f"{sysfs}/devices/system/node/node{node}/cpulist") as f:
+            return _parse_cpulist(f.read())
+    except Exception:
+        return set()
+
+
+def _prefer_node_memory(node: int) -> bool:
+    """set_mempolicy(MPOL_PREFERRED, {node}): new pages of this thread come from ``node`` when it
+    has room (x86-64 / aarch64 syscall numbers; anything else is skipped)."""
+    try:
+        nr = {"x86_64": 238, "aarch64": 237}.get(os.uname().machine)
+        if nr is None or node >= 1024:
+            return False
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = (ctypes.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        MPOL_PREFERRED = 1
+        return libc.syscall(nr, MPOL_PREFERRED, mask, ctypes.c_ulong(1024 + 1)) == 0
+    except Exception:
+        return False
+
+
+def bind_to_gpu_node(device_index: int, sysfs: str = "/sys") -> Optional[dict]:
+    """Restrict this process to the CPUs of the GPU's NUMA node and prefer its memory.
+    Returns ``{"node", "cpus", "mempolicy"}`` when something was done, else None."""
+    if os.environ.get("PSB_NUMA_BIND", "1") == "0":
+        return None
+    try:
+        nodes = [d for d in os.listdir(f"{sysfs}/devices/system/node") if d[4:].isdigit()
+                 and d.startswith("node")]
+    except OSError:
+        return None
+    if len(nodes) < 2:
+        return None  # one node: nothing to choose
+    node = gpu_numa_node(device_index, sysfs)
+    if node is None:
+        return None
+    try:
+        allowed = os.sched_getaffinity(0)
+        want = node_cpus(node, sysfs) & allowed
+        if not want:
+            return None
+        os.sched_setaffinity(0, want)
+    except (OSError, AttributeError):
+        return None
+    return {"node": node, "cpus": len(want), "mempolicy": _prefer_node_memory(node)}
