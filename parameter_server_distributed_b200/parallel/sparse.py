@@ -325,6 +325,65 @@ class ShardedEmbedding:
             self.step_word.fill_(self.steps)
         self.sync_table()
 
+    # ------------------------------------------------------------------ whole-table checkpoints
+    def _gather_rows(self, t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """Every rank's shard of ``t`` -> the full ``[vocab, dim]`` fp32 tensor on the host."""
+        if t is None:
+            return None
+        if self.world == 1:
+            parts = [t]
+        elif self.cuda:
+            if self._emulated:
+                raise RuntimeError("emulated ranks have no collective gather")
+            parts = self.fabric.all_gather(t)
+        else:
+            parts = [torch.empty_like(t) for _ in range(self.world)]
+            dist.all_gather(parts, t.contiguous(), group=self.group)
+        return torch.cat([p.detach().cpu() for p in parts], 0)[:self.vocab]
+
+    def save(self, path: str, name: str = "embedding", epoch: int = 0) -> None:
+        """Collective.  The whole table as ONE tensor in the reference's checkpoint format
+        (readable by the reference's ``load_checkpoint`` and by
+        ``utils.checkpoint.read_reference_file``) plus the ``.psb`` sidecar with m / v and the
+        step count; rank 0 writes, atomically.  Full tensors: loads at any world size."""
+        from ..utils.checkpoint import _write_sidecar, write_reference_file
+        full = [self._gather_rows(t) for t in (self.master, self.m, self.v)]
+        if self.rank == 0:
+            write_reference_file(path, epoch, self.steps,
+                                 [(name, (self.vocab, self.dim), full[0].numpy())])
+            empty = torch.empty(0).numpy()
+            _write_sidecar(path + ".psb", self.optim.kind, self.steps,
+                           [(full[1].numpy() if full[1] is not None else empty,
+                             full[2].numpy() if full[2] is not None else empty)])
+        self._barrier()
+
+    def load(self, path: str) -> int:
+        """Every rank reads the file and keeps its rows (any world size); optimizer state comes
+        back when the sidecar exists and was written by the same optimizer kind.  Returns the
+        step count."""
+        import os
+        from ..utils.checkpoint import _read_sidecar, read_reference_file
+        _, steps, tensors = read_reference_file(path)
+        name, shape, data = tensors[0]
+        if tuple(shape) != (self.vocab, self.dim):
+            raise ValueError(f"{path}: table {name!r} is {tuple(shape)}, expected "
+                             f"{(self.vocab, self.dim)}")
+        n = self.hi - self.lo
+        full = torch.from_numpy(data).view(self.vocab, self.dim)
+        self.master[:n].copy_(full[self.lo:self.hi])
+        if os.path.exists(path + ".psb"):
+            kind, steps, states = _read_sidecar(path + ".psb")
+            if kind == self.optim.kind and states:
+                for mine, saved in zip((self.m, self.v), states[0]):
+                    if mine is not None and saved.size == self.vocab * self.dim:
+                        mine[:n].copy_(torch.from_numpy(saved).view(self.vocab, self.dim)
+                                       [self.lo:self.hi])
+        self.steps = int(steps)
+        if self.cuda:
+            self.step_word.fill_(self.steps)
+        self.sync_table()
+        return self.steps
+
     def close(self) -> None:
         for b in getattr(self, "_bufs", []):
             b.free()

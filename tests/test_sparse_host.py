@@ -183,3 +183,55 @@ def test_example_trains_a_sharded_table_with_a_dense_tower(nproc):
     assert r.returncode == 0, r.stdout[-600:] + r.stderr[-600:]
     first, last = re.search(r"loss ([0-9.]+) -> ([0-9.]+)", r.stdout).groups()
     assert float(last) < 0.8 * float(first)
+
+
+def _ckpt_worker(rank, world, port, path, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cfg = OptimConfig(kind="adam", lr=0.05)
+    e = ShardedEmbedding(V + 3, D, cfg, capacity=64, rank=rank, world=world, grad_dtype=torch.float32)
+    gen = torch.Generator().manual_seed(21)
+    for _ in range(2):
+        idx = torch.randint(0, V + 3, (world, 50), generator=gen)
+        g = torch.randn(world, 50, D, generator=gen)
+        e.push(idx[rank], g[rank])
+    e.save(path, name="emb", epoch=3)
+    q.put((rank, e.full_table().float()))
+    dist.destroy_process_group()
+
+
+def test_whole_table_checkpoint_written_by_three_ranks_loads_at_world_one(tmp_path):
+    """save(): one tensor in the reference's file format + sidecar; load() at another world size
+    restores rows, Adam state and step count — the next push lands where the writers' would."""
+    from parameter_server_distributed_b200.utils.checkpoint import read_reference_file
+    path = str(tmp_path / "table.ckpt")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_ckpt_worker, args=(r, 3, port, path, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    epoch, iteration, tensors = read_reference_file(path)
+    assert (epoch, iteration) == (3, 2) and tensors[0][0] == "emb" and tensors[0][1] == (V + 3, D)
+    cfg = OptimConfig(kind="adam", lr=0.05)
+    one = ShardedEmbedding(V + 3, D, cfg, capacity=256, grad_dtype=torch.float32, seed=5)
+    assert one.load(path) == 2
+    assert torch.equal(one.table.float(), res[0])
+    # the state is the writers': replay the same two steps from scratch and take a third one
+    ref = ShardedEmbedding(V + 3, D, cfg, capacity=256, grad_dtype=torch.float32)
+    gen = torch.Generator().manual_seed(21)
+    for _ in range(2):
+        idx = torch.randint(0, V + 3, (3, 50), generator=gen)
+        g = torch.randn(3, 50, D, generator=gen)
+        ref.push(idx.reshape(-1), g.reshape(-1, D) / 3)
+    idx, g = torch.arange(0, 40), torch.ones(40, D)
+    one.push(idx, g)
+    ref.push(idx, g)
+    assert (one.master - ref.master).abs().max() < 1e-5
+    with pytest.raises(ValueError, match="expected"):
+        ShardedEmbedding(V, D, cfg, capacity=8).load(path)
