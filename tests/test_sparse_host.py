@@ -235,3 +235,27 @@ def test_whole_table_checkpoint_written_by_three_ranks_loads_at_world_one(tmp_pa
     assert (one.master - ref.master).abs().max() < 1e-5
     with pytest.raises(ValueError, match="expected"):
         ShardedEmbedding(V, D, cfg, capacity=8).load(path)
+
+
+def test_c_abi_rejects_bad_arguments_before_any_launch():
+    """psb_sparse_pull / psb_sparse_apply validate on the host (no GPU needed to see it)."""
+    import ctypes as C
+    from parameter_server_distributed_b200 import _lib
+    lib = _lib.load()
+    s = _lib.PsbSparse()
+    s.fabric.rank, s.fabric.world = 0, 1
+    s.vocab, s.rows_per_rank, s.dim, s.cap = 100, 100, 12, 8
+    s.table[0] = 4096
+    assert lib.psb_sparse_pull(C.byref(s), 4096, 1, 4096, None) != 0
+    assert b"multiple of 8" in lib.psb_last_error()
+    s.dim, s.rows_per_rank = 16, 10
+    assert lib.psb_sparse_pull(C.byref(s), 4096, 1, 4096, None) != 0
+    assert b"do not cover" in lib.psb_last_error()
+    s.rows_per_rank = 100
+    assert lib.psb_sparse_pull(C.byref(s), None, 0, None, None) == 0      # nothing to pull
+    assert lib.psb_sparse_apply(C.byref(s), None) != 0
+    assert b"staging range" in lib.psb_last_error()
+    s.stage_idx[0] = s.stage_grad[0] = s.stage_cnt[0] = 4096
+    assert lib.psb_sparse_apply(C.byref(s), None) != 0
+    assert b"owner state" in lib.psb_last_error()
+    assert lib.psb_sparse_init(None, 5, None) != 0
