@@ -46,9 +46,10 @@ def _batches(worker, world):
     return out
 
 
-def _drive(coord, kind, lr, shards=0):
+def _drive(coord, kind, lr, shards=0, lockstep=True):
     """Two worker threads: create, read the initial table, STEPS x (push, pull after it)."""
     res, errs = {}, []
+    pushed = threading.Barrier(2)  # async mode: the final read comes after everybody's last push
 
     def work(w):
         try:
@@ -59,8 +60,10 @@ def _drive(coord, kind, lr, shards=0):
                 for it, (idx, g) in enumerate(_batches(w, 2)):
                     ps.push_sparse(it, [("emb", idx[w].numpy(), g[w].numpy())])
                     last = ps.pull_rows("emb", idx[w].numpy(), after_iteration=it)
+                pushed.wait(timeout=60)
                 res[w] = (init, ps.pull_rows("emb", np.arange(-1, V + 1)), last)
         except BaseException as e:  # noqa: BLE001
+            pushed.abort()
             errs.append(repr(e))
 
     ts = [threading.Thread(target=work, args=(w,)) for w in range(2)]
@@ -83,7 +86,8 @@ def _drive(coord, kind, lr, shards=0):
     idx = _batches(0, 2)[-1][0][0].numpy()
     assert np.array_equal(last[idx == -1], np.zeros((1, D), np.float32))
     ok = (idx >= 0) & (idx < V)
-    assert np.array_equal(last[ok], final[1:-1][idx[ok]])     # the pull after the last push is final
+    if lockstep:  # sync: the pull after the last push already is the final table
+        assert np.array_equal(last[ok], final[1:-1][idx[ok]])
 
 
 @pytest.fixture()
@@ -104,6 +108,13 @@ def plane(tmp_path, request):
                          indirect=["plane"])
 def test_two_workers_through_the_cpp_server_match_the_oracle(plane, kind, lr):
     _drive(plane[0], kind, lr)
+
+
+@pytest.mark.parametrize("plane", [["--optimizer=sgd", "--lr=0.5", "--mode=async"]], indirect=True)
+def test_async_server_applies_every_sparse_push_once(plane):
+    """--mode=async: a push is applied at once with a 1/N share.  SGD updates commute, so the
+    final table equals the synchronous mean whatever the interleaving of the two workers."""
+    _drive(plane[0], "sgd", 0.5, lockstep=False)
 
 
 @pytest.mark.parametrize("plane", [["--optimizer=momentum", "--lr=0.05"]], indirect=True)
