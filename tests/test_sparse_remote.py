@@ -56,6 +56,7 @@ def _drive(coord, kind, lr, shards=0, lockstep=True):
             with psd.RemoteParameterServer(coord, w, heartbeat_s=0.2, shards=shards) as ps:
                 ps.create_table("emb", V, D, init_std=0.1, seed=11)
                 init = ps.pull_rows("emb", np.arange(V))
+                pushed.wait(timeout=60)  # nobody pushes before everybody has read the start
                 last = None
                 for it, (idx, g) in enumerate(_batches(w, 2)):
                     ps.push_sparse(it, [("emb", idx[w].numpy(), g[w].numpy())])
