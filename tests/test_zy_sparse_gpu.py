@@ -53,7 +53,7 @@ def test_one_rank_matches_the_host_path(kind, dim, gdt):
     q = torch.cat([torch.randint(0, vocab, (300,)), torch.tensor([-1, vocab, 0, vocab - 1])])
     got, want = dev.pull(q.to(DEV)).cpu(), host.pull(q)
     assert got.dtype == torch.bfloat16 and got.shape == (304, dim)
-    assert (got.float() - want.float()).abs().max() < 1e-3
+    _assert_close(got.float(), want.float(), 1e-3)
     assert got[300].abs().sum() == 0 and got[301].abs().sum() == 0
     assert torch.equal(got[302], dev.master[0].to(torch.bfloat16).cpu())
     # scratch is back to its resting state: nothing leaks into the next step
@@ -66,7 +66,7 @@ def test_four_emulated_ranks_match_one_host_worker_with_the_mean_gradient():
     cfg = OptimConfig(kind="adamw", lr=0.02, weight_decay=0.05)
     fabs = Fabric.local_group(world, DEV, 64 << 20)
     embs = [ShardedEmbedding(vocab, dim, cfg, capacity=n, fabric=f, seed=7) for f in fabs]
-    host = ShardedEmbedding(vocab, dim, cfg, capacity=n * world, seed=7)
+    host = ShardedEmbedding(vocab, dim, cfg, capacity=n * world, seed=7, grad_dtype=torch.float32)
     try:
         for idx, g in _batches(world, n, vocab, dim, 3, seed=12):
             for r, e in enumerate(embs):
@@ -80,7 +80,7 @@ def test_four_emulated_ranks_match_one_host_worker_with_the_mean_gradient():
             _assert_close(e.master[:e.hi - e.lo].cpu(), host.master[e.lo:e.hi], 2e-4)
         want = host.table.float()
         for e in (embs[0], embs[3]):              # every rank reads every owner's rows
-            assert (e.full_table().cpu().float() - want).abs().max() < 1e-3
+            _assert_close(e.full_table().cpu().float(), want, 1e-3)
     finally:
         for e in embs:
             e.close()
