@@ -45,6 +45,8 @@ static const char kUsage[] =
     "  --resume=PATH|latest       load a checkpoint before serving\n"
     "  --long-poll-ms=N           hold a 'not ready' status answer up to N ms (25)\n"
     "  --stats-every-s=N          one JSON line of counters on stdout every N seconds\n"
+    "  Besides the reference's ParameterServer service it answers psb.ParameterServerExt\n"
+    "  (CreateTable / PushSparse / PullRows: sparse embedding tables, same optimizer and mode).\n"
     "  Every flag has a PSB_* environment twin (PSB_MODE, PSB_OPTIMIZER, ...).\n";
 
 int main(int argc, char** argv) {

@@ -152,6 +152,8 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     }
     pb::SparsePushResponse out;
     std::string err;
+    sparse_pushes_++;
+    for (const auto& g : grads) rows_pushed_ += g.indices.size();
     out.aggregation_complete = sparse_.push(in.worker_id, in.iteration, std::move(grads),
                                             core_.get_total_workers(), out.workers_received, err);
     out.success = err.empty();
@@ -165,6 +167,8 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     pb::RowsRequest in;
     if (!in.decode(req)) return Status{grpc_lite::INTERNAL, "malformed RowsRequest"};
     pb::RowsResponse out;
+    row_pulls_++;
+    rows_pulled_ += in.indices.size();
     out.ready = sparse_.ready(in.iteration, core_.options().long_poll_ms);
     if (!sparse_.rows(in.name, in.indices, out.values, out.dim)) {
       out.ready = false;
@@ -315,7 +319,9 @@ std::string ParameterServerService::stats_json() {
     << ", \"total_workers\": " << core_.get_total_workers() << ", \"pushes\": " << pushes
     << ", \"pulls\": " << pulls_.load() << ", \"status_polls\": " << status_polls_.load()
     << ", \"bytes_in\": " << bytes_in_.load() << ", \"bytes_out\": " << bytes_out_.load()
-    << ", \"push_ms_mean\": " << (pushes ? push_us_.load() / 1000.0 / pushes : 0.0) << "}";
+    << ", \"push_ms_mean\": " << (pushes ? push_us_.load() / 1000.0 / pushes : 0.0)
+    << ", \"sparse_pushes\": " << sparse_pushes_.load() << ", \"rows_pushed\": " << rows_pushed_.load()
+    << ", \"row_pulls\": " << row_pulls_.load() << ", \"rows_pulled\": " << rows_pulled_.load() << "}";
   return o.str();
 }
 

@@ -70,7 +70,7 @@ class ParameterServerService {
   std::thread shard_thread_;
   std::thread stats_thread_;
   std::atomic<uint64_t> pushes_{0}, pulls_{0}, status_polls_{0}, bytes_in_{0}, bytes_out_{0},
-      push_us_{0};
+      push_us_{0}, sparse_pushes_{0}, row_pulls_{0}, rows_pushed_{0}, rows_pulled_{0};
   int configured_workers_;
   std::atomic<bool> running_{true};
 };
