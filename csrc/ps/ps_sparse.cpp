@@ -7,9 +7,36 @@
 #include <cstdio>
 #include <fstream>
 #include <random>
+#include <thread>
 #include <unordered_map>
 
 namespace psb {
+
+namespace {
+// body(lo, hi) over [0, n) on up to `threads` threads (the caller's included)
+template <class F>
+void parallel_rows(size_t n, int threads, const F& body) {
+  const size_t t = std::min<size_t>(static_cast<size_t>(std::max(1, threads)), n / 1024 + 1);
+  if (t <= 1) {
+    body(size_t{0}, n);
+    return;
+  }
+  std::vector<std::thread> th;
+  const size_t step = (n + t - 1) / t;
+  for (size_t k = 1; k < t; ++k) {
+    const size_t lo = k * step, hi = std::min(n, lo + step);
+    if (lo >= hi) break;
+    th.emplace_back([&body, lo, hi] { body(lo, hi); });
+  }
+  body(size_t{0}, std::min(n, step));
+  for (auto& x : th) x.join();
+}
+}  // namespace
+
+SparseTables::SparseTables(const PsOptions& opt) : opt_(opt) {
+  int t = opt_.threads > 0 ? opt_.threads : static_cast<int>(std::thread::hardware_concurrency());
+  opt_.threads = t < 1 ? 1 : (t > 16 ? 16 : t);
+}
 
 bool SparseTables::create(const std::string& name, int64_t rows, int32_t dim, float init_std,
                           int64_t seed) {
@@ -60,8 +87,7 @@ void SparseTables::update_row(Table& t, int64_t row, const float* g, float scale
     for (size_t k = 0; k < n; ++k) p[k] -= lr * (g[k] * scale + wd * p[k]);
     return;
   }
-  if (t.m.size() != t.data.size()) t.m.assign(t.data.size(), 0.0f);
-  float* m = t.m.data() + at;
+  float* m = t.m.data() + at;  // state arrays are sized by apply_locked before the row loop
   if (kind == "momentum") {
     for (size_t k = 0; k < n; ++k) {
       m[k] = opt_.momentum * m[k] + (g[k] * scale + wd * p[k]);
@@ -69,7 +95,6 @@ void SparseTables::update_row(Table& t, int64_t row, const float* g, float scale
     }
     return;
   }
-  if (t.v.size() != t.data.size()) t.v.assign(t.data.size(), 0.0f);
   float* v = t.v.data() + at;
   const bool decoupled = kind == "adamw";
   const float b1 = opt_.beta1, b2 = opt_.beta2;
@@ -113,7 +138,16 @@ void SparseTables::apply_locked(Iter& it) {
           for (size_t k = 0; k < dim; ++k) a[k] += src[k];
         }
       }
-    for (size_t s = 0; s < touched.size(); ++s) update_row(t, touched[s], acc.data() + s * dim, scale);
+    if (touched.empty()) continue;
+    // optimizer state appears with the first update (before the threads start)
+    if (opt_.optimizer != "sgd" && t.m.size() != t.data.size()) t.m.assign(t.data.size(), 0.0f);
+    if ((opt_.optimizer == "adam" || opt_.optimizer == "adamw") && t.v.size() != t.data.size())
+      t.v.assign(t.data.size(), 0.0f);
+    // touched rows are distinct: their updates are independent (a random walk over the table,
+    // bound by memory latency - worth spreading over cores for large batches)
+    parallel_rows(touched.size(), opt_.threads, [&](size_t lo, size_t hi) {
+      for (size_t s = lo; s < hi; ++s) update_row(t, touched[s], acc.data() + s * dim, scale);
+    });
   }
   it.staged.clear();  // staged gradients are not kept after aggregation
   it.applied = true;

@@ -32,7 +32,7 @@ struct SparseGrad {
 
 class SparseTables {
  public:
-  explicit SparseTables(const PsOptions& opt) : opt_(opt) {}
+  explicit SparseTables(const PsOptions& opt);
 
   // Idempotent for an identical (rows, dim) spec; false on a conflicting or invalid one.
   bool create(const std::string& name, int64_t rows, int32_t dim, float init_std, int64_t seed);

@@ -207,6 +207,27 @@ static int sparse_tables() {
   CHECK(t.push(0, 5, grad({1, 3}, 1.0f, 2), 1, got, err) && u.push(0, 5, grad({1, 3}, 1.0f, 2), 1, got, err));
   CHECK(t.rows("emb", {0, 1, 3}, a, dim) && u.rows("emb", {0, 1, 3}, b, dim) && a == b);  // state too
   std::remove(path.c_str());
+  // large pushes update their rows on several threads: same bits as on one
+  {
+    PsOptions o1, o4;
+    o1.optimizer = o4.optimizer = "adam", o1.lr = o4.lr = 0.01f;
+    o1.threads = 1, o4.threads = 4;
+    SparseTables one(o1), four(o4);
+    CHECK(one.create("emb", 20000, 8, 0.1f, 3) && four.create("emb", 20000, 8, 0.1f, 3));
+    SparseGrad g;
+    g.name = "emb", g.dim = 8;
+    for (int i = 0; i < 6000; ++i) {
+      g.indices.push_back((i * 7919) % 20000);
+      for (int k = 0; k < 8; ++k) g.values.push_back(0.001f * static_cast<float>((i * 31 + k) % 97) - 0.04f);
+    }
+    for (int it = 0; it < 2; ++it) {
+      CHECK(one.push(0, it, std::vector<SparseGrad>{g}, 1, got, err));
+      CHECK(four.push(0, it, std::vector<SparseGrad>{g}, 1, got, err));
+    }
+    std::vector<int64_t> all(20000);
+    for (int i = 0; i < 20000; ++i) all[i] = i;
+    CHECK(one.rows("emb", all, a, dim) && four.rows("emb", all, b, dim) && a == b);
+  }
   // async: a share of 1 / N at once, each clock once
   PsOptions as;
   as.mode = PsMode::kAsync, as.lr = 1.0f;

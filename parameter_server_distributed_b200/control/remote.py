@@ -167,26 +167,27 @@ def encode_sparse_push(worker_id: int, iteration: int,
                        tables: Iterable[Tuple[str, int, np.ndarray, np.ndarray]]) -> bytes:
     """psb.SparsePush from (name, dim, int64 ids, fp32 values[len(ids), dim]) entries; ids and
     values go out as packed sfixed64 / float blocks straight from numpy."""
-    out = bytearray()
+    chunks: List[bytes] = []  # joined once: no repeated copies of the value blocks
     if worker_id:
-        out += b"\x08" + _varint(worker_id)
+        chunks.append(b"\x08" + _varint(worker_id))
     if iteration:
-        out += b"\x10" + _varint(iteration)
+        chunks.append(b"\x10" + _varint(iteration))
     for name, dim, ids, vals in tables:
         ids = np.ascontiguousarray(ids, dtype="<i8").ravel()
         vals = np.ascontiguousarray(vals, dtype="<f4").ravel()
         if vals.size != ids.size * dim:
             raise ValueError(f"table {name!r}: {vals.size} values for {ids.size} rows of {dim}")
-        body = bytearray()
         nb = name.encode()
-        body += b"\x0a" + _varint(len(nb)) + nb
+        head = b"\x0a" + _varint(len(nb)) + nb
         if dim:
-            body += b"\x10" + _varint(dim)
+            head += b"\x10" + _varint(dim)
+        body = [head]
         if ids.size:
-            body += b"\x1a" + _varint(ids.nbytes) + ids.tobytes()
-            body += b"\x22" + _varint(vals.nbytes) + vals.tobytes()
-        out += b"\x1a" + _varint(len(body)) + body
-    return bytes(out)
+            body += [b"\x1a" + _varint(ids.nbytes), ids.data.cast("B"),
+                     b"\x22" + _varint(vals.nbytes), vals.data.cast("B")]
+        chunks.append(b"\x1a" + _varint(sum(len(c) for c in body)))
+        chunks += body
+    return b"".join(chunks)
 
 
 def decode_rows_response(buf: bytes) -> Tuple[bool, int, np.ndarray, str]:
