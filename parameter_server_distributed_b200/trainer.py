@@ -165,8 +165,13 @@ class Trainer:
                  fused_first_layer: Optional[bool] = None, overlap: bool = True,
                  staleness: int = 0, push_grid: int = 0, push_tma: Optional[bool] = None,
                  checkpoint_every: int = 0, checkpoint_path: Optional[str] = None,
-                 split_mb: Optional[float] = None, push_nvls: Optional[bool] = None):
-        """``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
+                 split_mb: Optional[float] = None, push_nvls: Optional[bool] = None,
+                 tables=()):
+        """``tables``: sparse embedding tables the model looks rows up in
+        (``parallel.sparse.ShardedEmbedding``); after every backward pass their collected row
+        gradients are pushed (``apply_gradients``) next to the dense push.
+
+        ``pull``: ``"broadcast"`` — owners write new slices into every replica inside K1;
         ``"gather"`` — owners publish locally, workers pull (K2, and K2f for the first layer);
         ``"hybrid"`` — broadcast for every bucket except the first layer's, whose all-gather is
         fused into the first GEMM of the next forward (K2f).
@@ -178,6 +183,7 @@ class Trainer:
             raise ValueError(f"unknown mode {mode!r}")
         self.model, self.loss_fn, self.ctx = model, loss_fn, ctx
         self.device = ctx.device
+        self.tables = list(tables)
         dedicated = ()
         first = getattr(model, "first_weight_name", None)
         if pull not in ("broadcast", "gather", "hybrid"):
@@ -266,6 +272,8 @@ class Trainer:
         loss = self.loss_fn(out, target)
         loss.backward()
         self.ps.step()
+        for t in self.tables:  # sparse rows: collective, once per step on every rank
+            t.apply_gradients()
         self._after_step()
         return loss.detach()
 
@@ -347,6 +355,8 @@ class Trainer:
         loss_val.record_stream(self._loss_stream)
         loss.backward()
         self.ps.step()
+        for t in self.tables:
+            t.apply_gradients()
         done = torch.cuda.Event()
         done.record(cur)
         self._consumed[slot] = done

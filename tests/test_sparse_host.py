@@ -259,3 +259,30 @@ def test_c_abi_rejects_bad_arguments_before_any_launch():
     assert lib.psb_sparse_apply(C.byref(s), None) != 0
     assert b"owner state" in lib.psb_last_error()
     assert lib.psb_sparse_init(None, 5, None) != 0
+
+
+def test_trainer_pushes_table_gradients_next_to_the_dense_ones():
+    """psd.Trainer(tables=[...]): one call per step trains the dense tower (engine) and the
+    embedding rows (sparse push); ids travel as the model input."""
+    import parameter_server_distributed_b200 as psd
+    from parameter_server_distributed_b200.models import EmbeddingMLP, EmbeddingMLPConfig
+    ctx = psd.init()
+    cfg = EmbeddingMLPConfig(vocab=300, dim=8, fields=3, hidden=(16,), classes=2)
+    optim = OptimConfig(kind="adam", lr=0.02)
+    table = ShardedEmbedding.from_context(ctx, cfg.vocab, cfg.dim, optim, capacity=64 * 3,
+                                          init_std=0.1, grad_dtype=torch.float32)
+    torch.manual_seed(0)
+    model = EmbeddingMLP(cfg, table)
+    tr = psd.Trainer(model, lambda out, y: torch.nn.functional.cross_entropy(out.float(), y), ctx,
+                     optim, bucket_mb=1, tables=[table])
+    score = torch.randn(cfg.vocab, generator=torch.Generator().manual_seed(1))
+    gen = torch.Generator().manual_seed(2)
+    before = table.master.clone()
+    losses = []
+    for _ in range(60):
+        ids = torch.randint(0, cfg.vocab, (64, cfg.fields), generator=gen)
+        losses.append(tr.step(ids, (score[ids].sum(1) > 0).long()).item())
+    assert table.steps == 60 and tr.steps == 60
+    assert (table.master - before).abs().max() > 1e-2
+    assert sum(losses[-10:]) < 0.8 * sum(losses[:10]), (losses[:3], losses[-3:])
+    ctx.close()
