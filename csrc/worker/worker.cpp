@@ -401,6 +401,52 @@ bool Worker::check_sync_ready(int iteration, int& workers_received, int& total_w
   return ready;
 }
 
+bool Worker::create_table(const std::string& name, int64_t rows, int32_t dim, float init_std,
+                          int64_t seed) {
+  pb::TableSpec req;
+  req.name = name, req.rows = rows, req.dim = dim, req.init_std = init_std, req.seed = seed;
+  std::string resp;
+  Status st = shard_channel(0).call("/psb.ParameterServerExt/CreateTable", req.encode(), resp, 10000);
+  pb::Ack out;
+  return st.ok() && out.decode(resp) && out.success;
+}
+
+bool Worker::push_sparse(int iteration, const std::string& name, int32_t dim,
+                         const std::vector<int64_t>& indices, const std::vector<float>& values,
+                         bool* complete) {
+  pb::SparsePush req;
+  req.worker_id = worker_id_, req.iteration = iteration;
+  pb::SparseRows rows;
+  rows.name = name, rows.dim = dim, rows.indices = indices, rows.values = values;
+  req.tables.push_back(std::move(rows));
+  std::string resp;
+  Status st = shard_channel(0).call("/psb.ParameterServerExt/PushSparse", req.encode(), resp, 10000);
+  pb::SparsePushResponse out;
+  if (!st.ok() || !out.decode(resp) || !out.success) return false;
+  if (complete) *complete = out.aggregation_complete;
+  return true;
+}
+
+bool Worker::pull_rows(const std::string& name, const std::vector<int64_t>& indices,
+                       int after_iteration, std::vector<float>& out, int timeout_ms) {
+  pb::RowsRequest req;
+  req.worker_id = worker_id_, req.iteration = after_iteration, req.name = name;
+  req.indices = indices;
+  const std::string encoded = req.encode();
+  const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+  do {  // a "not yet" answer was already held by the server for its long-poll time
+    std::string resp;
+    Status st = shard_channel(0).call("/psb.ParameterServerExt/PullRows", encoded, resp, 10000);
+    pb::RowsResponse r;
+    if (!st.ok() || !r.decode(resp) || !r.message.empty()) return false;
+    if (r.ready) {
+      out = std::move(r.values);
+      return true;
+    }
+  } while (std::chrono::steady_clock::now() < deadline);
+  return false;
+}
+
 bool Worker::load_checkpoint_from_server(const std::string& checkpoint_path, int32_t& epoch) {
   if (!initialized_ && ps_address_.empty() && !discover_parameter_server()) return false;
   if (opt_.shards > 1 && shard_addrs_.empty() && !discover_shards()) return false;

@@ -75,6 +75,18 @@ class Worker {
   // The newest iteration any worker has pushed to the server (shard 0), -1 if it cannot be
   // asked: where a restarted or late worker joins the job (worker_main --join).
   int server_iteration();
+  // Sparse embedding tables (psb.ParameterServerExt; no counterpart in the reference, whose
+  // Tensor is dense).  Single parameter server: the table lives on the server this worker
+  // pushes to (shard 0 of a sharded job).
+  bool create_table(const std::string& name, int64_t rows, int32_t dim, float init_std = 0.0f,
+                    int64_t seed = 0);
+  // One (rows, gradients) push for `iteration`; *complete = every live worker has pushed.
+  bool push_sparse(int iteration, const std::string& name, int32_t dim,
+                   const std::vector<int64_t>& indices, const std::vector<float>& values,
+                   bool* complete = nullptr);
+  // Rows once the sparse pushes of `after_iteration` are applied (-1: at once).
+  bool pull_rows(const std::string& name, const std::vector<int64_t>& indices, int after_iteration,
+                 std::vector<float>& out, int timeout_ms = 10000);
   std::vector<std::string> discover_peer_workers();
   const std::string& ps_address() const { return ps_address_; }
   // Replace the synthetic gradient source (default: every element = 0.01).

@@ -38,6 +38,8 @@ static const char kUsage[] =
     "  --join                  start at the iteration the job has reached (a restarted worker)\n"
     "  --trace                 pull / compute / push / wait milliseconds of every iteration\n"
     "  --quiet                 no per-iteration line, one summary line at the end\n"
+    "  --sparse-rows=N [--sparse-table=ROWSxDIM (100000x16)]  also train a sparse embedding table:\n"
+    "                          every iteration pushes the gradient 0.01 for N rows and pulls them back\n"
     "  --compute-ms=F --straggle-prob=P --straggle-factor=X --seed=N   simulated compute time\n";
 
 int main(int argc, char** argv) {
@@ -53,6 +55,9 @@ int main(int argc, char** argv) {
   int32_t worker_port = 0;
   psb::WorkerOptions opt;
   bool quiet = false, join = false;
+  int sparse_rows = 0;  // > 0: the synthetic sparse workload next to the dense one
+  long long table_rows = 100000;
+  int table_dim = 16;
   if (const char* e = std::getenv("PSB_MODE")) opt.mode = e;
   if (const char* e = std::getenv("PSB_DEVICE")) opt.device = std::atoi(e);
   if (const char* e = std::getenv("PSB_HEARTBEAT_MS")) opt.heartbeat_ms = std::atoi(e);
@@ -73,6 +78,15 @@ int main(int argc, char** argv) {
     else if (a == "--trace") opt.trace = true;
     else if (a == "--join") join = true;
     else if (flag(a, "shards", v)) opt.shards = std::atoi(v.c_str());
+    else if (flag(a, "sparse-rows", v)) sparse_rows = std::atoi(v.c_str());
+    else if (flag(a, "sparse-table", v)) {
+      const size_t x = v.find('x');
+      if (x == std::string::npos || (table_rows = std::atoll(v.c_str())) <= 0 ||
+          (table_dim = std::atoi(v.c_str() + x + 1)) <= 0) {
+        std::cerr << "--sparse-table wants ROWSxDIM" << std::endl;
+        return 2;
+      }
+    }
     else if (a.rfind("--", 0) == 0 && a.size() > 2) {
       std::cerr << "unknown flag " << a << std::endl;
       return 2;
@@ -105,10 +119,29 @@ int main(int argc, char** argv) {
     first = std::max(0, w.server_iteration());
     std::cout << "worker " << worker_id << " joining at iteration " << first << std::endl;
   }
+  // The sparse twin of the reference worker's fabricated dense gradient (src/worker.cpp:316-320):
+  // iteration i touches rows [i*N, (i+1)*N) mod ROWS with 0.01 in every element and reads them back.
+  if (sparse_rows > 0 && !w.create_table("embedding", table_rows, table_dim)) {
+    std::cerr << "worker " << worker_id << " could not create the sparse table" << std::endl;
+    return 1;
+  }
   const auto t0 = std::chrono::steady_clock::now();
   int completed = 0;
   for (int it = first; it < iterations; ++it) {
     bool done = w.run_iteration(it);
+    if (sparse_rows > 0) {
+      std::vector<int64_t> ids(static_cast<size_t>(sparse_rows));
+      for (int i = 0; i < sparse_rows; ++i)
+        ids[i] = (static_cast<long long>(it) * sparse_rows + i) % table_rows;
+      std::vector<float> g(ids.size() * table_dim, opt.synthetic_grad), rows;
+      const bool ok = w.push_sparse(it, "embedding", table_dim, ids, g) &&
+                      (opt.mode != "sync" ? w.pull_rows("embedding", ids, -1, rows)
+                                          : w.pull_rows("embedding", ids, it, rows, opt.sync_timeout_ms));
+      done = done && ok && rows.size() == g.size();
+      if (!quiet && ok)
+        std::cout << "worker " << worker_id << " iter " << it << " sparse rows=" << sparse_rows
+                  << " row0[0]=" << rows[0] << std::endl;
+    }
     completed += done ? 1 : 0;
     if (!quiet)
       std::cout << "worker " << worker_id << " iter " << it << " done=" << (done ? "true" : "false")

@@ -218,3 +218,25 @@ def test_remote_trainer_with_an_embedding_table_learns(plane):
         losses = res[w][0]
         assert sum(losses[-5:]) / 5 < 0.8 * sum(losses[:5]) / 5, losses
     assert np.array_equal(res[0][1], res[1][1])
+
+
+@pytest.mark.parametrize("plane", [["--optimizer=sgd", "--lr=1.0"]], indirect=True)
+def test_cpp_workers_train_a_sparse_table_next_to_the_dense_model(plane):
+    """worker_main --sparse-rows: the reference worker's fabricated gradient (0.01 everywhere),
+    but for the rows of an embedding table — two C++ workers, then the table read from Python:
+    rows touched in iteration i moved by -lr * mean(0.01) exactly once, the others not at all."""
+    import subprocess
+    coord, ps_proc, tmp = plane
+    runs = [subprocess.Popen([f"{BIN}/worker_main", coord, str(w), "4", "--sparse-rows=8",
+                              "--sparse-table=100x4"], stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT, text=True) for w in range(2)]
+    outs = [r.communicate(timeout=120)[0] for r in runs]
+    for r, o in zip(runs, outs):
+        assert r.returncode == 0, o
+        assert o.count("done=true") == 4, o
+        # the row read back after iteration 3 already holds that iteration's update
+        assert "iter 3 sparse rows=8 row0[0]=-0.01" in o, o
+    with psd.RemoteParameterServer(coord, 0, heartbeat_s=0.2) as ps:
+        ps.create_table("embedding", 100, 4)
+        table = ps.pull_rows("embedding", np.arange(100))
+    assert np.allclose(table[:32], -0.01, atol=1e-7) and not table[32:].any()
