@@ -172,7 +172,7 @@ ParameterServerService::ParameterServerService(int total_workers, int checkpoint
     out.ready = sparse_.ready(in.iteration, core_.options().long_poll_ms);
     if (!sparse_.rows(in.name, in.indices, out.values, out.dim)) {
       out.ready = false;
-      out.message = "unknown table '" + in.name + "'";
+      out.message = "unknown table '" + in.name + "' (or more than 2^30 values asked for at once)";
     }
     resp = out.encode();
     bytes_out_ += resp.body.size();

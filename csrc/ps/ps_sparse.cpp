@@ -207,6 +207,8 @@ bool SparseTables::rows(const std::string& name, const std::vector<int64_t>& ind
   const Table& t = it->second;
   dim = t.dim;
   const size_t n = static_cast<size_t>(t.dim);
+  // an 8-byte id asks for dim * 4 bytes: bound what one request can make the server allocate
+  if (indices.size() > (size_t{1} << 30) / n) return false;
   out.assign(indices.size() * n, 0.0f);
   for (size_t i = 0; i < indices.size(); ++i) {
     const int64_t row = indices[i];

@@ -42,7 +42,8 @@ class SparseTables {
             int total_workers, int32_t& workers_received, std::string& err);
   // Is `iteration` applied?  A negative answer is held up to `wait_ms` for it to change.
   bool ready(int32_t iteration, int wait_ms);
-  // Rows of `name` (zero rows for ids outside the table); false if the table does not exist.
+  // Rows of `name` (zero rows for ids outside the table); false if the table does not exist or
+  // the answer would exceed 2^30 floats (4 GiB) — split such a pull.
   bool rows(const std::string& name, const std::vector<int64_t>& indices, std::vector<float>& out,
             int32_t& dim);
   // Membership follows the coordinator: pending iterations complete for the new count apply.
