@@ -76,5 +76,15 @@ if len(sys.argv) > 2 and sys.argv[2] == "train":
         native.colsum(gz)
         loss = native.mse_fwd(a_in, zin)
         native.mse_bwd(a_in, zin, None)
+# K5: sparse embedding pull and push (mark / accumulate / apply), a 1 Mi x 128 table, 64 Ki rows
+if "--sparse" in sys.argv:
+    from parameter_server_distributed_b200 import ShardedEmbedding
+    table = ShardedEmbedding(1 << 20, 128, OptimConfig(kind="adam", lr=1e-3), capacity=64 << 10,
+                             device=DEV)
+    ids = torch.randint(0, 1 << 20, (64 << 10,), device=DEV)
+    gr = torch.randn(64 << 10, 128, device=DEV).to(torch.bfloat16)
+    for _ in range(reps):
+        table.pull(ids)
+        table.push(ids, gr)
 torch.cuda.synchronize()
 print("ncu_target ok")
