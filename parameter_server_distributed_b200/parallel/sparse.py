@@ -29,6 +29,7 @@ from .. import _lib
 from .._lib import PsbFabric, PsbSparse, check
 from ..ops import reference as ref
 from ..ops.native import OptimConfig
+from ..utils.tracing import Metrics, nvtx_range
 
 _BARRIER_SLOT = 8      # device-barrier slot of the sparse path (0-4 belong to the engines)
 _INIT_BLOCK = 4096     # rows per seeded block of the initialiser (layout independent of world)
@@ -72,6 +73,7 @@ class ShardedEmbedding:
         self.lo = min(self.vocab, rank * self.rows_per_rank)
         self.hi = min(self.vocab, self.lo + self.rows_per_rank)
         self.steps = 0
+        self.metrics = Metrics("psb_sparse")  # rows / bytes by construction, Prometheus text
         self._pending: List[Tuple[torch.Tensor, torch.Tensor]] = []
         R, D, dev = self.rows_per_rank, self.dim, self.device
         self.master = torch.zeros(R, D, dtype=torch.float32, device=dev)
@@ -186,10 +188,13 @@ class ShardedEmbedding:
         outside ``[0, vocab)`` gives a zero row (padding)."""
         idx = indices.reshape(-1).to(device=self.device, dtype=torch.int64).contiguous()
         n = idx.numel()
+        self.metrics.inc("pulls")
+        self.metrics.inc("rows_pulled", n)
+        self.metrics.inc("pull_bytes", n * self.dim * 2)
         if self.cuda:
             out = torch.empty(n, self.dim, dtype=torch.bfloat16, device=self.device)
             if n:
-                with torch.cuda.device(self.device):
+                with torch.cuda.device(self.device), nvtx_range("psb.sparse_pull"):
                     check(self.lib.psb_sparse_pull(C.byref(self._c), idx.data_ptr(), n,
                                                    out.data_ptr(), self._stream()),
                           "psb_sparse_pull")
@@ -219,6 +224,8 @@ class ShardedEmbedding:
             raise ValueError("one gradient row per index")
         if n > self.capacity:
             raise ValueError(f"{n} rows pushed, staging capacity is {self.capacity}")
+        self.metrics.inc("rows_pushed", n)
+        self.metrics.inc("push_bytes", n * (8 + self.dim * g.element_size()))
         if self.cuda:
             self.stage_idx[:n].copy_(idx)
             self.stage_grad[:n].copy_(g)
@@ -229,8 +236,9 @@ class ShardedEmbedding:
     def apply(self) -> None:
         """Owner half of a push: mean of the staged gradients of the rows this rank owns
         through the optimizer (``psb_sparse_apply``: mark, accumulate, apply)."""
+        self.metrics.inc("pushes")
         if self.cuda:
-            with torch.cuda.device(self.device):
+            with torch.cuda.device(self.device), nvtx_range("psb.sparse_apply"):
                 check(self.lib.psb_sparse_apply(C.byref(self._c), self._stream()),
                       "psb_sparse_apply")
                 check(self.lib.psb_counter_add(self.step_word.data_ptr(), 1, self._stream()),

@@ -286,3 +286,13 @@ def test_trainer_pushes_table_gradients_next_to_the_dense_ones():
     assert (table.master - before).abs().max() > 1e-2
     assert sum(losses[-10:]) < 0.8 * sum(losses[:10]), (losses[:3], losses[-3:])
     ctx.close()
+
+
+def test_metrics_count_rows_and_bytes():
+    e = ShardedEmbedding(V, D, OptimConfig(), capacity=16, grad_dtype=torch.float32)
+    e.pull(torch.arange(5))
+    e.push(torch.tensor([1, 2, 2]), torch.zeros(3, D))
+    snap = e.metrics.snapshot()
+    assert snap["rows_pulled"] == 5 and snap["pull_bytes"] == 5 * D * 2
+    assert snap["rows_pushed"] == 3 and snap["pushes"] == 1 and snap["push_bytes"] == 3 * (8 + D * 4)
+    assert "psb_sparse_rows_pushed 3" in e.metrics.prometheus()
