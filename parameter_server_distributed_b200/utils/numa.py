@@ -8,8 +8,8 @@ node *before* the first pinned allocation puts those pages — and the threads t
 next to it.  The reference pins nothing (its tensors are ``std::vector``s copied with blocking
 ``cudaMemcpy``, /root/reference/src/worker.cpp:408-448).
 
-Best effort by design: any missing piece of information (no sysfs, one node, a cpuset that does
-not intersect, ``PSB_NUMA_BIND=0``) leaves the process as it was.
+Best effort by design: any missing piece of information (no sysfs, one node, a cpuset that
+leaves fewer than four of the node's CPUs, ``PSB_NUMA_BIND=0``) leaves the process as it was.
 """
 from __future__ import annotations
 
@@ -83,8 +83,8 @@ def bind_to_gpu_node(device_index: int, sysfs: str = "/sys") -> Optional[dict]:
     try:
         allowed = os.sched_getaffinity(0)
         want = node_cpus(node, sysfs) & allowed
-        if not want:
-            return None
+        if len(want) < min(4, len(allowed)):
+            return None  # a cpuset that leaves (almost) nothing of that node: better unbound
         os.sched_setaffinity(0, want)
     except (OSError, AttributeError):
         return None

@@ -56,6 +56,10 @@ def test_best_effort_cases_leave_the_process_alone(tmp_path, fake_gpu, monkeypat
     nowhere = _sysfs(tmp_path / "nowhere", {0: "100000-100003", 1: "100004-100007"}, gpu_node=1)
     assert numa.bind_to_gpu_node(0, nowhere) is None                  # cpuset does not intersect
     assert numa.bind_to_gpu_node(0, str(tmp_path / "missing")) is None
+    if len(os.sched_getaffinity(0)) >= 4:
+        first = str(min(os.sched_getaffinity(0)))
+        sliver = _sysfs(tmp_path / "sliver", {0: "100000-100003", 1: first}, gpu_node=1)
+        assert numa.bind_to_gpu_node(0, sliver) is None              # one CPU of that node allowed
     two = _sysfs(tmp_path / "two", {0: "0-3", 1: "0-7"}, gpu_node=1)
     monkeypatch.setenv("PSB_NUMA_BIND", "0")
     assert numa.bind_to_gpu_node(0, two) is None
