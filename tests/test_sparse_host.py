@@ -296,3 +296,19 @@ def test_metrics_count_rows_and_bytes():
     assert snap["rows_pulled"] == 5 and snap["pull_bytes"] == 5 * D * 2
     assert snap["rows_pushed"] == 3 and snap["pushes"] == 1 and snap["push_bytes"] == 3 * (8 + D * 4)
     assert "psb_sparse_rows_pushed 3" in e.metrics.prometheus()
+
+
+def test_sparse_benchmark_script_runs_on_the_host_path():
+    """benchmarks/sparse_bench.py without a GPU: small table, host path — keeps the script that
+    will produce the K5 numbers on a GPU from rotting."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "benchmarks", "sparse_bench.py"),
+                        "--vocab", "5000", "--dim", "16", "--rows", "512"], capture_output=True,
+                       text=True, timeout=300, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert r.returncode == 0, r.stdout[-400:] + r.stderr[-400:]
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert [l["kernel"].split()[1] for l in lines] == ["pull", "push"]
+    assert all(l["ms_median"] > 0 and l["unique_rows"] <= 512 for l in lines)
