@@ -241,8 +241,10 @@ def run_nccl(args) -> int:
     prev[1].synchronize()
     e2e_loss = float(prev[0].item())
     s1.record()
+    torch.cuda.synchronize(device)  # same clock as the other arm: local completion, then max over ranks
+    wall_ms = (time.perf_counter() - t0) * 1e3
     barrier()
-    e2e_ms = max_over_ranks(max(s0.elapsed_time(s1), (time.perf_counter() - t0) * 1e3))
+    e2e_ms = max_over_ranks(max(s0.elapsed_time(s1), wall_ms))
 
     gb = wl.batch * world
     if rank == 0:

@@ -219,8 +219,13 @@ def run_ours(args):
         prev = h
     e2e_loss = prev.item()
     s1.record()
+    # this rank's K steps end when its GPU has finished them; the job's time is the max over the
+    # ranks of that (they left one barrier together).  The closing barrier itself — an RPC round
+    # through the coordinator — is not part of any step and stays outside the clock.
+    torch.cuda.synchronize(ctx.device)
+    wall_ms = (time.perf_counter() - t0) * 1e3
     host_barrier(ctx)
-    e2e_ms = max(s0.elapsed_time(s1), (time.perf_counter() - t0) * 1e3)
+    e2e_ms = max(s0.elapsed_time(s1), wall_ms)
     e2e_ms = max_over_ranks(e2e_ms, ctx)
     if args.mode != "sync":
         ps.drain()  # apply what is still in flight so every rank ends with the same model
