@@ -7,6 +7,8 @@
 //
 //   pull    one sub-warp per requested row: 16-byte loads from the owner's bf16 shard (a peer
 //           address when the owner is another GPU), 16-byte stores into the local output.
+//   stage   worker side of a push, one launch: ids, gradient rows (cast to the staging dtype) and
+//           the count into this rank's range of the symmetric heap.
 //   apply   owner side of a push, three launches between two device barriers:
 //             mark        a thread per staged (worker, entry): rows this rank owns get a slot in
 //                         a compact accumulator (atomicCAS on slot[row] + an atomic counter)
@@ -66,6 +68,37 @@ __global__ void __launch_bounds__(kThreads)
     const uint4* src = reinterpret_cast<const uint4*>(
         reinterpret_cast<const __nv_bfloat16*>(s.table[owner]) + lrow * s.dim);
     for (int v = l; v < vecs; v += lpr) st_stream_16(dst + v, ld_stream_16(src + v));
+  }
+}
+
+// Worker half of a push in one launch: ids, gradient rows (cast to the staging dtype on the way)
+// and the entry count into this rank's staging range.  A thread moves 8 elements.
+template <int IN, int OUT>
+__global__ void __launch_bounds__(kThreads)
+    sparse_stage_kernel(const int64_t* __restrict__ idx, const void* __restrict__ grad, int64_t n,
+                        int dim, int64_t* __restrict__ stage_idx, void* __restrict__ stage_grad,
+                        uint32_t* __restrict__ stage_cnt) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (tid == 0) *stage_cnt = (uint32_t)n;
+  for (int64_t i = tid; i < n; i += stride) stage_idx[i] = idx[i];
+  const int64_t nvec = n * dim / 8;
+  for (int64_t v = tid; v < nvec; v += stride) {
+    float g[8];
+    if constexpr (IN == PSB_BF16) {
+      unpack8(ld_stream_16(reinterpret_cast<const __nv_bfloat16*>(grad) + v * 8), g);
+    } else {
+      const float* src = reinterpret_cast<const float*>(grad) + v * 8;
+      const float4 x = ld_stream_f4(src), y = ld_stream_f4(src + 4);
+      g[0] = x.x, g[1] = x.y, g[2] = x.z, g[3] = x.w, g[4] = y.x, g[5] = y.y, g[6] = y.z, g[7] = y.w;
+    }
+    if constexpr (OUT == PSB_BF16) {
+      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(stage_grad) + v * 8) = pack8(g);
+    } else {
+      float* dst = reinterpret_cast<float*>(stage_grad) + v * 8;
+      *reinterpret_cast<float4*>(dst) = make_float4(g[0], g[1], g[2], g[3]);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(g[4], g[5], g[6], g[7]);
+    }
   }
 }
 
@@ -253,6 +286,38 @@ extern "C" int psb_sparse_pull(const PsbSparse* s, const int64_t* idx, int64_t n
   sparse_pull_kernel<<<grid_for(n, lpr), kThreads, 0, (cudaStream_t)stream>>>(
       *s, idx, n, reinterpret_cast<__nv_bfloat16*>(out_bf16));
   PSB_LAUNCH_OK("sparse_pull_kernel");
+  return 0;
+}
+
+extern "C" int psb_sparse_stage(const PsbSparse* s, const int64_t* idx, const void* grad,
+                                int grad_dtype, int64_t n, psb_stream_t stream) {
+  if (int rc = validate(s, "psb_sparse_stage", true)) return rc;
+  PSB_REQUIRE(n >= 0 && n <= s->cap, PSB_ERANGE, "psb_sparse_stage: %lld rows, staging capacity %d",
+              (long long)n, s->cap);
+  PSB_REQUIRE(n == 0 || (idx != nullptr && grad != nullptr), PSB_EINVAL,
+              "psb_sparse_stage: null ids / gradients");
+  PSB_REQUIRE(grad_dtype == PSB_F32 || grad_dtype == PSB_BF16, PSB_EINVAL,
+              "psb_sparse_stage: gradient dtype %d", grad_dtype);
+  PSB_REQUIRE((reinterpret_cast<uintptr_t>(grad) & 15u) == 0, PSB_EINVAL,
+              "psb_sparse_stage: gradients are not 16-byte aligned");
+  const int r = s->fabric.rank;
+  int64_t* sidx = const_cast<int64_t*>(reinterpret_cast<const int64_t*>(s->stage_idx[r]));
+  void* sgrad = const_cast<void*>(s->stage_grad[r]);
+  uint32_t* scnt = const_cast<uint32_t*>(reinterpret_cast<const uint32_t*>(s->stage_cnt[r]));
+  const int64_t work = n * s->dim / 8 > n ? n * s->dim / 8 : n;
+  int64_t g = (work + kThreads - 1) / kThreads;
+  const int grid = (int)(g < 1 ? 1 : (g > (int64_t)kNumSMs * 8 ? (int64_t)kNumSMs * 8 : g));
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool in_bf = grad_dtype == PSB_BF16, out_bf = s->grad_dtype == PSB_BF16;
+  if (in_bf && out_bf)
+    sparse_stage_kernel<PSB_BF16, PSB_BF16><<<grid, kThreads, 0, st>>>(idx, grad, n, s->dim, sidx, sgrad, scnt);
+  else if (in_bf)
+    sparse_stage_kernel<PSB_BF16, PSB_F32><<<grid, kThreads, 0, st>>>(idx, grad, n, s->dim, sidx, sgrad, scnt);
+  else if (out_bf)
+    sparse_stage_kernel<PSB_F32, PSB_BF16><<<grid, kThreads, 0, st>>>(idx, grad, n, s->dim, sidx, sgrad, scnt);
+  else
+    sparse_stage_kernel<PSB_F32, PSB_F32><<<grid, kThreads, 0, st>>>(idx, grad, n, s->dim, sidx, sgrad, scnt);
+  PSB_LAUNCH_OK("sparse_stage_kernel");
   return 0;
 }
 

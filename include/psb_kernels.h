@@ -497,6 +497,10 @@ typedef struct PsbSparse {
 int psb_sparse_init(int32_t* slot, int64_t rows, psb_stream_t stream);  // slot[:] = -1
 int psb_sparse_pull(const PsbSparse* s, const int64_t* idx, int64_t n, void* out_bf16,
                     psb_stream_t stream);
+// worker half of a push in one launch: ids, gradient rows (fp32 or bf16, cast to s->grad_dtype) and
+// the count into this rank's staging range; n <= s->cap, grad 16-byte aligned
+int psb_sparse_stage(const PsbSparse* s, const int64_t* idx, const void* grad, int grad_dtype,
+                     int64_t n, psb_stream_t stream);
 int psb_sparse_apply(const PsbSparse* s, psb_stream_t stream);
 
 #ifdef __cplusplus

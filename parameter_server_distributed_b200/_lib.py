@@ -185,6 +185,7 @@ def _declare(lib) -> None:
         "psb_mse_bwd_bf16": (i32, [vp, vp, vp, sz, vp, vp]),
         "psb_sparse_init": (i32, [vp, C.c_int64, vp]),
         "psb_sparse_pull": (i32, [C.POINTER(PsbSparse), vp, C.c_int64, vp, vp]),
+        "psb_sparse_stage": (i32, [C.POINTER(PsbSparse), vp, vp, i32, C.c_int64, vp]),
         "psb_sparse_apply": (i32, [C.POINTER(PsbSparse), vp]),
     }
     for name, (res, args) in sig.items():

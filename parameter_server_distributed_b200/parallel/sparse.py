@@ -227,9 +227,18 @@ class ShardedEmbedding:
         self.metrics.inc("rows_pushed", n)
         self.metrics.inc("push_bytes", n * (8 + self.dim * g.element_size()))
         if self.cuda:
-            self.stage_idx[:n].copy_(idx)
-            self.stage_grad[:n].copy_(g)
-            self.stage_cnt[:1].fill_(n)
+            # one launch: ids, rows (cast to the staging dtype on the way) and the count
+            g = g.to(self.device)
+            if g.dtype not in (torch.bfloat16, torch.float32):
+                g = g.float()
+            g, idx = g.contiguous(), idx.contiguous()
+            if g.data_ptr() % 16:  # a row slice of a wider tensor: the kernel wants 16-byte vectors
+                g = g.clone()
+            with torch.cuda.device(self.device), nvtx_range("psb.sparse_stage"):
+                check(self.lib.psb_sparse_stage(
+                    C.byref(self._c), idx.data_ptr() if n else None, g.data_ptr() if n else None,
+                    _lib.BF16 if g.dtype == torch.bfloat16 else _lib.F32, n, self._stream()),
+                    "psb_sparse_stage")
         else:
             self._staged = (idx.clone(), g.to(self.grad_dtype))
 

@@ -7,6 +7,7 @@
 // from the real sources so that this file never holds a copy of the kernels.
 #include "cuda_shim.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <map>
 #include <random>
@@ -129,6 +130,65 @@ int run(int world, int64_t vocab, int dim, int cap, int kind, int gdt, int steps
             s[d] += g;
           }
         }
+    }
+    // ---- the staging kernel must reproduce exactly what was written above: hand it the first
+    //      n entries as user buffers (fp32 or bf16 gradients), wipe the staged copy, restage
+    for (int w = 0; w < world; ++w) {
+      Rank& k = rk[w];
+      const int64_t n = k.cnt[0];
+      const bool in_bf = ((seed + w + it) & 1) != 0;
+      const std::vector<int64_t> want_idx(k.stage_idx.begin(), k.stage_idx.begin() + n);
+      const std::vector<unsigned char> want_grad(k.stage_grad.begin(),
+                                                 k.stage_grad.begin() + (size_t)n * dim * gsz);
+      std::vector<unsigned char> user((size_t)n * dim * (in_bf ? 2 : 4) + 16);
+      for (int64_t e = 0; e < n * dim; ++e) {
+        float g;
+        if (gdt == PSB_BF16) {
+          __nv_bfloat16 h;
+          std::memcpy(&h, &want_grad[e * 2], 2);
+          g = bf16_to_float(h);
+        } else {
+          std::memcpy(&g, &want_grad[e * 4], 4);
+          if (in_bf) g = bf16_to_float(float_to_bf16_rn(g));  // what a bf16 caller would hold
+        }
+        if (in_bf) {
+          __nv_bfloat16 h = float_to_bf16_rn(g);
+          std::memcpy(&user[e * 2], &h, 2);
+        } else {
+          std::memcpy(&user[e * 4], &g, 4);
+        }
+      }
+      std::fill(k.stage_idx.begin(), k.stage_idx.begin() + n, (int64_t)-77);
+      std::fill(k.stage_grad.begin(), k.stage_grad.begin() + (size_t)n * dim * gsz, (unsigned char)0xAB);
+      k.cnt[0] = 0xdead;
+      const int64_t work = std::max<int64_t>(n * dim / 8, n);
+      const int grid = tiny_grid ? 1 : (int)std::max<int64_t>(1, (work + kThreads - 1) / kThreads);
+      if (in_bf && gdt == PSB_BF16)
+        emu_launch(sparse_stage_kernel<PSB_BF16, PSB_BF16>, grid, kThreads, want_idx.data(), (const void*)user.data(), n, dim, k.stage_idx.data(), (void*)k.stage_grad.data(), k.cnt);
+      else if (in_bf)
+        emu_launch(sparse_stage_kernel<PSB_BF16, PSB_F32>, grid, kThreads, want_idx.data(), (const void*)user.data(), n, dim, k.stage_idx.data(), (void*)k.stage_grad.data(), k.cnt);
+      else if (gdt == PSB_BF16)
+        emu_launch(sparse_stage_kernel<PSB_F32, PSB_BF16>, grid, kThreads, want_idx.data(), (const void*)user.data(), n, dim, k.stage_idx.data(), (void*)k.stage_grad.data(), k.cnt);
+      else
+        emu_launch(sparse_stage_kernel<PSB_F32, PSB_F32>, grid, kThreads, want_idx.data(), (const void*)user.data(), n, dim, k.stage_idx.data(), (void*)k.stage_grad.data(), k.cnt);
+      if (k.cnt[0] != (uint32_t)n) return fail("staged count", k.cnt[0], n);
+      if (!std::equal(want_idx.begin(), want_idx.end(), k.stage_idx.begin())) return fail("staged ids", w);
+      if (gdt == PSB_F32 && in_bf) {
+        // fp32 staging of bf16 inputs holds the bf16-rounded values: restate the reference sums
+        for (int64_t i = 0; i < n; ++i) {
+          const int64_t id = want_idx[i];
+          if (id < 0 || id >= vocab) continue;
+          for (int d = 0; d < dim; ++d) {
+            float a, b;
+            std::memcpy(&a, &want_grad[((size_t)i * dim + d) * 4], 4);
+            std::memcpy(&b, &k.stage_grad[((size_t)i * dim + d) * 4], 4);
+            if (b != bf16_to_float(float_to_bf16_rn(a))) return fail("staged bf16 -> fp32", w, i);
+            sums[id][d] += (double)b - (double)a;
+          }
+        }
+      } else if (!std::equal(want_grad.begin(), want_grad.end(), k.stage_grad.begin())) {
+        return fail("staged gradients", w);
+      }
     }
     std::vector<Rank> before = rk;  // untouched rows must come out bit-identical
     // ---- owners apply (the launches of psb_sparse_apply)

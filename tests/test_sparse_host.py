@@ -259,6 +259,12 @@ def test_c_abi_rejects_bad_arguments_before_any_launch():
     assert lib.psb_sparse_apply(C.byref(s), None) != 0
     assert b"owner state" in lib.psb_last_error()
     assert lib.psb_sparse_init(None, 5, None) != 0
+    s.master = s.slot = s.touched = s.n_touched = s.acc = 4096
+    assert lib.psb_sparse_stage(C.byref(s), 4096, 4096, _lib.F32, 9, None) == -2   # PSB_ERANGE
+    assert b"staging capacity 8" in lib.psb_last_error()
+    assert lib.psb_sparse_stage(C.byref(s), 4096, 4100, _lib.F32, 2, None) != 0
+    assert b"16-byte aligned" in lib.psb_last_error()
+    assert lib.psb_sparse_stage(C.byref(s), 4096, 4096, 7, 2, None) != 0
 
 
 def test_trainer_pushes_table_gradients_next_to_the_dense_ones():
