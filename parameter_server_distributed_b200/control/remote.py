@@ -190,6 +190,22 @@ def encode_sparse_push(worker_id: int, iteration: int,
     return b"".join(chunks)
 
 
+def encode_rows_request(worker_id: int, iteration: int, name: str, ids: np.ndarray) -> bytes:
+    """psb.RowsRequest with the ids as one packed sfixed64 block."""
+    ids = np.ascontiguousarray(ids, dtype="<i8").ravel()
+    nb = name.encode()
+    parts = []
+    if worker_id:
+        parts.append(b"\x08" + _varint(worker_id))
+    if iteration:
+        parts.append(b"\x10" + _varint(iteration))
+    if nb:
+        parts.append(b"\x1a" + _varint(len(nb)) + nb)
+    if ids.size:
+        parts += [b"\x22" + _varint(ids.nbytes), ids.data.cast("B")]
+    return b"".join(parts)
+
+
 def decode_rows_response(buf: bytes) -> Tuple[bool, int, np.ndarray, str]:
     """psb.RowsResponse -> (ready, dim, fp32 values (flat, read-only view), message)."""
     view = memoryview(buf)
@@ -468,7 +484,6 @@ class RemoteParameterServer:
         table), once the sparse pushes of ``after_iteration`` are applied (-1: at once)."""
         rows, dim, per, ids, shard = self._split_rows(name, ids)
         n = len(self._stubs)
-        Req = protos.msg("psb.RowsRequest")
         out = np.zeros((ids.size, dim), dtype=np.float32)
         end = time.monotonic() + timeout_s
 
@@ -476,9 +491,7 @@ class RemoteParameterServer:
             pick = np.nonzero(shard == k)[0]
             if pick.size == 0 and after_iteration < 0:
                 return
-            req = Req(worker_id=self.worker_id, iteration=after_iteration, name=name)
-            req.indices.extend((ids[pick] - k * per).tolist())
-            body = req.SerializeToString()
+            body = encode_rows_request(self.worker_id, after_iteration, name, ids[pick] - k * per)
             while True:
                 ready, d, vals, msg = decode_rows_response(
                     self._raw_pull_rows[k](body, timeout=self.timeout))

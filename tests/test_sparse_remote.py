@@ -11,6 +11,7 @@ import torch
 import parameter_server_distributed_b200 as psd
 from parameter_server_distributed_b200.control import protos
 from parameter_server_distributed_b200.control.remote import (decode_rows_response,
+                                                               encode_rows_request,
                                                                encode_sparse_push)
 from tests._native import BIN, Proc, ensure_binaries, free_port, wait_port
 
@@ -27,6 +28,10 @@ def test_numpy_codec_matches_the_protobuf_runtime():
     assert list(m.tables[0].indices) == ids.tolist() and list(m.tables[0].values) == vals.ravel().tolist()
     assert m.tables[1].name == "empty" and len(m.tables[1].indices) == 0
     assert m.SerializeToString() == mine            # byte-identical with the runtime's encoding
+    Q = protos.msg("psb.RowsRequest")
+    for wid, it, ids_ in ((3, -1, ids), (0, 0, ids[:0]), (1, 7, ids[:1])):
+        assert encode_rows_request(wid, it, "emb", ids_) == Q(
+            worker_id=wid, iteration=it, name="emb", indices=ids_.tolist()).SerializeToString()
     R = protos.msg("psb.RowsResponse")
     ready, dim, got, msg = decode_rows_response(R(ready=True, dim=2, values=[1.5, -2.0]).SerializeToString())
     assert ready and dim == 2 and got.tolist() == [1.5, -2.0] and msg == ""
