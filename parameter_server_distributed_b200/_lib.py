@@ -188,6 +188,10 @@ def _declare(lib) -> None:
         "psb_sparse_stage": (i32, [C.POINTER(PsbSparse), vp, vp, i32, C.c_int64, vp]),
         "psb_sparse_apply": (i32, [C.POINTER(PsbSparse), vp]),
     }
+    missing = [name for name in sig if not hasattr(lib, name)]
+    if missing:  # a library built from older sources: say so instead of an AttributeError
+        raise PsbError(f"{_LIB_PATH} is older than this package (no {', '.join(missing)}); "
+                       f"rebuild it with `python __graft_entry__.py`")
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
         fn.restype = res
