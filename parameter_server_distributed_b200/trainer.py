@@ -236,12 +236,18 @@ class Trainer:
         # kernels give up their waits only once the abort word is set, so state gathered while
         # it is still clear is sound; anything else must not replace the last good file
         save_checkpoint(self.ps, path, epoch=epoch, validate=self._guard)
+        for i, t in enumerate(self.tables):  # each table as one tensor next to the model's file
+            t.save(f"{path}.table{i}", name=f"table{i}", epoch=epoch)
 
     def load_checkpoint(self, path: str):
         """Collective.  Restores master weights (and optimizer state when the sidecar exists);
         returns ``(epoch, iteration)``."""
         from .utils.checkpoint import load_checkpoint
-        return load_checkpoint(self.ps, path)
+        out = load_checkpoint(self.ps, path)
+        for i, t in enumerate(self.tables):
+            if os.path.exists(f"{path}.table{i}"):
+                t.load(f"{path}.table{i}")
+        return out
 
     # ------------------------------------------------------------------ failure handling
     def _guard(self) -> None:

@@ -318,3 +318,38 @@ def test_sparse_benchmark_script_runs_on_the_host_path():
     lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
     assert [l["kernel"].split()[1] for l in lines] == ["pull", "push"]
     assert all(l["ms_median"] > 0 and l["unique_rows"] <= 512 for l in lines)
+
+
+def test_trainer_checkpoint_carries_the_tables(tmp_path):
+    """Trainer.save_checkpoint / load_checkpoint: the model's file plus one `<path>.table<i>` per
+    sparse table; a fresh trainer that loads them continues exactly like the one that wrote them."""
+    import parameter_server_distributed_b200 as psd
+    from parameter_server_distributed_b200.models import EmbeddingMLP, EmbeddingMLPConfig
+    cfg = EmbeddingMLPConfig(vocab=120, dim=8, fields=2, hidden=(8,), classes=2)
+    optim = OptimConfig(kind="adam", lr=0.05)
+    loss = lambda out, y: torch.nn.functional.cross_entropy(out.float(), y)  # noqa: E731
+    gen = torch.Generator().manual_seed(4)
+    batches = [(torch.randint(0, cfg.vocab, (16, cfg.fields), generator=gen),
+                torch.randint(0, 2, (16,), generator=gen)) for _ in range(6)]
+
+    def make(seed):
+        ctx = psd.init()
+        table = ShardedEmbedding.from_context(ctx, cfg.vocab, cfg.dim, optim, capacity=64,
+                                              init_std=0.1, grad_dtype=torch.float32, seed=seed)
+        torch.manual_seed(seed)
+        return ctx, table, psd.Trainer(EmbeddingMLP(cfg, table), loss, ctx, optim, bucket_mb=1,
+                                       tables=[table])
+
+    ctx, table, tr = make(0)
+    for ids, y in batches[:3]:
+        tr.step(ids, y).item()
+    path = str(tmp_path / "job.ckpt")
+    tr.save_checkpoint(path, epoch=1)
+    assert os.path.exists(path + ".table0") and os.path.exists(path + ".table0.psb")
+    ctx2, table2, tr2 = make(7)            # different initial values everywhere
+    tr2.load_checkpoint(path)
+    assert torch.equal(table2.master, table.master) and table2.steps == 3
+    for ids, y in batches[3:]:
+        a, b = tr.step(ids, y).item(), tr2.step(ids, y).item()
+        assert abs(a - b) < 1e-6
+    assert torch.equal(table2.master, table.master)
