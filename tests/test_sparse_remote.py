@@ -245,3 +245,25 @@ def test_cpp_workers_train_a_sparse_table_next_to_the_dense_model(plane):
         ps.create_table("embedding", 100, 4)
         table = ps.pull_rows("embedding", np.arange(100))
     assert np.allclose(table[:32], -0.01, atol=1e-7) and not table[32:].any()
+
+
+@pytest.mark.parametrize("plane", [["--optimizer=adam", "--lr=0.02"]], indirect=True)
+def test_remote_trainer_example_with_embedding(plane):
+    """examples/remote_trainer.py --embedding, two worker processes; the server writes the model
+    and `<path>.tables`."""
+    import os
+    import subprocess
+    import sys
+    coord, _, tmp = plane
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, "examples", "remote_trainer.py"), "--coordinator", coord,
+           "--embedding", "--steps", "12"]
+    ckpt = str(tmp / "e.ckpt")
+    ps = [subprocess.Popen(cmd + ["--worker-id", str(w)] + (["--checkpoint", ckpt] if w == 0 else []),
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+          for w in range(2)]
+    outs = [p.communicate(timeout=180)[0] for p in ps]
+    for p, o in zip(ps, outs):
+        assert p.returncode == 0, o[-800:]
+        assert "iter 12 loss" in o, o[-400:]
+    assert os.path.exists(ckpt) and os.path.exists(ckpt + ".tables")
