@@ -31,6 +31,7 @@ from ..ops import reference as ref
 from ..ops.native import OptimConfig
 from ..utils.tracing import Metrics, nvtx_range
 
+_DEVICE_PATH_ON_HOST = False
 _BARRIER_SLOT = 8      # device-barrier slot of the sparse path (0-4 belong to the engines)
 _INIT_BLOCK = 4096     # rows per seeded block of the initialiser (layout independent of world)
 
@@ -80,7 +81,9 @@ class ShardedEmbedding:
         self.master[:self.hi - self.lo] = _init_rows(self.lo, self.hi, D, init_std, seed).to(dev)
         self.m = torch.zeros(R, D, dtype=torch.float32, device=dev) if optim.needs_m() else None
         self.v = torch.zeros(R, D, dtype=torch.float32, device=dev) if optim.needs_v() else None
-        self.cuda = self.device.type == "cuda"
+        # _DEVICE_PATH_ON_HOST: test hook (tests/test_sparse_device_path_emulated.py) — the device
+        # code path below on host tensors, against the kernels compiled for the host
+        self.cuda = self.device.type == "cuda" or _DEVICE_PATH_ON_HOST
         if self.cuda:
             self._build_device()
         else:
