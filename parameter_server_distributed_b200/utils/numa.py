@@ -67,7 +67,15 @@ def _prefer_node_memory(node: int) -> bool:
 
 def bind_to_gpu_node(device_index: int, sysfs: str = "/sys") -> Optional[dict]:
     """Restrict this process to the CPUs of the GPU's NUMA node and prefer its memory.
-    Returns ``{"node", "cpus", "mempolicy"}`` when something was done, else None."""
+    Returns ``{"node", "cpus", "mempolicy"}`` when something was done, else None.  Never raises:
+    placement is an optimisation, a job must not fail to start over it."""
+    try:
+        return _bind_to_gpu_node(device_index, sysfs)
+    except Exception:
+        return None
+
+
+def _bind_to_gpu_node(device_index: int, sysfs: str) -> Optional[dict]:
     if os.environ.get("PSB_NUMA_BIND", "1") == "0":
         return None
     try:
