@@ -267,3 +267,39 @@ def test_remote_trainer_example_with_embedding(plane):
         assert p.returncode == 0, o[-800:]
         assert "iter 12 loss" in o, o[-400:]
     assert os.path.exists(ckpt) and os.path.exists(ckpt + ".tables")
+
+
+def test_restarted_server_resumes_its_tables(tmp_path):
+    """parameter_server --resume=latest: the newest checkpoint's `.tables` file comes back with
+    the model (SIGKILL, so nothing is written on the way out)."""
+    ps_port, co_port = free_port(), free_port()
+    args = [f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "1", "0", "--optimizer=adam", "--lr=0.05"]
+    ps = Proc(args, str(tmp_path), str(tmp_path / "ps.log"))
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        ids, g = np.arange(0, 40, 3), np.ones((14, D), np.float32)
+        with psd.RemoteParameterServer(f"127.0.0.1:{co_port}", 0, heartbeat_s=0.2) as w:
+            w.create_table("emb", V, D, init_std=0.1)
+            w.push(0, [("w", np.ones(4, np.float32))])          # a dense model to checkpoint
+            w.push_sparse(0, [("emb", ids, g)])
+            before = w.pull_rows("emb", np.arange(V), after_iteration=0)
+            w.save_checkpoint(7, "checkpoint_epoch_7.ckpt")      # relative: the server's directory
+            w.push_sparse(1, [("emb", ids, g)])                  # not in the checkpoint
+        ps.p.kill()
+        ps.p.wait(timeout=10)
+        ps.f.close()
+        ps = Proc(args + ["--resume=latest"], str(tmp_path), str(tmp_path / "ps2.log"))
+        assert wait_port(ps_port)
+        with psd.RemoteParameterServer(f"127.0.0.1:{co_port}", 0, heartbeat_s=0.2) as w:
+            w.create_table("emb", V, D)                          # exists: same shape, kept as loaded
+            assert np.array_equal(w.pull_rows("emb", np.arange(V)), before)
+            # Adam's state and step count resumed too: the lost push, repeated, moves the rows as before
+            w.push_sparse(0, [("emb", ids, g)])
+            again = w.pull_rows("emb", ids, after_iteration=0)
+            assert np.abs(again - before[ids]).max() > 1e-3
+        assert "resumed from checkpoint_epoch_7.ckpt" in ps.output()
+    finally:
+        ps.stop()
+        co.stop()
