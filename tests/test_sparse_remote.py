@@ -303,3 +303,35 @@ def test_restarted_server_resumes_its_tables(tmp_path):
     finally:
         ps.stop()
         co.stop()
+
+
+def test_evicted_worker_stops_blocking_a_pending_sparse_iteration(tmp_path):
+    """Two workers, one goes silent before it pushes: once the coordinator has evicted it the
+    server (which follows the registry) completes the sparse iteration with the live worker's
+    rows alone — the dense barrier's rule, applied to tables."""
+    import time
+    fast = {"PSB_STALE_SCAN_MS": "100", "PSB_STALE_TIMEOUT_S": "1"}
+    ps_port, co_port = free_port(), free_port()
+    co = Proc([f"{BIN}/coordinator", f"127.0.0.1:{co_port}", f"127.0.0.1:{ps_port}"],
+              str(tmp_path), str(tmp_path / "co.log"), env=fast)
+    ps = Proc([f"{BIN}/parameter_server", f"127.0.0.1:{ps_port}", "2", "0", "--optimizer=sgd",
+               "--lr=1.0", f"--coordinator=127.0.0.1:{co_port}", "--membership-poll-ms=100"],
+              str(tmp_path), str(tmp_path / "ps.log"))
+    try:
+        assert wait_port(ps_port) and wait_port(co_port)
+        coord = f"127.0.0.1:{co_port}"
+        a = psd.RemoteParameterServer(coord, 0, heartbeat_s=0.1)
+        b = psd.RemoteParameterServer(coord, 1, heartbeat_s=0.1)
+        a.create_table("emb", 50, D)
+        time.sleep(0.5)                      # the server has seen the job complete (2 live)
+        b.close()                            # worker 1 goes silent without pushing
+        ids, g = np.array([1, 2]), np.ones((2, D), np.float32)
+        assert a.push_sparse(0, [("emb", ids, g)]) is False          # 1 of 2 so far
+        rows = a.pull_rows("emb", ids, after_iteration=0, timeout_s=20)  # opens after the eviction
+        assert np.allclose(rows, -1.0)       # divisor = the one live pusher, lr 1
+        assert "evicted stale worker 1" in co.output()
+        assert "membership: total_workers 2 -> 1" in ps.output()
+        a.close()
+    finally:
+        ps.stop()
+        co.stop()
